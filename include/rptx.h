@@ -1,0 +1,215 @@
+/* rptx.h — C ABI of the B200 light-transport core for neevparikh/rpt.
+ *
+ * The reference has no FFI: its boundary is the Rust library API
+ * (Renderer builder src/renderer.rs:23-134, render()/iterative_render() :137-156,
+ * photon_render src/photon.rs:642-655, get_closest_hit src/renderer.rs:416-425,
+ * Scene/SceneAdd src/scene.rs:12-81, Object src/object.rs:10-31, Light src/light.rs:7-19,
+ * Material src/material.rs:8-98, Medium src/medium.rs:80-121, Camera src/camera.rs:9-27).
+ * A Rust `rpt` mirror lowers those types into the POD records below and calls
+ * these entry points (binding shown in INTEGRATION.md).  Everything is plain
+ * pointers and sizes; all reals are f64 as in the reference (src/color.rs:2).
+ *
+ * Every function returns 0 on success, non-zero on error; the message is
+ * available from rptx_last_error().  Nothing aborts across the boundary
+ * (the reference panics: src/buffer.rs:26,33,55,89, src/photon.rs:798).
+ *
+ * Threading: one host thread per context at a time; one context per device
+ * (one process per GPU).  Contexts are independent.
+ */
+#ifndef RPTX_H
+#define RPTX_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RPTX_ABI_VERSION 1
+
+/* ---- shapes: src/shape.rs:19-26 (trait Shape), :102-109 (Transformed<T>) ---- */
+enum {
+    RPTX_SHAPE_SPHERE = 0, /* unit sphere, src/shape/sphere.rs:10 */
+    RPTX_SHAPE_PLANE  = 1, /* x.normal = value, src/shape/plane.rs:7-13 */
+    RPTX_SHAPE_CUBE   = 2, /* unit cube [-.5,.5]^3, src/shape/cube.rs:9 */
+    RPTX_SHAPE_MESH   = 3, /* Mesh = KdTree<Triangle>, src/shape/mesh.rs:103 */
+    RPTX_SHAPE_GROUP  = 4  /* KdTree<Box<dyn Bounded>> of transformed children, src/kdtree.rs:103 */
+};
+
+typedef struct rptx_shape_desc {
+    int32_t  kind;
+    int32_t  has_transform;     /* 1: wrapped in Transformed<T> with `transform` */
+    double   transform[16];     /* row-major 4x4, M[r][c] = transform[4*r+c] */
+    uint32_t mesh_id;           /* MESH: id returned by rptx_scene_add_mesh */
+    uint32_t n_children;        /* GROUP */
+    double   plane_normal[3];   /* PLANE */
+    double   plane_value;       /* PLANE */
+    const struct rptx_shape_desc* children; /* GROUP: n_children leaf shapes (SPHERE/CUBE/MESH) */
+} rptx_shape_desc;
+
+/* ---- materials: src/material.rs:8-23 ---- */
+enum {
+    RPTX_MAT_LAMBERTIAN   = 0,
+    RPTX_MAT_PHONG        = 1,
+    RPTX_MAT_MIRROR       = 2,
+    RPTX_MAT_TRANSMISSIVE = 3
+};
+
+typedef struct rptx_material {
+    int32_t kind;
+    int32_t _pad;
+    double  albedo[3];
+    double  emittance;
+    double  shininess;  /* Phong exponent (the reference stores "roughness" here, src/material.rs:44-50) */
+    double  ior;
+} rptx_material;
+
+/* ---- lights: src/light.rs:7-19 ---- */
+enum {
+    RPTX_LIGHT_POINT       = 0, /* color, vec = location */
+    RPTX_LIGHT_AMBIENT     = 1, /* color */
+    RPTX_LIGHT_DIRECTIONAL = 2, /* color, vec = direction */
+    RPTX_LIGHT_OBJECT      = 3  /* shape + material (emissive object, invisible unless also added as object) */
+};
+
+typedef struct rptx_light {
+    int32_t         kind;
+    int32_t         _pad;
+    double          color[3];
+    double          vec[3];
+    rptx_shape_desc shape;
+    rptx_material   material;
+} rptx_light;
+
+/* ---- media: src/medium.rs:80-121 (the only two constructors) ---- */
+enum {
+    RPTX_MEDIUM_NONE                  = 0,
+    RPTX_MEDIUM_HOMOGENEOUS_ISOTROPIC = 1,
+    RPTX_MEDIUM_COLORED_GLOWING_FOG   = 2
+};
+
+/* ---- camera: src/camera.rs:9-27 ---- */
+typedef struct rptx_camera {
+    double eye[3];
+    double direction[3];
+    double up[3];
+    double fov;
+    double aperture;
+    double focal_distance;
+} rptx_camera;
+
+/* ---- Renderer builder fields: src/renderer.rs:23-56, defaults :60-76 ---- */
+typedef struct rptx_params {
+    uint32_t width, height;
+    double   exposure_value;
+    uint32_t filter_radius;       /* Filter::Box(r), src/buffer.rs:98-108 */
+    uint32_t max_bounces;
+    uint32_t num_samples;
+    uint32_t _pad;
+    uint64_t gather_size;
+    uint64_t gather_size_volume;
+    double   watts;
+    double   stepsize;            /* stored, never read (src/renderer.rs:42-43) */
+    uint64_t seed;                /* the reference seeds from OS entropy; here runs are reproducible */
+    /* Multi-GPU sample sharding: this rank renders sample indices
+     * {s : s % shard_count == shard_index} of every batch.  (1,0) = all. */
+    uint32_t shard_count, shard_index;
+} rptx_params;
+
+enum { /* PhotonRenderKind, src/photon.rs:629-637 */
+    RPTX_PHOTON_MAP        = 0,
+    RPTX_PHOTON_POINT_BEAM = 1,
+    RPTX_PHOTON_BEAM_BEAM  = 2
+};
+
+typedef struct rptx_ctx   rptx_ctx;
+typedef struct rptx_scene rptx_scene;
+typedef struct rptx_film  rptx_film;
+
+typedef struct rptx_stats {
+    uint64_t path_samples;     /* camera paths started */
+    uint64_t extend_rays;      /* closest-hit queries for path segments */
+    uint64_t shadow_rays;      /* closest-hit queries for NEE */
+    uint64_t waves;            /* wavefront iterations */
+    uint64_t kernel_launches;  /* kernels of this library launched */
+    double   device_ms;        /* CUDA-event time of the last render_sample call */
+    double   trace_ms;         /* of which: extend+shadow kernels */
+    uint64_t photons_emitted, photons_surface, photons_volume;
+    uint64_t gather_queries;
+} rptx_stats;
+
+int         rptx_abi_version(void);
+
+/* context = one CUDA device + its streams */
+int         rptx_ctx_create(int device_id, rptx_ctx** out);
+void        rptx_ctx_destroy(rptx_ctx* ctx);
+const char* rptx_last_error(const rptx_ctx* ctx);
+
+/* Scene (src/scene.rs:12-24).  Caller-owned arrays are copied. */
+int  rptx_scene_create(rptx_ctx* ctx, rptx_scene** out);
+void rptx_scene_destroy(rptx_scene* scene);
+/* triangles as [ntri][3 vertices][xyz]; normals same layout or NULL (=> face normals,
+ * Triangle::from_vertices src/shape/mesh.rs:27-38) */
+int  rptx_scene_add_mesh(rptx_scene* scene, const double* vertices, const double* normals,
+                         size_t ntri, uint32_t* mesh_id);
+/* SceneAdd<Object> src/scene.rs:40-44 */
+int  rptx_scene_add_object(rptx_scene* scene, const rptx_shape_desc* shape,
+                           const rptx_material* material, uint32_t* object_id);
+/* SceneAdd<Light> src/scene.rs:46-50 */
+int  rptx_scene_add_light(rptx_scene* scene, const rptx_light* light);
+/* SceneAdd<Medium> src/scene.rs:77-81; only media[0] is ever used (src/renderer.rs:190) */
+int  rptx_scene_set_medium(rptx_scene* scene, int32_t kind, double absorption, double scattering);
+/* Environment::Color src/environment.rs:56-68 */
+int  rptx_scene_set_environment_color(rptx_scene* scene, const double rgb[3]);
+/* Environment::Hdri src/environment.rs:5-52; pixels as [height][width][3] f64 */
+int  rptx_scene_set_environment_hdri(rptx_scene* scene, uint32_t width, uint32_t height,
+                                     const double* pixels);
+/* flatten, upload, build the BVHs on the device */
+int  rptx_scene_commit(rptx_scene* scene);
+
+/* Renderer::new(...).width(..)... ; Buffer::new (src/renderer.rs:138,148) */
+int  rptx_render_begin(rptx_ctx* ctx, rptx_scene* scene, const rptx_camera* camera,
+                       const rptx_params* params, rptx_film** out);
+void rptx_film_destroy(rptx_film* film);
+/* Renderer::sample(iterations, &mut buffer) src/renderer.rs:158-171: one batch = one
+ * mean colour per pixel pushed into the Buffer. */
+int  rptx_render_sample(rptx_film* film, uint32_t iterations);
+/* Split form used for multi-GPU: trace this rank's shard of the batch into the batch-sum
+ * buffer (device, f64 [h][w][3]); the caller may all-reduce that buffer (NCCL) between the
+ * two calls; commit divides by `iterations`, applies 2^EV and pushes the batch mean. */
+int  rptx_render_sample_trace(rptx_film* film, uint32_t iterations);
+int  rptx_render_sample_commit(rptx_film* film, uint32_t iterations);
+void* rptx_film_batch_sum_device_ptr(rptx_film* film);  /* device pointer, 3*w*h doubles */
+/* Buffer::image() src/buffer.rs:43-56 (box filter, clamp, gamma 2.2, truncating u8) */
+int  rptx_film_image_rgb8(rptx_film* film, uint8_t* out_rgb /* [h][w][3] */);
+/* Buffer::variance() src/buffer.rs:59-73 */
+int  rptx_film_variance(rptx_film* film, double* out);
+/* mean over batches of the batch means, unfiltered, linear; [h][w][3] f64 */
+int  rptx_film_mean(rptx_film* film, double* out);
+
+/* photon_render src/photon.rs:655-720 */
+int  rptx_photon_render(rptx_ctx* ctx, rptx_scene* scene, const rptx_camera* camera,
+                        const rptx_params* params, uint64_t photon_count, int32_t kind,
+                        uint8_t* out_rgb8 /* [h][w][3] or NULL */,
+                        double* out_mean /* [h][w][3] or NULL */);
+
+/* Parity hooks.
+ * get_closest_hit (src/renderer.rs:416-425) over a batch of rays given as host arrays
+ * o[n][3], d[n][3].  Outputs (host): t[n] (+inf on miss), object_id[n] (UINT32_MAX on miss),
+ * prim_id[n] (triangle index within its mesh, 0 for analytic shapes), inst_id[n] (child index
+ * within a GROUP, else 0), normal[n][3].  Any output pointer may be NULL. */
+int  rptx_intersect_batch(rptx_scene* scene, const double* o, const double* d, size_t n,
+                          double t_min, double* t, uint32_t* object_id, uint32_t* prim_id,
+                          uint32_t* inst_id, double* normal);
+/* Same query with all arrays resident on the device (used by bench.py for the kernel-only
+ * roofline number). */
+int  rptx_intersect_batch_device(rptx_scene* scene, const void* d_o, const void* d_d, size_t n,
+                                 double t_min, void* d_t, void* d_object_id, void* d_prim_id,
+                                 void* d_inst_id, void* d_normal);
+int  rptx_stats_get(const rptx_film* film, rptx_stats* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RPTX_H */

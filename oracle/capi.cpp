@@ -1,0 +1,316 @@
+// ORACLE — TEST INFRASTRUCTURE ONLY (see vec.hpp header).
+// C entry points over the CPU restatement, consumed through ctypes by tests/,
+// __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs ONLY.
+// They take the same POD records as include/rptx.h so that one scene description
+// drives both the CUDA library and this checker.
+#include <chrono>
+#include <cstring>
+#include <string>
+
+#include "../include/rptx.h"
+#include "photon.hpp"
+#include "render.hpp"
+
+using namespace orc;
+
+namespace {
+
+struct OScene {
+    Scene scene;
+    std::vector<std::shared_ptr<const Shape>> meshes;
+    std::vector<bool> object_is_group;
+    std::string err;
+};
+
+struct OFilm {
+    OScene* scene;
+    Renderer r;
+    Buffer buf;
+    uint64_t next_sample = 0;
+    Counters ctr;
+    double last_seconds = 0;
+    OFilm(OScene* s, uint32_t w, uint32_t h, uint32_t fr) : scene(s), buf(w, h, fr) {}
+};
+
+Mat4 to_mat4(const double* t) {
+    Mat4 m;
+    for (int r = 0; r < 4; r++)
+        for (int c = 0; c < 4; c++) m.m[r][c] = t[4 * r + c];
+    return m;
+}
+
+Material to_material(const rptx_material* m) {
+    Material out;
+    out.kind = (Material::Kind)m->kind;
+    out.albedo = Vec3(m->albedo[0], m->albedo[1], m->albedo[2]);
+    out.emittance_ = m->emittance;
+    out.shininess = m->shininess;
+    out.ior = m->ior;
+    return out;
+}
+
+std::shared_ptr<const Shape> build_shape(OScene* s, const rptx_shape_desc* d, bool* is_group) {
+    std::shared_ptr<const Shape> base;
+    if (is_group) *is_group = false;
+    switch (d->kind) {
+        case RPTX_SHAPE_SPHERE: base = std::make_shared<Sphere>(); break;
+        case RPTX_SHAPE_CUBE: base = std::make_shared<Cube>(); break;
+        case RPTX_SHAPE_PLANE:
+            base = std::make_shared<Plane>(Vec3(d->plane_normal[0], d->plane_normal[1], d->plane_normal[2]), d->plane_value);
+            break;
+        case RPTX_SHAPE_MESH:
+            if (d->mesh_id >= s->meshes.size()) { s->err = "bad mesh id"; return nullptr; }
+            base = s->meshes[d->mesh_id];
+            break;
+        case RPTX_SHAPE_GROUP: {
+            std::vector<std::shared_ptr<const Shape>> kids;
+            for (uint32_t i = 0; i < d->n_children; i++) {
+                if (d->children[i].kind == RPTX_SHAPE_GROUP || d->children[i].kind == RPTX_SHAPE_PLANE) {
+                    s->err = "group children must be bounded leaf shapes";
+                    return nullptr;
+                }
+                auto k = build_shape(s, &d->children[i], nullptr);
+                if (!k) return nullptr;
+                kids.push_back(k);
+            }
+            base = std::make_shared<KdTree>(std::move(kids), true);
+            if (is_group) *is_group = true;
+            break;
+        }
+        default: s->err = "bad shape kind"; return nullptr;
+    }
+    if (d->has_transform) base = std::make_shared<Transformed>(base, to_mat4(d->transform));
+    return base;
+}
+
+}  // namespace
+
+extern "C" {
+
+void* orc_scene_create() { return new OScene(); }
+void orc_scene_destroy(void* s) { delete (OScene*)s; }
+const char* orc_last_error(void* s) { return ((OScene*)s)->err.c_str(); }
+
+int orc_scene_add_mesh(void* sp, const double* v, const double* n, size_t ntri, uint32_t* mesh_id) {
+    OScene* s = (OScene*)sp;
+    std::vector<std::shared_ptr<const Shape>> tris;
+    tris.reserve(ntri);
+    for (size_t i = 0; i < ntri; i++) {
+        const double* p = v + 9 * i;
+        auto t = std::make_shared<Triangle>();
+        if (n) {
+            const double* q = n + 9 * i;
+            t->v1 = Vec3(p[0], p[1], p[2]); t->v2 = Vec3(p[3], p[4], p[5]); t->v3 = Vec3(p[6], p[7], p[8]);
+            t->n1 = Vec3(q[0], q[1], q[2]); t->n2 = Vec3(q[3], q[4], q[5]); t->n3 = Vec3(q[6], q[7], q[8]);
+        } else {
+            *t = Triangle::from_vertices(Vec3(p[0], p[1], p[2]), Vec3(p[3], p[4], p[5]), Vec3(p[6], p[7], p[8]));
+        }
+        tris.push_back(t);
+    }
+    s->meshes.push_back(std::make_shared<KdTree>(std::move(tris), false));
+    *mesh_id = (uint32_t)s->meshes.size() - 1;
+    return 0;
+}
+
+int orc_scene_add_object(void* sp, const rptx_shape_desc* d, const rptx_material* m, uint32_t* id) {
+    OScene* s = (OScene*)sp;
+    bool grp = false;
+    auto sh = build_shape(s, d, &grp);
+    if (!sh) return 1;
+    s->scene.objects.push_back({sh, to_material(m)});
+    s->object_is_group.push_back(grp);
+    if (id) *id = (uint32_t)s->scene.objects.size() - 1;
+    return 0;
+}
+
+int orc_scene_add_light(void* sp, const rptx_light* l) {
+    OScene* s = (OScene*)sp;
+    Light out;
+    out.kind = (Light::Kind)l->kind;
+    out.color = Vec3(l->color[0], l->color[1], l->color[2]);
+    out.vec = Vec3(l->vec[0], l->vec[1], l->vec[2]);
+    if (l->kind == RPTX_LIGHT_OBJECT) {
+        auto sh = build_shape(s, &l->shape, nullptr);
+        if (!sh) return 1;
+        out.object = {sh, to_material(&l->material)};
+    }
+    s->scene.lights.push_back(out);
+    return 0;
+}
+
+int orc_scene_set_medium(void* sp, int32_t kind, double a, double sc) {
+    OScene* s = (OScene*)sp;
+    s->scene.media.clear();
+    if (kind == RPTX_MEDIUM_NONE) return 0;
+    Medium m;
+    m.kind = (Medium::Kind)kind; m.absorption_ = a; m.scattering_ = sc;
+    s->scene.media.push_back(m);
+    return 0;
+}
+
+int orc_scene_set_environment_color(void* sp, const double rgb[3]) {
+    OScene* s = (OScene*)sp;
+    s->scene.environment.is_hdri = false;
+    s->scene.environment.color = Vec3(rgb[0], rgb[1], rgb[2]);
+    return 0;
+}
+
+int orc_scene_set_environment_hdri(void* sp, uint32_t w, uint32_t h, const double* px) {
+    OScene* s = (OScene*)sp;
+    auto& e = s->scene.environment;
+    e.is_hdri = true; e.width = w; e.height = h;
+    e.buf.resize((size_t)w * h);
+    for (size_t i = 0; i < e.buf.size(); i++) e.buf[i] = Vec3(px[3 * i], px[3 * i + 1], px[3 * i + 2]);
+    return 0;
+}
+
+// kd-tree statistics of a mesh (nodes, leaves, leaf items) — informational
+int orc_mesh_kd_stats(void* sp, uint32_t mesh_id, uint64_t out[3]) {
+    OScene* s = (OScene*)sp;
+    if (mesh_id >= s->meshes.size()) return 1;
+    auto* k = (const KdTree*)s->meshes[mesh_id].get();
+    out[0] = k->n_nodes; out[1] = k->n_leaves; out[2] = k->n_leaf_items;
+    return 0;
+}
+
+static void fill_renderer(Renderer& r, OScene* s, const rptx_camera* c, const rptx_params* p, int threads) {
+    r.scene = &s->scene;
+    r.camera.eye = Vec3(c->eye[0], c->eye[1], c->eye[2]);
+    r.camera.direction = Vec3(c->direction[0], c->direction[1], c->direction[2]);
+    r.camera.up = Vec3(c->up[0], c->up[1], c->up[2]);
+    r.camera.fov = c->fov; r.camera.aperture = c->aperture; r.camera.focal_distance = c->focal_distance;
+    r.width = p->width; r.height = p->height; r.exposure_value = p->exposure_value;
+    r.filter_radius = p->filter_radius; r.max_bounces = p->max_bounces; r.num_samples = p->num_samples;
+    r.gather_size = p->gather_size; r.gather_size_volume = p->gather_size_volume; r.watts = p->watts;
+    r.seed = p->seed; r.threads = threads;
+}
+
+void* orc_render_begin(void* sp, const rptx_camera* c, const rptx_params* p, int threads) {
+    OScene* s = (OScene*)sp;
+    OFilm* f = new OFilm(s, p->width, p->height, p->filter_radius);
+    fill_renderer(f->r, s, c, p, threads);
+    return f;
+}
+void orc_film_destroy(void* f) { delete (OFilm*)f; }
+
+int orc_render_sample(void* fp, uint32_t iterations) {
+    OFilm* f = (OFilm*)fp;
+    const auto t0 = std::chrono::steady_clock::now();
+    f->r.sample(f->next_sample, iterations, f->buf, &f->ctr, nullptr);
+    f->last_seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    f->next_sample += iterations;
+    return 0;
+}
+// Render only rows [y0,y1) of one batch without touching the Buffer (bounded timing sample).
+double orc_time_rows(void* fp, uint32_t y0, uint32_t y1, uint32_t iterations, uint64_t counters[4]) {
+    OFilm* f = (OFilm*)fp;
+    Renderer r = f->r;
+    const int nt = r.threads > 0 ? r.threads : std::max(1, (int)std::thread::hardware_concurrency());
+    std::vector<Counters> ctrs(nt);
+    std::atomic<uint32_t> next{y0};
+    std::vector<Vec3> sink(nt);
+    const auto t0 = std::chrono::steady_clock::now();
+    std::vector<std::thread> pool;
+    for (int t = 0; t < nt; t++)
+        pool.emplace_back([&, t] {
+            for (;;) {
+                const uint32_t y = next.fetch_add(1);
+                if (y >= y1) break;
+                for (uint32_t x = 0; x < r.width; x++) sink[t] += r.get_color(x, y, 0, iterations, &ctrs[t], nullptr);
+            }
+        });
+    for (auto& th : pool) th.join();
+    const double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    Counters tot;
+    for (auto& c : ctrs) { tot.extend_rays += c.extend_rays; tot.shadow_rays += c.shadow_rays; tot.shadow_pass += c.shadow_pass; tot.shadow_near += c.shadow_near; }
+    if (counters) { counters[0] = tot.extend_rays; counters[1] = tot.shadow_rays; counters[2] = tot.shadow_pass; counters[3] = tot.shadow_near; }
+    return sec;
+}
+double orc_film_last_seconds(void* fp) { return ((OFilm*)fp)->last_seconds; }
+int orc_film_counters(void* fp, uint64_t out[4]) {
+    OFilm* f = (OFilm*)fp;
+    out[0] = f->ctr.extend_rays; out[1] = f->ctr.shadow_rays; out[2] = f->ctr.shadow_pass; out[3] = f->ctr.shadow_near;
+    return 0;
+}
+int orc_film_image_rgb8(void* fp, uint8_t* out) { ((OFilm*)fp)->buf.image(out); return 0; }
+int orc_film_variance(void* fp, double* out) { *out = ((OFilm*)fp)->buf.variance(); return 0; }
+int orc_film_mean(void* fp, double* out) { ((OFilm*)fp)->buf.mean(out); return 0; }
+
+// per-sample radiance (no exposure, no averaging) for listed (pixel, sample) pairs
+int orc_sample_radiance(void* fp, const uint32_t* px, const uint32_t* py, const uint64_t* sample, size_t n, double* out) {
+    OFilm* f = (OFilm*)fp;
+    for (size_t i = 0; i < n; i++) {
+        const Color c = f->r.sample_radiance(px[i], py[i], sample[i]);
+        out[3 * i] = c.x; out[3 * i + 1] = c.y; out[3 * i + 2] = c.z;
+    }
+    return 0;
+}
+
+// dump up to cap rays (every closest-hit query) of one batch rendered serially
+size_t orc_dump_rays(void* fp, uint32_t iterations, size_t cap, double* o, double* d, uint8_t* kind) {
+    OFilm* f = (OFilm*)fp;
+    RayLog log;
+    log.cap = cap;
+    Buffer tmp(f->r.width, f->r.height, 0);
+    f->r.sample(0, iterations, tmp, nullptr, &log);
+    const size_t n = log.kind.size();
+    std::memcpy(o, log.o.data(), n * 3 * sizeof(double));
+    std::memcpy(d, log.d.data(), n * 3 * sizeof(double));
+    std::memcpy(kind, log.kind.data(), n);
+    return n;
+}
+
+// get_closest_hit over a batch (threads > 1 splits the batch)
+int orc_intersect_batch(void* sp, const double* o, const double* d, size_t n, double t_min, double* t, uint32_t* object_id,
+                        uint32_t* prim_id, uint32_t* inst_id, double* normal, int threads) {
+    OScene* s = (OScene*)sp;
+    int nt = threads > 0 ? threads : 1;
+    auto work = [&](size_t lo, size_t hi) {
+        for (size_t i = lo; i < hi; i++) {
+            const Ray ray{Vec3(o[3 * i], o[3 * i + 1], o[3 * i + 2]), Vec3(d[3 * i], d[3 * i + 1], d[3 * i + 2])};
+            HitRecord h;
+            uint32_t id = 0xffffffffu;
+            for (size_t k = 0; k < s->scene.objects.size(); k++)
+                if (s->scene.objects[k].shape->intersect(ray, t_min, h)) id = (uint32_t)k;
+            const bool hit = id != 0xffffffffu;
+            if (t) t[i] = hit ? h.time : INF;
+            if (object_id) object_id[i] = id;
+            if (prim_id) prim_id[i] = hit ? h.prim_id : 0;
+            if (inst_id) inst_id[i] = (hit && s->object_is_group[id]) ? h.inst_id : 0;
+            if (normal) { normal[3 * i] = h.normal.x; normal[3 * i + 1] = h.normal.y; normal[3 * i + 2] = h.normal.z; }
+        }
+    };
+    if (nt == 1) { work(0, n); return 0; }
+    std::vector<std::thread> pool;
+    for (int k = 0; k < nt; k++) pool.emplace_back(work, n * k / nt, n * (k + 1) / nt);
+    for (auto& th : pool) th.join();
+    return 0;
+}
+
+// known-answer helpers for tests
+void orc_hex_color(uint32_t x, double out[3]) { Color c = hex_color(x); out[0] = c.x; out[1] = c.y; out[2] = c.z; }
+void orc_color_bytes(const double c[3], uint8_t out[3]) { color_bytes(Vec3(c[0], c[1], c[2]), out); }
+uint64_t orc_rng_u64(uint64_t seed, uint64_t domain, uint64_t a, uint64_t b, uint32_t skip) {
+    Rng r(seed, domain, a, b);
+    for (uint32_t i = 0; i < skip; i++) r.next_u64();
+    return r.next_u64();
+}
+int orc_hardware_threads() { return (int)std::thread::hardware_concurrency(); }
+
+// photon_render (src/photon.rs:655-720)
+int orc_photon_render(void* sp, const rptx_camera* c, const rptx_params* p, uint64_t photon_count, int32_t kind, int threads,
+                      uint8_t* out_rgb8, double* out_mean, uint64_t counts[2], double seconds[3]) {
+    OScene* s = (OScene*)sp;
+    Renderer r;
+    fill_renderer(r, s, c, p, threads);
+    PhotonStats st;
+    Buffer buf(p->width, p->height, p->filter_radius);
+    if (!photon_render(r, photon_count, (PhotonRenderKind)kind, buf, &st)) { s->err = "Only found non-object lights while photon mapping"; return 1; }
+    if (out_rgb8) buf.image(out_rgb8);
+    if (out_mean) buf.mean(out_mean);
+    if (counts) { counts[0] = st.n_surface; counts[1] = st.n_volume; }
+    if (seconds) { seconds[0] = st.emit_s; seconds[1] = st.build_s; seconds[2] = st.gather_s; }
+    return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,187 @@
+// GPU LBVH build — see bvh_build.cuh.
+#include <cub/cub.cuh>
+
+#include "bvh_build.cuh"
+
+namespace rptx {
+
+namespace {
+
+__device__ __forceinline__ uint32_t expand_bits10(uint32_t v) {
+    v = (v * 0x00010001u) & 0xFF0000FFu;
+    v = (v * 0x00000101u) & 0x0F00F00Fu;
+    v = (v * 0x00000011u) & 0xC30C30C3u;
+    v = (v * 0x00000005u) & 0x49249249u;
+    return v;
+}
+
+__global__ void k_morton(const PrimBox* __restrict__ boxes, uint32_t n, float3 cmin, float3 cinv, uint64_t* __restrict__ keys) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const PrimBox b = boxes[i];
+    const float cx = (0.5f * (b.mn[0] + b.mx[0]) - cmin.x) * cinv.x;
+    const float cy = (0.5f * (b.mn[1] + b.mx[1]) - cmin.y) * cinv.y;
+    const float cz = (0.5f * (b.mn[2] + b.mx[2]) - cmin.z) * cinv.z;
+    const uint32_t x = (uint32_t)fminf(fmaxf(cx * 1024.0f, 0.0f), 1023.0f);
+    const uint32_t y = (uint32_t)fminf(fmaxf(cy * 1024.0f, 0.0f), 1023.0f);
+    const uint32_t z = (uint32_t)fminf(fmaxf(cz * 1024.0f, 0.0f), 1023.0f);
+    const uint32_t code = (expand_bits10(x) << 2) | (expand_bits10(y) << 1) | expand_bits10(z);
+    keys[i] = ((uint64_t)code << 32) | (uint64_t)i;  // index makes every key unique
+}
+
+__device__ __forceinline__ int delta(const uint64_t* __restrict__ keys, int n, int i, int j) {
+    if (j < 0 || j >= n) return -1;
+    return __clzll((long long)(keys[i] ^ keys[j]));
+}
+
+// Karras 2012: one thread per internal node
+__global__ void k_hierarchy(const uint64_t* __restrict__ keys, int n, int* __restrict__ left, int* __restrict__ right,
+                            int* __restrict__ first, int* __restrict__ last, int* __restrict__ parent_i,
+                            int* __restrict__ parent_l) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n - 1) return;
+    const int d = (delta(keys, n, i, i + 1) - delta(keys, n, i, i - 1)) >= 0 ? 1 : -1;
+    const int dmin = delta(keys, n, i, i - d);
+    int lmax = 2;
+    while (delta(keys, n, i, i + lmax * d) > dmin) lmax *= 2;
+    int l = 0;
+    for (int t = lmax / 2; t >= 1; t /= 2)
+        if (delta(keys, n, i, i + (l + t) * d) > dmin) l += t;
+    const int j = i + l * d;
+    const int dnode = delta(keys, n, i, j);
+    int s = 0;
+    int t = l;
+    do {
+        t = (t + 1) / 2;
+        if (delta(keys, n, i, i + (s + t) * d) > dnode) s += t;
+    } while (t > 1);
+    const int gamma = i + s * d + min(d, 0);
+    const int lo = min(i, j), hi = max(i, j);
+    // children encoded: >= 0 internal, < 0 leaf ~index
+    const int lc = (lo == gamma) ? ~gamma : gamma;
+    const int rc = (hi == gamma + 1) ? ~(gamma + 1) : gamma + 1;
+    left[i] = lc; right[i] = rc; first[i] = lo; last[i] = hi;
+    if (lc >= 0) parent_i[lc] = i; else parent_l[~lc] = i;
+    if (rc >= 0) parent_i[rc] = i; else parent_l[~rc] = i;
+    if (i == 0) parent_i[0] = -1;
+}
+
+__device__ __forceinline__ PrimBox merge(const PrimBox& a, const PrimBox& b) {
+    PrimBox r;
+#pragma unroll
+    for (int k = 0; k < 3; k++) { r.mn[k] = fminf(a.mn[k], b.mn[k]); r.mx[k] = fmaxf(a.mx[k], b.mx[k]); }
+    return r;
+}
+
+// L2-coherent read of a box written by another thread of the same launch
+__device__ __forceinline__ PrimBox load_cg(const PrimBox* p) {
+    PrimBox r;
+#pragma unroll
+    for (int k = 0; k < 3; k++) { r.mn[k] = __ldcg(&p->mn[k]); r.mx[k] = __ldcg(&p->mx[k]); }
+    return r;
+}
+
+// bottom-up refit: one thread per leaf, second arrival at a node merges its children
+__global__ void k_refit(const PrimBox* __restrict__ boxes, const uint64_t* __restrict__ keys, int n, const int* __restrict__ left,
+                        const int* __restrict__ right, const int* __restrict__ parent_i, const int* __restrict__ parent_l,
+                        int* __restrict__ flags, PrimBox* __restrict__ ibox) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    int p = parent_l[k];
+    while (p >= 0) {
+        __threadfence();
+        if (atomicAdd(&flags[p], 1) == 0) return;
+        __threadfence();
+        const int lc = left[p], rc = right[p];
+        const PrimBox a = lc >= 0 ? load_cg(&ibox[lc]) : boxes[(uint32_t)(keys[~lc] & 0xffffffffu)];
+        const PrimBox b = rc >= 0 ? load_cg(&ibox[rc]) : boxes[(uint32_t)(keys[~rc] & 0xffffffffu)];
+        ibox[p] = merge(a, b);
+        p = parent_i[p];
+    }
+}
+
+__device__ __forceinline__ void child_out(int c, const PrimBox* __restrict__ boxes, const uint64_t* __restrict__ keys,
+                                          const PrimBox* __restrict__ ibox, const int* __restrict__ first,
+                                          const int* __restrict__ last, float pad, float* mn, float* mx, int* ref) {
+    PrimBox b;
+    if (c >= 0) {
+        b = ibox[c];
+        const int sz = last[c] - first[c] + 1;
+        *ref = (sz <= kLeafMax) ? make_leaf_ref((uint32_t)first[c], (uint32_t)sz) : c;
+    } else {
+        b = boxes[(uint32_t)(keys[~c] & 0xffffffffu)];
+        *ref = make_leaf_ref((uint32_t)(~c), 1u);
+    }
+#pragma unroll
+    for (int k = 0; k < 3; k++) { mn[k] = __fsub_rd(b.mn[k], pad); mx[k] = __fadd_ru(b.mx[k], pad); }
+}
+
+__global__ void k_emit(const PrimBox* __restrict__ boxes, const uint64_t* __restrict__ keys, int n, const int* __restrict__ left,
+                       const int* __restrict__ right, const int* __restrict__ first, const int* __restrict__ last,
+                       const PrimBox* __restrict__ ibox, float pad, BvhNode* __restrict__ nodes, uint32_t* __restrict__ perm) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) perm[i] = (uint32_t)(keys[i] & 0xffffffffu);
+    if (i >= n - 1) return;
+    BvhNode nd;
+    child_out(left[i], boxes, keys, ibox, first, last, pad, nd.lmin, nd.lmax, &nd.left);
+    child_out(right[i], boxes, keys, ibox, first, last, pad, nd.rmin, nd.rmax, &nd.right);
+    nd.pad0 = 0; nd.pad1 = 0;
+    nodes[i] = nd;
+}
+
+}  // namespace
+
+int build_lbvh(const PrimBox* d_boxes, uint32_t n, float pad, const double cmin[3], const double cmax[3], BvhNode* d_nodes,
+               uint32_t* d_perm, int* root_ref, cudaStream_t stream, uint64_t* launches) {
+    if (n == 0) { *root_ref = 0; return 0; }
+    cudaError_t e;
+    uint64_t *keys_in = nullptr, *keys_out = nullptr;
+    int* ints = nullptr;
+    PrimBox* ibox = nullptr;
+    void* tmp = nullptr;
+    size_t tmp_bytes = 0;
+#define RPTX_CK(x) do { e = (x); if (e != cudaSuccess) goto fail; } while (0)
+    RPTX_CK(cudaMalloc(&keys_in, sizeof(uint64_t) * n));
+    RPTX_CK(cudaMalloc(&keys_out, sizeof(uint64_t) * n));
+    RPTX_CK(cudaMalloc(&ints, sizeof(int) * (size_t)n * 7));
+    RPTX_CK(cudaMalloc(&ibox, sizeof(PrimBox) * n));
+    {
+        float3 fmin = make_float3((float)cmin[0], (float)cmin[1], (float)cmin[2]);
+        float3 finv;
+        finv.x = cmax[0] > cmin[0] ? (float)(1.0 / (cmax[0] - cmin[0])) : 0.f;
+        finv.y = cmax[1] > cmin[1] ? (float)(1.0 / (cmax[1] - cmin[1])) : 0.f;
+        finv.z = cmax[2] > cmin[2] ? (float)(1.0 / (cmax[2] - cmin[2])) : 0.f;
+        const int T = 128;
+        const int B = (int)((n + T - 1) / T);
+        k_morton<<<B, T, 0, stream>>>(d_boxes, n, fmin, finv, keys_in);
+        (*launches)++;
+        RPTX_CK(cub::DeviceRadixSort::SortKeys(nullptr, tmp_bytes, keys_in, keys_out, (int)n, 0, 64, stream));
+        RPTX_CK(cudaMalloc(&tmp, tmp_bytes ? tmp_bytes : 16));
+        RPTX_CK(cub::DeviceRadixSort::SortKeys(tmp, tmp_bytes, keys_in, keys_out, (int)n, 0, 64, stream));
+        (*launches) += 1;
+        int* left = ints;
+        int* right = ints + n;
+        int* first = ints + 2 * (size_t)n;
+        int* last = ints + 3 * (size_t)n;
+        int* parent_i = ints + 4 * (size_t)n;
+        int* parent_l = ints + 5 * (size_t)n;
+        int* flags = ints + 6 * (size_t)n;
+        RPTX_CK(cudaMemsetAsync(flags, 0, sizeof(int) * n, stream));
+        if (n > 1) {
+            k_hierarchy<<<B, T, 0, stream>>>(keys_out, (int)n, left, right, first, last, parent_i, parent_l);
+            k_refit<<<B, T, 0, stream>>>(d_boxes, keys_out, (int)n, left, right, parent_i, parent_l, flags, ibox);
+            (*launches) += 2;
+        }
+        k_emit<<<B, T, 0, stream>>>(d_boxes, keys_out, (int)n, left, right, first, last, ibox, pad, d_nodes, d_perm);
+        (*launches)++;
+        RPTX_CK(cudaGetLastError());
+        RPTX_CK(cudaStreamSynchronize(stream));
+        *root_ref = (n <= (uint32_t)kLeafMax) ? make_leaf_ref(0u, n) : 0;
+    }
+fail:
+#undef RPTX_CK
+    cudaFree(keys_in); cudaFree(keys_out); cudaFree(ints); cudaFree(ibox); cudaFree(tmp);
+    return (int)e;
+}
+
+}  // namespace rptx

@@ -1,0 +1,78 @@
+// Host-side objects behind the opaque handles of include/rptx.h.
+#pragma once
+#include <array>
+#include <string>
+#include <vector>
+
+#include "../../include/rptx.h"
+#include "common.cuh"
+#include "path.cuh"
+
+struct rptx_ctx {
+    int device = 0;
+    int sm_count = 148;
+    cudaStream_t stream = nullptr;
+    void* h_pinned = nullptr;
+    uint64_t launches = 0;
+    std::string err;
+};
+
+struct HostMesh {
+    std::vector<rptx::RawTri> tris;  // original order
+    bool has_normals = true;
+    double bmin[3], bmax[3];
+    // filled by commit
+    uint32_t raw_base = 0, tri_base = 0, node_base = 0;
+    int root_ref = 0;
+    float pad = 0.f;
+};
+
+struct HostObject {
+    rptx_shape_desc desc;
+    std::vector<rptx_shape_desc> children;
+    rptx_material material;
+};
+
+struct rptx_scene {
+    rptx_ctx* ctx = nullptr;
+    std::vector<HostMesh> meshes;
+    std::vector<HostObject> objects;
+    std::vector<rptx_light> lights;
+    int medium_kind = RPTX_MEDIUM_NONE;
+    double sigma_a = 0, sigma_s = 0;
+    bool env_is_hdri = false;
+    double env_color[3] = {0, 0, 0};
+    uint32_t env_w = 0, env_h = 0;
+    std::vector<double> env_pixels;
+    // device state
+    bool committed = false;
+    const rptx::BvhNode* d_nodes = nullptr;
+    const rptx::Instance* d_instances = nullptr;
+    const rptx::TriRec* d_tris = nullptr;
+    const rptx::TriNormals* d_tri_normals = nullptr;
+    const uint32_t* d_tri_orig = nullptr;
+    const rptx::Material* d_materials = nullptr;
+    const rptx::Light* d_lights = nullptr;
+    const rptx::RawTri* d_raw = nullptr;
+    const double* d_env = nullptr;
+    int tlas_root_ref = 0;
+    uint32_t n_bounded = 0, n_unbounded = 0, n_shadow_lights = 0;
+    double wmin[3] = {0, 0, 0}, wmax[3] = {0, 0, 0};
+};
+
+struct rptx_film {
+    rptx_ctx* ctx = nullptr;
+    rptx_scene* scene = nullptr;
+    rptx_params params;
+    rptx::Camera cam;
+    rptx::PathPool pool;
+    rptx::Queues q;
+    std::vector<void*> owned;
+    double* d_batch_sum = nullptr;
+    double* d_film_sum = nullptr;
+    std::vector<double*> batches;  // one mean image per Renderer::sample call, as Buffer keeps them
+    double** d_batch_ptrs = nullptr;
+    uint64_t next_sample = 0;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    rptx_stats stats = {};
+};

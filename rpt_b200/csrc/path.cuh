@@ -1,0 +1,56 @@
+// Wavefront path tracer state: structure-of-arrays path pool in HBM + ballot-compacted queues.
+// One slot owns pixel (slot % n_pixels) and sample lane (slot / n_pixels); it walks its
+// samples one after another (path regeneration), summing their radiance into its own f64
+// accumulator, so the film needs no atomics and sums are deterministic.
+#pragma once
+#include "common.cuh"
+#include "rng.cuh"
+
+namespace rptx {
+
+struct PathPool {
+    uint32_t n_slots, n_pixels, n_lanes, n_shadow;  // n_shadow = non-ambient, non-directional lights
+    uint32_t stack_depth;                           // max_bounces + 1 (surface mode only)
+    // current segment
+    double *ox, *oy, *oz, *dx, *dy, *dz;
+    // closest hit of the segment
+    double* ht;
+    uint32_t* hobj;
+    double *hnx, *hny, *hnz;
+    // per-path bookkeeping
+    uint64_t* rng;
+    uint32_t* sample_j;  // index into this rank's sample list of the path in flight
+    uint32_t* depth;
+    uint32_t* flags;
+    // vertex being assembled
+    double *dirx, *diry, *dirz;                  // direct light of the current vertex
+    double *fx, *fy, *fz, *pdf, *abscos;          // continuation weights
+    double *sdx, *sdy, *sdz, *sdist, *scx, *scy, *scz;  // [n_shadow][n_slots] NEE candidates
+    // forward accumulation (medium mode): throughput and radiance
+    double *bx, *by, *bz, *lx, *ly, *lz;
+    // per-level records for the clamped back-fold (surface mode): [stack_depth][8][n_slots]
+    double* stack;
+    // lane film: sum of finished samples of this slot in the current batch
+    double *ax, *ay, *az;
+};
+
+enum PathFlags : uint32_t { kFlagTerminate = 1u, kFlagHasShadow = 2u };
+
+struct Queues {
+    uint32_t* cur;        // slot ids to process this wave
+    uint32_t* next;       // slot ids alive after this wave
+    uint32_t* counters;   // [0] cur count, [1] next count, [2] extend work head, [3] connect work head
+    unsigned long long* stats;  // [0] paths started, [1] extend rays, [2] shadow rays
+};
+
+struct BatchParams {
+    uint32_t width, height;
+    uint32_t max_bounces;
+    uint64_t seed;
+    uint64_t batch_base;    // global index of the batch's first sample
+    uint32_t iterations;    // samples per pixel in this batch (all ranks together)
+    uint32_t shard_count, shard_index;
+    uint32_t n_local;       // samples of this rank in this batch
+};
+
+}  // namespace rptx

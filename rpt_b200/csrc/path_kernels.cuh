@@ -1,0 +1,447 @@
+// Wavefront kernels of the path tracer: generate -> extend -> shade (surface / medium scatter)
+// -> connect (shadow/NEE resolve, vertex finalise, accumulate, regenerate).  Together they
+// evaluate Renderer::trace_ray (src/renderer.rs:187-322) iteratively:
+//  * surface branch (:286-321): per-level records (direct, f, pdf, |cos|) are kept in HBM and
+//    folded back to front when the path ends, because each level's whole indirect term is
+//    clamped per channel to FIREFLY_CLAMP (:311-313);
+//  * medium branch (:188-285): linear, so radiance is accumulated forward with a throughput.
+#pragma once
+#include "path.cuh"
+#include "shading.cuh"
+#include "trace.cuh"
+
+namespace rptx {
+
+constexpr int kBlock = 128;
+
+RPTX_D uint32_t lane_id() { return threadIdx.x & 31u; }
+
+// warp-ballot compaction: append `slot` of every lane with pred to q, one atomic per warp
+RPTX_D void queue_push(uint32_t* __restrict__ q, uint32_t* __restrict__ count, bool pred, uint32_t slot) {
+    const unsigned active = __activemask();
+    const unsigned mask = __ballot_sync(active, pred);
+    if (mask == 0) return;
+    const int leader = __ffs(mask) - 1;
+    uint32_t base = 0;
+    if ((int)lane_id() == leader) base = atomicAdd(count, (uint32_t)__popc(mask));
+    base = __shfl_sync(active, base, leader);
+    if (pred) q[base + __popc(mask & ((1u << lane_id()) - 1u))] = slot;
+}
+
+template <bool MEDIUM>
+RPTX_D void start_path(const PathPool& p, const BatchParams& bp, const Camera& cam, uint32_t slot, uint32_t j) {
+    const uint32_t pixel = slot % p.n_pixels;
+    const uint32_t x = pixel % bp.width, y = pixel / bp.width;
+    const uint64_t s = bp.batch_base + bp.shard_index + (uint64_t)j * bp.shard_count;
+    Rng rng = Rng::make(bp.seed, kDomainCamera, pixel, s);
+    d3 o, d;
+    primary_ray(cam, bp.width, bp.height, x, y, rng, &o, &d);
+    p.ox[slot] = o.x; p.oy[slot] = o.y; p.oz[slot] = o.z;
+    p.dx[slot] = d.x; p.dy[slot] = d.y; p.dz[slot] = d.z;
+    p.rng[slot] = rng.state;
+    p.sample_j[slot] = j;
+    p.depth[slot] = 0;
+    p.flags[slot] = 0;
+    if (MEDIUM) {
+        p.bx[slot] = 1.0; p.by[slot] = 1.0; p.bz[slot] = 1.0;
+        p.lx[slot] = 0.0; p.ly[slot] = 0.0; p.lz[slot] = 0.0;
+    }
+}
+
+template <bool MEDIUM>
+__global__ void __launch_bounds__(kBlock) k_generate(PathPool p, Queues q, BatchParams bp, Camera cam) {
+    const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
+    if (slot >= p.n_slots) return;
+    p.ax[slot] = 0.0; p.ay[slot] = 0.0; p.az[slot] = 0.0;
+    const uint32_t lane = slot / p.n_pixels;
+    const bool active = lane < p.n_lanes && lane < bp.n_local;
+    if (active) start_path<MEDIUM>(p, bp, cam, slot, lane);
+    queue_push(q.cur, &q.counters[0], active, slot);
+    if (active) atomicAdd(&q.stats[0], 1ull);
+}
+
+// extend: persistent warps pull 32 rays at a time from the queue
+__global__ void __launch_bounds__(kBlock) k_extend(const __grid_constant__ SceneDev sc, PathPool p, Queues q) {
+    const uint32_t count = q.counters[0];
+    for (;;) {
+        uint32_t base = 0;
+        if (lane_id() == 0) base = atomicAdd(&q.counters[2], 32u);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (base >= count) break;
+        const uint32_t i = base + lane_id();
+        if (i < count) {
+            const uint32_t slot = q.cur[i];
+            RayD ray;
+            ray.o = mk3(p.ox[slot], p.oy[slot], p.oz[slot]);
+            ray.d = mk3(p.dx[slot], p.dy[slot], p.dz[slot]);
+            Hit h;
+            h.t = CUDART_INF;
+            closest_hit<false>(sc, ray, kEpsilon, 0.0, h);
+            if (h.inst != kNoHit) {
+                uint32_t prim, inst;
+                const d3 n = hit_normal(sc, ray, h, &prim, &inst);
+                p.ht[slot] = h.t;
+                p.hobj[slot] = h.obj;
+                p.hnx[slot] = n.x; p.hny[slot] = n.y; p.hnz[slot] = n.z;
+            } else {
+                p.ht[slot] = CUDART_INF;
+                p.hobj[slot] = kNoHit;
+            }
+        }
+    }
+    if (threadIdx.x == 0 && blockIdx.x == 0) atomicAdd(&q.stats[1], (unsigned long long)count);
+}
+
+// NEE candidates of one vertex (Renderer::sample_lights / sample_lights_for_media).  Ambient
+// lights are added to `direct` here; every other light leaves a shadow job (direction,
+// distance, radiance if unoccluded) for k_connect.  Directional lights have dist = +inf, which
+// can never pass |t - dist| < 1e-12 (src/renderer.rs:396), so no job is emitted for them.
+template <bool SURFACE>
+RPTX_D void sample_lights_dev(const SceneDev& sc, const PathPool& p, uint32_t slot, const Material* mat, const MediumDev* md,
+                              d3 pos, d3 n, d3 wo, d3 mc, Rng& rng, d3* direct) {
+    uint32_t k = 0;
+    for (uint32_t li = 0; li < sc.n_lights; li++) {
+        const Light& l = sc.lights[li];
+        if (l.kind == 1) {
+            const d3 amb = mk3(l.color[0], l.color[1], l.color[2]);
+            *direct = *direct + cmul(amb, SURFACE ? mat_color(*mat) : mc);
+            continue;
+        }
+        d3 intensity, wi;
+        double dist;
+        illuminate(sc, l, pos, rng, &intensity, &wi, &dist);
+        if (l.kind == 2) continue;
+        d3 c;
+        if (SURFACE) {
+            c = cmul(mat_bsdf(*mat, n, wo, wi), intensity) * dot(wi, n);
+        } else {
+            c = (md->sigma_s / md->extinction()) * cmul(intensity, mc) * md->phase;
+        }
+        const size_t o = (size_t)k * p.n_slots + slot;
+        p.sdx[o] = wi.x; p.sdy[o] = wi.y; p.sdz[o] = wi.z;
+        p.sdist[o] = dist;
+        p.scx[o] = c.x; p.scy[o] = c.y; p.scz[o] = c.z;
+        k++;
+    }
+}
+
+template <bool MEDIUM>
+__global__ void __launch_bounds__(kBlock) k_shade(const __grid_constant__ SceneDev sc, PathPool p, Queues q, BatchParams bp,
+                                                   MediumDev md) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= q.counters[0]) return;
+    const uint32_t slot = q.cur[i];
+    const d3 o = mk3(p.ox[slot], p.oy[slot], p.oz[slot]);
+    const d3 d = mk3(p.dx[slot], p.dy[slot], p.dz[slot]);
+    const double t = p.ht[slot];
+    const uint32_t obj = p.hobj[slot];
+    const uint32_t depth = p.depth[slot];
+    Rng rng;
+    rng.state = p.rng[slot];
+    uint32_t flags = 0;
+    d3 direct = mk3(0, 0, 0);
+
+    double dsamp = 0.0;
+    if (MEDIUM) dsamp = medium_sample_d(md, rng);
+    const bool hit = obj != kNoHit;
+    const double max_dist = hit ? t : kBackgroundDist;
+
+    if (MEDIUM && dsamp < max_dist) {
+        // medium vertex, src/renderer.rs:243-283
+        const d3 wo = -normalize(d);
+        const d3 collision = o + dsamp * d;
+        const d3 mc = md.color(collision);
+        if (depth == 0) direct = md.emission * mc;
+        sample_lights_dev<false>(sc, p, slot, nullptr, &md, collision, mk3(0, 0, 0), wo, mc, rng, &direct);
+        if (p.n_shadow) flags |= kFlagHasShadow;
+        p.ox[slot] = collision.x; p.oy[slot] = collision.y; p.oz[slot] = collision.z;
+        if (rng.gen() < kRrMedium) {
+            d3 wi;
+            medium_sample_ph(rng, &wi);
+            const double ph_p = md.phase;
+            const double sa = md.sigma_s / md.extinction();
+            // indirect = ((sa * L) / ph_p) (.) mc * phase / rr_p
+            p.fx[slot] = ((sa / ph_p) * mc.x * md.phase) / kRrMedium;
+            p.fy[slot] = ((sa / ph_p) * mc.y * md.phase) / kRrMedium;
+            p.fz[slot] = ((sa / ph_p) * mc.z * md.phase) / kRrMedium;
+            p.dx[slot] = wi.x; p.dy[slot] = wi.y; p.dz[slot] = wi.z;
+        } else {
+            flags |= kFlagTerminate;
+        }
+    } else if (!hit) {
+        // miss: environment (medium mode: only reached when d >= background_dist)
+        direct = env_color(sc, d);
+        flags |= kFlagTerminate;
+    } else {
+        // surface vertex, src/renderer.rs:207-236 (medium mode) / :289-319
+        const d3 n = mk3(p.hnx[slot], p.hny[slot], p.hnz[slot]);
+        const d3 pos = o + t * d;
+        const Material mat = sc.materials[obj];
+        const d3 wo = -normalize(d);
+        if (depth == 0) direct = mat_emittance(mat) * mat_color(mat);
+        sample_lights_dev<true>(sc, p, slot, &mat, nullptr, pos, n, wo, mk3(0, 0, 0), rng, &direct);
+        if (p.n_shadow) flags |= kFlagHasShadow;
+        p.ox[slot] = pos.x; p.oy[slot] = pos.y; p.oz[slot] = pos.z;
+        bool go = MEDIUM ? (rng.gen() < kRrMedium) : (depth < bp.max_bounces);
+        if (go) {
+            d3 wi;
+            double pdf;
+            if (mat_sample_f(mat, n, wo, rng, &wi, &pdf)) {
+                const d3 f = mat_bsdf(mat, n, wo, wi);
+                const double ac = fabs(dot(wi, n));
+                if (MEDIUM) {
+                    const double s = 1.0 / (pdf * kRrMedium);
+                    p.fx[slot] = s * f.x * ac; p.fy[slot] = s * f.y * ac; p.fz[slot] = s * f.z * ac;
+                } else {
+                    p.fx[slot] = f.x; p.fy[slot] = f.y; p.fz[slot] = f.z;
+                    p.pdf[slot] = pdf;
+                    p.abscos[slot] = ac;
+                }
+                p.dx[slot] = wi.x; p.dy[slot] = wi.y; p.dz[slot] = wi.z;
+            } else {
+                go = false;
+            }
+        }
+        if (!go) flags |= kFlagTerminate;
+    }
+    p.dirx[slot] = direct.x; p.diry[slot] = direct.y; p.dirz[slot] = direct.z;
+    p.flags[slot] = flags;
+    p.rng[slot] = rng.state;
+}
+
+// connect: shadow rays of the vertex (closest hit must sit within 1e-12 of the light sample,
+// src/renderer.rs:348,396), then finalise the vertex; finished paths are folded, added to the
+// slot's lane film and the slot regenerates its next sample.
+template <bool MEDIUM>
+__global__ void __launch_bounds__(kBlock) k_connect(const __grid_constant__ SceneDev sc, PathPool p, Queues q, BatchParams bp,
+                                                     Camera cam) {
+    const uint32_t count = q.counters[0];
+    unsigned long long my_shadow = 0, my_started = 0;
+    for (;;) {
+        uint32_t base = 0;
+        if (lane_id() == 0) base = atomicAdd(&q.counters[3], 32u);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (base >= count) break;
+        const uint32_t i = base + lane_id();
+        bool alive = false;
+        uint32_t slot = 0;
+        if (i < count) {
+            slot = q.cur[i];
+            const uint32_t flags = p.flags[slot];
+            d3 direct = mk3(p.dirx[slot], p.diry[slot], p.dirz[slot]);
+            if (flags & kFlagHasShadow) {
+                RayD ray;
+                ray.o = mk3(p.ox[slot], p.oy[slot], p.oz[slot]);
+                for (uint32_t k = 0; k < p.n_shadow; k++) {
+                    const size_t off = (size_t)k * p.n_slots + slot;
+                    ray.d = mk3(p.sdx[off], p.sdy[off], p.sdz[off]);
+                    const double dist = p.sdist[off];
+                    Hit h;
+                    h.t = dist + 2e-12;
+                    closest_hit<true>(sc, ray, kEpsilon, dist - 2e-12, h);
+                    my_shadow++;
+                    if (h.inst != kNoHit && fabs(h.t - dist) < kEpsilon)
+                        direct = direct + mk3(p.scx[off], p.scy[off], p.scz[off]);
+                }
+            }
+            const uint32_t depth = p.depth[slot];
+            bool finished = (flags & kFlagTerminate) != 0;
+            d3 L;
+            if (MEDIUM) {
+                const d3 beta = mk3(p.bx[slot], p.by[slot], p.bz[slot]);
+                L = mk3(p.lx[slot], p.ly[slot], p.lz[slot]) + cmul(beta, direct);
+                if (!finished) {
+                    p.lx[slot] = L.x; p.ly[slot] = L.y; p.lz[slot] = L.z;
+                    p.bx[slot] = beta.x * p.fx[slot]; p.by[slot] = beta.y * p.fy[slot]; p.bz[slot] = beta.z * p.fz[slot];
+                }
+            } else {
+                if (!finished) {
+                    double* st = p.stack + (size_t)depth * 8 * p.n_slots + slot;
+                    const size_t ns = p.n_slots;
+                    st[0] = direct.x; st[ns] = direct.y; st[2 * ns] = direct.z;
+                    st[3 * ns] = p.fx[slot]; st[4 * ns] = p.fy[slot]; st[5 * ns] = p.fz[slot];
+                    st[6 * ns] = p.pdf[slot]; st[7 * ns] = p.abscos[slot];
+                } else {
+                    L = direct;
+                    for (int j = (int)depth - 1; j >= 0; j--) {
+                        const double* st = p.stack + (size_t)j * 8 * p.n_slots + slot;
+                        const size_t ns = p.n_slots;
+                        const d3 f = mk3(st[3 * ns], st[4 * ns], st[5 * ns]);
+                        const d3 ind = 1.0 / st[6 * ns] * cmul(f, L) * st[7 * ns];
+                        L = mk3(st[0] + fmin(ind.x, kFireflyClamp), st[ns] + fmin(ind.y, kFireflyClamp),
+                                st[2 * ns] + fmin(ind.z, kFireflyClamp));
+                    }
+                }
+            }
+            if (finished) {
+                p.ax[slot] += L.x; p.ay[slot] += L.y; p.az[slot] += L.z;
+                const uint32_t jn = p.sample_j[slot] + p.n_lanes;
+                if (jn < bp.n_local) {
+                    start_path<MEDIUM>(p, bp, cam, slot, jn);
+                    my_started++;
+                    alive = true;
+                }
+            } else {
+                p.depth[slot] = depth + 1;
+                alive = true;
+            }
+        }
+        queue_push(q.next, &q.counters[1], alive, slot);
+    }
+    if (my_shadow) atomicAdd(&q.stats[2], my_shadow);
+    if (my_started) atomicAdd(&q.stats[0], my_started);
+}
+
+// end of wave: next becomes cur (pointers are swapped on the host), heads reset
+__global__ void k_wave_end(Queues q) {
+    q.counters[0] = q.counters[1];
+    q.counters[1] = 0;
+    q.counters[2] = 0;
+    q.counters[3] = 0;
+}
+
+// raw closest-hit batch (parity hook + kernel-only benchmark)
+__global__ void __launch_bounds__(kBlock) k_intersect_batch(const __grid_constant__ SceneDev sc, const double* __restrict__ o,
+                                                             const double* __restrict__ d, size_t n, double t_min,
+                                                             double* __restrict__ t, uint32_t* __restrict__ object_id,
+                                                             uint32_t* __restrict__ prim_id, uint32_t* __restrict__ inst_id,
+                                                             double* __restrict__ normal) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    RayD ray;
+    ray.o = mk3(o[3 * i], o[3 * i + 1], o[3 * i + 2]);
+    ray.d = mk3(d[3 * i], d[3 * i + 1], d[3 * i + 2]);
+    Hit h;
+    h.t = CUDART_INF;
+    closest_hit<false>(sc, ray, t_min, 0.0, h);
+    uint32_t prim = 0, inst = 0;
+    d3 n3 = mk3(0, 0, 0);
+    if (h.inst != kNoHit) n3 = hit_normal(sc, ray, h, &prim, &inst);
+    if (t) t[i] = h.inst != kNoHit ? h.t : CUDART_INF;
+    if (object_id) object_id[i] = h.obj;
+    if (prim_id) prim_id[i] = prim;
+    if (inst_id) inst_id[i] = inst;
+    if (normal) { normal[3 * i] = n3.x; normal[3 * i + 1] = n3.y; normal[3 * i + 2] = n3.z; }
+}
+
+// ---- film ----
+
+// batch_sum[pixel] = sum over lanes of the lane films (fixed order)
+__global__ void k_batch_reduce(PathPool p, double* __restrict__ batch_sum) {
+    const uint32_t pixel = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pixel >= p.n_pixels) return;
+    double x = 0, y = 0, z = 0;
+    for (uint32_t l = 0; l < p.n_lanes; l++) {
+        const size_t s = (size_t)l * p.n_pixels + pixel;
+        x += p.ax[s]; y += p.ay[s]; z += p.az[s];
+    }
+    batch_sum[3 * (size_t)pixel] = x; batch_sum[3 * (size_t)pixel + 1] = y; batch_sum[3 * (size_t)pixel + 2] = z;
+}
+
+// Renderer::get_color's mean and exposure (src/renderer.rs:183) + Buffer::add_samples
+__global__ void k_batch_commit(const double* __restrict__ batch_sum, size_t n3, double iterations, double exposure,
+                               double* __restrict__ batch_mean, double* __restrict__ film_sum) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n3) return;
+    const double m = batch_sum[i] / iterations * exposure;
+    batch_mean[i] = m;
+    film_sum[i] += m;
+}
+
+// Buffer::image (src/buffer.rs:43-56,75-94) + color_bytes (src/color.rs:18-24)
+__global__ void k_image(const double* __restrict__ film_sum, uint32_t w, uint32_t h, uint32_t r, uint32_t nbatches,
+                        uint8_t* __restrict__ out) {
+    const uint32_t x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y * blockDim.y + threadIdx.y;
+    if (x >= w || y >= h) return;
+    double cx = 0, cy = 0, cz = 0;
+    uint64_t count = 0;
+    const uint32_t i0 = x >= r ? x - r : 0, j0 = y >= r ? y - r : 0;
+    for (uint32_t i = i0; i <= x + r; i++)
+        for (uint32_t j = j0; j <= y + r; j++)
+            if (i < w && j < h) {
+                const size_t idx = 3 * ((size_t)j * w + i);
+                cx += film_sum[idx]; cy += film_sum[idx + 1]; cz += film_sum[idx + 2];
+                count += nbatches;
+            }
+    const double c[3] = {cx / (double)count, cy / (double)count, cz / (double)count};
+    for (int k = 0; k < 3; k++) {
+        const double v = pow(fmin(fmax(c[k], 0.0), 1.0), 1.0 / 2.2) * 255.0;
+        out[3 * ((size_t)y * w + x) + k] = (uint8_t)(v != v ? 0 : (v >= 255.0 ? 255 : (v <= 0.0 ? 0 : (int)v)));
+    }
+}
+
+// Buffer::variance (src/buffer.rs:59-73): per-pixel unbiased variance of the batch means
+__global__ void k_variance(const double* const* __restrict__ batches, uint32_t nbatches, const double* __restrict__ film_sum,
+                           size_t n_pixels, double* __restrict__ out) {
+    double acc = 0.0;
+    for (size_t pidx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; pidx < n_pixels; pidx += (size_t)gridDim.x * blockDim.x) {
+        const double mx = film_sum[3 * pidx] / (double)nbatches, my = film_sum[3 * pidx + 1] / (double)nbatches,
+                     mz = film_sum[3 * pidx + 2] / (double)nbatches;
+        double ss = 0.0;
+        for (uint32_t b = 0; b < nbatches; b++) {
+            const double* s = batches[b] + 3 * pidx;
+            const double ex = s[0] - mx, ey = s[1] - my, ez = s[2] - mz;
+            ss += ex * ex + ey * ey + ez * ez;
+        }
+        acc += ss / ((double)nbatches - 1.0);
+    }
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, o);
+    if ((threadIdx.x & 31) == 0) atomicAdd(out, acc);
+}
+
+__global__ void k_film_mean(const double* __restrict__ film_sum, size_t n3, double nbatches, double* __restrict__ out) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n3) out[i] = film_sum[i] / nbatches;
+}
+
+// ---- mesh preparation ----
+__global__ void k_tri_boxes(const RawTri* __restrict__ raw, uint32_t n, PrimBox* __restrict__ boxes) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const RawTri t = raw[i];
+    PrimBox b;
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+        const double lo = fmin(fmin(t.v[k], t.v[3 + k]), t.v[6 + k]);
+        const double hi = fmax(fmax(t.v[k], t.v[3 + k]), t.v[6 + k]);
+        b.mn[k] = __double2float_rd(lo);
+        b.mx[k] = __double2float_ru(hi);
+    }
+    boxes[i] = b;
+}
+
+// per-triangle constants of Triangle::intersect, same f64 operations as src/shape/mesh.rs:51-66
+__global__ void k_tri_prepare(const RawTri* __restrict__ raw, const uint32_t* __restrict__ perm, uint32_t n, TriRec* __restrict__ out,
+                              TriNormals* __restrict__ nrm, uint32_t* __restrict__ orig) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t src = perm[i];
+    const RawTri t = raw[src];
+    const d3 v1 = mk3(t.v[0], t.v[1], t.v[2]), v2 = mk3(t.v[3], t.v[4], t.v[5]), v3 = mk3(t.v[6], t.v[7], t.v[8]);
+    const d3 d0 = v2 - v1, d1 = v3 - v1;
+    const d3 pn = normalize(cross(d0, d1));
+    TriRec r;
+    r.v1[0] = v1.x; r.v1[1] = v1.y; r.v1[2] = v1.z;
+    r.d0[0] = d0.x; r.d0[1] = d0.y; r.d0[2] = d0.z;
+    r.d1[0] = d1.x; r.d1[1] = d1.y; r.d1[2] = d1.z;
+    r.pn[0] = pn.x; r.pn[1] = pn.y; r.pn[2] = pn.z;
+    r.d00 = dot(d0, d0); r.d01 = dot(d0, d1); r.d11 = dot(d1, d1);
+    r.denom = r.d00 * r.d11 - r.d01 * r.d01;
+    out[i] = r;
+    TriNormals tn;
+    for (int k = 0; k < 3; k++) { tn.n1[k] = t.n[k]; tn.n2[k] = t.n[3 + k]; tn.n3[k] = t.n[6 + k]; }
+    nrm[i] = tn;
+    orig[i] = src;
+}
+
+// Triangle::from_vertices (src/shape/mesh.rs:27-38) for meshes uploaded without normals
+__global__ void k_face_normals(RawTri* __restrict__ raw, uint32_t n) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    RawTri t = raw[i];
+    const d3 v1 = mk3(t.v[0], t.v[1], t.v[2]), v2 = mk3(t.v[3], t.v[4], t.v[5]), v3 = mk3(t.v[6], t.v[7], t.v[8]);
+    const d3 nn = normalize(cross(v2 - v1, v3 - v1));
+    for (int k = 0; k < 3; k++) { raw[i].n[3 * k] = nn.x; raw[i].n[3 * k + 1] = nn.y; raw[i].n[3 * k + 2] = nn.z; }
+}
+
+}  // namespace rptx

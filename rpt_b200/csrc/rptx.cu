@@ -1,0 +1,865 @@
+// C ABI of the B200 light-transport core (include/rptx.h): scene lowering + upload, GPU BVH
+// builds, the wavefront render loop and the film.  Host logic only; the kernels live in
+// path_kernels.cuh / trace.cuh / bvh_build.cu.
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "../../include/rptx.h"
+#include "bvh_build.cuh"
+#include "host_types.hpp"
+#include "path_kernels.cuh"
+
+using namespace rptx;
+
+namespace {
+
+#define CK(call)                                                                         \
+    do {                                                                                 \
+        cudaError_t e_ = (call);                                                         \
+        if (e_ != cudaSuccess) return ctx_fail(ctx, std::string(#call) + ": " + cudaGetErrorString(e_)); \
+    } while (0)
+
+int ctx_fail(rptx_ctx* ctx, const std::string& msg) {
+    if (ctx) ctx->err = msg;
+    return 1;
+}
+
+// ---- small host linear algebra (same closed forms nalgebra uses) ----
+struct M4 { double m[4][4]; };
+struct M3 { double m[3][3]; };
+
+M4 m4_from(const double* t) {
+    M4 r;
+    for (int i = 0; i < 4; i++) for (int j = 0; j < 4; j++) r.m[i][j] = t[4 * i + j];
+    return r;
+}
+M4 m4_inverse(const M4& a) {  // cofactor expansion on the column-major array (glm::inverse)
+    double m[16], inv[16];
+    for (int c = 0; c < 4; c++) for (int r = 0; r < 4; r++) m[c * 4 + r] = a.m[r][c];
+    inv[0] = m[5] * m[10] * m[15] - m[5] * m[11] * m[14] - m[9] * m[6] * m[15] + m[9] * m[7] * m[14] + m[13] * m[6] * m[11] - m[13] * m[7] * m[10];
+    inv[4] = -m[4] * m[10] * m[15] + m[4] * m[11] * m[14] + m[8] * m[6] * m[15] - m[8] * m[7] * m[14] - m[12] * m[6] * m[11] + m[12] * m[7] * m[10];
+    inv[8] = m[4] * m[9] * m[15] - m[4] * m[11] * m[13] - m[8] * m[5] * m[15] + m[8] * m[7] * m[13] + m[12] * m[5] * m[11] - m[12] * m[7] * m[9];
+    inv[12] = -m[4] * m[9] * m[14] + m[4] * m[10] * m[13] + m[8] * m[5] * m[14] - m[8] * m[6] * m[13] - m[12] * m[5] * m[10] + m[12] * m[6] * m[9];
+    inv[1] = -m[1] * m[10] * m[15] + m[1] * m[11] * m[14] + m[9] * m[2] * m[15] - m[9] * m[3] * m[14] - m[13] * m[2] * m[11] + m[13] * m[3] * m[10];
+    inv[5] = m[0] * m[10] * m[15] - m[0] * m[11] * m[14] - m[8] * m[2] * m[15] + m[8] * m[3] * m[14] + m[12] * m[2] * m[11] - m[12] * m[3] * m[10];
+    inv[9] = -m[0] * m[9] * m[15] + m[0] * m[11] * m[13] + m[8] * m[1] * m[15] - m[8] * m[3] * m[13] - m[12] * m[1] * m[11] + m[12] * m[3] * m[9];
+    inv[13] = m[0] * m[9] * m[14] - m[0] * m[10] * m[13] - m[8] * m[1] * m[14] + m[8] * m[2] * m[13] + m[12] * m[1] * m[10] - m[12] * m[2] * m[9];
+    inv[2] = m[1] * m[6] * m[15] - m[1] * m[7] * m[14] - m[5] * m[2] * m[15] + m[5] * m[3] * m[14] + m[13] * m[2] * m[7] - m[13] * m[3] * m[6];
+    inv[6] = -m[0] * m[6] * m[15] + m[0] * m[7] * m[14] + m[4] * m[2] * m[15] - m[4] * m[3] * m[14] - m[12] * m[2] * m[7] + m[12] * m[3] * m[6];
+    inv[10] = m[0] * m[5] * m[15] - m[0] * m[7] * m[13] - m[4] * m[1] * m[15] + m[4] * m[3] * m[13] + m[12] * m[1] * m[7] - m[12] * m[3] * m[5];
+    inv[14] = -m[0] * m[5] * m[14] + m[0] * m[6] * m[13] + m[4] * m[1] * m[14] - m[4] * m[2] * m[13] - m[12] * m[1] * m[6] + m[12] * m[2] * m[5];
+    inv[3] = -m[1] * m[6] * m[11] + m[1] * m[7] * m[10] + m[5] * m[2] * m[11] - m[5] * m[3] * m[10] - m[9] * m[2] * m[7] + m[9] * m[3] * m[6];
+    inv[7] = m[0] * m[6] * m[11] - m[0] * m[7] * m[10] - m[4] * m[2] * m[11] + m[4] * m[3] * m[10] + m[8] * m[2] * m[7] - m[8] * m[3] * m[6];
+    inv[11] = -m[0] * m[5] * m[11] + m[0] * m[7] * m[9] + m[4] * m[1] * m[11] - m[4] * m[3] * m[9] - m[8] * m[1] * m[7] + m[8] * m[3] * m[5];
+    inv[15] = m[0] * m[5] * m[10] - m[0] * m[6] * m[9] - m[4] * m[1] * m[10] + m[4] * m[2] * m[9] + m[8] * m[1] * m[6] - m[8] * m[2] * m[5];
+    const double det = m[0] * inv[0] + m[1] * inv[4] + m[2] * inv[8] + m[3] * inv[12];
+    M4 out;
+    if (det == 0.0) { std::memset(&out, 0, sizeof(out)); return out; }
+    const double inv_det = 1.0 / det;
+    for (int c = 0; c < 4; c++) for (int r = 0; r < 4; r++) out.m[r][c] = inv[c * 4 + r] * inv_det;
+    return out;
+}
+M3 m3_of(const M4& a) {
+    M3 r;
+    for (int i = 0; i < 3; i++) for (int j = 0; j < 3; j++) r.m[i][j] = a.m[i][j];
+    return r;
+}
+void m3_minors(const M3& a, double* p, double* q, double* r, double* det) {
+    *p = a.m[1][1] * a.m[2][2] - a.m[2][1] * a.m[1][2];
+    *q = a.m[1][0] * a.m[2][2] - a.m[2][0] * a.m[1][2];
+    *r = a.m[1][0] * a.m[2][1] - a.m[2][0] * a.m[1][1];
+    *det = a.m[0][0] * *p - a.m[0][1] * *q + a.m[0][2] * *r;
+}
+double m3_det(const M3& a) {
+    double p, q, r, d;
+    m3_minors(a, &p, &q, &r, &d);
+    return d;
+}
+M3 m3_inverse_transpose(const M3& a) {
+    double p, q, r, det;
+    m3_minors(a, &p, &q, &r, &det);
+    const double m11 = a.m[0][0], m12 = a.m[0][1], m13 = a.m[0][2], m21 = a.m[1][0], m22 = a.m[1][1], m23 = a.m[1][2],
+                 m31 = a.m[2][0], m32 = a.m[2][1], m33 = a.m[2][2];
+    M3 inv;
+    inv.m[0][0] = p / det;
+    inv.m[0][1] = (m13 * m32 - m33 * m12) / det;
+    inv.m[0][2] = (m12 * m23 - m22 * m13) / det;
+    inv.m[1][0] = -q / det;
+    inv.m[1][1] = (m11 * m33 - m31 * m13) / det;
+    inv.m[1][2] = (m13 * m21 - m23 * m11) / det;
+    inv.m[2][0] = r / det;
+    inv.m[2][1] = (m12 * m31 - m32 * m11) / det;
+    inv.m[2][2] = (m11 * m22 - m21 * m12) / det;
+    M3 t;
+    for (int i = 0; i < 3; i++) for (int j = 0; j < 3; j++) t.m[i][j] = inv.m[j][i];
+    return t;
+}
+Affine affine_of(const M4& a) {
+    Affine r;
+    for (int i = 0; i < 3; i++) for (int j = 0; j < 4; j++) r.m[4 * i + j] = a.m[i][j];
+    return r;
+}
+Mat3 mat3_of(const M3& a) {
+    Mat3 r;
+    for (int i = 0; i < 3; i++) for (int j = 0; j < 3; j++) r.m[3 * i + j] = a.m[i][j];
+    return r;
+}
+Affine affine_identity() {
+    Affine r;
+    std::memset(&r, 0, sizeof(r));
+    r.m[0] = r.m[5] = r.m[10] = 1.0;
+    return r;
+}
+Mat3 mat3_identity() {
+    Mat3 r;
+    std::memset(&r, 0, sizeof(r));
+    r.m[0] = r.m[4] = r.m[8] = 1.0;
+    return r;
+}
+float f32_down(double x) {
+    float f = (float)x;
+    if ((double)f > x) f = std::nextafterf(f, -INFINITY);
+    return f;
+}
+float f32_upf(double x) {
+    float f = (float)x;
+    if ((double)f < x) f = std::nextafterf(f, INFINITY);
+    return f;
+}
+
+template <class T>
+cudaError_t upload(T** dst, const std::vector<T>& src) {
+    *dst = nullptr;
+    cudaError_t e = cudaMalloc((void**)dst, std::max<size_t>(src.size(), 1) * sizeof(T));
+    if (e != cudaSuccess) return e;
+    if (!src.empty()) e = cudaMemcpy(*dst, src.data(), src.size() * sizeof(T), cudaMemcpyHostToDevice);
+    return e;
+}
+
+int grid_for(size_t n, int block) { return (int)std::max<size_t>(1, (n + block - 1) / block); }
+
+void free_scene_device(rptx_scene* s) {
+    cudaFree((void*)s->d_nodes); cudaFree((void*)s->d_instances); cudaFree((void*)s->d_tris);
+    cudaFree((void*)s->d_tri_normals); cudaFree((void*)s->d_tri_orig); cudaFree((void*)s->d_materials);
+    cudaFree((void*)s->d_lights); cudaFree((void*)s->d_raw); cudaFree((void*)s->d_env);
+    s->d_nodes = nullptr; s->d_instances = nullptr; s->d_tris = nullptr; s->d_tri_normals = nullptr;
+    s->d_tri_orig = nullptr; s->d_materials = nullptr; s->d_lights = nullptr; s->d_raw = nullptr; s->d_env = nullptr;
+    s->committed = false;
+}
+
+Material to_material(const rptx_material& m) {
+    Material r;
+    std::memset(&r, 0, sizeof(r));
+    r.kind = m.kind;
+    for (int k = 0; k < 3; k++) r.albedo[k] = m.albedo[k];
+    r.emittance = m.emittance; r.shininess = m.shininess; r.ior = m.ior;
+    return r;
+}
+
+// local bounds of a leaf shape (Bounded::bounding_box of the reference)
+bool local_bounds(const rptx_scene* s, const rptx_shape_desc& d, double mn[3], double mx[3]) {
+    if (d.kind == RPTX_SHAPE_SPHERE) { for (int k = 0; k < 3; k++) { mn[k] = -1; mx[k] = 1; } return true; }
+    if (d.kind == RPTX_SHAPE_CUBE) { for (int k = 0; k < 3; k++) { mn[k] = -0.5; mx[k] = 0.5; } return true; }
+    if (d.kind == RPTX_SHAPE_MESH) {
+        const HostMesh& m = s->meshes[d.mesh_id];
+        for (int k = 0; k < 3; k++) { mn[k] = m.bmin[k]; mx[k] = m.bmax[k]; }
+        return true;
+    }
+    return false;
+}
+
+// lower one leaf shape (SPHERE/PLANE/CUBE/MESH) into an instance record + world box
+int lower_leaf(rptx_scene* s, const rptx_shape_desc& d, uint32_t object_id, uint32_t inst_id, Instance* out, double wmn[3],
+               double wmx[3], bool* bounded) {
+    rptx_ctx* ctx = s->ctx;
+    Instance in;
+    std::memset(&in, 0, sizeof(in));
+    in.object_id = object_id;
+    in.inst_id = inst_id;
+    in.has_transform = d.has_transform ? 1 : 0;
+    in.inv = affine_identity();
+    in.nrm = mat3_identity();
+    M4 fwd = m4_from(d.transform);
+    if (d.has_transform) {
+        in.inv = affine_of(m4_inverse(fwd));
+        in.nrm = mat3_of(m3_inverse_transpose(m3_of(fwd)));
+    }
+    switch (d.kind) {
+        case RPTX_SHAPE_SPHERE: in.kind = kSphere; break;
+        case RPTX_SHAPE_CUBE: in.kind = kCube; break;
+        case RPTX_SHAPE_PLANE:
+            in.kind = kPlane;
+            for (int k = 0; k < 3; k++) in.plane_n[k] = d.plane_normal[k];
+            in.plane_v = d.plane_value;
+            break;
+        case RPTX_SHAPE_MESH: {
+            if (d.mesh_id >= s->meshes.size()) return ctx_fail(ctx, "shape refers to an unknown mesh id");
+            const HostMesh& m = s->meshes[d.mesh_id];
+            if (m.tris.empty()) return ctx_fail(ctx, "empty mesh cannot be instanced");
+            in.kind = kMesh;
+            in.root_ref = m.root_ref; in.node_base = m.node_base; in.tri_base = m.tri_base; in.ntri = (uint32_t)m.tris.size();
+            in.lpad = m.pad;
+            for (int k = 0; k < 3; k++) { in.lmin[k] = m.bmin[k] - (double)m.pad; in.lmax[k] = m.bmax[k] + (double)m.pad; }
+            break;
+        }
+        default: return ctx_fail(ctx, "unsupported leaf shape kind");
+    }
+    double mn[3], mx[3];
+    *bounded = local_bounds(s, d, mn, mx);
+    if (*bounded) {
+        for (int k = 0; k < 3; k++) { wmn[k] = INFINITY; wmx[k] = -INFINITY; }
+        for (int c = 0; c < 8; c++) {
+            const double p[3] = {c & 4 ? mx[0] : mn[0], c & 2 ? mx[1] : mn[1], c & 1 ? mx[2] : mn[2]};
+            double w[3] = {p[0], p[1], p[2]};
+            if (d.has_transform)
+                for (int r = 0; r < 3; r++) w[r] = fwd.m[r][0] * p[0] + fwd.m[r][1] * p[1] + fwd.m[r][2] * p[2] + fwd.m[r][3];
+            for (int k = 0; k < 3; k++) { wmn[k] = std::fmin(wmn[k], w[k]); wmx[k] = std::fmax(wmx[k], w[k]); }
+        }
+    }
+    *out = in;
+    return 0;
+}
+
+int lower_light(rptx_scene* s, const rptx_light& l, Light* out) {
+    rptx_ctx* ctx = s->ctx;
+    Light r;
+    std::memset(&r, 0, sizeof(r));
+    r.kind = l.kind;
+    for (int k = 0; k < 3; k++) { r.color[k] = l.color[k]; r.vec[k] = l.vec[k]; }
+    r.fwd = affine_identity(); r.inv = affine_identity(); r.lin = mat3_identity(); r.nrm = mat3_identity(); r.scale = 1.0;
+    if (l.kind == RPTX_LIGHT_OBJECT) {
+        const rptx_shape_desc& d = l.shape;
+        r.material = to_material(l.material);
+        r.has_transform = d.has_transform ? 1 : 0;
+        if (d.has_transform) {
+            const M4 fwd = m4_from(d.transform);
+            r.fwd = affine_of(fwd);
+            r.inv = affine_of(m4_inverse(fwd));
+            const M3 lin = m3_of(fwd);
+            r.lin = mat3_of(lin);
+            r.scale = m3_det(lin);
+            r.nrm = mat3_of(m3_inverse_transpose(lin));
+        }
+        if (d.kind == RPTX_SHAPE_MESH) {
+            if (d.mesh_id >= s->meshes.size()) return ctx_fail(ctx, "light refers to an unknown mesh id");
+            r.shape_kind = kMesh;
+            r.tri_base = s->meshes[d.mesh_id].raw_base;
+            r.ntri = (uint32_t)s->meshes[d.mesh_id].tris.size();
+        } else if (d.kind == RPTX_SHAPE_CUBE) r.shape_kind = kCube;
+        else if (d.kind == RPTX_SHAPE_SPHERE) r.shape_kind = kSphere;
+        else return ctx_fail(ctx, "object lights must be mesh, cube or sphere (Plane::sample is unimplemented, src/shape/plane.rs:34)");
+    }
+    *out = r;
+    return 0;
+}
+
+MediumDev medium_dev(const rptx_scene* s) {
+    MediumDev md;
+    std::memset(&md, 0, sizeof(md));
+    md.kind = s->medium_kind;
+    md.sigma_a = s->sigma_a; md.sigma_s = s->sigma_s;
+    auto hex = [](uint32_t x) {
+        return mk3(std::pow((double)((x >> 16) & 0xff) / 255.0, 2.2), std::pow((double)((x >> 8) & 0xff) / 255.0, 2.2),
+                   std::pow((double)(x & 0xff) / 255.0, 2.2));
+    };
+    if (s->medium_kind == RPTX_MEDIUM_COLORED_GLOWING_FOG) {  // src/medium.rs:99-121
+        md.color_lo = hex(0x0000FF); md.color_hi = hex(0xFF0000);
+        md.emission = 10.0;
+        md.phase = 1.0 / 4.0 * kPi;
+    } else {  // src/medium.rs:80-96
+        md.color_lo = hex(0xD2B48C); md.color_hi = md.color_lo;
+        md.emission = 0.0;
+        md.phase = 1.0 / (4.0 * kPi);
+    }
+    return md;
+}
+
+SceneDev scene_dev(const rptx_scene* s) {
+    SceneDev sc;
+    std::memset(&sc, 0, sizeof(sc));
+    sc.nodes = s->d_nodes; sc.instances = s->d_instances; sc.tris = s->d_tris; sc.tri_normals = s->d_tri_normals;
+    sc.tri_orig = s->d_tri_orig; sc.materials = s->d_materials; sc.lights = s->d_lights; sc.light_tris = s->d_raw;
+    sc.tlas_root_ref = s->tlas_root_ref;
+    sc.n_bounded = s->n_bounded; sc.n_unbounded = s->n_unbounded;
+    sc.n_lights = (uint32_t)s->lights.size(); sc.n_shadow_lights = s->n_shadow_lights;
+    for (int k = 0; k < 3; k++) { sc.wmin[k] = s->wmin[k]; sc.wmax[k] = s->wmax[k]; sc.env_color[k] = s->env_color[k]; }
+    sc.medium_kind = s->medium_kind; sc.sigma_a = s->sigma_a; sc.sigma_s = s->sigma_s;
+    sc.env_is_hdri = s->env_is_hdri ? 1 : 0; sc.env_w = s->env_w; sc.env_h = s->env_h; sc.env_pixels = s->d_env;
+    return sc;
+}
+
+}  // namespace
+
+extern "C" {
+
+int rptx_abi_version(void) { return RPTX_ABI_VERSION; }
+
+int rptx_ctx_create(int device_id, rptx_ctx** out) {
+    if (!out) return 1;
+    *out = nullptr;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    rptx_ctx* ctx = new rptx_ctx();
+    *out = ctx;
+    if (e != cudaSuccess || n == 0) return ctx_fail(ctx, std::string("no CUDA device: ") + cudaGetErrorString(e));
+    if (device_id < 0 || device_id >= n) return ctx_fail(ctx, "device id out of range");
+    ctx->device = device_id;
+    CK(cudaSetDevice(device_id));
+    CK(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, device_id));
+    ctx->sm_count = prop.multiProcessorCount;
+    CK(cudaMallocHost((void**)&ctx->h_pinned, 64));
+    return 0;
+}
+
+void rptx_ctx_destroy(rptx_ctx* ctx) {
+    if (!ctx) return;
+    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    if (ctx->h_pinned) cudaFreeHost(ctx->h_pinned);
+    delete ctx;
+}
+
+const char* rptx_last_error(const rptx_ctx* ctx) { return ctx ? ctx->err.c_str() : "null context"; }
+
+int rptx_scene_create(rptx_ctx* ctx, rptx_scene** out) {
+    if (!ctx || !out) return 1;
+    rptx_scene* s = new rptx_scene();
+    s->ctx = ctx;
+    *out = s;
+    return 0;
+}
+
+void rptx_scene_destroy(rptx_scene* s) {
+    if (!s) return;
+    cudaSetDevice(s->ctx->device);
+    free_scene_device(s);
+    delete s;
+}
+
+int rptx_scene_add_mesh(rptx_scene* s, const double* v, const double* n, size_t ntri, uint32_t* mesh_id) {
+    if (!s) return 1;
+    rptx_ctx* ctx = s->ctx;
+    if (!v || !mesh_id) return ctx_fail(ctx, "rptx_scene_add_mesh: null argument");
+    if (ntri >= (1u << 28)) return ctx_fail(ctx, "mesh too large (>= 2^28 triangles)");
+    HostMesh m;
+    m.has_normals = n != nullptr;
+    m.tris.resize(ntri);
+    for (int k = 0; k < 3; k++) { m.bmin[k] = INFINITY; m.bmax[k] = -INFINITY; }
+    for (size_t i = 0; i < ntri; i++) {
+        std::memcpy(m.tris[i].v, v + 9 * i, 9 * sizeof(double));
+        if (n) std::memcpy(m.tris[i].n, n + 9 * i, 9 * sizeof(double));
+        else std::memset(m.tris[i].n, 0, 9 * sizeof(double));
+        for (int c = 0; c < 3; c++)
+            for (int k = 0; k < 3; k++) {
+                const double x = v[9 * i + 3 * c + k];
+                if (!(x == x) || std::isinf(x)) return ctx_fail(ctx, "mesh vertex is not finite");
+                m.bmin[k] = std::fmin(m.bmin[k], x); m.bmax[k] = std::fmax(m.bmax[k], x);
+            }
+    }
+    s->meshes.push_back(std::move(m));
+    *mesh_id = (uint32_t)s->meshes.size() - 1;
+    s->committed = false;
+    return 0;
+}
+
+int rptx_scene_add_object(rptx_scene* s, const rptx_shape_desc* shape, const rptx_material* material, uint32_t* object_id) {
+    if (!s) return 1;
+    rptx_ctx* ctx = s->ctx;
+    if (!shape || !material) return ctx_fail(ctx, "rptx_scene_add_object: null argument");
+    HostObject o;
+    o.desc = *shape;
+    o.material = *material;
+    if (shape->kind == RPTX_SHAPE_GROUP) {
+        if (shape->has_transform) return ctx_fail(ctx, "transformed groups are not supported");
+        if (shape->n_children == 0 || !shape->children) return ctx_fail(ctx, "empty group");
+        o.children.assign(shape->children, shape->children + shape->n_children);
+        for (const auto& c : o.children)
+            if (c.kind != RPTX_SHAPE_SPHERE && c.kind != RPTX_SHAPE_CUBE && c.kind != RPTX_SHAPE_MESH)
+                return ctx_fail(ctx, "group children must be bounded leaf shapes (sphere, cube, mesh)");
+        o.desc.children = nullptr;
+    } else if (shape->kind < RPTX_SHAPE_SPHERE || shape->kind > RPTX_SHAPE_GROUP) {
+        return ctx_fail(ctx, "unknown shape kind");
+    }
+    if (shape->kind == RPTX_SHAPE_MESH && shape->mesh_id >= s->meshes.size()) return ctx_fail(ctx, "unknown mesh id");
+    s->objects.push_back(std::move(o));
+    if (object_id) *object_id = (uint32_t)s->objects.size() - 1;
+    s->committed = false;
+    return 0;
+}
+
+int rptx_scene_add_light(rptx_scene* s, const rptx_light* light) {
+    if (!s) return 1;
+    rptx_ctx* ctx = s->ctx;
+    if (!light) return ctx_fail(ctx, "rptx_scene_add_light: null argument");
+    if (light->kind < RPTX_LIGHT_POINT || light->kind > RPTX_LIGHT_OBJECT) return ctx_fail(ctx, "unknown light kind");
+    s->lights.push_back(*light);
+    s->committed = false;
+    return 0;
+}
+
+int rptx_scene_set_medium(rptx_scene* s, int32_t kind, double absorption, double scattering) {
+    if (!s) return 1;
+    if (kind < RPTX_MEDIUM_NONE || kind > RPTX_MEDIUM_COLORED_GLOWING_FOG) return ctx_fail(s->ctx, "unknown medium kind");
+    s->medium_kind = kind; s->sigma_a = absorption; s->sigma_s = scattering;
+    return 0;
+}
+
+int rptx_scene_set_environment_color(rptx_scene* s, const double rgb[3]) {
+    if (!s || !rgb) return 1;
+    s->env_is_hdri = false;
+    for (int k = 0; k < 3; k++) s->env_color[k] = rgb[k];
+    return 0;
+}
+
+int rptx_scene_set_environment_hdri(rptx_scene* s, uint32_t w, uint32_t h, const double* px) {
+    if (!s) return 1;
+    if (!px || w == 0 || h == 0) return ctx_fail(s->ctx, "bad HDRI");
+    s->env_is_hdri = true; s->env_w = w; s->env_h = h;
+    s->env_pixels.assign(px, px + (size_t)w * h * 3);
+    s->committed = false;
+    return 0;
+}
+
+int rptx_scene_commit(rptx_scene* s) {
+    if (!s) return 1;
+    rptx_ctx* ctx = s->ctx;
+    CK(cudaSetDevice(ctx->device));
+    free_scene_device(s);
+    cudaStream_t st = ctx->stream;
+
+    // 1. meshes: upload raw triangles, build one BLAS per mesh on the device
+    std::vector<RawTri> raw_all;
+    uint32_t tri_total = 0, node_total = 0;
+    for (auto& m : s->meshes) {
+        m.raw_base = (uint32_t)raw_all.size();
+        m.tri_base = tri_total;
+        raw_all.insert(raw_all.end(), m.tris.begin(), m.tris.end());
+        tri_total += (uint32_t)m.tris.size();
+    }
+    // count bounded instances for the TLAS node range
+    uint32_t n_leaf_shapes = 0;
+    for (const auto& o : s->objects) n_leaf_shapes += o.desc.kind == RPTX_SHAPE_GROUP ? (uint32_t)o.children.size() : 1u;
+    node_total = std::max<uint32_t>(n_leaf_shapes, 1);
+    for (auto& m : s->meshes) { m.node_base = node_total; node_total += std::max<uint32_t>((uint32_t)m.tris.size(), 1); }
+
+    RawTri* d_raw = nullptr;
+    CK(upload(&d_raw, raw_all));
+    s->d_raw = d_raw;
+    BvhNode* d_nodes = nullptr;
+    CK(cudaMalloc((void**)&d_nodes, sizeof(BvhNode) * node_total));
+    CK(cudaMemsetAsync(d_nodes, 0, sizeof(BvhNode) * node_total, st));
+    s->d_nodes = d_nodes;
+    TriRec* d_tris = nullptr; TriNormals* d_tn = nullptr; uint32_t* d_orig = nullptr;
+    CK(cudaMalloc((void**)&d_tris, sizeof(TriRec) * std::max<uint32_t>(tri_total, 1)));
+    CK(cudaMalloc((void**)&d_tn, sizeof(TriNormals) * std::max<uint32_t>(tri_total, 1)));
+    CK(cudaMalloc((void**)&d_orig, sizeof(uint32_t) * std::max<uint32_t>(tri_total, 1)));
+    s->d_tris = d_tris; s->d_tri_normals = d_tn; s->d_tri_orig = d_orig;
+
+    for (auto& m : s->meshes) {
+        const uint32_t n = (uint32_t)m.tris.size();
+        if (n == 0) continue;
+        if (!m.has_normals) {
+            k_face_normals<<<grid_for(n, 128), 128, 0, st>>>(d_raw + m.raw_base, n);
+            ctx->launches++;
+        }
+        PrimBox* d_boxes = nullptr; uint32_t* d_perm = nullptr;
+        CK(cudaMalloc((void**)&d_boxes, sizeof(PrimBox) * n));
+        CK(cudaMalloc((void**)&d_perm, sizeof(uint32_t) * n));
+        k_tri_boxes<<<grid_for(n, 128), 128, 0, st>>>(d_raw + m.raw_base, n, d_boxes);
+        ctx->launches++;
+        double e_abs = 0.0;
+        for (int k = 0; k < 3; k++) e_abs = std::fmax(e_abs, std::fmax(std::fabs(m.bmin[k]), std::fabs(m.bmax[k])));
+        m.pad = f32_upf(std::fmax(e_abs, 1e-30) * (1.0 / 2097152.0));  // E * 2^-21
+        const int rc = build_lbvh(d_boxes, n, m.pad, m.bmin, m.bmax, d_nodes + m.node_base, d_perm, &m.root_ref, st, &ctx->launches);
+        if (rc != 0) { cudaFree(d_boxes); cudaFree(d_perm); return ctx_fail(ctx, std::string("BLAS build: ") + cudaGetErrorString((cudaError_t)rc)); }
+        k_tri_prepare<<<grid_for(n, 128), 128, 0, st>>>(d_raw + m.raw_base, d_perm, n, d_tris + m.tri_base, d_tn + m.tri_base,
+                                                         d_orig + m.tri_base);
+        ctx->launches++;
+        CK(cudaStreamSynchronize(st));
+        cudaFree(d_boxes); cudaFree(d_perm);
+    }
+    if (!s->meshes.empty()) {
+        // light sampling reads face normals from the raw pool: pull the computed ones back
+        // is unnecessary on the host; the device copy is authoritative.
+    }
+
+    // 2. instances
+    std::vector<Instance> bounded, unbounded;
+    std::vector<PrimBox> boxes;
+    double wmn[3] = {INFINITY, INFINITY, INFINITY}, wmx[3] = {-INFINITY, -INFINITY, -INFINITY};
+    std::vector<std::array<double, 6>> wboxes;
+    for (uint32_t oi = 0; oi < s->objects.size(); oi++) {
+        const HostObject& o = s->objects[oi];
+        const uint32_t nc = o.desc.kind == RPTX_SHAPE_GROUP ? (uint32_t)o.children.size() : 1u;
+        for (uint32_t c = 0; c < nc; c++) {
+            const rptx_shape_desc& d = o.desc.kind == RPTX_SHAPE_GROUP ? o.children[c] : o.desc;
+            Instance in;
+            double bmn[3], bmx[3];
+            bool is_bounded = false;
+            if (lower_leaf(s, d, oi, o.desc.kind == RPTX_SHAPE_GROUP ? c : 0u, &in, bmn, bmx, &is_bounded)) return 1;
+            if (is_bounded) {
+                bounded.push_back(in);
+                wboxes.push_back({bmn[0], bmn[1], bmn[2], bmx[0], bmx[1], bmx[2]});
+                for (int k = 0; k < 3; k++) { wmn[k] = std::fmin(wmn[k], bmn[k]); wmx[k] = std::fmax(wmx[k], bmx[k]); }
+            } else {
+                unbounded.push_back(in);
+            }
+        }
+    }
+    s->n_bounded = (uint32_t)bounded.size();
+    s->n_unbounded = (uint32_t)unbounded.size();
+    std::vector<Instance> ordered;
+    s->tlas_root_ref = 0;
+    if (!bounded.empty()) {
+        double e_abs = 0.0;
+        for (int k = 0; k < 3; k++) e_abs = std::fmax(e_abs, std::fmax(std::fabs(wmn[k]), std::fabs(wmx[k])));
+        const float wpad = f32_upf(std::fmax(e_abs, 1e-30) * (1.0 / 2097152.0));
+        for (const auto& b : wboxes) {
+            PrimBox pb;
+            for (int k = 0; k < 3; k++) { pb.mn[k] = f32_down(b[k]); pb.mx[k] = f32_upf(b[3 + k]); }
+            boxes.push_back(pb);
+        }
+        PrimBox* d_boxes = nullptr; uint32_t* d_perm = nullptr;
+        CK(upload(&d_boxes, boxes));
+        CK(cudaMalloc((void**)&d_perm, sizeof(uint32_t) * boxes.size()));
+        const int rc = build_lbvh(d_boxes, (uint32_t)boxes.size(), wpad, wmn, wmx, d_nodes, d_perm, &s->tlas_root_ref, st, &ctx->launches);
+        if (rc != 0) { cudaFree(d_boxes); cudaFree(d_perm); return ctx_fail(ctx, std::string("TLAS build: ") + cudaGetErrorString((cudaError_t)rc)); }
+        std::vector<uint32_t> perm(boxes.size());
+        CK(cudaMemcpy(perm.data(), d_perm, sizeof(uint32_t) * perm.size(), cudaMemcpyDeviceToHost));
+        cudaFree(d_boxes); cudaFree(d_perm);
+        for (uint32_t k : perm) ordered.push_back(bounded[k]);
+        for (int k = 0; k < 3; k++) { s->wmin[k] = wmn[k] - 2.0 * (double)wpad; s->wmax[k] = wmx[k] + 2.0 * (double)wpad; }
+    }
+    ordered.insert(ordered.end(), unbounded.begin(), unbounded.end());
+    Instance* d_inst = nullptr;
+    CK(upload(&d_inst, ordered));
+    s->d_instances = d_inst;
+
+    // 3. materials, lights, environment
+    std::vector<Material> mats;
+    for (const auto& o : s->objects) mats.push_back(to_material(o.material));
+    Material* d_mats = nullptr;
+    CK(upload(&d_mats, mats));
+    s->d_materials = d_mats;
+    std::vector<Light> lights;
+    s->n_shadow_lights = 0;
+    for (const auto& l : s->lights) {
+        Light r;
+        if (lower_light(s, l, &r)) return 1;
+        if (l.kind == RPTX_LIGHT_POINT || l.kind == RPTX_LIGHT_OBJECT) s->n_shadow_lights++;
+        lights.push_back(r);
+    }
+    Light* d_lights = nullptr;
+    CK(upload(&d_lights, lights));
+    s->d_lights = d_lights;
+    if (s->env_is_hdri) {
+        double* d_env = nullptr;
+        CK(upload(&d_env, s->env_pixels));
+        s->d_env = d_env;
+    }
+    CK(cudaStreamSynchronize(st));
+    s->committed = true;
+    return 0;
+}
+
+// ---------------------------------------------------------------- film / render loop
+
+static int film_alloc(rptx_film* f) {
+    rptx_ctx* ctx = f->ctx;
+    PathPool& p = f->pool;
+    const size_t ns = p.n_slots;
+    std::vector<double**> dptrs = {&p.ox, &p.oy, &p.oz, &p.dx, &p.dy, &p.dz, &p.ht, &p.hnx, &p.hny, &p.hnz, &p.dirx, &p.diry, &p.dirz,
+                                   &p.fx, &p.fy, &p.fz, &p.pdf, &p.abscos, &p.bx, &p.by, &p.bz, &p.lx, &p.ly, &p.lz, &p.ax, &p.ay, &p.az};
+    for (double** d : dptrs) { CK(cudaMalloc((void**)d, sizeof(double) * ns)); f->owned.push_back(*d); }
+    std::vector<double**> sptrs = {&p.sdx, &p.sdy, &p.sdz, &p.sdist, &p.scx, &p.scy, &p.scz};
+    for (double** d : sptrs) { CK(cudaMalloc((void**)d, sizeof(double) * ns * std::max<uint32_t>(p.n_shadow, 1))); f->owned.push_back(*d); }
+    CK(cudaMalloc((void**)&p.stack, sizeof(double) * ns * 8 * std::max<uint32_t>(p.stack_depth, 1))); f->owned.push_back(p.stack);
+    CK(cudaMalloc((void**)&p.hobj, sizeof(uint32_t) * ns)); f->owned.push_back(p.hobj);
+    CK(cudaMalloc((void**)&p.rng, sizeof(uint64_t) * ns)); f->owned.push_back(p.rng);
+    CK(cudaMalloc((void**)&p.sample_j, sizeof(uint32_t) * ns)); f->owned.push_back(p.sample_j);
+    CK(cudaMalloc((void**)&p.depth, sizeof(uint32_t) * ns)); f->owned.push_back(p.depth);
+    CK(cudaMalloc((void**)&p.flags, sizeof(uint32_t) * ns)); f->owned.push_back(p.flags);
+    CK(cudaMalloc((void**)&f->q.cur, sizeof(uint32_t) * ns)); f->owned.push_back(f->q.cur);
+    CK(cudaMalloc((void**)&f->q.next, sizeof(uint32_t) * ns)); f->owned.push_back(f->q.next);
+    CK(cudaMalloc((void**)&f->q.counters, sizeof(uint32_t) * 8)); f->owned.push_back(f->q.counters);
+    CK(cudaMalloc((void**)&f->q.stats, sizeof(unsigned long long) * 8)); f->owned.push_back(f->q.stats);
+    CK(cudaMemset(f->q.stats, 0, sizeof(unsigned long long) * 8));
+    const size_t n3 = (size_t)p.n_pixels * 3;
+    CK(cudaMalloc((void**)&f->d_batch_sum, sizeof(double) * n3)); f->owned.push_back(f->d_batch_sum);
+    CK(cudaMalloc((void**)&f->d_film_sum, sizeof(double) * n3)); f->owned.push_back(f->d_film_sum);
+    CK(cudaMemset(f->d_film_sum, 0, sizeof(double) * n3));
+    CK(cudaMemset(f->d_batch_sum, 0, sizeof(double) * n3));
+    CK(cudaEventCreate(&f->ev0)); CK(cudaEventCreate(&f->ev1));
+    return 0;
+}
+
+int rptx_render_begin(rptx_ctx* ctx, rptx_scene* scene, const rptx_camera* camera, const rptx_params* params, rptx_film** out) {
+    if (!ctx || !out) return 1;
+    *out = nullptr;
+    if (!scene || !camera || !params) return ctx_fail(ctx, "rptx_render_begin: null argument");
+    if (scene->ctx != ctx) return ctx_fail(ctx, "scene belongs to another context");
+    if (!scene->committed) return ctx_fail(ctx, "scene not committed");
+    if (params->width == 0 || params->height == 0) return ctx_fail(ctx, "empty image");
+    if (params->shard_count == 0 || params->shard_index >= params->shard_count) return ctx_fail(ctx, "bad shard");
+    CK(cudaSetDevice(ctx->device));
+    rptx_film* f = new rptx_film();
+    f->ctx = ctx; f->scene = scene; f->params = *params;
+    f->cam.eye = mk3(camera->eye[0], camera->eye[1], camera->eye[2]);
+    f->cam.direction = mk3(camera->direction[0], camera->direction[1], camera->direction[2]);
+    f->cam.up = mk3(camera->up[0], camera->up[1], camera->up[2]);
+    f->cam.fov = camera->fov; f->cam.aperture = camera->aperture; f->cam.focal_distance = camera->focal_distance;
+    PathPool& p = f->pool;
+    std::memset(&p, 0, sizeof(p));
+    const uint64_t n_pixels = (uint64_t)params->width * params->height;
+    if (n_pixels >= (1ull << 31)) { delete f; return ctx_fail(ctx, "image too large"); }
+    p.n_pixels = (uint32_t)n_pixels;
+    const uint64_t target = 1ull << 21;
+    uint64_t lanes = std::max<uint64_t>(1, target / n_pixels);
+    lanes = std::min<uint64_t>(lanes, 4096);
+    p.n_lanes = (uint32_t)lanes;
+    p.n_slots = (uint32_t)(n_pixels * lanes);
+    p.n_shadow = scene->n_shadow_lights;
+    p.stack_depth = scene->medium_kind == RPTX_MEDIUM_NONE ? params->max_bounces + 1 : 1;
+    if (film_alloc(f)) { rptx_film_destroy(f); return 1; }
+    *out = f;
+    return 0;
+}
+
+void rptx_film_destroy(rptx_film* f) {
+    if (!f) return;
+    cudaSetDevice(f->ctx->device);
+    for (void* p : f->owned) cudaFree(p);
+    for (double* b : f->batches) cudaFree(b);
+    if (f->d_batch_ptrs) cudaFree(f->d_batch_ptrs);
+    if (f->ev0) cudaEventDestroy(f->ev0);
+    if (f->ev1) cudaEventDestroy(f->ev1);
+    delete f;
+}
+
+}  // extern "C"
+
+template <bool MEDIUM>
+static int run_waves(rptx_film* f, const BatchParams& bp) {
+    rptx_ctx* ctx = f->ctx;
+    cudaStream_t st = ctx->stream;
+    const SceneDev sc = scene_dev(f->scene);
+    const MediumDev md = medium_dev(f->scene);
+    PathPool& p = f->pool;
+    Queues q = f->q;
+    CK(cudaMemsetAsync(q.counters, 0, sizeof(uint32_t) * 8, st));
+    k_generate<MEDIUM><<<grid_for(p.n_slots, kBlock), kBlock, 0, st>>>(p, q, bp, f->cam);
+    ctx->launches++;
+    const int persistent_blocks = ctx->sm_count * 8;
+    uint32_t* h_count = (uint32_t*)ctx->h_pinned;
+    uint32_t active = std::min<uint64_t>(p.n_slots, (uint64_t)p.n_pixels * std::min(p.n_lanes, bp.n_local));
+    while (active > 0) {
+        const int blocks = (int)std::min<uint64_t>(persistent_blocks, grid_for(active, kBlock));
+        k_extend<<<blocks, kBlock, 0, st>>>(sc, p, q);
+        k_shade<MEDIUM><<<grid_for(active, kBlock), kBlock, 0, st>>>(sc, p, q, bp, md);
+        k_connect<MEDIUM><<<blocks, kBlock, 0, st>>>(sc, p, q, bp, f->cam);
+        k_wave_end<<<1, 1, 0, st>>>(q);
+        ctx->launches += 4;
+        f->stats.waves++;
+        std::swap(q.cur, q.next);
+        CK(cudaMemcpyAsync(h_count, q.counters, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        active = *h_count;
+    }
+    CK(cudaGetLastError());
+    return 0;
+}
+
+extern "C" {
+
+int rptx_render_sample_trace(rptx_film* f, uint32_t iterations) {
+    if (!f) return 1;
+    rptx_ctx* ctx = f->ctx;
+    if (iterations == 0) return ctx_fail(ctx, "iterations must be > 0");
+    CK(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    BatchParams bp;
+    bp.width = f->params.width; bp.height = f->params.height; bp.max_bounces = f->params.max_bounces;
+    bp.seed = f->params.seed; bp.batch_base = f->next_sample; bp.iterations = iterations;
+    bp.shard_count = f->params.shard_count; bp.shard_index = f->params.shard_index;
+    bp.n_local = iterations > bp.shard_index ? (iterations - bp.shard_index + bp.shard_count - 1) / bp.shard_count : 0;
+    CK(cudaEventRecord(f->ev0, st));
+    PathPool& p = f->pool;
+    const uint32_t full_lanes = p.n_lanes;
+    p.n_lanes = std::max<uint32_t>(1, std::min(full_lanes, bp.n_local));
+    int rc = f->scene->medium_kind == RPTX_MEDIUM_NONE ? run_waves<false>(f, bp) : run_waves<true>(f, bp);
+    if (rc == 0) {
+        k_batch_reduce<<<grid_for(p.n_pixels, 128), 128, 0, st>>>(p, f->d_batch_sum);
+        ctx->launches++;
+    }
+    p.n_lanes = full_lanes;
+    if (rc) return rc;
+    CK(cudaEventRecord(f->ev1, st));
+    CK(cudaStreamSynchronize(st));
+    float ms = 0.f;
+    CK(cudaEventElapsedTime(&ms, f->ev0, f->ev1));
+    f->stats.device_ms = ms;
+    return 0;
+}
+
+int rptx_render_sample_commit(rptx_film* f, uint32_t iterations) {
+    if (!f) return 1;
+    rptx_ctx* ctx = f->ctx;
+    if (iterations == 0) return ctx_fail(ctx, "iterations must be > 0");
+    CK(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    const size_t n3 = (size_t)f->pool.n_pixels * 3;
+    double* mean = nullptr;
+    CK(cudaMalloc((void**)&mean, sizeof(double) * n3));
+    f->batches.push_back(mean);
+    const double exposure = std::pow(2.0, f->params.exposure_value);
+    k_batch_commit<<<grid_for(n3, 256), 256, 0, st>>>(f->d_batch_sum, n3, (double)iterations, exposure, mean, f->d_film_sum);
+    ctx->launches++;
+    CK(cudaStreamSynchronize(st));
+    f->next_sample += iterations;
+    return 0;
+}
+
+int rptx_render_sample(rptx_film* f, uint32_t iterations) {
+    if (int rc = rptx_render_sample_trace(f, iterations)) return rc;
+    return rptx_render_sample_commit(f, iterations);
+}
+
+void* rptx_film_batch_sum_device_ptr(rptx_film* f) { return f ? (void*)f->d_batch_sum : nullptr; }
+
+int rptx_film_image_rgb8(rptx_film* f, uint8_t* out) {
+    if (!f) return 1;
+    rptx_ctx* ctx = f->ctx;
+    if (!out) return ctx_fail(ctx, "null output");
+    if (f->batches.empty()) return ctx_fail(ctx, "Pixel found with no samples");  // src/buffer.rs:89
+    CK(cudaSetDevice(ctx->device));
+    const uint32_t w = f->params.width, h = f->params.height;
+    uint8_t* d_out = nullptr;
+    CK(cudaMalloc((void**)&d_out, (size_t)w * h * 3));
+    dim3 blk(16, 16), grd((w + 15) / 16, (h + 15) / 16);
+    k_image<<<grd, blk, 0, ctx->stream>>>(f->d_film_sum, w, h, f->params.filter_radius, (uint32_t)f->batches.size(), d_out);
+    ctx->launches++;
+    cudaError_t e = cudaMemcpyAsync(out, d_out, (size_t)w * h * 3, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    cudaFree(d_out);
+    if (e != cudaSuccess) return ctx_fail(ctx, cudaGetErrorString(e));
+    return 0;
+}
+
+int rptx_film_variance(rptx_film* f, double* out) {
+    if (!f) return 1;
+    rptx_ctx* ctx = f->ctx;
+    if (!out) return ctx_fail(ctx, "null output");
+    CK(cudaSetDevice(ctx->device));
+    const uint32_t nb = (uint32_t)f->batches.size();
+    if (nb == 0) { *out = NAN; return 0; }
+    if (f->d_batch_ptrs) { cudaFree(f->d_batch_ptrs); f->d_batch_ptrs = nullptr; }
+    CK(cudaMalloc((void**)&f->d_batch_ptrs, sizeof(double*) * nb));
+    CK(cudaMemcpy(f->d_batch_ptrs, f->batches.data(), sizeof(double*) * nb, cudaMemcpyHostToDevice));
+    double* d_acc = nullptr;
+    CK(cudaMalloc((void**)&d_acc, sizeof(double)));
+    CK(cudaMemsetAsync(d_acc, 0, sizeof(double), ctx->stream));
+    k_variance<<<ctx->sm_count * 4, 256, 0, ctx->stream>>>(f->d_batch_ptrs, nb, f->d_film_sum, f->pool.n_pixels, d_acc);
+    ctx->launches++;
+    double acc = 0.0;
+    cudaError_t e = cudaMemcpyAsync(&acc, d_acc, sizeof(double), cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    cudaFree(d_acc);
+    if (e != cudaSuccess) return ctx_fail(ctx, cudaGetErrorString(e));
+    *out = acc / (double)f->pool.n_pixels;
+    return 0;
+}
+
+int rptx_film_mean(rptx_film* f, double* out) {
+    if (!f) return 1;
+    rptx_ctx* ctx = f->ctx;
+    if (!out) return ctx_fail(ctx, "null output");
+    if (f->batches.empty()) return ctx_fail(ctx, "no batches rendered");
+    CK(cudaSetDevice(ctx->device));
+    const size_t n3 = (size_t)f->pool.n_pixels * 3;
+    double* d_out = nullptr;
+    CK(cudaMalloc((void**)&d_out, sizeof(double) * n3));
+    k_film_mean<<<grid_for(n3, 256), 256, 0, ctx->stream>>>(f->d_film_sum, n3, (double)f->batches.size(), d_out);
+    ctx->launches++;
+    cudaError_t e = cudaMemcpyAsync(out, d_out, sizeof(double) * n3, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    cudaFree(d_out);
+    if (e != cudaSuccess) return ctx_fail(ctx, cudaGetErrorString(e));
+    return 0;
+}
+
+int rptx_stats_get(const rptx_film* f, rptx_stats* out) {
+    if (!f || !out) return 1;
+    cudaSetDevice(f->ctx->device);
+    unsigned long long st[8] = {0};
+    cudaMemcpy(st, f->q.stats, sizeof(st), cudaMemcpyDeviceToHost);
+    *out = f->stats;
+    out->path_samples = st[0]; out->extend_rays = st[1]; out->shadow_rays = st[2];
+    out->kernel_launches = f->ctx->launches;
+    return 0;
+}
+
+// ---------------------------------------------------------------- parity hooks
+
+int rptx_intersect_batch_device(rptx_scene* s, const void* d_o, const void* d_d, size_t n, double t_min, void* d_t,
+                                void* d_object_id, void* d_prim_id, void* d_inst_id, void* d_normal) {
+    if (!s) return 1;
+    rptx_ctx* ctx = s->ctx;
+    if (!s->committed) return ctx_fail(ctx, "scene not committed");
+    if (n == 0) return 0;
+    if (!d_o || !d_d) return ctx_fail(ctx, "null ray arrays");
+    CK(cudaSetDevice(ctx->device));
+    const SceneDev sc = scene_dev(s);
+    k_intersect_batch<<<grid_for(n, kBlock), kBlock, 0, ctx->stream>>>(sc, (const double*)d_o, (const double*)d_d, n, t_min, (double*)d_t,
+                                                                        (uint32_t*)d_object_id, (uint32_t*)d_prim_id,
+                                                                        (uint32_t*)d_inst_id, (double*)d_normal);
+    ctx->launches++;
+    CK(cudaGetLastError());
+    CK(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+int rptx_intersect_batch(rptx_scene* s, const double* o, const double* d, size_t n, double t_min, double* t, uint32_t* object_id,
+                         uint32_t* prim_id, uint32_t* inst_id, double* normal) {
+    if (!s) return 1;
+    rptx_ctx* ctx = s->ctx;
+    if (!s->committed) return ctx_fail(ctx, "scene not committed");
+    if (n == 0) return 0;
+    if (!o || !d) return ctx_fail(ctx, "null ray arrays");
+    CK(cudaSetDevice(ctx->device));
+    double *d_o = nullptr, *d_d = nullptr, *d_t = nullptr, *d_n = nullptr;
+    uint32_t *d_obj = nullptr, *d_prim = nullptr, *d_inst = nullptr;
+    int rc = 0;
+    auto cleanup = [&] { cudaFree(d_o); cudaFree(d_d); cudaFree(d_t); cudaFree(d_n); cudaFree(d_obj); cudaFree(d_prim); cudaFree(d_inst); };
+#define CKC(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { cleanup(); return ctx_fail(ctx, std::string(#call) + ": " + cudaGetErrorString(e_)); } } while (0)
+    CKC(cudaMalloc((void**)&d_o, sizeof(double) * 3 * n));
+    CKC(cudaMalloc((void**)&d_d, sizeof(double) * 3 * n));
+    CKC(cudaMalloc((void**)&d_t, sizeof(double) * n));
+    CKC(cudaMalloc((void**)&d_n, sizeof(double) * 3 * n));
+    CKC(cudaMalloc((void**)&d_obj, sizeof(uint32_t) * n));
+    CKC(cudaMalloc((void**)&d_prim, sizeof(uint32_t) * n));
+    CKC(cudaMalloc((void**)&d_inst, sizeof(uint32_t) * n));
+    CKC(cudaMemcpy(d_o, o, sizeof(double) * 3 * n, cudaMemcpyHostToDevice));
+    CKC(cudaMemcpy(d_d, d, sizeof(double) * 3 * n, cudaMemcpyHostToDevice));
+    rc = rptx_intersect_batch_device(s, d_o, d_d, n, t_min, d_t, d_obj, d_prim, d_inst, d_n);
+    if (rc == 0) {
+        if (t) CKC(cudaMemcpy(t, d_t, sizeof(double) * n, cudaMemcpyDeviceToHost));
+        if (object_id) CKC(cudaMemcpy(object_id, d_obj, sizeof(uint32_t) * n, cudaMemcpyDeviceToHost));
+        if (prim_id) CKC(cudaMemcpy(prim_id, d_prim, sizeof(uint32_t) * n, cudaMemcpyDeviceToHost));
+        if (inst_id) CKC(cudaMemcpy(inst_id, d_inst, sizeof(uint32_t) * n, cudaMemcpyDeviceToHost));
+        if (normal) CKC(cudaMemcpy(normal, d_n, sizeof(double) * 3 * n, cudaMemcpyDeviceToHost));
+    }
+#undef CKC
+    cleanup();
+    return rc;
+}
+
+int rptx_photon_render(rptx_ctx* ctx, rptx_scene*, const rptx_camera*, const rptx_params*, uint64_t, int32_t, uint8_t*, double*) {
+    return ctx_fail(ctx, "rptx_photon_render: photon integrators are not built yet");
+}
+
+}  // extern "C"

@@ -1,0 +1,203 @@
+"""ctypes driver of the ORACLE (oracle/liborc_oracle.so) — test infrastructure only.
+
+It consumes the same lowered scene (rpt_b200.world.lower_scene) as the CUDA library, so one
+scene description feeds the checker and the product.  Nothing under rpt_b200/ imports this.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+from rpt_b200 import _abi as A
+from rpt_b200.world import lower_scene, upload_scene
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORC_DIR = os.path.join(ROOT, "oracle")
+ORC_LIB = os.path.join(ORC_DIR, "liborc_oracle.so")
+
+P, DP, U32P, U8P, U64P = C.c_void_p, A.DP, A.U32P, A.U8P, C.POINTER(C.c_uint64)
+_lib = None
+
+
+def build():
+    subprocess.check_call(["make", "-s", "-C", ORC_DIR])
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(ORC_LIB):
+            build()
+        L = C.CDLL(ORC_LIB)
+        sig = {
+            "orc_scene_create": (P, []),
+            "orc_scene_destroy": (None, [P]),
+            "orc_last_error": (C.c_char_p, [P]),
+            "orc_scene_add_mesh": (C.c_int, [P, DP, DP, C.c_size_t, U32P]),
+            "orc_scene_add_object": (C.c_int, [P, C.POINTER(A.ShapeDesc), C.POINTER(A.MaterialDesc), U32P]),
+            "orc_scene_add_light": (C.c_int, [P, C.POINTER(A.LightDesc)]),
+            "orc_scene_set_medium": (C.c_int, [P, C.c_int32, C.c_double, C.c_double]),
+            "orc_scene_set_environment_color": (C.c_int, [P, DP]),
+            "orc_scene_set_environment_hdri": (C.c_int, [P, C.c_uint32, C.c_uint32, DP]),
+            "orc_mesh_kd_stats": (C.c_int, [P, C.c_uint32, U64P]),
+            "orc_render_begin": (P, [P, C.POINTER(A.CameraDesc), C.POINTER(A.Params), C.c_int]),
+            "orc_film_destroy": (None, [P]),
+            "orc_render_sample": (C.c_int, [P, C.c_uint32]),
+            "orc_time_rows": (C.c_double, [P, C.c_uint32, C.c_uint32, C.c_uint32, U64P]),
+            "orc_film_last_seconds": (C.c_double, [P]),
+            "orc_film_counters": (C.c_int, [P, U64P]),
+            "orc_film_image_rgb8": (C.c_int, [P, U8P]),
+            "orc_film_variance": (C.c_int, [P, DP]),
+            "orc_film_mean": (C.c_int, [P, DP]),
+            "orc_sample_radiance": (C.c_int, [P, U32P, U32P, U64P, C.c_size_t, DP]),
+            "orc_dump_rays": (C.c_size_t, [P, C.c_uint32, C.c_size_t, DP, DP, U8P]),
+            "orc_intersect_batch": (C.c_int, [P, DP, DP, C.c_size_t, C.c_double, DP, U32P, U32P, U32P, DP, C.c_int]),
+            "orc_hex_color": (None, [C.c_uint32, DP]),
+            "orc_color_bytes": (None, [DP, U8P]),
+            "orc_rng_u64": (C.c_uint64, [C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint32]),
+            "orc_hardware_threads": (C.c_int, []),
+            "orc_photon_render": (C.c_int, [P, C.POINTER(A.CameraDesc), C.POINTER(A.Params), C.c_uint64, C.c_int32, C.c_int, U8P, DP, U64P, DP]),
+        }
+        for name, (res, args) in sig.items():
+            fn = getattr(L, name)
+            fn.restype, fn.argtypes = res, args
+        _lib = L
+    return _lib
+
+
+def _dp(a):
+    return a.ctypes.data_as(DP)
+
+
+class OracleScene:
+    def __init__(self, scene):
+        self.L = lib()
+        self.h = self.L.orc_scene_create()
+        self.low = lower_scene(scene)
+        upload_scene(self.low, self)
+
+    def _ck(self, rc, what):
+        if rc:
+            raise RuntimeError(f"{what}: {self.L.orc_last_error(self.h).decode()}")
+
+    def add_mesh(self, v, n):
+        mid = C.c_uint32()
+        v = np.ascontiguousarray(v, np.float64)
+        nptr = None
+        if n is not None:
+            n = np.ascontiguousarray(n, np.float64)
+            nptr = _dp(n)
+        self._ck(self.L.orc_scene_add_mesh(self.h, _dp(v), nptr, len(v), C.byref(mid)), "add_mesh")
+        return mid.value
+
+    def add_object(self, sd, md):
+        self._ck(self.L.orc_scene_add_object(self.h, C.byref(sd), C.byref(md), None), "add_object")
+
+    def add_light(self, ld):
+        self._ck(self.L.orc_scene_add_light(self.h, C.byref(ld)), "add_light")
+
+    def set_medium(self, kind, a, s):
+        self._ck(self.L.orc_scene_set_medium(self.h, kind, a, s), "set_medium")
+
+    def set_environment_color(self, rgb):
+        self._ck(self.L.orc_scene_set_environment_color(self.h, (C.c_double * 3)(*rgb)), "env")
+
+    def set_environment_hdri(self, w, h, buf):
+        buf = np.ascontiguousarray(buf, np.float64)
+        self._ck(self.L.orc_scene_set_environment_hdri(self.h, w, h, _dp(buf)), "hdri")
+
+    def commit(self):
+        pass
+
+    def intersect_batch(self, o, d, t_min=1e-12, threads=0):
+        o = np.ascontiguousarray(o, np.float64).reshape(-1, 3)
+        d = np.ascontiguousarray(d, np.float64).reshape(-1, 3)
+        n = len(o)
+        t = np.empty(n, np.float64)
+        obj, prim, inst = np.empty(n, np.uint32), np.empty(n, np.uint32), np.empty(n, np.uint32)
+        nrm = np.empty((n, 3), np.float64)
+        threads = threads or self.L.orc_hardware_threads()
+        self._ck(self.L.orc_intersect_batch(self.h, _dp(o), _dp(d), n, t_min, _dp(t), obj.ctypes.data_as(U32P), prim.ctypes.data_as(U32P),
+                                            inst.ctypes.data_as(U32P), _dp(nrm), threads), "intersect_batch")
+        return t, obj, prim, inst, nrm
+
+    def kd_stats(self, mesh_id):
+        out = (C.c_uint64 * 3)()
+        self._ck(self.L.orc_mesh_kd_stats(self.h, mesh_id, out), "kd_stats")
+        return tuple(out)
+
+    def photon_render(self, camera, params, photon_count, kind, threads=0):
+        w, h = params.width, params.height
+        img = np.empty((h, w, 3), np.uint8)
+        mean = np.empty((h, w, 3), np.float64)
+        counts = (C.c_uint64 * 2)()
+        secs = (C.c_double * 3)()
+        cam = camera.lower()
+        self._ck(self.L.orc_photon_render(self.h, C.byref(cam), C.byref(params), photon_count, kind, threads, img.ctypes.data_as(U8P),
+                                          _dp(mean), counts, secs), "photon_render")
+        return img, mean, tuple(counts), tuple(secs)
+
+    def __del__(self):
+        try:
+            self.L.orc_scene_destroy(self.h)
+        except Exception:
+            pass
+
+
+class OracleFilm:
+    def __init__(self, oscene, camera, params, threads=0):
+        self.L, self.oscene = oscene.L, oscene
+        self.w, self.h_px = params.width, params.height
+        cam = camera.lower()
+        self.h = self.L.orc_render_begin(oscene.h, C.byref(cam), C.byref(params), threads)
+
+    def sample(self, iterations):
+        self.L.orc_render_sample(self.h, iterations)
+
+    def seconds(self):
+        return self.L.orc_film_last_seconds(self.h)
+
+    def time_rows(self, y0, y1, iterations):
+        ctr = (C.c_uint64 * 4)()
+        sec = self.L.orc_time_rows(self.h, y0, y1, iterations, ctr)
+        return sec, tuple(ctr)
+
+    def counters(self):
+        out = (C.c_uint64 * 4)()
+        self.L.orc_film_counters(self.h, out)
+        return dict(extend_rays=out[0], shadow_rays=out[1], shadow_pass=out[2], shadow_near=out[3])
+
+    def image(self):
+        out = np.empty((self.h_px, self.w, 3), np.uint8)
+        self.L.orc_film_image_rgb8(self.h, out.ctypes.data_as(U8P))
+        return out
+
+    def variance(self):
+        v = C.c_double()
+        self.L.orc_film_variance(self.h, C.byref(v))
+        return v.value
+
+    def mean(self):
+        out = np.empty((self.h_px, self.w, 3), np.float64)
+        self.L.orc_film_mean(self.h, _dp(out))
+        return out
+
+    def sample_radiance(self, px, py, sample):
+        px, py = np.ascontiguousarray(px, np.uint32), np.ascontiguousarray(py, np.uint32)
+        sample = np.ascontiguousarray(sample, np.uint64)
+        out = np.empty((len(px), 3), np.float64)
+        self.L.orc_sample_radiance(self.h, px.ctypes.data_as(U32P), py.ctypes.data_as(U32P), sample.ctypes.data_as(U64P), len(px), _dp(out))
+        return out
+
+    def dump_rays(self, iterations, cap):
+        o, d = np.empty((cap, 3), np.float64), np.empty((cap, 3), np.float64)
+        kind = np.empty(cap, np.uint8)
+        n = self.L.orc_dump_rays(self.h, iterations, cap, _dp(o), _dp(d), kind.ctypes.data_as(U8P))
+        return o[:n].copy(), d[:n].copy(), kind[:n].copy()
+
+    def __del__(self):
+        try:
+            self.L.orc_film_destroy(self.h)
+        except Exception:
+            pass
