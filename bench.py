@@ -1,0 +1,298 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the B200 light-transport core.
+
+  python bench.py --gpus N --steps K --warmup W [--impl reference] [--workload NAME]
+
+A "step" is one pass of the hot path over one batch: Renderer::sample(spp) over the whole
+image (src/renderer.rs:158-171), i.e. width*height*spp path-samples per GPU.  Metric:
+Mpath-samples/s (BASELINE.json).  Default workload = BASELINE.json configs[1]:
+examples/fractal_teapots.rs at 1920x1080, 256 spp, the example's own max_bounces (0).
+
+N > 1 (torchrun, one rank per GPU): weak scaling — the batch grows to N*spp samples per pixel,
+rank r traces the samples s % N == r, the per-rank f64 batch sums are all-reduced with NCCL and
+every rank commits the same batch mean (north_star: "per-GPU accumulation buffers are reduced").
+
+`--impl reference` times the reference's algorithm on the host CPU cores.  rpt is Rust and
+cannot be built in this image (no rustc/cargo, dependencies not vendored), so that arm runs the
+oracle port (oracle/, C++ f64 restatement with rpt's linear object loop, kd-trees, recursion and
+one task per image row) on a bounded sample of the same workload.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+METRIC = "Mpath-samples/s"
+
+# algorithmic HBM bytes of one extend-kernel ray (DESIGN.md "k_extend"): queue entry 4 B +
+# ray origin/direction 48 B read; t 8 B + object id 4 B + normal 24 B written
+EXTEND_BYTES_PER_RAY = 4 + 48 + 8 + 4 + 24
+
+
+def workload(name):
+    from rpt_b200 import scenes
+
+    if name == "fractal_teapots":
+        scene, cam, d = scenes.fractal_teapots()
+    elif name == "fractal_teapots_mb5":
+        scene, cam, d = scenes.fractal_teapots()
+        d = dict(d, max_bounces=5)
+    elif name == "teapot":
+        scene, cam, d = scenes.teapot()
+    elif name == "cornell":
+        scene, cam, d = scenes.cornell()
+    elif name == "lampshade":
+        scene, cam, d = scenes.lampshade("pathtrace")
+    else:
+        raise SystemExit(f"unknown workload {name}")
+    return scene, cam, d
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
+
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+        sm = sorted(int(float(r[0])) for r in self.rows if r and r[0].replace(".", "").isdigit())
+        mx = [int(float(r[1])) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        reasons = set()
+        for r in self.rows:
+            for name, v in zip(["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"], r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def measured_peak_gbs():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured"
+    except Exception:
+        return 6650.0, "fallback"
+
+
+def cpu_sample(scene, cam, params, seconds, threads=0):
+    """Time the oracle on every k-th image row of the same workload for ~`seconds`."""
+    import orc
+
+    osc = orc.OracleScene(scene)
+    of = orc.OracleFilm(osc, cam, params, threads)
+    h, w = params.height, params.width
+    cores = threads or orc.lib().orc_hardware_threads()
+    # calibrate on 1 spp over ~64 spread rows
+    stride = max(1, h // 64)
+    sec, ctr = of.time_rows(0, h, stride, 1)
+    rows = len(range(0, h, stride))
+    rate = rows * w / max(sec, 1e-9)  # path-samples/s
+    spp = int(max(1, min(params.num_samples, seconds * rate / (rows * w))))
+    sec, ctr = of.time_rows(0, h, stride, spp)
+    paths = rows * w * spp
+    return dict(value=paths / sec / 1e6, unit=METRIC, cores=cores, kind="port",
+                sample=f"{rows} of {h} rows (every {stride}th) x {w} px x {spp} spp = {paths} path-samples in {sec:.2f} s; "
+                       f"{(ctr[0] + ctr[1]) / sec / 1e6:.2f} Mrays/s"), sec
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    scene, cam, d = workload(args.workload)
+    from rpt_b200.scenes import make_renderer
+
+    params = make_renderer(scene, cam, d).params()
+    for _ in range(args.warmup):
+        cpu_sample(scene, cam, params, 0.5)
+    vals, secs, last = [], 0.0, None
+    for _ in range(args.steps):
+        last, sec = cpu_sample(scene, cam, params, args.cpu_seconds)
+        vals.append(last["value"])
+        secs += sec
+    v = sum(vals) / len(vals)
+    last["value"] = v
+    line = dict(impl="reference", metric=METRIC, value=v, unit=METRIC, n_gpus=args.gpus, steps=args.steps, warmup=args.warmup,
+                ms_per_step=1e3 * secs / args.steps, higher_is_better=True, scaling="weak", vs_baseline=None, dtype="f64", data="synthetic",
+                config=config_of(args, d), cpu_baseline=last,
+                e2e=dict(value=v, unit=METRIC, h2d_bytes_per_step=0, d2h_bytes_per_step=0))
+    print(json.dumps(line))
+
+
+def config_of(args, d):
+    return dict(workload=f"{args.workload}: examples/{args.workload.split('_mb')[0]}.rs scene, {d['width']}x{d['height']}, {d['num_samples']} spp, "
+                         f"max_bounces {d['max_bounces']}",
+                width=d["width"], height=d["height"], spp=d["num_samples"], max_bounces=d["max_bounces"],
+                l2_policy="per-step path state (>= 1.4 GB) and film exceed the 126 MB L2; no explicit flush",
+                parallelism=f"sample-sharded x{args.gpus}")
+
+
+def run_ours(args):
+    import numpy as np
+    import torch
+
+    from rpt_b200.scenes import make_renderer
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    torch.cuda.set_device(local)
+    from rpt_b200 import Context
+
+    ctx = Context(local)
+    scene, cam, d = workload(args.workload)
+    w, h, spp = d["width"], d["height"], d["num_samples"]
+    r = make_renderer(scene, cam, d, seed=0)
+    r._ctx = ctx
+    r.shard(world, rank)
+    batch = spp * world  # weak scaling: every rank traces `spp` samples per pixel
+    film = r.begin()
+
+    class _View:  # the film's device batch-sum buffer as a torch tensor (no copy)
+        __cuda_array_interface__ = dict(shape=(h * w * 3,), typestr="<f8", data=(film.batch_sum_ptr(), False), version=3)
+
+    batch_sum = torch.as_tensor(_View(), device=f"cuda:{local}")
+
+    def step():
+        film.sample_trace(batch)
+        if dist is not None:
+            dist.all_reduce(batch_sum)
+            torch.cuda.synchronize()
+        film.sample_commit(batch)
+        return film.stats()
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step()
+    launches0 = film.stats()["kernel_launches"]
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+    barrier()
+    dev_ms = ext_ms = con_ms = shd_ms = 0.0
+    rays_e = rays_s = 0
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        before = film.stats()
+        st = step()
+        dev_ms += st["device_ms"]  # CUDA events on the library's own stream around the traced batch
+        ext_ms += st["extend_ms"]; con_ms += st["connect_ms"]; shd_ms += st["shade_ms"]
+        rays_e += st["extend_rays"] - before["extend_rays"]
+        rays_s += st["shadow_rays"] - before["shadow_rays"]
+    barrier()
+    wall = time.perf_counter() - t0
+    clk = clocks.stop() if rank == 0 else None
+    launches = film.stats()["kernel_launches"] - launches0
+    # max over ranks of the per-rank time (device events; wall clock includes the all-reduce)
+    t = torch.tensor([wall, dev_ms / 1e3], device=f"cuda:{local}", dtype=torch.float64)
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    wall_max, dev_max = float(t[0]), float(t[1])
+    step_time = wall_max if world > 1 else max(dev_max, 1e-12)
+    paths = w * h * spp * world * args.steps
+    value = paths / step_time / 1e6
+
+    # e2e: the user-facing call from HOST data: lower + upload scene, GPU BVH build, render, image to host
+    h2d = sum(v.nbytes + (0 if n is None else n.nbytes) for v, n in r.device_scene().low.meshes)
+    e2e_t = 0.0
+    n_e2e = max(1, min(args.steps, 2))
+    for _ in range(n_e2e):
+        barrier()
+        t1 = time.perf_counter()
+        rr = make_renderer(scene, cam, d, seed=1)
+        rr._ctx = ctx
+        rr.shard(world, rank)
+        f2 = rr.begin()
+        f2.sample_trace(batch)
+        if dist is not None:
+            v2 = type("_V", (), {"__cuda_array_interface__": dict(shape=(h * w * 3,), typestr="<f8", data=(f2.batch_sum_ptr(), False), version=3)})()
+            dist.all_reduce(torch.as_tensor(v2, device=f"cuda:{local}"))
+            torch.cuda.synchronize()
+        f2.sample_commit(batch)
+        img = f2.image()
+        barrier()
+        e2e_t += time.perf_counter() - t1
+        assert img.shape == (h, w, 3)
+        f2.close(); rr.device_scene().close()
+    te = torch.tensor([e2e_t / n_e2e], device=f"cuda:{local}", dtype=torch.float64)
+    if dist is not None:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    e2e_val = w * h * spp * world / float(te[0]) / 1e6
+
+    if rank == 0:
+        peak, which = measured_peak_gbs()
+        ext_s = ext_ms / 1e3 / args.steps
+        ach = EXTEND_BYTES_PER_RAY * (rays_e / args.steps) / max(ext_s, 1e-12) / 1e9
+        cpu = None
+        if world == 1 and args.cpu_seconds > 0:
+            cpu, _ = cpu_sample(scene, cam, r.params(), args.cpu_seconds)
+        line = dict(metric=METRIC, value=value, unit=METRIC, n_gpus=world, steps=args.steps, warmup=args.warmup,
+                    ms_per_step=1e3 * step_time / args.steps, higher_is_better=True, scaling="weak", vs_baseline=None, dtype="f64",
+                    data="synthetic", config=config_of(args, d),
+                    e2e=dict(value=e2e_val, unit=METRIC, h2d_bytes_per_step=int(h2d), d2h_bytes_per_step=int(w * h * 3),
+                             note="Renderer -> scene lowering + upload + GPU BVH build + path pool alloc + render + rgb8 image to host"),
+                    gpu_launches=int(launches), clocks=clk,
+                    roofline=dict(bound="hbm", kernel="k_extend", achieved=ach, peak=peak, unit="GB/s", frac=ach / peak, traffic=None,
+                                  peak_source=which,
+                                  note="closest-hit traversal is issue/latency-bound, not HBM-bound (scene is L2-resident): see DESIGN.md and profiles/"),
+                    rays_per_s=dict(extend=rays_e / max(ext_ms / 1e3, 1e-12), shadow=rays_s / max(con_ms / 1e3, 1e-12),
+                                    total_step=(rays_e + rays_s) / step_time),
+                    kernel_ms_per_step=dict(extend=ext_ms / args.steps, shade=shd_ms / args.steps, connect=con_ms / args.steps,
+                                            device=dev_ms / args.steps, wall=1e3 * wall / args.steps),
+                    cpu_baseline=cpu)
+        print(json.dumps(line))
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="fractal_teapots")
+    ap.add_argument("--cpu-seconds", type=float, default=15.0, help="CPU work per cpu_baseline / reference sample")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -201,20 +201,22 @@ int orc_render_sample(void* fp, uint32_t iterations) {
     f->next_sample += iterations;
     return 0;
 }
-// Render only rows [y0,y1) of one batch without touching the Buffer (bounded timing sample).
-double orc_time_rows(void* fp, uint32_t y0, uint32_t y1, uint32_t iterations, uint64_t counters[4]) {
+// Render only rows y0, y0+stride, ... < y1 of one batch without touching the Buffer (bounded
+// timing sample of the CPU baseline).
+double orc_time_rows(void* fp, uint32_t y0, uint32_t y1, uint32_t stride, uint32_t iterations, uint64_t counters[4]) {
     OFilm* f = (OFilm*)fp;
     Renderer r = f->r;
     const int nt = r.threads > 0 ? r.threads : std::max(1, (int)std::thread::hardware_concurrency());
     std::vector<Counters> ctrs(nt);
-    std::atomic<uint32_t> next{y0};
+    if (stride == 0) stride = 1;
+    std::atomic<uint32_t> next{0};
     std::vector<Vec3> sink(nt);
     const auto t0 = std::chrono::steady_clock::now();
     std::vector<std::thread> pool;
     for (int t = 0; t < nt; t++)
         pool.emplace_back([&, t] {
             for (;;) {
-                const uint32_t y = next.fetch_add(1);
+                const uint32_t y = y0 + next.fetch_add(1) * stride;
                 if (y >= y1) break;
                 for (uint32_t x = 0; x < r.width; x++) sink[t] += r.get_color(x, y, 0, iterations, &ctrs[t], nullptr);
             }

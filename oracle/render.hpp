@@ -118,7 +118,7 @@ struct Renderer {
             if (light.kind == Light::Ambient) {
                 color += cmul(light.color, material.color());
             } else {
-                Color intensity; Vec3 wi; double dist;
+                Color intensity; Vec3 wi; double dist = 0.0;
                 light.illuminate(pos, rng, &intensity, &wi, &dist);
                 const Ray ray{pos, wi};
                 HitRecord h; const Object* o;
@@ -148,7 +148,7 @@ struct Renderer {
             if (light.kind == Light::Ambient) {
                 color += cmul(light.color, medium_color);
             } else {
-                Color intensity; Vec3 wi; double dist;
+                Color intensity; Vec3 wi; double dist = 0.0;
                 light.illuminate(pos, rng, &intensity, &wi, &dist);
                 const Ray ray{pos, wi};
                 HitRecord h; const Object* o;

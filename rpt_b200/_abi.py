@@ -93,6 +93,9 @@ class Stats(C.Structure):
         ("kernel_launches", C.c_uint64),
         ("device_ms", C.c_double),
         ("trace_ms", C.c_double),
+        ("extend_ms", C.c_double),
+        ("shade_ms", C.c_double),
+        ("connect_ms", C.c_double),
         ("photons_emitted", C.c_uint64),
         ("photons_surface", C.c_uint64),
         ("photons_volume", C.c_uint64),

@@ -74,5 +74,6 @@ struct rptx_film {
     double** d_batch_ptrs = nullptr;
     uint64_t next_sample = 0;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    cudaEvent_t evw[4] = {nullptr, nullptr, nullptr, nullptr};  // per-wave kernel boundaries
     rptx_stats stats = {};
 };

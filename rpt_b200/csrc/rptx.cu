@@ -131,12 +131,20 @@ float f32_upf(double x) {
     return f;
 }
 
+// Host->device copy ordered on the context's (non-blocking) stream.  A plain cudaMemcpy from
+// pageable memory may return before the DMA lands and does not order against that stream.
+cudaError_t copy_h2d(void* dst, const void* src, size_t bytes, cudaStream_t st) {
+    cudaError_t e = cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    return e;
+}
+
 template <class T>
-cudaError_t upload(T** dst, const std::vector<T>& src) {
+cudaError_t upload(T** dst, const std::vector<T>& src, cudaStream_t st) {
     *dst = nullptr;
     cudaError_t e = cudaMalloc((void**)dst, std::max<size_t>(src.size(), 1) * sizeof(T));
     if (e != cudaSuccess) return e;
-    if (!src.empty()) e = cudaMemcpy(*dst, src.data(), src.size() * sizeof(T), cudaMemcpyHostToDevice);
+    if (!src.empty()) e = copy_h2d(*dst, src.data(), src.size() * sizeof(T), st);
     return e;
 }
 
@@ -448,7 +456,7 @@ int rptx_scene_commit(rptx_scene* s) {
     for (auto& m : s->meshes) { m.node_base = node_total; node_total += std::max<uint32_t>((uint32_t)m.tris.size(), 1); }
 
     RawTri* d_raw = nullptr;
-    CK(upload(&d_raw, raw_all));
+    CK(upload(&d_raw, raw_all, st));
     s->d_raw = d_raw;
     BvhNode* d_nodes = nullptr;
     CK(cudaMalloc((void**)&d_nodes, sizeof(BvhNode) * node_total));
@@ -525,7 +533,7 @@ int rptx_scene_commit(rptx_scene* s) {
             boxes.push_back(pb);
         }
         PrimBox* d_boxes = nullptr; uint32_t* d_perm = nullptr;
-        CK(upload(&d_boxes, boxes));
+        CK(upload(&d_boxes, boxes, st));
         CK(cudaMalloc((void**)&d_perm, sizeof(uint32_t) * boxes.size()));
         const int rc = build_lbvh(d_boxes, (uint32_t)boxes.size(), wpad, wmn, wmx, d_nodes, d_perm, &s->tlas_root_ref, st, &ctx->launches);
         if (rc != 0) { cudaFree(d_boxes); cudaFree(d_perm); return ctx_fail(ctx, std::string("TLAS build: ") + cudaGetErrorString((cudaError_t)rc)); }
@@ -537,14 +545,14 @@ int rptx_scene_commit(rptx_scene* s) {
     }
     ordered.insert(ordered.end(), unbounded.begin(), unbounded.end());
     Instance* d_inst = nullptr;
-    CK(upload(&d_inst, ordered));
+    CK(upload(&d_inst, ordered, st));
     s->d_instances = d_inst;
 
     // 3. materials, lights, environment
     std::vector<Material> mats;
     for (const auto& o : s->objects) mats.push_back(to_material(o.material));
     Material* d_mats = nullptr;
-    CK(upload(&d_mats, mats));
+    CK(upload(&d_mats, mats, st));
     s->d_materials = d_mats;
     std::vector<Light> lights;
     s->n_shadow_lights = 0;
@@ -555,11 +563,11 @@ int rptx_scene_commit(rptx_scene* s) {
         lights.push_back(r);
     }
     Light* d_lights = nullptr;
-    CK(upload(&d_lights, lights));
+    CK(upload(&d_lights, lights, st));
     s->d_lights = d_lights;
     if (s->env_is_hdri) {
         double* d_env = nullptr;
-        CK(upload(&d_env, s->env_pixels));
+        CK(upload(&d_env, s->env_pixels, st));
         s->d_env = d_env;
     }
     CK(cudaStreamSynchronize(st));
@@ -588,13 +596,15 @@ static int film_alloc(rptx_film* f) {
     CK(cudaMalloc((void**)&f->q.next, sizeof(uint32_t) * ns)); f->owned.push_back(f->q.next);
     CK(cudaMalloc((void**)&f->q.counters, sizeof(uint32_t) * 8)); f->owned.push_back(f->q.counters);
     CK(cudaMalloc((void**)&f->q.stats, sizeof(unsigned long long) * 8)); f->owned.push_back(f->q.stats);
-    CK(cudaMemset(f->q.stats, 0, sizeof(unsigned long long) * 8));
+    CK(cudaMemsetAsync(f->q.stats, 0, sizeof(unsigned long long) * 8, ctx->stream));
     const size_t n3 = (size_t)p.n_pixels * 3;
     CK(cudaMalloc((void**)&f->d_batch_sum, sizeof(double) * n3)); f->owned.push_back(f->d_batch_sum);
     CK(cudaMalloc((void**)&f->d_film_sum, sizeof(double) * n3)); f->owned.push_back(f->d_film_sum);
-    CK(cudaMemset(f->d_film_sum, 0, sizeof(double) * n3));
-    CK(cudaMemset(f->d_batch_sum, 0, sizeof(double) * n3));
+    CK(cudaMemsetAsync(f->d_film_sum, 0, sizeof(double) * n3, ctx->stream));
+    CK(cudaMemsetAsync(f->d_batch_sum, 0, sizeof(double) * n3, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
     CK(cudaEventCreate(&f->ev0)); CK(cudaEventCreate(&f->ev1));
+    for (int k = 0; k < 4; k++) CK(cudaEventCreate(&f->evw[k]));
     return 0;
 }
 
@@ -638,6 +648,7 @@ void rptx_film_destroy(rptx_film* f) {
     if (f->d_batch_ptrs) cudaFree(f->d_batch_ptrs);
     if (f->ev0) cudaEventDestroy(f->ev0);
     if (f->ev1) cudaEventDestroy(f->ev1);
+    for (int k = 0; k < 4; k++) if (f->evw[k]) cudaEventDestroy(f->evw[k]);
     delete f;
 }
 
@@ -659,9 +670,13 @@ static int run_waves(rptx_film* f, const BatchParams& bp) {
     uint32_t active = std::min<uint64_t>(p.n_slots, (uint64_t)p.n_pixels * std::min(p.n_lanes, bp.n_local));
     while (active > 0) {
         const int blocks = (int)std::min<uint64_t>(persistent_blocks, grid_for(active, kBlock));
+        cudaEventRecord(f->evw[0], st);
         k_extend<<<blocks, kBlock, 0, st>>>(sc, p, q);
+        cudaEventRecord(f->evw[1], st);
         k_shade<MEDIUM><<<grid_for(active, kBlock), kBlock, 0, st>>>(sc, p, q, bp, md);
+        cudaEventRecord(f->evw[2], st);
         k_connect<MEDIUM><<<blocks, kBlock, 0, st>>>(sc, p, q, bp, f->cam);
+        cudaEventRecord(f->evw[3], st);
         k_wave_end<<<1, 1, 0, st>>>(q);
         ctx->launches += 4;
         f->stats.waves++;
@@ -669,6 +684,10 @@ static int run_waves(rptx_film* f, const BatchParams& bp) {
         CK(cudaMemcpyAsync(h_count, q.counters, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
         CK(cudaStreamSynchronize(st));
         active = *h_count;
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, f->evw[0], f->evw[1]) == cudaSuccess) f->stats.extend_ms += ms;
+        if (cudaEventElapsedTime(&ms, f->evw[1], f->evw[2]) == cudaSuccess) f->stats.shade_ms += ms;
+        if (cudaEventElapsedTime(&ms, f->evw[2], f->evw[3]) == cudaSuccess) f->stats.connect_ms += ms;
     }
     CK(cudaGetLastError());
     return 0;
@@ -688,6 +707,7 @@ int rptx_render_sample_trace(rptx_film* f, uint32_t iterations) {
     bp.shard_count = f->params.shard_count; bp.shard_index = f->params.shard_index;
     bp.n_local = iterations > bp.shard_index ? (iterations - bp.shard_index + bp.shard_count - 1) / bp.shard_count : 0;
     CK(cudaEventRecord(f->ev0, st));
+    f->stats.extend_ms = f->stats.shade_ms = f->stats.connect_ms = 0.0;
     PathPool& p = f->pool;
     const uint32_t full_lanes = p.n_lanes;
     p.n_lanes = std::max<uint32_t>(1, std::min(full_lanes, bp.n_local));
@@ -703,6 +723,7 @@ int rptx_render_sample_trace(rptx_film* f, uint32_t iterations) {
     float ms = 0.f;
     CK(cudaEventElapsedTime(&ms, f->ev0, f->ev1));
     f->stats.device_ms = ms;
+    f->stats.trace_ms = f->stats.extend_ms + f->stats.connect_ms;
     return 0;
 }
 
@@ -759,7 +780,7 @@ int rptx_film_variance(rptx_film* f, double* out) {
     if (nb == 0) { *out = NAN; return 0; }
     if (f->d_batch_ptrs) { cudaFree(f->d_batch_ptrs); f->d_batch_ptrs = nullptr; }
     CK(cudaMalloc((void**)&f->d_batch_ptrs, sizeof(double*) * nb));
-    CK(cudaMemcpy(f->d_batch_ptrs, f->batches.data(), sizeof(double*) * nb, cudaMemcpyHostToDevice));
+    CK(copy_h2d(f->d_batch_ptrs, f->batches.data(), sizeof(double*) * nb, ctx->stream));
     double* d_acc = nullptr;
     CK(cudaMalloc((void**)&d_acc, sizeof(double)));
     CK(cudaMemsetAsync(d_acc, 0, sizeof(double), ctx->stream));
@@ -796,6 +817,7 @@ int rptx_stats_get(const rptx_film* f, rptx_stats* out) {
     if (!f || !out) return 1;
     cudaSetDevice(f->ctx->device);
     unsigned long long st[8] = {0};
+    cudaStreamSynchronize(f->ctx->stream);
     cudaMemcpy(st, f->q.stats, sizeof(st), cudaMemcpyDeviceToHost);
     *out = f->stats;
     out->path_samples = st[0]; out->extend_rays = st[1]; out->shadow_rays = st[2];
@@ -843,8 +865,8 @@ int rptx_intersect_batch(rptx_scene* s, const double* o, const double* d, size_t
     CKC(cudaMalloc((void**)&d_obj, sizeof(uint32_t) * n));
     CKC(cudaMalloc((void**)&d_prim, sizeof(uint32_t) * n));
     CKC(cudaMalloc((void**)&d_inst, sizeof(uint32_t) * n));
-    CKC(cudaMemcpy(d_o, o, sizeof(double) * 3 * n, cudaMemcpyHostToDevice));
-    CKC(cudaMemcpy(d_d, d, sizeof(double) * 3 * n, cudaMemcpyHostToDevice));
+    CKC(copy_h2d(d_o, o, sizeof(double) * 3 * n, ctx->stream));
+    CKC(copy_h2d(d_d, d, sizeof(double) * 3 * n, ctx->stream));
     rc = rptx_intersect_batch_device(s, d_o, d_d, n, t_min, d_t, d_obj, d_prim, d_inst, d_n);
     if (rc == 0) {
         if (t) CKC(cudaMemcpy(t, d_t, sizeof(double) * n, cudaMemcpyDeviceToHost));

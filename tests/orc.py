@@ -44,7 +44,7 @@ def lib():
             "orc_render_begin": (P, [P, C.POINTER(A.CameraDesc), C.POINTER(A.Params), C.c_int]),
             "orc_film_destroy": (None, [P]),
             "orc_render_sample": (C.c_int, [P, C.c_uint32]),
-            "orc_time_rows": (C.c_double, [P, C.c_uint32, C.c_uint32, C.c_uint32, U64P]),
+            "orc_time_rows": (C.c_double, [P, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, U64P]),
             "orc_film_last_seconds": (C.c_double, [P]),
             "orc_film_counters": (C.c_int, [P, U64P]),
             "orc_film_image_rgb8": (C.c_int, [P, U8P]),
@@ -158,9 +158,9 @@ class OracleFilm:
     def seconds(self):
         return self.L.orc_film_last_seconds(self.h)
 
-    def time_rows(self, y0, y1, iterations):
+    def time_rows(self, y0, y1, stride, iterations):
         ctr = (C.c_uint64 * 4)()
-        sec = self.L.orc_time_rows(self.h, y0, y1, iterations, ctr)
+        sec = self.L.orc_time_rows(self.h, y0, y1, stride, iterations, ctr)
         return sec, tuple(ctr)
 
     def counters(self):

@@ -1,0 +1,137 @@
+"""-m gpu: image parity of the wavefront path tracer (rptx_render_sample) against the oracle.
+
+The reference is not reproducible (entropy-seeded RNG), so the oracle and the CUDA path share a
+counter-based stream per (pixel, sample).  With the same seed every sample must then agree to
+f64 rounding: the only differences are ulp-level (CUDA vs glibc libm, forward vs recursive
+accumulation order), which can flip a discontinuous decision (hit/miss, the 1e-12 shadow test,
+Russian roulette) for a vanishing fraction of samples.  Tolerances are written below."""
+import numpy as np
+import pytest
+
+import orc
+from rpt_b200 import scenes
+
+pytestmark = pytest.mark.gpu
+
+RTOL = 1e-9          # per-pixel relative agreement of the batch mean at equal seed
+# Fraction of pixels (<= 4 spp each) that must agree to RTOL.  It is not 1.0 because the
+# reference's own tests are epsilon-fragile: the NEE visibility test |t_hit - dist| < 1e-12
+# (src/renderer.rs:396) and t_min = 1e-12 self-intersection sit at the rounding noise of
+# coordinates ~500 (ulp 1.1e-13), so a 1-ulp libm difference in a bounce direction re-rolls
+# them for ~0.1 % of rays per bounce (measured: 0 of 4096 samples differ at max_bounces 0,
+# 5 at 1, 19 at 5).  A flipped sample is another valid outcome of the same estimator.
+MIN_MATCH = 0.97
+MAX_REL_RMSE = 2e-2  # whole-image relative RMSE bound at equal seed (flipped samples only)
+
+
+def _same_seed(scene, cam, defaults, w, h, spp, batches=1, **over):
+    r = scenes.make_renderer(scene, cam, defaults, width=w, height=h, num_samples=spp * batches, seed=11, **over)
+    film = r.begin()
+    osc = orc.OracleScene(scene)
+    of = orc.OracleFilm(osc, cam, r.params())
+    for _ in range(batches):
+        film.sample(spp)
+        of.sample(spp)
+    got, want = film.mean(), of.mean()
+    match = np.isclose(got, want, rtol=RTOL, atol=1e-12).all(axis=2).mean()
+    rel_rmse = np.sqrt(np.mean((got - want) ** 2)) / max(np.mean(want), 1e-300)
+    return film, of, match, rel_rmse
+
+
+def test_cornell_same_seed():
+    scene, cam, d = scenes.cornell()
+    film, of, match, rmse = _same_seed(scene, cam, d, 64, 64, 4)
+    assert match >= MIN_MATCH, match
+    assert rmse <= MAX_REL_RMSE, rmse
+    st, oc = film.stats(), of.counters()
+    assert st["path_samples"] == 64 * 64 * 4
+    assert abs(st["extend_rays"] - oc["extend_rays"]) <= 2e-3 * oc["extend_rays"]  # flipped samples change path length
+    assert abs(st["shadow_rays"] - oc["shadow_rays"]) <= 2e-3 * oc["shadow_rays"]
+
+
+def test_cornell_direct_only_is_exact():
+    """max_bounces 0: no libm call sits between the RNG and the epsilon tests -> every pixel equal."""
+    scene, cam, d = scenes.cornell()
+    film, of, match, rmse = _same_seed(scene, cam, d, 64, 64, 4, max_bounces=0)
+    assert match == 1.0, match
+    assert rmse < 1e-12
+
+
+def test_cornell_batches_image_and_variance():
+    scene, cam, d = scenes.cornell()
+    film, of, match, rmse = _same_seed(scene, cam, d, 48, 40, 2, batches=3, max_bounces=2)
+    assert match >= MIN_MATCH and rmse <= MAX_REL_RMSE
+    gi, oi = film.image().astype(int), of.image().astype(int)
+    assert np.mean(np.abs(gi - oi) <= 1) > 0.97  # box filter r=1 spreads a flipped sample over 9 pixels
+    gv, ov = film.variance(), of.variance()
+    assert abs(gv - ov) <= 2e-2 * abs(ov), (gv, ov)
+
+
+def test_film_image_and_variance_exact_when_samples_equal():
+    """Buffer::image / variance semantics (box filter, gamma, truncation, unbiased variance of
+    batch means) on a direct-only render where every sample equals the oracle's."""
+    scene, cam, d = scenes.cornell()
+    film, of, match, rmse = _same_seed(scene, cam, d, 40, 30, 2, batches=3, max_bounces=0)
+    assert match == 1.0
+    assert np.array_equal(film.image(), of.image())
+    gv, ov = film.variance(), of.variance()
+    assert abs(gv - ov) <= 1e-12 * abs(ov), (gv, ov)
+
+
+def test_lampshade_medium_same_seed():
+    scene, cam, d = scenes.lampshade("pathtrace")
+    film, of, match, rmse = _same_seed(scene, cam, d, 48, 48, 4)
+    assert match >= MIN_MATCH, match
+    assert rmse <= MAX_REL_RMSE, rmse
+
+
+def test_teapot_same_seed():
+    scene, cam, d = scenes.teapot()
+    film, of, match, rmse = _same_seed(scene, cam, d, 80, 45, 2, max_bounces=3)
+    assert match >= MIN_MATCH, match
+    assert rmse <= MAX_REL_RMSE, rmse
+
+
+def test_fractal_teapots_same_seed():
+    scene, cam, d = scenes.fractal_teapots()
+    film, of, match, rmse = _same_seed(scene, cam, d, 80, 45, 1, max_bounces=2)
+    assert match >= MIN_MATCH, match
+    assert rmse <= MAX_REL_RMSE, rmse
+
+
+def test_shards_sum_to_whole():
+    """Multi-GPU sample sharding: two shards' batch sums add up to the unsharded batch."""
+    import ctypes as C
+
+    scene, cam, d = scenes.cornell()
+    w, h, spp = 32, 32, 6
+    whole = scenes.make_renderer(scene, cam, d, width=w, height=h, num_samples=spp, seed=3).begin()
+    whole.sample(spp)
+    parts = []
+    for i in range(2):
+        f = scenes.make_renderer(scene, cam, d, width=w, height=h, num_samples=spp, seed=3).shard(2, i).begin()
+        f.sample_trace(spp)
+        parts.append(f)
+    # emulate the all-reduce on the host: copy sums, add, compare to the whole batch mean * spp
+    import torch
+
+    sums = []
+    for f in parts:
+        class _W:  # __cuda_array_interface__ view of the film's batch-sum buffer
+            __cuda_array_interface__ = dict(shape=(h, w, 3), typestr="<f8", data=(f.batch_sum_ptr(), False), version=3)
+        sums.append(torch.as_tensor(_W(), device="cuda").cpu().numpy().copy())
+    total = (sums[0] + sums[1]) / spp
+    assert np.allclose(total, whole.mean(), rtol=1e-12, atol=1e-14)
+
+
+def test_render_api_and_errors():
+    from rpt_b200 import Filter, Renderer, RptxError
+
+    scene, cam, d = scenes.cornell()
+    img = Renderer.new(scene, cam).width(40).height(30).filter(Filter.Box(1)).max_bounces(1).num_samples(2).render()
+    assert img.shape == (30, 40, 3) and img.dtype == np.uint8 and img.max() > 0
+    seen = []
+    Renderer(scene, cam).width(16).height(16).num_samples(5).iterative_render(2, lambda it, buf: seen.append((it, buf.image().shape)))
+    assert [s[0] for s in seen] == [2, 4, 5]
+    with pytest.raises(RptxError):
+        Renderer(scene, cam).width(0).height(16).render()
