@@ -36,6 +36,9 @@ METRIC = "Mpath-samples/s"
 EXTEND_BYTES_PER_RAY = 4 + 48 + 8 + 4 + 24
 
 
+_OVERRIDES = {}
+
+
 def workload(name):
     from rpt_b200 import scenes
 
@@ -52,6 +55,9 @@ def workload(name):
         scene, cam, d = scenes.lampshade("pathtrace")
     else:
         raise SystemExit(f"unknown workload {name}")
+    for k, v in _OVERRIDES.items():
+        if v:
+            d[k] = v
     return scene, cam, d
 
 
@@ -287,7 +293,11 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="fractal_teapots")
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="CPU work per cpu_baseline / reference sample")
+    ap.add_argument("--width", type=int, default=0, help="override (profiling runs only)")
+    ap.add_argument("--height", type=int, default=0)
+    ap.add_argument("--spp", type=int, default=0)
     args = ap.parse_args()
+    _OVERRIDES.update(width=args.width, height=args.height, num_samples=args.spp)
     if args.impl == "reference":
         run_reference(args)
     else:
