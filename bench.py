@@ -208,7 +208,7 @@ def run_ours(args):
     if rank == 0:
         clocks.start()
     barrier()
-    dev_ms = ext_ms = con_ms = shd_ms = 0.0
+    dev_ms = ext_ms = con_ms = shd_ms = sdw_ms = 0.0
     rays_e = rays_s = 0
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t0 = time.perf_counter()
@@ -216,7 +216,7 @@ def run_ours(args):
         before = film.stats()
         st = step()
         dev_ms += st["device_ms"]  # CUDA events on the library's own stream around the traced batch
-        ext_ms += st["extend_ms"]; con_ms += st["connect_ms"]; shd_ms += st["shade_ms"]
+        ext_ms += st["extend_ms"]; con_ms += st["connect_ms"]; shd_ms += st["shade_ms"]; sdw_ms += st["shadow_ms"]
         rays_e += st["extend_rays"] - before["extend_rays"]
         rays_s += st["shadow_rays"] - before["shadow_rays"]
     barrier()
@@ -275,9 +275,9 @@ def run_ours(args):
                     roofline=dict(bound="hbm", kernel="k_extend", achieved=ach, peak=peak, unit="GB/s", frac=ach / peak, traffic=None,
                                   peak_source=which,
                                   note="closest-hit traversal is issue/latency-bound, not HBM-bound (scene is L2-resident): see DESIGN.md and profiles/"),
-                    rays_per_s=dict(extend=rays_e / max(ext_ms / 1e3, 1e-12), shadow=rays_s / max(con_ms / 1e3, 1e-12),
+                    rays_per_s=dict(extend=rays_e / max(ext_ms / 1e3, 1e-12), shadow=rays_s / max(sdw_ms / 1e3, 1e-12),
                                     total_step=(rays_e + rays_s) / step_time),
-                    kernel_ms_per_step=dict(extend=ext_ms / args.steps, shade=shd_ms / args.steps, connect=con_ms / args.steps,
+                    kernel_ms_per_step=dict(extend=ext_ms / args.steps, shade=shd_ms / args.steps, shadow=sdw_ms / args.steps, connect=con_ms / args.steps,
                                             device=dev_ms / args.steps, wall=1e3 * wall / args.steps),
                     cpu_baseline=cpu)
         print(json.dumps(line))

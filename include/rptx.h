@@ -134,8 +134,8 @@ typedef struct rptx_stats {
     uint64_t waves;            /* wavefront iterations */
     uint64_t kernel_launches;  /* kernels of this library launched */
     double   device_ms;        /* CUDA-event time of the last render_sample call */
-    double   trace_ms;         /* of which: extend + connect kernels (all ray queries) */
-    double   extend_ms, shade_ms, connect_ms; /* per-kernel CUDA-event sums of the last call */
+    double   trace_ms;         /* of which: extend + shadow kernels (all ray queries) */
+    double   extend_ms, shade_ms, connect_ms, shadow_ms; /* per-kernel CUDA-event sums of the last call */
     uint64_t photons_emitted, photons_surface, photons_volume;
     uint64_t gather_queries;
 } rptx_stats;

@@ -96,6 +96,7 @@ class Stats(C.Structure):
         ("extend_ms", C.c_double),
         ("shade_ms", C.c_double),
         ("connect_ms", C.c_double),
+        ("shadow_ms", C.c_double),
         ("photons_emitted", C.c_uint64),
         ("photons_surface", C.c_uint64),
         ("photons_volume", C.c_uint64),

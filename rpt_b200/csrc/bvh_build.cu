@@ -102,12 +102,12 @@ __global__ void k_refit(const PrimBox* __restrict__ boxes, const uint64_t* __res
 
 __device__ __forceinline__ void child_out(int c, const PrimBox* __restrict__ boxes, const uint64_t* __restrict__ keys,
                                           const PrimBox* __restrict__ ibox, const int* __restrict__ first,
-                                          const int* __restrict__ last, float pad, float* mn, float* mx, int* ref) {
+                                          const int* __restrict__ last, float pad, int leaf_max, float* mn, float* mx, int* ref) {
     PrimBox b;
     if (c >= 0) {
         b = ibox[c];
         const int sz = last[c] - first[c] + 1;
-        *ref = (sz <= kLeafMax) ? make_leaf_ref((uint32_t)first[c], (uint32_t)sz) : c;
+        *ref = (sz <= leaf_max) ? make_leaf_ref((uint32_t)first[c], (uint32_t)sz) : c;
     } else {
         b = boxes[(uint32_t)(keys[~c] & 0xffffffffu)];
         *ref = make_leaf_ref((uint32_t)(~c), 1u);
@@ -118,20 +118,20 @@ __device__ __forceinline__ void child_out(int c, const PrimBox* __restrict__ box
 
 __global__ void k_emit(const PrimBox* __restrict__ boxes, const uint64_t* __restrict__ keys, int n, const int* __restrict__ left,
                        const int* __restrict__ right, const int* __restrict__ first, const int* __restrict__ last,
-                       const PrimBox* __restrict__ ibox, float pad, BvhNode* __restrict__ nodes, uint32_t* __restrict__ perm) {
+                       const PrimBox* __restrict__ ibox, float pad, int leaf_max, BvhNode* __restrict__ nodes, uint32_t* __restrict__ perm) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) perm[i] = (uint32_t)(keys[i] & 0xffffffffu);
     if (i >= n - 1) return;
     BvhNode nd;
-    child_out(left[i], boxes, keys, ibox, first, last, pad, nd.lmin, nd.lmax, &nd.left);
-    child_out(right[i], boxes, keys, ibox, first, last, pad, nd.rmin, nd.rmax, &nd.right);
+    child_out(left[i], boxes, keys, ibox, first, last, pad, leaf_max, nd.lmin, nd.lmax, &nd.left);
+    child_out(right[i], boxes, keys, ibox, first, last, pad, leaf_max, nd.rmin, nd.rmax, &nd.right);
     nd.pad0 = 0; nd.pad1 = 0;
     nodes[i] = nd;
 }
 
 }  // namespace
 
-int build_lbvh(const PrimBox* d_boxes, uint32_t n, float pad, const double cmin[3], const double cmax[3], BvhNode* d_nodes,
+int build_lbvh(const PrimBox* d_boxes, uint32_t n, float pad, int leaf_max, const double cmin[3], const double cmax[3], BvhNode* d_nodes,
                uint32_t* d_perm, int* root_ref, cudaStream_t stream, uint64_t* launches) {
     if (n == 0) { *root_ref = 0; return 0; }
     cudaError_t e;
@@ -172,11 +172,11 @@ int build_lbvh(const PrimBox* d_boxes, uint32_t n, float pad, const double cmin[
             k_refit<<<B, T, 0, stream>>>(d_boxes, keys_out, (int)n, left, right, parent_i, parent_l, flags, ibox);
             (*launches) += 2;
         }
-        k_emit<<<B, T, 0, stream>>>(d_boxes, keys_out, (int)n, left, right, first, last, ibox, pad, d_nodes, d_perm);
+        k_emit<<<B, T, 0, stream>>>(d_boxes, keys_out, (int)n, left, right, first, last, ibox, pad, leaf_max, d_nodes, d_perm);
         (*launches)++;
         RPTX_CK(cudaGetLastError());
         RPTX_CK(cudaStreamSynchronize(stream));
-        *root_ref = (n <= (uint32_t)kLeafMax) ? make_leaf_ref(0u, n) : 0;
+        *root_ref = (n <= (uint32_t)leaf_max) ? make_leaf_ref(0u, n) : 0;
     }
 fail:
 #undef RPTX_CK

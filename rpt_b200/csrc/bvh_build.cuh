@@ -16,8 +16,8 @@ struct LbvhScratch;  // opaque
 
 // d_boxes: n primitive boxes (device).  d_nodes: room for max(n-1,1) nodes (device).
 // d_perm: n entries (device), perm[k] = original index of the k-th primitive in leaf order.
-// pad: absolute outward padding baked into every child box.  Returns cudaError_t as int.
-int build_lbvh(const PrimBox* d_boxes, uint32_t n, float pad, const double cmin[3], const double cmax[3],
+// pad: absolute outward padding baked into every child box.  leaf_max: primitives per leaf (<= 8).  Returns cudaError_t as int.
+int build_lbvh(const PrimBox* d_boxes, uint32_t n, float pad, int leaf_max, const double cmin[3], const double cmax[3],
                BvhNode* d_nodes, uint32_t* d_perm, int* root_ref, cudaStream_t stream, uint64_t* launches);
 
 }  // namespace rptx

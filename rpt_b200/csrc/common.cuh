@@ -83,6 +83,12 @@ struct __align__(16) TriRec {
 struct __align__(16) TriNormals {  // fetched only for the winning hit
     double n1[3], n2[3], n3[3];
 };
+// f32 copy for the conservative pre-test in front of the exact f64 test: 3 x float4
+struct __align__(16) TriF {
+    float v0[3], pad0;
+    float e1[3], pad1;
+    float e2[3], pad2;
+};
 struct RawTri {  // upload format
     double v[9], n[9];
 };
@@ -134,6 +140,7 @@ struct SceneDev {
     const BvhNode* nodes;       // node pool: TLAS first, then BLASes
     const Instance* instances;  // sorted in TLAS leaf order, then unbounded ones
     const TriRec* tris;         // per mesh, BLAS leaf order
+    const TriF* trif;           // same order, f32 pre-test records
     const TriNormals* tri_normals;
     const uint32_t* tri_orig;   // original triangle index within its mesh
     const Material* materials;  // per object

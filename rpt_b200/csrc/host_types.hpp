@@ -49,6 +49,7 @@ struct rptx_scene {
     const rptx::BvhNode* d_nodes = nullptr;
     const rptx::Instance* d_instances = nullptr;
     const rptx::TriRec* d_tris = nullptr;
+    const rptx::TriF* d_trif = nullptr;
     const rptx::TriNormals* d_tri_normals = nullptr;
     const uint32_t* d_tri_orig = nullptr;
     const rptx::Material* d_materials = nullptr;
@@ -74,6 +75,6 @@ struct rptx_film {
     double** d_batch_ptrs = nullptr;
     uint64_t next_sample = 0;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
-    cudaEvent_t evw[4] = {nullptr, nullptr, nullptr, nullptr};  // per-wave kernel boundaries
+    cudaEvent_t evw[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};  // per-wave kernel boundaries
     rptx_stats stats = {};
 };

@@ -209,41 +209,59 @@ __global__ void __launch_bounds__(kBlock) k_shade(const __grid_constant__ SceneD
     p.rng[slot] = rng.state;
 }
 
-// connect: shadow rays of the vertex (closest hit must sit within 1e-12 of the light sample,
-// src/renderer.rs:348,396), then finalise the vertex; finished paths are folded, added to the
-// slot's lane film and the slot regenerates its next sample.
-template <bool MEDIUM>
-__global__ void __launch_bounds__(kBlock) k_connect(const __grid_constant__ SceneDev sc, PathPool p, Queues q, BatchParams bp,
-                                                     Camera cam) {
+// shadow: NEE visibility rays of the vertex.  The reference asks for the CLOSEST hit to sit within
+// 1e-12 of the light sample (src/renderer.rs:348,396); the search is bounded to dist + 2e-12 and
+// stops at the first hit below dist - 2e-12 (the test can only fail then).  Passing candidates
+// are added to the vertex's direct light in light order.
+__global__ void __launch_bounds__(kBlock) k_shadow(const __grid_constant__ SceneDev sc, PathPool p, Queues q) {
     const uint32_t count = q.counters[0];
-    unsigned long long my_shadow = 0, my_started = 0;
+    unsigned long long my_shadow = 0;
     for (;;) {
         uint32_t base = 0;
         if (lane_id() == 0) base = atomicAdd(&q.counters[3], 32u);
         base = __shfl_sync(0xffffffffu, base, 0);
         if (base >= count) break;
         const uint32_t i = base + lane_id();
+        if (i >= count) continue;
+        const uint32_t slot = q.cur[i];
+        if (!(p.flags[slot] & kFlagHasShadow)) continue;
+        d3 add = mk3(0, 0, 0);
+        bool any = false;
+        RayD ray;
+        ray.o = mk3(p.ox[slot], p.oy[slot], p.oz[slot]);
+        for (uint32_t k = 0; k < p.n_shadow; k++) {
+            const size_t off = (size_t)k * p.n_slots + slot;
+            ray.d = mk3(p.sdx[off], p.sdy[off], p.sdz[off]);
+            const double dist = p.sdist[off];
+            Hit h;
+            h.t = dist + 2e-12;
+            closest_hit<true>(sc, ray, kEpsilon, dist - 2e-12, h);
+            my_shadow++;
+            if (h.inst != kNoHit && fabs(h.t - dist) < kEpsilon) {
+                // direct += contribution, in light order like the reference's loop
+                if (!any) { add = mk3(p.dirx[slot], p.diry[slot], p.dirz[slot]); any = true; }
+                add = add + mk3(p.scx[off], p.scy[off], p.scz[off]);
+            }
+        }
+        if (any) { p.dirx[slot] = add.x; p.diry[slot] = add.y; p.dirz[slot] = add.z; }
+    }
+    if (my_shadow) atomicAdd(&q.stats[2], my_shadow);
+}
+
+// connect: finalise the vertex; finished paths are folded (surface mode), added to the slot's
+// lane film and the slot regenerates its next sample; survivors are compacted into the next queue.
+template <bool MEDIUM>
+__global__ void __launch_bounds__(kBlock) k_connect(PathPool p, Queues q, BatchParams bp, Camera cam) {
+    const uint32_t count = q.counters[0];
+    unsigned long long my_started = 0;
+    {
+        const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
         bool alive = false;
         uint32_t slot = 0;
         if (i < count) {
             slot = q.cur[i];
             const uint32_t flags = p.flags[slot];
-            d3 direct = mk3(p.dirx[slot], p.diry[slot], p.dirz[slot]);
-            if (flags & kFlagHasShadow) {
-                RayD ray;
-                ray.o = mk3(p.ox[slot], p.oy[slot], p.oz[slot]);
-                for (uint32_t k = 0; k < p.n_shadow; k++) {
-                    const size_t off = (size_t)k * p.n_slots + slot;
-                    ray.d = mk3(p.sdx[off], p.sdy[off], p.sdz[off]);
-                    const double dist = p.sdist[off];
-                    Hit h;
-                    h.t = dist + 2e-12;
-                    closest_hit<true>(sc, ray, kEpsilon, dist - 2e-12, h);
-                    my_shadow++;
-                    if (h.inst != kNoHit && fabs(h.t - dist) < kEpsilon)
-                        direct = direct + mk3(p.scx[off], p.scy[off], p.scz[off]);
-                }
-            }
+            const d3 direct = mk3(p.dirx[slot], p.diry[slot], p.dirz[slot]);
             const uint32_t depth = p.depth[slot];
             bool finished = (flags & kFlagTerminate) != 0;
             d3 L;
@@ -288,7 +306,6 @@ __global__ void __launch_bounds__(kBlock) k_connect(const __grid_constant__ Scen
         }
         queue_push(q.next, &q.counters[1], alive, slot);
     }
-    if (my_shadow) atomicAdd(&q.stats[2], my_shadow);
     if (my_started) atomicAdd(&q.stats[0], my_started);
 }
 
@@ -412,7 +429,7 @@ __global__ void k_tri_boxes(const RawTri* __restrict__ raw, uint32_t n, PrimBox*
 
 // per-triangle constants of Triangle::intersect, same f64 operations as src/shape/mesh.rs:51-66
 __global__ void k_tri_prepare(const RawTri* __restrict__ raw, const uint32_t* __restrict__ perm, uint32_t n, TriRec* __restrict__ out,
-                              TriNormals* __restrict__ nrm, uint32_t* __restrict__ orig) {
+                              TriF* __restrict__ outf, TriNormals* __restrict__ nrm, uint32_t* __restrict__ orig) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const uint32_t src = perm[i];
@@ -428,6 +445,11 @@ __global__ void k_tri_prepare(const RawTri* __restrict__ raw, const uint32_t* __
     r.d00 = dot(d0, d0); r.d01 = dot(d0, d1); r.d11 = dot(d1, d1);
     r.denom = r.d00 * r.d11 - r.d01 * r.d01;
     out[i] = r;
+    TriF tf;
+    tf.v0[0] = (float)v1.x; tf.v0[1] = (float)v1.y; tf.v0[2] = (float)v1.z; tf.pad0 = 0.f;
+    tf.e1[0] = (float)d0.x; tf.e1[1] = (float)d0.y; tf.e1[2] = (float)d0.z; tf.pad1 = 0.f;
+    tf.e2[0] = (float)d1.x; tf.e2[1] = (float)d1.y; tf.e2[2] = (float)d1.z; tf.pad2 = 0.f;
+    outf[i] = tf;
     TriNormals tn;
     for (int k = 0; k < 3; k++) { tn.n1[k] = t.n[k]; tn.n2[k] = t.n[3 + k]; tn.n3[k] = t.n[6 + k]; }
     nrm[i] = tn;

@@ -152,7 +152,7 @@ int grid_for(size_t n, int block) { return (int)std::max<size_t>(1, (n + block -
 
 void free_scene_device(rptx_scene* s) {
     cudaFree((void*)s->d_nodes); cudaFree((void*)s->d_instances); cudaFree((void*)s->d_tris);
-    cudaFree((void*)s->d_tri_normals); cudaFree((void*)s->d_tri_orig); cudaFree((void*)s->d_materials);
+    cudaFree((void*)s->d_tri_normals); cudaFree((void*)s->d_trif); s->d_trif = nullptr; cudaFree((void*)s->d_tri_orig); cudaFree((void*)s->d_materials);
     cudaFree((void*)s->d_lights); cudaFree((void*)s->d_raw); cudaFree((void*)s->d_env);
     s->d_nodes = nullptr; s->d_instances = nullptr; s->d_tris = nullptr; s->d_tri_normals = nullptr;
     s->d_tri_orig = nullptr; s->d_materials = nullptr; s->d_lights = nullptr; s->d_raw = nullptr; s->d_env = nullptr;
@@ -289,7 +289,7 @@ MediumDev medium_dev(const rptx_scene* s) {
 SceneDev scene_dev(const rptx_scene* s) {
     SceneDev sc;
     std::memset(&sc, 0, sizeof(sc));
-    sc.nodes = s->d_nodes; sc.instances = s->d_instances; sc.tris = s->d_tris; sc.tri_normals = s->d_tri_normals;
+    sc.nodes = s->d_nodes; sc.instances = s->d_instances; sc.tris = s->d_tris; sc.trif = s->d_trif; sc.tri_normals = s->d_tri_normals;
     sc.tri_orig = s->d_tri_orig; sc.materials = s->d_materials; sc.lights = s->d_lights; sc.light_tris = s->d_raw;
     sc.tlas_root_ref = s->tlas_root_ref;
     sc.n_bounded = s->n_bounded; sc.n_unbounded = s->n_unbounded;
@@ -462,7 +462,9 @@ int rptx_scene_commit(rptx_scene* s) {
     CK(cudaMalloc((void**)&d_nodes, sizeof(BvhNode) * node_total));
     CK(cudaMemsetAsync(d_nodes, 0, sizeof(BvhNode) * node_total, st));
     s->d_nodes = d_nodes;
-    TriRec* d_tris = nullptr; TriNormals* d_tn = nullptr; uint32_t* d_orig = nullptr;
+    TriRec* d_tris = nullptr; TriNormals* d_tn = nullptr; uint32_t* d_orig = nullptr; TriF* d_trif = nullptr;
+    CK(cudaMalloc((void**)&d_trif, sizeof(TriF) * std::max<uint32_t>(tri_total, 1)));
+    s->d_trif = d_trif;
     CK(cudaMalloc((void**)&d_tris, sizeof(TriRec) * std::max<uint32_t>(tri_total, 1)));
     CK(cudaMalloc((void**)&d_tn, sizeof(TriNormals) * std::max<uint32_t>(tri_total, 1)));
     CK(cudaMalloc((void**)&d_orig, sizeof(uint32_t) * std::max<uint32_t>(tri_total, 1)));
@@ -483,9 +485,9 @@ int rptx_scene_commit(rptx_scene* s) {
         double e_abs = 0.0;
         for (int k = 0; k < 3; k++) e_abs = std::fmax(e_abs, std::fmax(std::fabs(m.bmin[k]), std::fabs(m.bmax[k])));
         m.pad = f32_upf(std::fmax(e_abs, 1e-30) * (1.0 / 2097152.0));  // E * 2^-21
-        const int rc = build_lbvh(d_boxes, n, m.pad, m.bmin, m.bmax, d_nodes + m.node_base, d_perm, &m.root_ref, st, &ctx->launches);
+        const int rc = build_lbvh(d_boxes, n, m.pad, kLeafMax, m.bmin, m.bmax, d_nodes + m.node_base, d_perm, &m.root_ref, st, &ctx->launches);
         if (rc != 0) { cudaFree(d_boxes); cudaFree(d_perm); return ctx_fail(ctx, std::string("BLAS build: ") + cudaGetErrorString((cudaError_t)rc)); }
-        k_tri_prepare<<<grid_for(n, 128), 128, 0, st>>>(d_raw + m.raw_base, d_perm, n, d_tris + m.tri_base, d_tn + m.tri_base,
+        k_tri_prepare<<<grid_for(n, 128), 128, 0, st>>>(d_raw + m.raw_base, d_perm, n, d_tris + m.tri_base, d_trif + m.tri_base, d_tn + m.tri_base,
                                                          d_orig + m.tri_base);
         ctx->launches++;
         CK(cudaStreamSynchronize(st));
@@ -535,7 +537,7 @@ int rptx_scene_commit(rptx_scene* s) {
         PrimBox* d_boxes = nullptr; uint32_t* d_perm = nullptr;
         CK(upload(&d_boxes, boxes, st));
         CK(cudaMalloc((void**)&d_perm, sizeof(uint32_t) * boxes.size()));
-        const int rc = build_lbvh(d_boxes, (uint32_t)boxes.size(), wpad, wmn, wmx, d_nodes, d_perm, &s->tlas_root_ref, st, &ctx->launches);
+        const int rc = build_lbvh(d_boxes, (uint32_t)boxes.size(), wpad, 1, wmn, wmx, d_nodes, d_perm, &s->tlas_root_ref, st, &ctx->launches);
         if (rc != 0) { cudaFree(d_boxes); cudaFree(d_perm); return ctx_fail(ctx, std::string("TLAS build: ") + cudaGetErrorString((cudaError_t)rc)); }
         std::vector<uint32_t> perm(boxes.size());
         CK(cudaMemcpy(perm.data(), d_perm, sizeof(uint32_t) * perm.size(), cudaMemcpyDeviceToHost));
@@ -604,7 +606,7 @@ static int film_alloc(rptx_film* f) {
     CK(cudaMemsetAsync(f->d_batch_sum, 0, sizeof(double) * n3, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
     CK(cudaEventCreate(&f->ev0)); CK(cudaEventCreate(&f->ev1));
-    for (int k = 0; k < 4; k++) CK(cudaEventCreate(&f->evw[k]));
+    for (int k = 0; k < 5; k++) CK(cudaEventCreate(&f->evw[k]));
     return 0;
 }
 
@@ -648,7 +650,7 @@ void rptx_film_destroy(rptx_film* f) {
     if (f->d_batch_ptrs) cudaFree(f->d_batch_ptrs);
     if (f->ev0) cudaEventDestroy(f->ev0);
     if (f->ev1) cudaEventDestroy(f->ev1);
-    for (int k = 0; k < 4; k++) if (f->evw[k]) cudaEventDestroy(f->evw[k]);
+    for (int k = 0; k < 5; k++) if (f->evw[k]) cudaEventDestroy(f->evw[k]);
     delete f;
 }
 
@@ -675,10 +677,12 @@ static int run_waves(rptx_film* f, const BatchParams& bp) {
         cudaEventRecord(f->evw[1], st);
         k_shade<MEDIUM><<<grid_for(active, kBlock), kBlock, 0, st>>>(sc, p, q, bp, md);
         cudaEventRecord(f->evw[2], st);
-        k_connect<MEDIUM><<<blocks, kBlock, 0, st>>>(sc, p, q, bp, f->cam);
+        if (p.n_shadow) k_shadow<<<blocks, kBlock, 0, st>>>(sc, p, q);
         cudaEventRecord(f->evw[3], st);
+        k_connect<MEDIUM><<<grid_for(active, kBlock), kBlock, 0, st>>>(p, q, bp, f->cam);
+        cudaEventRecord(f->evw[4], st);
         k_wave_end<<<1, 1, 0, st>>>(q);
-        ctx->launches += 4;
+        ctx->launches += p.n_shadow ? 5 : 4;
         f->stats.waves++;
         std::swap(q.cur, q.next);
         CK(cudaMemcpyAsync(h_count, q.counters, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
@@ -687,7 +691,8 @@ static int run_waves(rptx_film* f, const BatchParams& bp) {
         float ms = 0.f;
         if (cudaEventElapsedTime(&ms, f->evw[0], f->evw[1]) == cudaSuccess) f->stats.extend_ms += ms;
         if (cudaEventElapsedTime(&ms, f->evw[1], f->evw[2]) == cudaSuccess) f->stats.shade_ms += ms;
-        if (cudaEventElapsedTime(&ms, f->evw[2], f->evw[3]) == cudaSuccess) f->stats.connect_ms += ms;
+        if (cudaEventElapsedTime(&ms, f->evw[2], f->evw[3]) == cudaSuccess) f->stats.shadow_ms += ms;
+        if (cudaEventElapsedTime(&ms, f->evw[3], f->evw[4]) == cudaSuccess) f->stats.connect_ms += ms;
     }
     CK(cudaGetLastError());
     return 0;
@@ -707,7 +712,7 @@ int rptx_render_sample_trace(rptx_film* f, uint32_t iterations) {
     bp.shard_count = f->params.shard_count; bp.shard_index = f->params.shard_index;
     bp.n_local = iterations > bp.shard_index ? (iterations - bp.shard_index + bp.shard_count - 1) / bp.shard_count : 0;
     CK(cudaEventRecord(f->ev0, st));
-    f->stats.extend_ms = f->stats.shade_ms = f->stats.connect_ms = 0.0;
+    f->stats.extend_ms = f->stats.shade_ms = f->stats.connect_ms = f->stats.shadow_ms = 0.0;
     PathPool& p = f->pool;
     const uint32_t full_lanes = p.n_lanes;
     p.n_lanes = std::max<uint32_t>(1, std::min(full_lanes, bp.n_local));
@@ -723,7 +728,7 @@ int rptx_render_sample_trace(rptx_film* f, uint32_t iterations) {
     float ms = 0.f;
     CK(cudaEventElapsedTime(&ms, f->ev0, f->ev1));
     f->stats.device_ms = ms;
-    f->stats.trace_ms = f->stats.extend_ms + f->stats.connect_ms;
+    f->stats.trace_ms = f->stats.extend_ms + f->stats.shadow_ms;
     return 0;
 }
 

@@ -63,44 +63,6 @@ RPTX_D void clip_f64(const double* bmin, const double* bmax, d3 o, d3 d, double*
     *t1 = fmin(fmin(fmax(ax, bx), fmax(ay, by)), fmax(az, bz));
 }
 
-// Generic BVH2 traversal.  leaf(first, count, tbest) tests primitives [first, first+count),
-// may lower tbest, returns true to stop the whole traversal.
-template <class LeafFn>
-RPTX_D bool bvh_traverse(const BvhNode* __restrict__ nodes, int root_ref, const RayF& r, float& tbest, LeafFn&& leaf) {
-    int stack[kStackSize];
-    float stack_t[kStackSize];
-    int sp = 0;
-    int cur = root_ref;
-    for (;;) {
-        if (cur < 0) {
-            const uint32_t code = (uint32_t)(~cur);
-            if (leaf(code >> 3, (code & 7u) + 1u, tbest)) return true;
-        } else {
-            const float4* np = reinterpret_cast<const float4*>(nodes + cur);
-            const float4 a = __ldg(np), b = __ldg(np + 1), c = __ldg(np + 2), d = __ldg(np + 3);
-            float tl, tr;
-            const bool hl = slab_f32(a.x, a.y, a.z, b.x, b.y, b.z, r, tbest, &tl);
-            const bool hr = slab_f32(c.x, c.y, c.z, d.x, d.y, d.z, r, tbest, &tr);
-            const int left = __float_as_int(a.w), right = __float_as_int(c.w);
-            if (hl && hr) {
-                const bool lf = tl <= tr;
-                stack[sp] = lf ? right : left;
-                stack_t[sp] = lf ? tr : tl;
-                sp++;
-                cur = lf ? left : right;
-                continue;
-            } else if (hl) { cur = left; continue; }
-            else if (hr) { cur = right; continue; }
-        }
-        // pop
-        for (;;) {
-            if (sp == 0) return false;
-            sp--;
-            if (stack_t[sp] <= tbest) { cur = stack[sp]; break; }
-        }
-    }
-}
-
 RPTX_D bool accept(const Hit& h, double t, uint32_t obj) { return t < h.t || (t == h.t && obj < h.obj); }
 
 // Triangle::intersect, src/shape/mesh.rs:50-83, on the prepared record
@@ -183,92 +145,197 @@ RPTX_D bool plane_test(const Instance& in, d3 o, d3 d, double t_min, double* t) 
     return false;
 }
 
-// One instance against the world ray.  SHADOW: stop as soon as a hit below t_stop is accepted.
-template <bool SHADOW>
-RPTX_D bool intersect_instance(const SceneDev& sc, uint32_t idx, const RayD& ray, double t_min, double t_stop, Hit& hit) {
-    const Instance* __restrict__ in = sc.instances + idx;
-    const int kind = in->kind;
-    const uint32_t obj = in->object_id;
-    d3 lo = ray.o, ld = ray.d;
-    if (in->has_transform) {
-        lo = xform_point(in->inv, ray.o);
-        ld = xform_dir(in->inv, ray.d);
-    }
-    if (kind == kMesh) {
-        const TriRec* __restrict__ tris = sc.tris + in->tri_base;
-        bool stop = false;
-        auto leaf = [&](uint32_t first, uint32_t count, float& tbest) -> bool {
-            for (uint32_t i = first; i < first + count; i++) {
-                TriRec tr;
-                load_tri(tris + i, &tr);
-                double t, v, w;
-                const bool eq_ok = obj < hit.obj;
-                if (tri_test(tr, lo, ld, t_min, hit.t, eq_ok, &t, &v, &w)) {
-                    hit.t = t; hit.inst = idx; hit.obj = obj; hit.prim = i; hit.v = v; hit.w = w;
-                    if (SHADOW && t < t_stop) { stop = true; return true; }
-                }
-            }
-            return false;
-        };
-        if (in->root_ref < 0) {  // tiny mesh: no BLAS nodes
-            float dummy = 0.f;
-            const uint32_t code = (uint32_t)(~in->root_ref);
-            leaf(code >> 3, (code & 7u) + 1u, dummy);
-            return stop;
-        }
-        double t0, t1;
-        clip_f64(in->lmin, in->lmax, lo, ld, &t0, &t1);
-        if (!(t0 <= t1) || t1 < 0.0 || t0 > hit.t) return false;
-        const double shift = t0 > 0.0 ? t0 : 0.0;
-        const RayF rf = make_rayf(lo + shift * ld, ld);
-        float tbest = f32_up(hit.t - shift);
-        tbest = tbest + fabsf(tbest) * kSlabSlack;
-        auto leaf2 = [&](uint32_t first, uint32_t count, float& tb) -> bool {
-            const double before = hit.t;
-            const bool s = leaf(first, count, tb);
-            if (hit.t != before) { tb = f32_up(hit.t - shift); tb = tb + fabsf(tb) * kSlabSlack; }
-            return s;
-        };
-        bvh_traverse(sc.nodes + in->node_base, in->root_ref, rf, tbest, leaf2);
-        return stop;
-    }
-    double t;
-    uint32_t code = 0;
-    bool ok;
-    if (kind == kSphere) ok = sphere_test(lo, ld, t_min, &t);
-    else if (kind == kCube) ok = cube_test(lo, ld, t_min, &t, &code);
-    else ok = plane_test(*in, lo, ld, t_min, &t);
-    if (ok && accept(hit, t, obj)) {
-        hit.t = t; hit.inst = idx; hit.obj = obj; hit.prim = code;
-        if (SHADOW && t < t_stop) return true;
-    }
-    return false;
+// Conservative f32 Moller-Trumbore pre-test.  Returns false only when the ray provably misses
+// the triangle: every comparison carries an absolute error bound built from L1 norms of the
+// operands (an f32 dot/cross of vectors with relative input error ~2^-23 is off by at most a
+// few 2^-23 * |a||b|; kPreEps = 4e-6 leaves > 10x margin).  Undecidable cases go to the exact
+// f64 test.
+constexpr float kPreEps = 4e-6f;
+RPTX_D float l1(float x, float y, float z) { return fabsf(x) + fabsf(y) + fabsf(z); }
+RPTX_D bool tri_maybe_hit(const TriF* __restrict__ tf, float ox, float oy, float oz, float dx, float dy, float dz) {
+    const float4* q = reinterpret_cast<const float4*>(tf);
+    const float4 v0 = __ldg(q), e1 = __ldg(q + 1), e2 = __ldg(q + 2);
+    const float px = dy * e2.z - dz * e2.y, py = dz * e2.x - dx * e2.z, pz = dx * e2.y - dy * e2.x;  // d x e2
+    const float det = e1.x * px + e1.y * py + e1.z * pz;
+    const float tx = ox - v0.x, ty = oy - v0.y, tz = oz - v0.z;
+    const float nd = l1(dx, dy, dz), ne1 = l1(e1.x, e1.y, e1.z), ne2 = l1(e2.x, e2.y, e2.z);
+    const float mag = l1(ox, oy, oz) + l1(v0.x, v0.y, v0.z);  // bounds |tvec| and its rounding error
+    const float np = 2.0f * nd * ne2;                          // >= |d x e2| (L1)
+    const float e_u = kPreEps * np * mag;
+    const float e_det = kPreEps * ne1 * np;
+    const float u = tx * px + ty * py + tz * pz;
+    const float qx = ty * e1.z - tz * e1.y, qy = tz * e1.x - tx * e1.z, qz = tx * e1.y - ty * e1.x;  // tvec x e1
+    const float v = dx * qx + dy * qy + dz * qz;
+    const float e_v = kPreEps * nd * 2.0f * ne1 * mag;
+    const float sgn = det < 0.0f ? -1.0f : 1.0f;
+    const float adet = fabsf(det);
+    const float us = u * sgn, vs = v * sgn;
+    if (us < -e_u || vs < -e_v) return false;
+    if (us + vs > adet + e_det + e_u + e_v) return false;
+    return true;  // includes NaN/inf cases (all comparisons false)
 }
 
-// get_closest_hit.  hit.t must be preset to the search bound (+inf for extend rays).
+// get_closest_hit over the two-level BVH as ONE loop (while-while): every lane of a warp runs
+// the same inner-node code whether it is in the instance BVH or inside a mesh BVH; entering a
+// mesh pushes a sentinel, swaps the f32 ray for the mesh-local one and continues.
+// hit.t must be preset to the search bound (+inf for extend rays).
+// SHADOW: stop as soon as a hit below t_stop is accepted (the NEE test can only fail then).
+constexpr int kSentinel = 0x7fffffff;
+
 template <bool SHADOW>
 RPTX_D void closest_hit(const SceneDev& sc, const RayD& ray, double t_min, double t_stop, Hit& hit) {
     hit.inst = kNoHit; hit.obj = kNoHit; hit.prim = 0; hit.v = 0; hit.w = 0;
     // unbounded shapes (planes) cannot enter the BVH (src/renderer.rs:413-415)
-    for (uint32_t i = 0; i < sc.n_unbounded; i++)
-        if (intersect_instance<SHADOW>(sc, sc.n_bounded + i, ray, t_min, t_stop, hit)) return;
+    for (uint32_t i = 0; i < sc.n_unbounded; i++) {
+        const uint32_t idx = sc.n_bounded + i;
+        const Instance* __restrict__ in = sc.instances + idx;
+        d3 lo = ray.o, ld = ray.d;
+        if (in->has_transform) { lo = xform_point(in->inv, ray.o); ld = xform_dir(in->inv, ray.d); }
+        double t;
+        if (plane_test(*in, lo, ld, t_min, &t) && accept(hit, t, in->object_id)) {
+            hit.t = t; hit.inst = idx; hit.obj = in->object_id; hit.prim = 0;
+            if (SHADOW && t < t_stop) return;
+        }
+    }
     if (sc.n_bounded == 0) return;
     double t0, t1;
     clip_f64(sc.wmin, sc.wmax, ray.o, ray.d, &t0, &t1);
     if (!(t0 <= t1) || t1 < 0.0 || t0 > hit.t) return;
-    const double shift = t0 > 0.0 ? t0 : 0.0;
-    const RayF rf = make_rayf(ray.o + shift * ray.d, ray.d);
+    const double wshift = t0 > 0.0 ? t0 : 0.0;
+    const RayF wrf = make_rayf(ray.o + wshift * ray.d, ray.d);
+
+    int stack[kStackSize];
+    float stack_t[kStackSize];
+    int sp = 0;
+    const BvhNode* __restrict__ nodes = sc.nodes;
+    RayF rf = wrf;
+    double shift = wshift;
     float tbest = f32_up(hit.t - shift);
     tbest = tbest + fabsf(tbest) * kSlabSlack;
-    auto leaf = [&](uint32_t first, uint32_t count, float& tb) -> bool {
+    bool in_blas = false;
+    // mesh context while in_blas
+    uint32_t cur_inst = 0, cur_obj = 0;
+    d3 lo = ray.o, ld = ray.d;
+    float fox = 0, foy = 0, foz = 0, fdx = 0, fdy = 0, fdz = 0;  // f32 local ray for the triangle pre-test
+    const TriRec* __restrict__ tris = sc.tris;
+    const TriF* __restrict__ trif = sc.trif;
+
+    auto test_tris = [&](uint32_t first, uint32_t count) -> bool {
+        bool improved = false;
         for (uint32_t i = first; i < first + count; i++) {
-            const double before = hit.t;
-            if (intersect_instance<SHADOW>(sc, i, ray, t_min, t_stop, hit)) return true;
-            if (hit.t != before) { tb = f32_up(hit.t - shift); tb = tb + fabsf(tb) * kSlabSlack; }
+            if (!tri_maybe_hit(trif + i, fox, foy, foz, fdx, fdy, fdz)) continue;
+            TriRec tr;
+            load_tri(tris + i, &tr);
+            double t, v, w;
+            if (tri_test(tr, lo, ld, t_min, hit.t, cur_obj < hit.obj, &t, &v, &w)) {
+                hit.t = t; hit.inst = cur_inst; hit.obj = cur_obj; hit.prim = i; hit.v = v; hit.w = w;
+                improved = true;
+                if (SHADOW && t < t_stop) return true;
+            }
         }
+        if (improved) { tbest = f32_up(hit.t - shift); tbest = tbest + fabsf(tbest) * kSlabSlack; }
         return false;
     };
-    bvh_traverse(sc.nodes, sc.tlas_root_ref, rf, tbest, leaf);
+
+    int cur = sc.tlas_root_ref;
+    for (;;) {
+        // ---- inner nodes (same code for both levels) ----
+        while (cur >= 0 && cur != kSentinel) {
+            const float4* np = reinterpret_cast<const float4*>(nodes + cur);
+            const float4 a = __ldg(np), b = __ldg(np + 1), c = __ldg(np + 2), d = __ldg(np + 3);
+            float tl, tr;
+            const bool hl = slab_f32(a.x, a.y, a.z, b.x, b.y, b.z, rf, tbest, &tl);
+            const bool hr = slab_f32(c.x, c.y, c.z, d.x, d.y, d.z, rf, tbest, &tr);
+            const int left = __float_as_int(a.w), right = __float_as_int(c.w);
+            if (hl && hr) {
+                const bool lf = tl <= tr;
+                stack[sp] = lf ? right : left;
+                stack_t[sp] = lf ? tr : tl;
+                sp++;
+                cur = lf ? left : right;
+            } else if (hl) {
+                cur = left;
+            } else if (hr) {
+                cur = right;
+            } else {
+                cur = kSentinel + 0;  // placeholder, replaced by the pop below
+                // pop
+                for (;;) {
+                    if (sp == 0) return;
+                    sp--;
+                    if (stack_t[sp] <= tbest) { cur = stack[sp]; break; }
+                }
+            }
+        }
+        // ---- leaf or sentinel ----
+        if (cur == kSentinel) {
+            in_blas = false;
+            nodes = sc.nodes; rf = wrf; shift = wshift;
+            tbest = f32_up(hit.t - shift);
+            tbest = tbest + fabsf(tbest) * kSlabSlack;
+        } else {
+            const uint32_t code = (uint32_t)(~cur);
+            const uint32_t first = code >> 3, count = (code & 7u) + 1u;
+            if (in_blas) {
+                if (test_tris(first, count)) return;
+            } else {
+                for (uint32_t idx = first; idx < first + count; idx++) {
+                    const Instance* __restrict__ in = sc.instances + idx;
+                    const int kind = in->kind;
+                    cur_obj = in->object_id;
+                    lo = ray.o; ld = ray.d;
+                    if (in->has_transform) { lo = xform_point(in->inv, ray.o); ld = xform_dir(in->inv, ray.d); }
+                    if (kind == kMesh) {
+                        cur_inst = idx;
+                        tris = sc.tris + in->tri_base;
+                        trif = sc.trif + in->tri_base;
+                        if (in->root_ref < 0) {  // tiny mesh: no BLAS nodes, test its triangles here
+                            fox = (float)lo.x; foy = (float)lo.y; foz = (float)lo.z;
+                            fdx = (float)ld.x; fdy = (float)ld.y; fdz = (float)ld.z;
+                            const uint32_t c2 = (uint32_t)(~in->root_ref);
+                            if (test_tris(c2 >> 3, (c2 & 7u) + 1u)) return;
+                            continue;
+                        }
+                        double l0, l1v;
+                        clip_f64(in->lmin, in->lmax, lo, ld, &l0, &l1v);
+                        if (!(l0 <= l1v) || l1v < 0.0 || l0 > hit.t) continue;
+                        // enter the mesh BVH (TLAS leaves hold one instance, so nothing is pending)
+                        shift = l0 > 0.0 ? l0 : 0.0;
+                        const d3 so = lo + shift * ld;
+                        rf = make_rayf(so, ld);
+                        fox = (float)so.x; foy = (float)so.y; foz = (float)so.z;
+                        fdx = (float)ld.x; fdy = (float)ld.y; fdz = (float)ld.z;
+                        tbest = f32_up(hit.t - shift);
+                        tbest = tbest + fabsf(tbest) * kSlabSlack;
+                        nodes = sc.nodes + in->node_base;
+                        in_blas = true;
+                        stack[sp] = kSentinel;
+                        stack_t[sp] = -CUDART_INF_F;
+                        sp++;
+                        stack[sp] = in->root_ref;
+                        stack_t[sp] = -CUDART_INF_F;
+                        sp++;
+                        break;
+                    }
+                    double t;
+                    uint32_t ccode = 0;
+                    const bool ok = kind == kSphere ? sphere_test(lo, ld, t_min, &t) : cube_test(lo, ld, t_min, &t, &ccode);
+                    if (ok && accept(hit, t, cur_obj)) {
+                        hit.t = t; hit.inst = idx; hit.obj = cur_obj; hit.prim = ccode;
+                        if (SHADOW && t < t_stop) return;
+                        tbest = f32_up(hit.t - shift);
+                        tbest = tbest + fabsf(tbest) * kSlabSlack;
+                    }
+                }
+            }
+        }
+        // pop next
+        for (;;) {
+            if (sp == 0) return;
+            sp--;
+            if (stack_t[sp] <= tbest) { cur = stack[sp]; break; }
+        }
+    }
 }
 
 // normal of the accepted hit (the per-shape normal code of the reference + Transformed's M^-T)
