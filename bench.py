@@ -183,17 +183,10 @@ def run_ours(args):
     batch = spp * world  # weak scaling: every rank traces `spp` samples per pixel
     film = r.begin()
 
-    class _View:  # the film's device batch-sum buffer as a torch tensor (no copy)
-        __cuda_array_interface__ = dict(shape=(h * w * 3,), typestr="<f8", data=(film.batch_sum_ptr(), False), version=3)
-
-    batch_sum = torch.as_tensor(_View(), device=f"cuda:{local}")
+    from rpt_b200 import dist as rd
 
     def step():
-        film.sample_trace(batch)
-        if dist is not None:
-            dist.all_reduce(batch_sum)
-            torch.cuda.synchronize()
-        film.sample_commit(batch)
+        rd.sample_batch(film, batch)  # trace local shard -> NCCL all-reduce of the f64 batch sums -> commit
         return film.stats()
 
     def barrier():
@@ -243,12 +236,7 @@ def run_ours(args):
         rr._ctx = ctx
         rr.shard(world, rank)
         f2 = rr.begin()
-        f2.sample_trace(batch)
-        if dist is not None:
-            v2 = type("_V", (), {"__cuda_array_interface__": dict(shape=(h * w * 3,), typestr="<f8", data=(f2.batch_sum_ptr(), False), version=3)})()
-            dist.all_reduce(torch.as_tensor(v2, device=f"cuda:{local}"))
-            torch.cuda.synchronize()
-        f2.sample_commit(batch)
+        rd.sample_batch(f2, batch)
         img = f2.image()
         barrier()
         e2e_t += time.perf_counter() - t1

@@ -16,6 +16,13 @@ constexpr int kBlock = 128;
 
 RPTX_D uint32_t lane_id() { return threadIdx.x & 31u; }
 
+// one atomic per warp for the run counters (a per-thread atomic on one address serialises)
+RPTX_D void stat_add(unsigned long long* __restrict__ dst, unsigned long long v) {
+    const unsigned active = __activemask();
+    const unsigned total = __reduce_add_sync(active, (unsigned)v);  // per-thread counts are small
+    if (lane_id() == (uint32_t)(__ffs(active) - 1) && total) atomicAdd(dst, (unsigned long long)total);
+}
+
 // warp-ballot compaction: append `slot` of every lane with pred to q, one atomic per warp
 RPTX_D void queue_push(uint32_t* __restrict__ q, uint32_t* __restrict__ count, bool pred, uint32_t slot) {
     const unsigned active = __activemask();
@@ -57,7 +64,7 @@ __global__ void __launch_bounds__(kBlock) k_generate(PathPool p, Queues q, Batch
     const bool active = lane < p.n_lanes && lane < bp.n_local;
     if (active) start_path<MEDIUM>(p, bp, cam, slot, lane);
     queue_push(q.cur, &q.counters[0], active, slot);
-    if (active) atomicAdd(&q.stats[0], 1ull);
+    stat_add(&q.stats[0], active ? 1ull : 0ull);
 }
 
 // extend: persistent warps pull 32 rays at a time from the queue
@@ -245,7 +252,7 @@ __global__ void __launch_bounds__(kBlock) k_shadow(const __grid_constant__ Scene
         }
         if (any) { p.dirx[slot] = add.x; p.diry[slot] = add.y; p.dirz[slot] = add.z; }
     }
-    if (my_shadow) atomicAdd(&q.stats[2], my_shadow);
+    stat_add(&q.stats[2], my_shadow);
 }
 
 // connect: finalise the vertex; finished paths are folded (surface mode), added to the slot's
@@ -306,7 +313,7 @@ __global__ void __launch_bounds__(kBlock) k_connect(PathPool p, Queues q, BatchP
         }
         queue_push(q.next, &q.counters[1], alive, slot);
     }
-    if (my_started) atomicAdd(&q.stats[0], my_started);
+    stat_add(&q.stats[0], my_started);
 }
 
 // end of wave: next becomes cur (pointers are swapped on the host), heads reset

@@ -1,0 +1,78 @@
+"""Multi-GPU plumbing of the render path: one process per GPU, torch.distributed (NCCL over
+NVLink on the box, gloo in the CPU tests).
+
+The reference has one address space: rayon tasks per image row / per photon, a serial
+`add_samples` and a serial `PhotonList::merge` (src/renderer.rs:159-171, src/photon.rs:663-675).
+Here the two exchange steps of the path are
+  * path tracing / gather pass: every rank traces the samples s with s % world == rank of each
+    pixel into its own f64 batch-sum film; one all-reduce(sum) makes every rank hold the batch;
+  * photon pass: rank r emits the photon indices [lo_r, hi_r); the deposit records are
+    all-gathered (ragged) so that every rank builds the same full map.
+Nothing here computes radiance; `film` / `photons` are the C-ABI objects (or test doubles with
+the same methods).
+"""
+import torch
+import torch.distributed as dist
+
+
+def world_rank(group=None):
+    if dist.is_available() and dist.is_initialized():
+        return dist.get_world_size(group), dist.get_rank(group)
+    return 1, 0
+
+
+def local_samples(iterations, world, rank):
+    """How many of the batch's sample indices {0..iterations-1} satisfy s % world == rank
+    (the same arithmetic as rptx_render_sample_trace)."""
+    return (iterations - rank + world - 1) // world if iterations > rank else 0
+
+
+def photon_range(photon_count, world, rank):
+    """Contiguous photon-index range of a rank; RNG streams are keyed by the global index, so
+    the union over ranks is the single-GPU photon set."""
+    return photon_count * rank // world, photon_count * (rank + 1) // world
+
+
+def all_reduce_sum_(t, group=None):
+    if world_rank(group)[0] > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group)
+    return t
+
+
+def all_gather_ragged(t, group=None):
+    """Concatenate per-rank [n_r, ...] tensors in rank order (n_r differs per rank): counts are
+    all-gathered first, rows padded to the maximum, gathered, trimmed."""
+    world, _ = world_rank(group)
+    if world == 1:
+        return t, [t.shape[0]]
+    n = torch.tensor([t.shape[0]], dtype=torch.int64, device=t.device)
+    counts = [torch.zeros_like(n) for _ in range(world)]
+    dist.all_gather(counts, n, group=group)
+    counts = [int(c.item()) for c in counts]
+    m = max(counts)
+    pad = t
+    if t.shape[0] < m:
+        pad = torch.zeros((m,) + tuple(t.shape[1:]), dtype=t.dtype, device=t.device)
+        pad[: t.shape[0]] = t
+    parts = [torch.empty_like(pad) for _ in range(world)]
+    dist.all_gather(parts, pad.contiguous(), group=group)
+    return torch.cat([p[:c] for p, c in zip(parts, counts)], dim=0), counts
+
+
+def sample_batch(film, iterations, group=None):
+    """Renderer::sample(iterations) across ranks: trace the local shard, all-reduce the f64
+    batch sums, commit the same batch mean on every rank."""
+    film.sample_trace(iterations)
+    all_reduce_sum_(film.batch_sum_tensor(), group)
+    if film.batch_sum_tensor().is_cuda:
+        torch.cuda.current_stream().synchronize()
+    film.sample_commit(iterations)
+
+
+def device_f64_view(ptr, n, device):
+    """torch view (no copy) of a device buffer owned by the C library."""
+
+    class _V:
+        __cuda_array_interface__ = dict(shape=(int(n),), typestr="<f8", data=(int(ptr), False), version=3)
+
+    return torch.as_tensor(_V(), device=device)

@@ -36,6 +36,7 @@ class Context:
 
     def __init__(self, device=0):
         self.lib = A.load()
+        self.device = int(device)
         h = C.c_void_p()
         rc = self.lib.rptx_ctx_create(int(device), C.byref(h))
         self.h = h
@@ -181,6 +182,14 @@ class Film:
 
     def batch_sum_ptr(self):
         return self.lib.rptx_film_batch_sum_device_ptr(self.h)
+
+    def batch_sum_tensor(self):
+        """The device batch-sum film ([h*w*3] f64) as a torch view, for the NCCL all-reduce."""
+        if getattr(self, "_bs", None) is None:
+            from .dist import device_f64_view
+
+            self._bs = device_f64_view(self.batch_sum_ptr(), self.h_px * self.w * 3, f"cuda:{self.ctx.device}")
+        return self._bs
 
     def image(self):
         out = np.empty((self.h_px, self.w, 3), np.uint8)
