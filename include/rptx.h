@@ -130,7 +130,9 @@ typedef struct rptx_film  rptx_film;
 typedef struct rptx_stats {
     uint64_t path_samples;     /* camera paths started */
     uint64_t extend_rays;      /* closest-hit queries for path segments */
-    uint64_t shadow_rays;      /* closest-hit queries for NEE */
+    uint64_t shadow_rays;      /* NEE visibility queries (one get_closest_hit each in the reference) */
+    uint64_t shadow_traced;    /* of which probed on the device (non-zero contribution) */
+    uint64_t shadow_occlusion; /* of which also needed the occlusion-segment search */
     uint64_t waves;            /* wavefront iterations */
     uint64_t kernel_launches;  /* kernels of this library launched */
     double   device_ms;        /* CUDA-event time of the last render_sample call */
@@ -189,11 +191,63 @@ int  rptx_film_variance(rptx_film* film, double* out);
 /* mean over batches of the batch means, unfiltered, linear; [h][w][3] f64 */
 int  rptx_film_mean(rptx_film* film, double* out);
 
-/* photon_render src/photon.rs:655-720 */
+/* ---- photon integrators, src/photon.rs -------------------------------------------------
+ * photon_render (:655-720) is three passes with a barrier between them; they are exposed
+ * one by one so that a multi-GPU host can shard pass 1 by photon index, all-gather the
+ * records (NCCL) and shard pass 3 by sample, and so that each pass can be checked alone. */
+typedef struct rptx_photons    rptx_photons;     /* PhotonList (:141-171) on the device */
+typedef struct rptx_photon_map rptx_photon_map;  /* PhotonMap (:185-189) on the device */
+
+/* One photon record = 13 x 8 bytes: position[3], direction[3] (= wo at the deposit),
+ * power[3], starting_position[3] as f64 (Photon, :25-34) + a u64 key
+ * (photon index << 16 | bounce depth) that makes list order canonical. */
+#define RPTX_PHOTON_ROW_BYTES 104
+
+/* PASS 1 (:663-675): shoot photons [first, first + count) of a run of photon_count_total
+ * (power = watts / photon_count_total each, :671).  kind matters for the beam-beam
+ * thinning of volume photons (:773-793).  Error if the scene has no Light::Object (:798). */
+int  rptx_photons_emit(rptx_ctx* ctx, rptx_scene* scene, const rptx_params* params,
+                       uint64_t photon_count_total, uint64_t first, uint64_t count,
+                       int32_t kind, rptx_photons** out);
+int  rptx_photons_create(rptx_ctx* ctx, rptx_photons** out);            /* empty list */
+void rptx_photons_destroy(rptx_photons* photons);
+/* PhotonList::merge (:153-160): append rows (which: 0 surface, 1 volume) from host or device memory */
+int  rptx_photons_append_host(rptx_photons* photons, int32_t which, const void* rows, size_t n);
+int  rptx_photons_append_device(rptx_photons* photons, int32_t which, const void* d_rows, size_t n);
+int  rptx_photons_count(const rptx_photons* photons, uint64_t counts[2]);
+void* rptx_photons_device_ptr(rptx_photons* photons, int32_t which);      /* rows on the device */
+int  rptx_photons_download(rptx_photons* photons, int32_t which, void* rows /* [n][13 x 8 B] */);
+int  rptx_photons_stats(const rptx_photons* photons, uint64_t* emitted, uint64_t* rays, double* emit_ms);
+
+/* PASS 2 (:693-702): PhotonMap::new_point_map_for_point_estimate / _for_beam_estimate /
+ * new_beam_map_for_beam_estimate (:193-305).  The list may be destroyed afterwards. */
+int  rptx_photon_map_build(rptx_ctx* ctx, rptx_scene* scene, rptx_photons* photons, int32_t kind,
+                           rptx_photon_map** out);
+void rptx_photon_map_destroy(rptx_photon_map* map);
+/* counts: surface photons, volume photons in the point map, spheres/beams in the BVH */
+int  rptx_photon_map_stats(const rptx_photon_map* map, uint64_t counts[3], double* build_ms);
+
+/* PASS 3 (:706-716): camera pass.  gather_begin makes a film without a path pool;
+ * gather_trace evaluates this rank's shard of `iterations` samples per pixel
+ * (get_color_with_photon_map, :950-985) into the film's batch-sum buffer; finish the batch
+ * with rptx_render_sample_commit (after an all-reduce of the batch sums when sharded). */
+int  rptx_photon_gather_begin(rptx_ctx* ctx, rptx_scene* scene, const rptx_camera* camera,
+                              const rptx_params* params, rptx_film** out);
+int  rptx_photon_gather_trace(rptx_film* film, rptx_photon_map* map, uint32_t iterations);
+
+/* photon_render (:655-720): the three passes on one device, num_samples per pixel. */
 int  rptx_photon_render(rptx_ctx* ctx, rptx_scene* scene, const rptx_camera* camera,
                         const rptx_params* params, uint64_t photon_count, int32_t kind,
                         uint8_t* out_rgb8 /* [h][w][3] or NULL */,
                         double* out_mean /* [h][w][3] or NULL */);
+
+/* Parity hook: KdTree::nearests (kd-tree 0.4.1; call sites :329-332, :401-404, :216-225) over
+ * host queries q[n][3]: keys[n][k] of the k nearest photons in ascending distance (~0 where
+ * the map holds fewer), d2[n][k] squared distances (+inf), counts[n]. */
+int  rptx_photon_map_knn(rptx_photon_map* map, int32_t which, const double* q, size_t n, uint32_t k,
+                         uint64_t* keys, double* d2, uint32_t* counts);
+/* Parity hook: PhotonSphere centres and radii (:212-236) of a point-beam map, BVH leaf order. */
+int  rptx_photon_map_spheres(rptx_photon_map* map, double* center /* [n][3] */, double* radius /* [n] */);
 
 /* Parity hooks.
  * get_closest_hit (src/renderer.rs:416-425) over a batch of rays given as host arrays

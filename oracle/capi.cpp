@@ -315,4 +315,100 @@ int orc_photon_render(void* sp, const rptx_camera* c, const rptx_params* p, uint
     return 0;
 }
 
+
+// ---- the photon passes one by one (rows = the 13 x 8-byte records of include/rptx.h) ----
+struct OPhotons { PhotonList list; };
+struct OPhotonMap { PhotonMap map; OScene* scene; };
+
+static void to_row(const Photon& p, double* row) {
+    row[0] = p.position.x; row[1] = p.position.y; row[2] = p.position.z;
+    row[3] = p.direction.x; row[4] = p.direction.y; row[5] = p.direction.z;
+    row[6] = p.power.x; row[7] = p.power.y; row[8] = p.power.z;
+    row[9] = p.starting_position.x; row[10] = p.starting_position.y; row[11] = p.starting_position.z;
+    const uint64_t k = p.key();
+    std::memcpy(&row[12], &k, 8);
+}
+static Photon from_row(const double* row) {
+    Photon p;
+    p.position = Vec3(row[0], row[1], row[2]); p.direction = Vec3(row[3], row[4], row[5]);
+    p.power = Vec3(row[6], row[7], row[8]); p.starting_position = Vec3(row[9], row[10], row[11]);
+    uint64_t k;
+    std::memcpy(&k, &row[12], 8);
+    p.index = k >> 16; p.depth = (uint32_t)(k & 0xffff);
+    return p;
+}
+
+void* orc_photons_emit(void* sp, const rptx_camera* c, const rptx_params* p, uint64_t photon_count, uint64_t first, uint64_t count,
+                       int32_t kind, int threads) {
+    OScene* s = (OScene*)sp;
+    Renderer r;
+    fill_renderer(r, s, c, p, threads);
+    OPhotons* out = new OPhotons();
+    if (!emit_photons(r, photon_count, (PhotonRenderKind)kind, &out->list, first, count)) {
+        s->err = "Only found non-object lights while photon mapping";
+        delete out;
+        return nullptr;
+    }
+    return out;
+}
+void orc_photons_destroy(void* h) { delete (OPhotons*)h; }
+void orc_photons_count(void* h, uint64_t counts[2]) {
+    counts[0] = ((OPhotons*)h)->list.surface.size(); counts[1] = ((OPhotons*)h)->list.volume.size();
+}
+void orc_photons_rows(void* h, int32_t which, double* rows) {
+    const auto& v = which == 0 ? ((OPhotons*)h)->list.surface : ((OPhotons*)h)->list.volume;
+    for (size_t i = 0; i < v.size(); i++) to_row(v[i], rows + 13 * i);
+}
+
+void* orc_photon_map_build(void* sp, const double* surface_rows, size_t ns, const double* volume_rows, size_t nv, int32_t kind) {
+    OPhotonMap* m = new OPhotonMap();
+    m->scene = (OScene*)sp;
+    PhotonList list;
+    for (size_t i = 0; i < ns; i++) list.surface.push_back(from_row(surface_rows + 13 * i));
+    for (size_t i = 0; i < nv; i++) list.volume.push_back(from_row(volume_rows + 13 * i));
+    m->map.build((PhotonRenderKind)kind, std::move(list));
+    return m;
+}
+void orc_photon_map_destroy(void* h) { delete (OPhotonMap*)h; }
+
+// KdTree::nearests over a batch of queries
+int orc_photon_map_knn(void* h, int32_t which, const double* q, size_t n, uint32_t k, uint64_t* keys, double* d2, uint32_t* counts) {
+    const PointKd& kd = which == 0 ? ((OPhotonMap*)h)->map.surface_map : ((OPhotonMap*)h)->map.volume_map;
+    std::vector<PointKd::Found> found;
+    for (size_t i = 0; i < n; i++) {
+        kd.nearests(Vec3(q[3 * i], q[3 * i + 1], q[3 * i + 2]), k, &found);
+        for (uint32_t j = 0; j < k; j++) {
+            keys[i * k + j] = j < found.size() ? found[j].item->key() : ~0ull;
+            d2[i * k + j] = j < found.size() ? found[j].d2 : INF;
+        }
+        counts[i] = (uint32_t)found.size();
+    }
+    return 0;
+}
+
+size_t orc_photon_map_spheres(void* h, double* center, double* radius) {
+    const auto& sp = ((OPhotonMap*)h)->map.spheres;
+    if (center)
+        for (size_t i = 0; i < sp.size(); i++) {
+            center[3 * i] = sp[i].position.x; center[3 * i + 1] = sp[i].position.y; center[3 * i + 2] = sp[i].position.z;
+            radius[i] = sp[i].radius;
+        }
+    return sp.size();
+}
+
+// PASS 3 over a prebuilt map
+int orc_photon_map_gather(void* h, const rptx_camera* c, const rptx_params* p, int threads, uint8_t* out_rgb8, double* out_mean,
+                          double* seconds) {
+    OPhotonMap* m = (OPhotonMap*)h;
+    Renderer r;
+    fill_renderer(r, m->scene, c, p, threads);
+    Buffer buf(p->width, p->height, p->filter_radius);
+    const auto t0 = std::chrono::steady_clock::now();
+    photon_gather(r, m->map, buf);
+    if (seconds) *seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    if (out_rgb8) buf.image(out_rgb8);
+    if (out_mean) buf.mean(out_mean);
+    return 0;
+}
+
 }  // extern "C"

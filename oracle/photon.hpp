@@ -29,6 +29,8 @@ constexpr uint64_t DOMAIN_THIN = 4;
 struct Photon {
     Vec3 position, direction, power, starting_position;
     uint32_t depth = 0;  // oracle addition: num_bounces at deposit (keys the thinning stream)
+    uint64_t index = 0;  // oracle addition: index of the emitted photon this deposit belongs to
+    uint64_t key() const { return (index << 16) | (uint64_t)(depth < 65535u ? depth : 65535u); }
 };
 
 struct PhotonList {
@@ -453,6 +455,8 @@ inline bool shoot_photon(const Renderer& r, double power, uint64_t photon_index,
         const Vec3 direction = mul(rot, hemi);
         PhotonList photons;
         trace_photon(r, Ray{pos, direction}, power * light.object.material.color(), rng, 0, &photons);
+        for (Photon& x : photons.surface) x.index = photon_index;
+        for (Photon& x : photons.volume) x.index = photon_index;
         out->surface.insert(out->surface.end(), photons.surface.begin(), photons.surface.end());
         for (const Photon& x : photons.volume) {
             if (kind == PhotonBeamBeam) {
@@ -473,16 +477,19 @@ inline bool shoot_photon(const Renderer& r, double power, uint64_t photon_index,
     return false;
 }
 
-inline bool emit_photons(const Renderer& r, uint64_t photon_count, PhotonRenderKind kind, PhotonList* list) {
+// photons [first, first + count) of a run of photon_count (the whole run by default)
+inline bool emit_photons(const Renderer& r, uint64_t photon_count, PhotonRenderKind kind, PhotonList* list, uint64_t first = 0,
+                         uint64_t count = ~0ull) {
+    if (count == ~0ull) count = photon_count - first;
     int nt = r.threads > 0 ? r.threads : std::max(1, (int)std::thread::hardware_concurrency());
-    if ((uint64_t)nt > photon_count) nt = (int)std::max<uint64_t>(1, photon_count);
+    if ((uint64_t)nt > count) nt = (int)std::max<uint64_t>(1, count);
     std::vector<PhotonList> parts(nt);
     std::atomic<bool> ok{true};
     const double power = r.watts / (double)photon_count;
     std::vector<std::thread> pool;
     for (int t = 0; t < nt; t++)
         pool.emplace_back([&, t] {
-            const uint64_t lo = photon_count * t / nt, hi = photon_count * (t + 1) / nt;
+            const uint64_t lo = first + count * t / nt, hi = first + count * (t + 1) / nt;
             for (uint64_t i = lo; i < hi; i++)
                 if (!shoot_photon(r, power, i, kind, &parts[t])) { ok = false; return; }
         });
@@ -502,6 +509,19 @@ inline Color photon_sample_radiance(const Renderer& r, const PhotonMap& map, uin
     return map.estimate_indirect(r, ray, r.scene->media.empty() ? nullptr : &r.scene->media[0], rng);
 }
 
+// PASS 3 of photon_render, src/photon.rs:706-716
+inline void photon_gather(const Renderer& r, const PhotonMap& map, Buffer& buffer) {
+    std::vector<Color> colors((size_t)r.width * r.height);
+    r.parallel_rows([&](uint32_t y, int) {
+        for (uint32_t x = 0; x < r.width; x++) {
+            Color c(0, 0, 0);
+            for (uint32_t s = 0; s < r.num_samples; s++) c += photon_sample_radiance(r, map, x, y, s);
+            colors[(size_t)y * r.width + x] = c / (double)r.num_samples * std::pow(2.0, r.exposure_value);
+        }
+    });
+    buffer.add_samples(colors);
+}
+
 // src/photon.rs:655-720
 inline bool photon_render(const Renderer& r, uint64_t photon_count, PhotonRenderKind kind, Buffer& buffer, PhotonStats* st) {
     using clk = std::chrono::steady_clock;
@@ -514,15 +534,7 @@ inline bool photon_render(const Renderer& r, uint64_t photon_count, PhotonRender
     PhotonMap map;
     map.build(kind, std::move(list));
     auto t2 = clk::now();
-    std::vector<Color> colors((size_t)r.width * r.height);
-    r.parallel_rows([&](uint32_t y, int) {
-        for (uint32_t x = 0; x < r.width; x++) {
-            Color c(0, 0, 0);
-            for (uint32_t s = 0; s < r.num_samples; s++) c += photon_sample_radiance(r, map, x, y, s);
-            colors[(size_t)y * r.width + x] = c / (double)r.num_samples * std::pow(2.0, r.exposure_value);
-        }
-    });
-    buffer.add_samples(colors);
+    photon_gather(r, map, buffer);
     auto t3 = clk::now();
     st->emit_s = std::chrono::duration<double>(t1 - t0).count();
     st->build_s = std::chrono::duration<double>(t2 - t1).count();

@@ -6,6 +6,6 @@ CUDA library rpt_b200/librptx.so.  There is no CPU path in this package.
 """
 from ._abi import LIB_PATH  # noqa: F401
 from .io import load_obj  # noqa: F401
-from .renderer import Buffer, Context, DeviceScene, Film, Filter, PhotonRenderKind, Renderer, RptxError  # noqa: F401
+from .renderer import Buffer, Context, DeviceScene, Film, Filter, PhotonList, PhotonMap, PhotonRenderKind, Renderer, RptxError  # noqa: F401
 from .scene import KdTree, Mesh, Triangle, cube, hex_color, plane, polygon, sphere, vec3  # noqa: F401
 from .world import Camera, Hdri, Light, Material, Medium, Object, Scene  # noqa: F401

@@ -89,6 +89,8 @@ class Stats(C.Structure):
         ("path_samples", C.c_uint64),
         ("extend_rays", C.c_uint64),
         ("shadow_rays", C.c_uint64),
+        ("shadow_traced", C.c_uint64),
+        ("shadow_occlusion", C.c_uint64),
         ("waves", C.c_uint64),
         ("kernel_launches", C.c_uint64),
         ("device_ms", C.c_double),
@@ -108,6 +110,8 @@ P = C.c_void_p
 DP = C.POINTER(C.c_double)
 U32P = C.POINTER(C.c_uint32)
 U8P = C.POINTER(C.c_uint8)
+U64P = C.POINTER(C.c_uint64)
+PHOTON_ROW_F64 = 13  # RPTX_PHOTON_ROW_BYTES / 8
 
 # name -> (restype, argtypes): every symbol include/rptx.h declares
 PROTOTYPES = {
@@ -133,7 +137,23 @@ PROTOTYPES = {
     "rptx_film_image_rgb8": (C.c_int, [P, U8P]),
     "rptx_film_variance": (C.c_int, [P, DP]),
     "rptx_film_mean": (C.c_int, [P, DP]),
+    "rptx_photons_emit": (C.c_int, [P, P, C.POINTER(Params), C.c_uint64, C.c_uint64, C.c_uint64, C.c_int32, C.POINTER(P)]),
+    "rptx_photons_create": (C.c_int, [P, C.POINTER(P)]),
+    "rptx_photons_destroy": (None, [P]),
+    "rptx_photons_append_host": (C.c_int, [P, C.c_int32, P, C.c_size_t]),
+    "rptx_photons_append_device": (C.c_int, [P, C.c_int32, P, C.c_size_t]),
+    "rptx_photons_count": (C.c_int, [P, U64P]),
+    "rptx_photons_device_ptr": (C.c_void_p, [P, C.c_int32]),
+    "rptx_photons_download": (C.c_int, [P, C.c_int32, P]),
+    "rptx_photons_stats": (C.c_int, [P, U64P, U64P, DP]),
+    "rptx_photon_map_build": (C.c_int, [P, P, P, C.c_int32, C.POINTER(P)]),
+    "rptx_photon_map_destroy": (None, [P]),
+    "rptx_photon_map_stats": (C.c_int, [P, U64P, DP]),
+    "rptx_photon_gather_begin": (C.c_int, [P, P, C.POINTER(CameraDesc), C.POINTER(Params), C.POINTER(P)]),
+    "rptx_photon_gather_trace": (C.c_int, [P, P, C.c_uint32]),
     "rptx_photon_render": (C.c_int, [P, P, C.POINTER(CameraDesc), C.POINTER(Params), C.c_uint64, C.c_int32, U8P, DP]),
+    "rptx_photon_map_knn": (C.c_int, [P, C.c_int32, DP, C.c_size_t, C.c_uint32, U64P, DP, U32P]),
+    "rptx_photon_map_spheres": (C.c_int, [P, DP, DP]),
     "rptx_intersect_batch": (C.c_int, [P, DP, DP, C.c_size_t, C.c_double, DP, U32P, U32P, U32P, DP]),
     "rptx_intersect_batch_device": (C.c_int, [P, P, P, C.c_size_t, C.c_double, P, P, P, P, P]),
     "rptx_stats_get": (C.c_int, [P, C.POINTER(Stats)]),

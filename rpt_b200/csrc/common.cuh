@@ -134,6 +134,7 @@ struct Light {
 struct Camera {
     d3 eye, direction, up;
     double fov, aperture, focal_distance;
+    double inv_tan_half_fov;  // 1 / tan(fov / 2) (src/camera.rs:66), evaluated once on the host
 };
 
 struct SceneDev {
@@ -146,8 +147,11 @@ struct SceneDev {
     const Material* materials;  // per object
     const Light* lights;
     const RawTri* light_tris;
+    const uint32_t* cube_instances;  // indices of the kCube instances (see closest_hit: rays lying in a face plane)
+    uint32_t n_cube_instances;
     int tlas_root_ref;
     uint32_t n_bounded, n_unbounded, n_lights, n_shadow_lights;
+    uint32_t shadow_probe_mask;  // bit k: k-th shadow-casting light is probed at its sample first (trace.cuh nee_visible)
     double wmin[3], wmax[3];    // padded world bounds of the bounded instances
     int medium_kind;
     double sigma_a, sigma_s;

@@ -7,6 +7,7 @@
 #include "../../include/rptx.h"
 #include "common.cuh"
 #include "path.cuh"
+#include "shading.cuh"
 
 struct rptx_ctx {
     int device = 0;
@@ -56,8 +57,10 @@ struct rptx_scene {
     const rptx::Light* d_lights = nullptr;
     const rptx::RawTri* d_raw = nullptr;
     const double* d_env = nullptr;
+    const uint32_t* d_cube_idx = nullptr;
+    uint32_t n_cubes = 0;
     int tlas_root_ref = 0;
-    uint32_t n_bounded = 0, n_unbounded = 0, n_shadow_lights = 0;
+    uint32_t n_bounded = 0, n_unbounded = 0, n_shadow_lights = 0, shadow_probe_mask = 0;
     double wmin[3] = {0, 0, 0}, wmax[3] = {0, 0, 0};
 };
 
@@ -78,3 +81,10 @@ struct rptx_film {
     cudaEvent_t evw[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};  // per-wave kernel boundaries
     rptx_stats stats = {};
 };
+
+// host helpers shared by rptx.cu and photon.cu
+namespace rptx_host {
+int ctx_fail(rptx_ctx* ctx, const std::string& msg);  // records the message, returns 1
+rptx::SceneDev scene_dev(const rptx_scene* s);
+rptx::MediumDev medium_dev(const rptx_scene* s);
+}  // namespace rptx_host

@@ -83,7 +83,7 @@ __global__ void __launch_bounds__(kBlock) k_extend(const __grid_constant__ Scene
             ray.d = mk3(p.dx[slot], p.dy[slot], p.dz[slot]);
             Hit h;
             h.t = CUDART_INF;
-            closest_hit<false>(sc, ray, kEpsilon, 0.0, h);
+            closest_hit<kClosest>(sc, ray, kEpsilon, 0.0, h);
             if (h.inst != kNoHit) {
                 uint32_t prim, inst;
                 const d3 n = hit_normal(sc, ray, h, &prim, &inst);
@@ -216,13 +216,13 @@ __global__ void __launch_bounds__(kBlock) k_shade(const __grid_constant__ SceneD
     p.rng[slot] = rng.state;
 }
 
-// shadow: NEE visibility rays of the vertex.  The reference asks for the CLOSEST hit to sit within
-// 1e-12 of the light sample (src/renderer.rs:348,396); the search is bounded to dist + 2e-12 and
-// stops at the first hit below dist - 2e-12 (the test can only fail then).  Passing candidates
-// are added to the vertex's direct light in light order.
+// shadow: NEE visibility of the vertex's light samples (nee_visible, trace.cuh).  Passing
+// candidates are added to the vertex's direct light in light order.  A candidate whose
+// contribution is exactly zero (light sample facing away, bsdf 0) is not traced: adding it
+// cannot change the sum.
 __global__ void __launch_bounds__(kBlock) k_shadow(const __grid_constant__ SceneDev sc, PathPool p, Queues q) {
     const uint32_t count = q.counters[0];
-    unsigned long long my_shadow = 0;
+    unsigned long long my_queries = 0, my_traced = 0, my_occl = 0;
     for (;;) {
         uint32_t base = 0;
         if (lane_id() == 0) base = atomicAdd(&q.counters[3], 32u);
@@ -238,21 +238,23 @@ __global__ void __launch_bounds__(kBlock) k_shadow(const __grid_constant__ Scene
         ray.o = mk3(p.ox[slot], p.oy[slot], p.oz[slot]);
         for (uint32_t k = 0; k < p.n_shadow; k++) {
             const size_t off = (size_t)k * p.n_slots + slot;
+            my_queries++;
+            const d3 c = mk3(p.scx[off], p.scy[off], p.scz[off]);
+            if (c.x == 0.0 && c.y == 0.0 && c.z == 0.0) continue;
             ray.d = mk3(p.sdx[off], p.sdy[off], p.sdz[off]);
             const double dist = p.sdist[off];
-            Hit h;
-            h.t = dist + 2e-12;
-            closest_hit<true>(sc, ray, kEpsilon, dist - 2e-12, h);
-            my_shadow++;
-            if (h.inst != kNoHit && fabs(h.t - dist) < kEpsilon) {
+            my_traced++;
+            if (nee_visible(sc, ray, dist, k < 32 && ((sc.shadow_probe_mask >> k) & 1u), &my_occl)) {
                 // direct += contribution, in light order like the reference's loop
                 if (!any) { add = mk3(p.dirx[slot], p.diry[slot], p.dirz[slot]); any = true; }
-                add = add + mk3(p.scx[off], p.scy[off], p.scz[off]);
+                add = add + c;
             }
         }
         if (any) { p.dirx[slot] = add.x; p.diry[slot] = add.y; p.dirz[slot] = add.z; }
     }
-    stat_add(&q.stats[2], my_shadow);
+    stat_add(&q.stats[2], my_queries);
+    stat_add(&q.stats[3], my_traced);
+    stat_add(&q.stats[4], my_occl);
 }
 
 // connect: finalise the vertex; finished paths are folded (surface mode), added to the slot's
@@ -337,7 +339,7 @@ __global__ void __launch_bounds__(kBlock) k_intersect_batch(const __grid_constan
     ray.d = mk3(d[3 * i], d[3 * i + 1], d[3 * i + 2]);
     Hit h;
     h.t = CUDART_INF;
-    closest_hit<false>(sc, ray, t_min, 0.0, h);
+    closest_hit<kClosest>(sc, ray, t_min, 0.0, h);
     uint32_t prim = 0, inst = 0;
     d3 n3 = mk3(0, 0, 0);
     if (h.inst != kNoHit) n3 = hit_normal(sc, ray, h, &prim, &inst);

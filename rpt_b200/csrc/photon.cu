@@ -1,0 +1,817 @@
+// Host side of the photon integrators (C ABI of include/rptx.h, "photon" section): emission
+// driver, photon-map builders and the camera pass.  Kernels: photon.cuh + the builders below.
+#include <cub/cub.cuh>
+
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/rptx.h"
+#include "bvh_build.cuh"
+#include "host_types.hpp"
+#include "photon.cuh"
+
+using namespace rptx;
+using rptx_host::ctx_fail;
+
+#define CK(call)                                                                         \
+    do {                                                                                 \
+        cudaError_t e_ = (call);                                                         \
+        if (e_ != cudaSuccess) return ctx_fail(ctx, std::string(#call) + ": " + cudaGetErrorString(e_)); \
+    } while (0)
+
+struct rptx_photons {
+    rptx_ctx* ctx = nullptr;
+    PhotonRec* d_rows[2] = {nullptr, nullptr};  // [0] surface, [1] volume
+    uint64_t n[2] = {0, 0}, cap[2] = {0, 0};
+    uint64_t emitted = 0, rays = 0;
+    double emit_ms = 0;
+};
+
+namespace {
+
+struct PointMapHost {
+    PointMapDev dev = {};
+    std::vector<void*> owned;
+};
+
+struct BoxBvhHost {
+    BoxBvhDev dev = {};
+    std::vector<void*> owned;
+};
+
+int grid_for(size_t n, int block) { return (int)std::max<size_t>(1, (n + block - 1) / block); }
+
+template <class T>
+cudaError_t dev_alloc(T** p, size_t n, std::vector<void*>* owned) {
+    *p = nullptr;
+    cudaError_t e = cudaMalloc((void**)p, std::max<size_t>(n, 1) * sizeof(T));
+    if (e == cudaSuccess && owned) owned->push_back(*p);
+    return e;
+}
+
+// ---- builders' kernels ----
+
+__global__ void k_rows_keys(const PhotonRec* __restrict__ rows, uint32_t n, uint64_t* __restrict__ keys, uint32_t* __restrict__ idx) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    keys[i] = rows[i].key;
+    idx[i] = i;
+}
+
+// per-block bounds of the photon positions (finalised on the host: <= 1184 x 6 doubles)
+__global__ void __launch_bounds__(256) k_rows_bounds(const PhotonRec* __restrict__ rows, uint32_t n, double* __restrict__ out) {
+    double mn[3] = {CUDART_INF, CUDART_INF, CUDART_INF}, mx[3] = {-CUDART_INF, -CUDART_INF, -CUDART_INF};
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+        for (int k = 0; k < 3; k++) { mn[k] = fmin(mn[k], rows[i].pos[k]); mx[k] = fmax(mx[k], rows[i].pos[k]); }
+    __shared__ double sh[6][8];
+    for (int k = 0; k < 3; k++) {
+        for (int o = 16; o > 0; o >>= 1) {
+            mn[k] = fmin(mn[k], __shfl_down_sync(0xffffffffu, mn[k], o));
+            mx[k] = fmax(mx[k], __shfl_down_sync(0xffffffffu, mx[k], o));
+        }
+        if ((threadIdx.x & 31) == 0) { sh[k][threadIdx.x >> 5] = mn[k]; sh[3 + k][threadIdx.x >> 5] = mx[k]; }
+    }
+    __syncthreads();
+    if (threadIdx.x < 6) {
+        double v = sh[threadIdx.x][0];
+        for (int w = 1; w < 8; w++) v = threadIdx.x < 3 ? fmin(v, sh[threadIdx.x][w]) : fmax(v, sh[threadIdx.x][w]);
+        out[6 * blockIdx.x + threadIdx.x] = v;
+    }
+}
+
+__device__ __forceinline__ uint64_t expand_bits21(uint64_t v) {
+    v &= 0x1fffffull;
+    v = (v | v << 32) & 0x1f00000000ffffull;
+    v = (v | v << 16) & 0x1f0000ff0000ffull;
+    v = (v | v << 8) & 0x100f00f00f00f00full;
+    v = (v | v << 4) & 0x10c30c30c30c30c3ull;
+    v = (v | v << 2) & 0x1249249249249249ull;
+    return v;
+}
+
+// 63-bit Morton key of row idx[i] (canonical order in, so that the stable sort breaks ties canonically)
+__global__ void k_rows_morton(const PhotonRec* __restrict__ rows, const uint32_t* __restrict__ idx, uint32_t n, double3 mn, double3 inv,
+                              uint64_t* __restrict__ keys) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const PhotonRec& r = rows[idx[i]];
+    const double s = 2097152.0;  // 2^21
+    const uint64_t x = (uint64_t)fmin(fmax((r.pos[0] - mn.x) * inv.x * s, 0.0), s - 1.0);
+    const uint64_t y = (uint64_t)fmin(fmax((r.pos[1] - mn.y) * inv.y * s, 0.0), s - 1.0);
+    const uint64_t z = (uint64_t)fmin(fmax((r.pos[2] - mn.z) * inv.z * s, 0.0), s - 1.0);
+    keys[i] = (expand_bits21(x) << 2) | (expand_bits21(y) << 1) | expand_bits21(z);
+}
+
+__global__ void k_rows_gather(const PhotonRec* __restrict__ rows, const uint32_t* __restrict__ idx, uint32_t n, double* __restrict__ px,
+                              double* __restrict__ py, double* __restrict__ pz, double* __restrict__ dir, double* __restrict__ power,
+                              uint64_t* __restrict__ key) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const PhotonRec r = rows[idx[i]];
+    px[i] = r.pos[0]; py[i] = r.pos[1]; pz[i] = r.pos[2];
+    for (int k = 0; k < 3; k++) { dir[3 * (size_t)i + k] = r.dir[k]; power[3 * (size_t)i + k] = r.power[k]; }
+    key[i] = r.key;
+}
+
+// leaves of the implicit tree: f32 boxes (rounded outward) of kPointLeaf consecutive photons
+__global__ void k_point_leaves(const double* __restrict__ px, const double* __restrict__ py, const double* __restrict__ pz, uint32_t n,
+                               uint32_t n_leaf_slots, uint32_t leaf_base, float4* __restrict__ node_box) {
+    const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n_leaf_slots) return;
+    float mn[3] = {CUDART_INF_F, CUDART_INF_F, CUDART_INF_F}, mx[3] = {-CUDART_INF_F, -CUDART_INF_F, -CUDART_INF_F};
+    const uint64_t first = (uint64_t)j * kPointLeaf;
+    for (uint64_t i = first; i < first + kPointLeaf && i < n; i++) {
+        mn[0] = fminf(mn[0], __double2float_rd(px[i])); mx[0] = fmaxf(mx[0], __double2float_ru(px[i]));
+        mn[1] = fminf(mn[1], __double2float_rd(py[i])); mx[1] = fmaxf(mx[1], __double2float_ru(py[i]));
+        mn[2] = fminf(mn[2], __double2float_rd(pz[i])); mx[2] = fmaxf(mx[2], __double2float_ru(pz[i]));
+    }
+    node_box[2 * (size_t)(leaf_base + j)] = make_float4(mn[0], mn[1], mn[2], 0.f);
+    node_box[2 * (size_t)(leaf_base + j) + 1] = make_float4(mx[0], mx[1], mx[2], 0.f);
+}
+
+// one level of inner nodes [first, first + count): union of the two children
+__global__ void k_point_level(uint32_t first, uint32_t count, float4* __restrict__ node_box) {
+    const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= count) return;
+    const size_t node = first + j, c0 = 2 * node + 1;
+    const float4 a0 = node_box[2 * c0], b0 = node_box[2 * c0 + 1], a1 = node_box[2 * c0 + 2], b1 = node_box[2 * c0 + 3];
+    node_box[2 * node] = make_float4(fminf(a0.x, a1.x), fminf(a0.y, a1.y), fminf(a0.z, a1.z), 0.f);
+    node_box[2 * node + 1] = make_float4(fmaxf(b0.x, b1.x), fmaxf(b0.y, b1.y), fmaxf(b0.z, b1.z), 0.f);
+}
+
+// radius of a photon sphere = distance to its 10th nearest volume photon, itself included
+// (src/photon.rs:212-236), + its f32 box (:119-128)
+__global__ void __launch_bounds__(128) k_sphere_radius(const __grid_constant__ PointMapDev vm, double* __restrict__ radius,
+                                                       Aabb32* __restrict__ boxes) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= vm.n) return;
+    const d3 p = mk3(vm.px[i], vm.py[i], vm.pz[i]);
+    KnnHeap<16> heap;
+    heap.k = kSphereKnn;
+    knn_query(vm, p, heap);
+    double m = -1.0;
+    for (uint32_t j = 0; j < heap.size; j++) m = fmax(m, heap.d2[j]);
+    const double r = sqrt(m);
+    radius[i] = r;
+    Aabb32 b;
+    b.mn[0] = (float)(p.x - r); b.mn[1] = (float)(p.y - r); b.mn[2] = (float)(p.z - r);
+    b.mx[0] = (float)(p.x + r); b.mx[1] = (float)(p.y + r); b.mx[2] = (float)(p.z + r);
+    boxes[i] = b;
+}
+
+__global__ void k_sphere_gather(const __grid_constant__ PointMapDev vm, const double* __restrict__ radius, const Aabb32* __restrict__ boxes,
+                                const uint32_t* __restrict__ perm, uint32_t n, double* __restrict__ center, double* __restrict__ rad,
+                                double* __restrict__ dir, double* __restrict__ power, Aabb32* __restrict__ obox) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t s = perm[i];
+    center[3 * (size_t)i] = vm.px[s]; center[3 * (size_t)i + 1] = vm.py[s]; center[3 * (size_t)i + 2] = vm.pz[s];
+    rad[i] = radius[s];
+    for (int k = 0; k < 3; k++) { dir[3 * (size_t)i + k] = vm.dir[3 * (size_t)s + k]; power[3 * (size_t)i + k] = vm.power[3 * (size_t)s + k]; }
+    obox[i] = boxes[s];
+}
+
+// PhotonBeam of a volume photon (src/photon.rs:264-288) + its f32 box (:76-105); canonical order
+__global__ void k_beam_make(const PhotonRec* __restrict__ rows, const uint32_t* __restrict__ idx, uint32_t n, double* __restrict__ start,
+                            double* __restrict__ dirn, double* __restrict__ len, double* __restrict__ power, Aabb32* __restrict__ boxes) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const PhotonRec r = rows[idx[i]];
+    const d3 a = mk3(r.start[0], r.start[1], r.start[2]), b = mk3(r.pos[0], r.pos[1], r.pos[2]);
+    const d3 dn = normalize(b - a);
+    const double l = length(b - a);
+    const double cx = (a.x - b.x) * (a.x - b.x), cy = (a.y - b.y) * (a.y - b.y), cz = (a.z - b.z) * (a.z - b.z);
+    const double sq = cx + cy + cz;
+    const double kx = sqrt((cy + cz) / sq), ky = sqrt((cx + cz) / sq), kz = sqrt((cx + cy) / sq);
+    const d3 adj = mk3(kx * kBeamRadius, ky * kBeamRadius, kz * kBeamRadius);
+    const d3 mn = mk3(fmin(a.x, b.x), fmin(a.y, b.y), fmin(a.z, b.z)) - adj;
+    const d3 mx = mk3(fmax(a.x, b.x), fmax(a.y, b.y), fmax(a.z, b.z)) + adj;
+    Aabb32 bx;
+    bx.mn[0] = (float)mn.x; bx.mn[1] = (float)mn.y; bx.mn[2] = (float)mn.z;
+    bx.mx[0] = (float)mx.x; bx.mx[1] = (float)mx.y; bx.mx[2] = (float)mx.z;
+    boxes[i] = bx;
+    start[3 * (size_t)i] = a.x; start[3 * (size_t)i + 1] = a.y; start[3 * (size_t)i + 2] = a.z;
+    dirn[3 * (size_t)i] = dn.x; dirn[3 * (size_t)i + 1] = dn.y; dirn[3 * (size_t)i + 2] = dn.z;
+    len[i] = l;
+    for (int k = 0; k < 3; k++) power[3 * (size_t)i + k] = r.power[k];
+}
+
+__global__ void k_beam_gather(const double* __restrict__ start, const double* __restrict__ dirn, const double* __restrict__ len,
+                              const double* __restrict__ power, const Aabb32* __restrict__ boxes, const uint32_t* __restrict__ perm, uint32_t n,
+                              double* __restrict__ ostart, double* __restrict__ odirn, double* __restrict__ olen, double* __restrict__ opower,
+                              Aabb32* __restrict__ obox) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t s = perm[i];
+    for (int k = 0; k < 3; k++) {
+        ostart[3 * (size_t)i + k] = start[3 * (size_t)s + k];
+        odirn[3 * (size_t)i + k] = dirn[3 * (size_t)s + k];
+        opower[3 * (size_t)i + k] = power[3 * (size_t)s + k];
+    }
+    olen[i] = len[s];
+    obox[i] = boxes[s];
+}
+
+// per-block bounds of finite f32 boxes (Morton normalisation of the box BVH)
+__global__ void __launch_bounds__(256) k_box_bounds(const Aabb32* __restrict__ boxes, uint32_t n, double* __restrict__ out) {
+    double mn[3] = {CUDART_INF, CUDART_INF, CUDART_INF}, mx[3] = {-CUDART_INF, -CUDART_INF, -CUDART_INF};
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+        for (int k = 0; k < 3; k++) {
+            const float a = boxes[i].mn[k], b = boxes[i].mx[k];
+            if (isfinite(a)) mn[k] = fmin(mn[k], (double)a);
+            if (isfinite(b)) mx[k] = fmax(mx[k], (double)b);
+        }
+    __shared__ double sh[6][8];
+    for (int k = 0; k < 3; k++) {
+        for (int o = 16; o > 0; o >>= 1) {
+            mn[k] = fmin(mn[k], __shfl_down_sync(0xffffffffu, mn[k], o));
+            mx[k] = fmax(mx[k], __shfl_down_sync(0xffffffffu, mx[k], o));
+        }
+        if ((threadIdx.x & 31) == 0) { sh[k][threadIdx.x >> 5] = mn[k]; sh[3 + k][threadIdx.x >> 5] = mx[k]; }
+    }
+    __syncthreads();
+    if (threadIdx.x < 6) {
+        double v = sh[threadIdx.x][0];
+        for (int w = 1; w < 8; w++) v = threadIdx.x < 3 ? fmin(v, sh[threadIdx.x][w]) : fmax(v, sh[threadIdx.x][w]);
+        out[6 * blockIdx.x + threadIdx.x] = v;
+    }
+}
+
+// batch_sum[pixel] = sum over lanes, fixed order (as k_batch_reduce of the path tracer)
+__global__ void k_lane_reduce(const double* __restrict__ ax, const double* __restrict__ ay, const double* __restrict__ az, uint32_t n_pixels,
+                              uint32_t n_lanes, double* __restrict__ batch_sum) {
+    const uint32_t pixel = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pixel >= n_pixels) return;
+    double x = 0, y = 0, z = 0;
+    for (uint32_t l = 0; l < n_lanes; l++) {
+        const size_t s = (size_t)l * n_pixels + pixel;
+        x += ax[s]; y += ay[s]; z += az[s];
+    }
+    batch_sum[3 * (size_t)pixel] = x; batch_sum[3 * (size_t)pixel + 1] = y; batch_sum[3 * (size_t)pixel + 2] = z;
+}
+
+// kNN parity hook: one thread per query
+template <int KMAX>
+__global__ void __launch_bounds__(128) k_knn_batch(const __grid_constant__ PointMapDev m, const double* __restrict__ q, size_t n, uint32_t k,
+                                                   uint64_t* __restrict__ keys, double* __restrict__ d2, uint32_t* __restrict__ counts) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    KnnHeap<KMAX> heap;
+    heap.k = k;
+    knn_query(m, mk3(q[3 * i], q[3 * i + 1], q[3 * i + 2]), heap);
+    heap.sort_ascending();
+    for (uint32_t j = 0; j < k; j++) {
+        keys[i * k + j] = j < heap.size ? m.key[heap.idx[j]] : ~0ull;
+        d2[i * k + j] = j < heap.size ? heap.d2[j] : CUDART_INF;
+    }
+    counts[i] = heap.size;
+}
+
+// ---- host helpers ----
+
+int reduce_bounds(rptx_ctx* ctx, const double* d_blocks, int blocks, double mn[3], double mx[3]) {
+    std::vector<double> h((size_t)blocks * 6);
+    CK(cudaMemcpyAsync(h.data(), d_blocks, sizeof(double) * h.size(), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    for (int k = 0; k < 3; k++) { mn[k] = INFINITY; mx[k] = -INFINITY; }
+    for (int b = 0; b < blocks; b++)
+        for (int k = 0; k < 3; k++) { mn[k] = std::fmin(mn[k], h[6 * b + k]); mx[k] = std::fmax(mx[k], h[6 * b + 3 + k]); }
+    return 0;
+}
+
+// stable radix sort of (key, value) pairs; result in keys_out / vals_out
+int sort_pairs(rptx_ctx* ctx, uint64_t* keys_in, uint64_t* keys_out, uint32_t* vals_in, uint32_t* vals_out, uint32_t n, int end_bit) {
+    size_t tmp_bytes = 0;
+    CK(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys_in, keys_out, vals_in, vals_out, (int)n, 0, end_bit, ctx->stream));
+    void* tmp = nullptr;
+    CK(cudaMalloc(&tmp, std::max<size_t>(tmp_bytes, 16)));
+    cudaError_t e = cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, keys_in, keys_out, vals_in, vals_out, (int)n, 0, end_bit, ctx->stream);
+    ctx->launches += 4;
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    cudaFree(tmp);
+    if (e != cudaSuccess) return ctx_fail(ctx, std::string("radix sort: ") + cudaGetErrorString(e));
+    return 0;
+}
+
+// canonical order of a photon list: permutation sorting the rows by key
+int canonical_order(rptx_ctx* ctx, const PhotonRec* rows, uint32_t n, uint32_t** d_idx_out) {
+    uint64_t *k0 = nullptr, *k1 = nullptr;
+    uint32_t *i0 = nullptr, *i1 = nullptr;
+    CK(dev_alloc(&k0, n, nullptr));
+    CK(dev_alloc(&k1, n, nullptr));
+    CK(dev_alloc(&i0, n, nullptr));
+    CK(dev_alloc(&i1, n, nullptr));
+    k_rows_keys<<<grid_for(n, 256), 256, 0, ctx->stream>>>(rows, n, k0, i0);
+    ctx->launches++;
+    const int rc = sort_pairs(ctx, k0, k1, i0, i1, n, 64);
+    cudaFree(k0); cudaFree(k1); cudaFree(i0);
+    if (rc) { cudaFree(i1); return rc; }
+    *d_idx_out = i1;
+    return 0;
+}
+
+void free_owned(std::vector<void*>& owned) {
+    for (void* p : owned) cudaFree(p);
+    owned.clear();
+}
+
+// KdTree::build_by (src/photon.rs:194-199): Morton-ordered structure-of-arrays + implicit box tree.
+// d_canon: canonical permutation of the rows.
+int build_point_map(rptx_ctx* ctx, const PhotonRec* rows, const uint32_t* d_canon, uint32_t n, PointMapHost* out) {
+    cudaStream_t st = ctx->stream;
+    out->dev = PointMapDev{};
+    out->dev.n = n;
+    double *px = nullptr, *py = nullptr, *pz = nullptr, *dir = nullptr, *power = nullptr;
+    uint64_t* key = nullptr;
+    CK(dev_alloc(&px, n, &out->owned)); CK(dev_alloc(&py, n, &out->owned)); CK(dev_alloc(&pz, n, &out->owned));
+    CK(dev_alloc(&dir, 3 * (size_t)n, &out->owned)); CK(dev_alloc(&power, 3 * (size_t)n, &out->owned));
+    CK(dev_alloc(&key, n, &out->owned));
+    const uint32_t n_leaf = (n + kPointLeaf - 1) / kPointLeaf;
+    uint32_t P = 1;
+    while (P < std::max<uint32_t>(n_leaf, 1)) P <<= 1;
+    float4* node_box = nullptr;
+    CK(dev_alloc(&node_box, 2 * (size_t)(2 * P - 1), &out->owned));
+    out->dev.leaf_base = P - 1;
+    out->dev.node_box = node_box;
+    out->dev.px = px; out->dev.py = py; out->dev.pz = pz; out->dev.dir = dir; out->dev.power = power; out->dev.key = key;
+    if (n > 0) {
+        const int blocks = std::min(grid_for(n, 256), 1184);
+        double* d_b = nullptr;
+        CK(dev_alloc(&d_b, (size_t)blocks * 6, nullptr));
+        k_rows_bounds<<<blocks, 256, 0, st>>>(rows, n, d_b);
+        ctx->launches++;
+        double mn[3], mx[3];
+        const int rc0 = reduce_bounds(ctx, d_b, blocks, mn, mx);
+        cudaFree(d_b);
+        if (rc0) return rc0;
+        uint64_t *k0 = nullptr, *k1 = nullptr;
+        uint32_t* i1 = nullptr;
+        CK(dev_alloc(&k0, n, nullptr)); CK(dev_alloc(&k1, n, nullptr)); CK(dev_alloc(&i1, n, nullptr));
+        const double3 dmn = make_double3(mn[0], mn[1], mn[2]);
+        const double3 inv = make_double3(mx[0] > mn[0] ? 1.0 / (mx[0] - mn[0]) : 0.0, mx[1] > mn[1] ? 1.0 / (mx[1] - mn[1]) : 0.0,
+                                         mx[2] > mn[2] ? 1.0 / (mx[2] - mn[2]) : 0.0);
+        k_rows_morton<<<grid_for(n, 256), 256, 0, st>>>(rows, d_canon, n, dmn, inv, k0);
+        ctx->launches++;
+        const int rc = sort_pairs(ctx, k0, k1, const_cast<uint32_t*>(d_canon), i1, n, 63);
+        if (rc == 0) {
+            k_rows_gather<<<grid_for(n, 256), 256, 0, st>>>(rows, i1, n, px, py, pz, dir, power, key);
+            ctx->launches++;
+        }
+        cudaError_t e = cudaStreamSynchronize(st);
+        cudaFree(k0); cudaFree(k1); cudaFree(i1);
+        if (rc) return rc;
+        if (e != cudaSuccess) return ctx_fail(ctx, std::string("point map gather: ") + cudaGetErrorString(e));
+    }
+    k_point_leaves<<<grid_for(P, 256), 256, 0, st>>>(px, py, pz, n, P, P - 1, node_box);
+    ctx->launches++;
+    for (uint32_t level = P / 2; level >= 1; level /= 2) {
+        k_point_level<<<grid_for(level, 256), 256, 0, st>>>(level - 1, level, node_box);
+        ctx->launches++;
+    }
+    CK(cudaGetLastError());
+    CK(cudaStreamSynchronize(st));
+    return 0;
+}
+
+// BVH::build over item boxes (bvh 0.6.0): LBVH with exact f32 unions.  perm[k] = item in leaf slot k.
+int build_box_bvh(rptx_ctx* ctx, const Aabb32* d_boxes, uint32_t n, BoxBvhHost* out, uint32_t** d_perm_out) {
+    out->dev = BoxBvhDev{};
+    out->dev.n = n;
+    *d_perm_out = nullptr;
+    BvhNode* nodes = nullptr;
+    CK(dev_alloc(&nodes, std::max<uint32_t>(n, 1), &out->owned));
+    out->dev.nodes = nodes;
+    if (n == 0) return 0;
+    const int blocks = std::min(grid_for(n, 256), 1184);
+    double* d_b = nullptr;
+    CK(dev_alloc(&d_b, (size_t)blocks * 6, nullptr));
+    k_box_bounds<<<blocks, 256, 0, ctx->stream>>>(d_boxes, n, d_b);
+    ctx->launches++;
+    double mn[3], mx[3];
+    const int rc0 = reduce_bounds(ctx, d_b, blocks, mn, mx);
+    cudaFree(d_b);
+    if (rc0) return rc0;
+    for (int k = 0; k < 3; k++)
+        if (!(mn[k] <= mx[k])) { mn[k] = 0.0; mx[k] = 1.0; }
+    uint32_t* perm = nullptr;
+    CK(dev_alloc(&perm, n, nullptr));
+    static_assert(sizeof(PrimBox) == sizeof(Aabb32), "box layouts match");
+    const int rc = build_lbvh(reinterpret_cast<const PrimBox*>(d_boxes), n, 0.0f, kLeafMax, mn, mx, nodes, perm, &out->dev.root_ref, ctx->stream,
+                              &ctx->launches);
+    if (rc != 0) { cudaFree(perm); return ctx_fail(ctx, std::string("photon BVH build: ") + cudaGetErrorString((cudaError_t)rc)); }
+    *d_perm_out = perm;
+    return 0;
+}
+
+int find_photon_light(const rptx_scene* s, uint32_t* index) {
+    for (size_t i = 0; i < s->lights.size(); i++)
+        if (s->lights[i].kind == RPTX_LIGHT_OBJECT) { *index = (uint32_t)i; return 0; }
+    return 1;
+}
+
+}  // namespace
+
+struct rptx_photon_map {
+    rptx_ctx* ctx = nullptr;
+    rptx_scene* scene = nullptr;
+    int kind = 0;
+    PointMapHost surface, volume;
+    BoxBvhHost bvh;
+    SphereMapDev spheres = {};
+    BeamMapDev beams = {};
+    std::vector<void*> owned;
+    double build_ms = 0;
+};
+
+namespace {
+
+// run the emission kernel once over [first, first + count); returns the deposit counts
+int emit_once(rptx_ctx* ctx, rptx_scene* scene, const EmitParams& ep, PhotonRec* d_surf, uint64_t cap_s, PhotonRec* d_vol, uint64_t cap_v,
+              uint64_t counts[3]) {
+    cudaStream_t st = ctx->stream;
+    unsigned long long* d_ctr = nullptr;  // [0] surface count, [1] volume count, [2] work head, [3] rays
+    CK(cudaMalloc((void**)&d_ctr, sizeof(unsigned long long) * 4));
+    CK(cudaMemsetAsync(d_ctr, 0, sizeof(unsigned long long) * 4, st));
+    PhotonSink surf{d_surf, d_ctr, cap_s}, vol{d_vol, d_ctr + 1, cap_v};
+    const SceneDev sc = rptx_host::scene_dev(scene);
+    const MediumDev md = rptx_host::medium_dev(scene);
+    const int blocks = (int)std::min<uint64_t>((uint64_t)ctx->sm_count * 8, (ep.count + 127) / 128);
+    k_photon_trace<<<std::max(blocks, 1), 128, 0, st>>>(sc, md, ep, surf, vol, d_ctr + 2, d_ctr + 3);
+    ctx->launches++;
+    unsigned long long h[4] = {0, 0, 0, 0};
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaMemcpyAsync(h, d_ctr, sizeof(h), cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    cudaFree(d_ctr);
+    if (e != cudaSuccess) return ctx_fail(ctx, std::string("photon emission: ") + cudaGetErrorString(e));
+    counts[0] = h[0]; counts[1] = h[1]; counts[2] = h[3];
+    return 0;
+}
+
+template <int KMAX>
+void launch_gather(const SceneDev& sc, const MediumDev& md, const PhotonMapDev& pm, const GatherArgs& ga, unsigned long long* stats,
+                   cudaStream_t st) {
+    const size_t threads = (size_t)ga.n_pixels * ga.n_lanes;
+    k_photon_gather<KMAX><<<grid_for(threads, 128), 128, 0, st>>>(sc, md, pm, ga, stats);
+}
+
+}  // namespace
+
+extern "C" {
+
+int rptx_photons_create(rptx_ctx* ctx, rptx_photons** out) {
+    if (!ctx || !out) return 1;
+    rptx_photons* p = new rptx_photons();
+    p->ctx = ctx;
+    *out = p;
+    return 0;
+}
+
+void rptx_photons_destroy(rptx_photons* p) {
+    if (!p) return;
+    cudaSetDevice(p->ctx->device);
+    cudaFree(p->d_rows[0]); cudaFree(p->d_rows[1]);
+    delete p;
+}
+
+int rptx_photons_emit(rptx_ctx* ctx, rptx_scene* scene, const rptx_params* params, uint64_t photon_count_total, uint64_t first,
+                      uint64_t count, int32_t kind, rptx_photons** out) {
+    if (!ctx || !out) return 1;
+    *out = nullptr;
+    if (!scene || !params) return ctx_fail(ctx, "rptx_photons_emit: null argument");
+    if (scene->ctx != ctx) return ctx_fail(ctx, "scene belongs to another context");
+    if (!scene->committed) return ctx_fail(ctx, "scene not committed");
+    if (kind < RPTX_PHOTON_MAP || kind > RPTX_PHOTON_BEAM_BEAM) return ctx_fail(ctx, "unknown photon render kind");
+    if (photon_count_total == 0 || first + count > photon_count_total) return ctx_fail(ctx, "bad photon range");
+    if (photon_count_total >= (1ull << 47)) return ctx_fail(ctx, "too many photons");
+    EmitParams ep;
+    ep.seed = params->seed; ep.first = first; ep.count = count; ep.kind = kind;
+    ep.power = params->watts / (double)photon_count_total;
+    if (find_photon_light(scene, &ep.light_index)) return ctx_fail(ctx, "Only found non-object lights while photon mapping");  // src/photon.rs:798
+    CK(cudaSetDevice(ctx->device));
+    cudaEvent_t e0, e1;
+    CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+    CK(cudaEventRecord(e0, ctx->stream));
+    rptx_photons* p = new rptx_photons();
+    p->ctx = ctx;
+    uint64_t counts[3] = {0, 0, 0};
+    uint64_t cap_s, cap_v;
+    int rc = 0;
+    if (count > (1ull << 17)) {
+        // counting-only pilot over the first 2^16 photons sizes the append buffers
+        EmitParams pilot = ep;
+        pilot.count = 1ull << 16;
+        rc = emit_once(ctx, scene, pilot, nullptr, 0, nullptr, 0, counts);
+        const double rs = (double)counts[0] / (double)pilot.count, rv = (double)counts[1] / (double)pilot.count;
+        cap_s = (uint64_t)((double)count * rs * 1.03) + 65536;
+        cap_v = (uint64_t)((double)count * rv * 1.03) + 65536;
+    } else {
+        cap_s = cap_v = count * 16 + 1024;
+    }
+    while (rc == 0) {
+        cudaFree(p->d_rows[0]); cudaFree(p->d_rows[1]);
+        p->d_rows[0] = p->d_rows[1] = nullptr;
+        cudaError_t e = cudaMalloc((void**)&p->d_rows[0], std::max<uint64_t>(cap_s, 1) * sizeof(PhotonRec));
+        if (e == cudaSuccess) e = cudaMalloc((void**)&p->d_rows[1], std::max<uint64_t>(cap_v, 1) * sizeof(PhotonRec));
+        if (e != cudaSuccess) { rc = ctx_fail(ctx, std::string("photon buffers: ") + cudaGetErrorString(e)); break; }
+        p->cap[0] = cap_s; p->cap[1] = cap_v;
+        rc = emit_once(ctx, scene, ep, p->d_rows[0], cap_s, p->d_rows[1], cap_v, counts);
+        if (rc) break;
+        if (counts[0] <= cap_s && counts[1] <= cap_v) break;
+        cap_s = std::max(cap_s, counts[0]); cap_v = std::max(cap_v, counts[1]);  // deterministic walk: exact sizes now known
+    }
+    if (rc == 0) {
+        cudaEventRecord(e1, ctx->stream);
+        cudaEventSynchronize(e1);
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, e0, e1);
+        p->emit_ms = ms;
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    if (rc) { rptx_photons_destroy(p); return rc; }
+    if (counts[0] >= (1ull << 32) || counts[1] >= (1ull << 32)) { rptx_photons_destroy(p); return ctx_fail(ctx, "photon list exceeds 2^32 records"); }
+    p->n[0] = counts[0]; p->n[1] = counts[1]; p->emitted = count; p->rays = counts[2];
+    *out = p;
+    return 0;
+}
+
+static int photons_reserve(rptx_photons* p, int which, uint64_t need) {
+    rptx_ctx* ctx = p->ctx;
+    if (need <= p->cap[which]) return 0;
+    const uint64_t cap = std::max<uint64_t>(need, p->cap[which] * 2);
+    PhotonRec* nr = nullptr;
+    CK(cudaMalloc((void**)&nr, cap * sizeof(PhotonRec)));
+    if (p->n[which]) CK(cudaMemcpyAsync(nr, p->d_rows[which], p->n[which] * sizeof(PhotonRec), cudaMemcpyDeviceToDevice, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    cudaFree(p->d_rows[which]);
+    p->d_rows[which] = nr;
+    p->cap[which] = cap;
+    return 0;
+}
+
+int rptx_photons_append_host(rptx_photons* p, int32_t which, const void* rows, size_t n) {
+    if (!p) return 1;
+    rptx_ctx* ctx = p->ctx;
+    if (which < 0 || which > 1) return ctx_fail(ctx, "which must be 0 (surface) or 1 (volume)");
+    if (n == 0) return 0;
+    if (!rows) return ctx_fail(ctx, "null rows");
+    CK(cudaSetDevice(ctx->device));
+    if (p->n[which] + n >= (1ull << 32)) return ctx_fail(ctx, "photon list exceeds 2^32 records");
+    if (int rc = photons_reserve(p, which, p->n[which] + n)) return rc;
+    CK(cudaMemcpyAsync(p->d_rows[which] + p->n[which], rows, n * sizeof(PhotonRec), cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    p->n[which] += n;
+    return 0;
+}
+
+int rptx_photons_append_device(rptx_photons* p, int32_t which, const void* d_rows, size_t n) {
+    if (!p) return 1;
+    rptx_ctx* ctx = p->ctx;
+    if (which < 0 || which > 1) return ctx_fail(ctx, "which must be 0 (surface) or 1 (volume)");
+    if (n == 0) return 0;
+    if (!d_rows) return ctx_fail(ctx, "null rows");
+    CK(cudaSetDevice(ctx->device));
+    if (p->n[which] + n >= (1ull << 32)) return ctx_fail(ctx, "photon list exceeds 2^32 records");
+    if (int rc = photons_reserve(p, which, p->n[which] + n)) return rc;
+    CK(cudaMemcpyAsync(p->d_rows[which] + p->n[which], d_rows, n * sizeof(PhotonRec), cudaMemcpyDeviceToDevice, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    p->n[which] += n;
+    return 0;
+}
+
+int rptx_photons_count(const rptx_photons* p, uint64_t counts[2]) {
+    if (!p || !counts) return 1;
+    counts[0] = p->n[0]; counts[1] = p->n[1];
+    return 0;
+}
+
+void* rptx_photons_device_ptr(rptx_photons* p, int32_t which) { return (p && which >= 0 && which <= 1) ? (void*)p->d_rows[which] : nullptr; }
+
+int rptx_photons_download(rptx_photons* p, int32_t which, void* rows) {
+    if (!p) return 1;
+    rptx_ctx* ctx = p->ctx;
+    if (which < 0 || which > 1 || !rows) return ctx_fail(ctx, "rptx_photons_download: bad argument");
+    CK(cudaSetDevice(ctx->device));
+    if (p->n[which]) CK(cudaMemcpyAsync(rows, p->d_rows[which], p->n[which] * sizeof(PhotonRec), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+int rptx_photons_stats(const rptx_photons* p, uint64_t* emitted, uint64_t* rays, double* emit_ms) {
+    if (!p) return 1;
+    if (emitted) *emitted = p->emitted;
+    if (rays) *rays = p->rays;
+    if (emit_ms) *emit_ms = p->emit_ms;
+    return 0;
+}
+
+void rptx_photon_map_destroy(rptx_photon_map* m) {
+    if (!m) return;
+    cudaSetDevice(m->ctx->device);
+    free_owned(m->surface.owned); free_owned(m->volume.owned); free_owned(m->bvh.owned); free_owned(m->owned);
+    delete m;
+}
+
+int rptx_photon_map_build(rptx_ctx* ctx, rptx_scene* scene, rptx_photons* photons, int32_t kind, rptx_photon_map** out) {
+    if (!ctx || !out) return 1;
+    *out = nullptr;
+    if (!scene || !photons) return ctx_fail(ctx, "rptx_photon_map_build: null argument");
+    if (photons->ctx != ctx || scene->ctx != ctx) return ctx_fail(ctx, "objects belong to another context");
+    if (kind < RPTX_PHOTON_MAP || kind > RPTX_PHOTON_BEAM_BEAM) return ctx_fail(ctx, "unknown photon render kind");
+    CK(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    cudaEvent_t e0, e1;
+    CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+    CK(cudaEventRecord(e0, st));
+    rptx_photon_map* m = new rptx_photon_map();
+    m->ctx = ctx; m->scene = scene; m->kind = kind;
+    int rc = 0;
+    uint32_t *canon_s = nullptr, *canon_v = nullptr, *perm = nullptr;
+    const uint32_t ns = (uint32_t)photons->n[0], nv = (uint32_t)photons->n[1];
+    auto body = [&]() -> int {
+        if (int r = canonical_order(ctx, photons->d_rows[0], ns, &canon_s)) return r;
+        if (int r = build_point_map(ctx, photons->d_rows[0], canon_s, ns, &m->surface)) return r;
+        if (int r = canonical_order(ctx, photons->d_rows[1], nv, &canon_v)) return r;
+        if (kind == RPTX_PHOTON_MAP || kind == RPTX_PHOTON_POINT_BEAM) {
+            if (int r = build_point_map(ctx, photons->d_rows[1], canon_v, nv, &m->volume)) return r;
+        }
+        if (kind == RPTX_PHOTON_POINT_BEAM) {
+            double *radius = nullptr, *center = nullptr, *rad = nullptr, *dir = nullptr, *power = nullptr;
+            Aabb32 *boxes = nullptr, *obox = nullptr;
+            CK(dev_alloc(&radius, nv, &m->owned));
+            CK(dev_alloc(&boxes, nv, &m->owned));
+            if (nv) {
+                k_sphere_radius<<<grid_for(nv, 128), 128, 0, st>>>(m->volume.dev, radius, boxes);
+                ctx->launches++;
+            }
+            if (int r = build_box_bvh(ctx, boxes, nv, &m->bvh, &perm)) return r;
+            CK(dev_alloc(&center, 3 * (size_t)nv, &m->owned)); CK(dev_alloc(&rad, nv, &m->owned));
+            CK(dev_alloc(&dir, 3 * (size_t)nv, &m->owned)); CK(dev_alloc(&power, 3 * (size_t)nv, &m->owned));
+            CK(dev_alloc(&obox, nv, &m->owned));
+            if (nv) {
+                k_sphere_gather<<<grid_for(nv, 256), 256, 0, st>>>(m->volume.dev, radius, boxes, perm, nv, center, rad, dir, power, obox);
+                ctx->launches++;
+            }
+            m->bvh.dev.boxes = obox;
+            m->spheres.bvh = m->bvh.dev;
+            m->spheres.center = center; m->spheres.radius = rad; m->spheres.dir = dir; m->spheres.power = power;
+        } else if (kind == RPTX_PHOTON_BEAM_BEAM) {
+            double *start = nullptr, *dirn = nullptr, *len = nullptr, *power = nullptr, *ostart = nullptr, *odirn = nullptr, *olen = nullptr,
+                   *opower = nullptr;
+            Aabb32 *boxes = nullptr, *obox = nullptr;
+            CK(dev_alloc(&start, 3 * (size_t)nv, &m->owned)); CK(dev_alloc(&dirn, 3 * (size_t)nv, &m->owned));
+            CK(dev_alloc(&len, nv, &m->owned)); CK(dev_alloc(&power, 3 * (size_t)nv, &m->owned));
+            CK(dev_alloc(&boxes, nv, &m->owned));
+            if (nv) {
+                k_beam_make<<<grid_for(nv, 256), 256, 0, st>>>(photons->d_rows[1], canon_v, nv, start, dirn, len, power, boxes);
+                ctx->launches++;
+            }
+            if (int r = build_box_bvh(ctx, boxes, nv, &m->bvh, &perm)) return r;
+            CK(dev_alloc(&ostart, 3 * (size_t)nv, &m->owned)); CK(dev_alloc(&odirn, 3 * (size_t)nv, &m->owned));
+            CK(dev_alloc(&olen, nv, &m->owned)); CK(dev_alloc(&opower, 3 * (size_t)nv, &m->owned));
+            CK(dev_alloc(&obox, nv, &m->owned));
+            if (nv) {
+                k_beam_gather<<<grid_for(nv, 256), 256, 0, st>>>(start, dirn, len, power, boxes, perm, nv, ostart, odirn, olen, opower, obox);
+                ctx->launches++;
+            }
+            m->bvh.dev.boxes = obox;
+            m->beams.bvh = m->bvh.dev;
+            m->beams.start = ostart; m->beams.dirn = odirn; m->beams.len = olen; m->beams.power = opower;
+        }
+        CK(cudaGetLastError());
+        CK(cudaStreamSynchronize(st));
+        return 0;
+    };
+    rc = body();
+    cudaFree(canon_s); cudaFree(canon_v); cudaFree(perm);
+    if (rc == 0) {
+        cudaEventRecord(e1, st);
+        cudaEventSynchronize(e1);
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, e0, e1);
+        m->build_ms = ms;
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    if (rc) { rptx_photon_map_destroy(m); return rc; }
+    *out = m;
+    return 0;
+}
+
+int rptx_photon_map_stats(const rptx_photon_map* m, uint64_t counts[3], double* build_ms) {
+    if (!m) return 1;
+    if (counts) { counts[0] = m->surface.dev.n; counts[1] = m->volume.dev.n; counts[2] = m->bvh.dev.n; }
+    if (build_ms) *build_ms = m->build_ms;
+    return 0;
+}
+
+int rptx_photon_gather_trace(rptx_film* f, rptx_photon_map* m, uint32_t iterations) {
+    if (!f) return 1;
+    rptx_ctx* ctx = f->ctx;
+    if (!m) return ctx_fail(ctx, "null photon map");
+    if (m->ctx != ctx || m->scene != f->scene) return ctx_fail(ctx, "photon map belongs to another context or scene");
+    if (iterations == 0) return ctx_fail(ctx, "iterations must be > 0");
+    const uint64_t kmax = std::max(f->params.gather_size, f->params.gather_size_volume);
+    if (kmax > 1024) return ctx_fail(ctx, "gather sizes above 1024 are not supported");
+    CK(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    GatherArgs ga;
+    ga.cam = f->cam;
+    BatchParams& bp = ga.bp;
+    bp.width = f->params.width; bp.height = f->params.height; bp.max_bounces = f->params.max_bounces;
+    bp.seed = f->params.seed; bp.batch_base = f->next_sample; bp.iterations = iterations;
+    bp.shard_count = f->params.shard_count; bp.shard_index = f->params.shard_index;
+    bp.n_local = iterations > bp.shard_index ? (iterations - bp.shard_index + bp.shard_count - 1) / bp.shard_count : 0;
+    ga.n_pixels = f->pool.n_pixels;
+    ga.n_lanes = std::max<uint32_t>(1, std::min(f->pool.n_lanes, bp.n_local));
+    ga.ax = f->pool.ax; ga.ay = f->pool.ay; ga.az = f->pool.az;
+    PhotonMapDev pm;
+    std::memset(&pm, 0, sizeof(pm));
+    pm.kind = m->kind;
+    pm.surface = m->surface.dev; pm.volume = m->volume.dev; pm.spheres = m->spheres; pm.beams = m->beams;
+    pm.gather_size = (uint32_t)f->params.gather_size; pm.gather_size_volume = (uint32_t)f->params.gather_size_volume;
+    const SceneDev sc = rptx_host::scene_dev(f->scene);
+    const MediumDev md = rptx_host::medium_dev(f->scene);
+    CK(cudaEventRecord(f->ev0, st));
+    if (kmax <= 32) launch_gather<32>(sc, md, pm, ga, f->q.stats, st);
+    else if (kmax <= 128) launch_gather<128>(sc, md, pm, ga, f->q.stats, st);
+    else launch_gather<1024>(sc, md, pm, ga, f->q.stats, st);
+    k_lane_reduce<<<grid_for(ga.n_pixels, 128), 128, 0, st>>>(ga.ax, ga.ay, ga.az, ga.n_pixels, ga.n_lanes, f->d_batch_sum);
+    ctx->launches += 2;
+    CK(cudaGetLastError());
+    CK(cudaEventRecord(f->ev1, st));
+    CK(cudaStreamSynchronize(st));
+    float ms = 0.f;
+    CK(cudaEventElapsedTime(&ms, f->ev0, f->ev1));
+    f->stats.device_ms = ms;
+    return 0;
+}
+
+int rptx_photon_map_knn(rptx_photon_map* m, int32_t which, const double* q, size_t n, uint32_t k, uint64_t* keys, double* d2,
+                        uint32_t* counts) {
+    if (!m) return 1;
+    rptx_ctx* ctx = m->ctx;
+    if (which < 0 || which > 1) return ctx_fail(ctx, "which must be 0 (surface) or 1 (volume)");
+    if (k == 0 || k > 1024) return ctx_fail(ctx, "k must be in 1..1024");
+    if (n == 0) return 0;
+    if (!q || !keys || !d2 || !counts) return ctx_fail(ctx, "rptx_photon_map_knn: null argument");
+    CK(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    double *d_q = nullptr, *d_d2 = nullptr;
+    uint64_t* d_keys = nullptr;
+    uint32_t* d_counts = nullptr;
+    std::vector<void*> tmp;
+    auto done = [&](int rc) { free_owned(tmp); return rc; };
+#define CKT(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return done(ctx_fail(ctx, std::string(#call) + ": " + cudaGetErrorString(e_))); } while (0)
+    CKT(dev_alloc(&d_q, 3 * n, &tmp)); CKT(dev_alloc(&d_d2, n * k, &tmp)); CKT(dev_alloc(&d_keys, n * k, &tmp)); CKT(dev_alloc(&d_counts, n, &tmp));
+    CKT(cudaMemcpyAsync(d_q, q, sizeof(double) * 3 * n, cudaMemcpyHostToDevice, st));
+    const PointMapDev pmap = which == 0 ? m->surface.dev : m->volume.dev;
+    if (k <= 32) k_knn_batch<32><<<grid_for(n, 128), 128, 0, st>>>(pmap, d_q, n, k, d_keys, d_d2, d_counts);
+    else if (k <= 128) k_knn_batch<128><<<grid_for(n, 128), 128, 0, st>>>(pmap, d_q, n, k, d_keys, d_d2, d_counts);
+    else k_knn_batch<1024><<<grid_for(n, 128), 128, 0, st>>>(pmap, d_q, n, k, d_keys, d_d2, d_counts);
+    ctx->launches++;
+    CKT(cudaGetLastError());
+    CKT(cudaMemcpyAsync(keys, d_keys, sizeof(uint64_t) * n * k, cudaMemcpyDeviceToHost, st));
+    CKT(cudaMemcpyAsync(d2, d_d2, sizeof(double) * n * k, cudaMemcpyDeviceToHost, st));
+    CKT(cudaMemcpyAsync(counts, d_counts, sizeof(uint32_t) * n, cudaMemcpyDeviceToHost, st));
+    CKT(cudaStreamSynchronize(st));
+#undef CKT
+    return done(0);
+}
+
+// sphere radii (PhotonPointBeam maps) keyed by photon, for parity checks: radius of the sphere in BVH slot i and its centre
+int rptx_photon_map_spheres(rptx_photon_map* m, double* center, double* radius) {
+    if (!m) return 1;
+    rptx_ctx* ctx = m->ctx;
+    if (m->kind != RPTX_PHOTON_POINT_BEAM) return ctx_fail(ctx, "not a point-beam map");
+    CK(cudaSetDevice(ctx->device));
+    const size_t n = m->bvh.dev.n;
+    if (n && center) CK(cudaMemcpyAsync(center, m->spheres.center, sizeof(double) * 3 * n, cudaMemcpyDeviceToHost, ctx->stream));
+    if (n && radius) CK(cudaMemcpyAsync(radius, m->spheres.radius, sizeof(double) * n, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+int rptx_photon_render(rptx_ctx* ctx, rptx_scene* scene, const rptx_camera* camera, const rptx_params* params, uint64_t photon_count,
+                       int32_t kind, uint8_t* out_rgb8, double* out_mean) {
+    if (!ctx) return 1;
+    if (!scene || !camera || !params) return ctx_fail(ctx, "rptx_photon_render: null argument");
+    rptx_photons* ph = nullptr;
+    rptx_photon_map* map = nullptr;
+    rptx_film* film = nullptr;
+    int rc = rptx_photons_emit(ctx, scene, params, photon_count, 0, photon_count, kind, &ph);
+    if (rc == 0) rc = rptx_photon_map_build(ctx, scene, ph, kind, &map);
+    if (ph) { rptx_photons_destroy(ph); ph = nullptr; }
+    if (rc == 0) rc = rptx_photon_gather_begin(ctx, scene, camera, params, &film);
+    if (rc == 0) rc = rptx_photon_gather_trace(film, map, params->num_samples);
+    if (rc == 0) rc = rptx_render_sample_commit(film, params->num_samples);
+    if (rc == 0 && out_rgb8) rc = rptx_film_image_rgb8(film, out_rgb8);
+    if (rc == 0 && out_mean) rc = rptx_film_mean(film, out_mean);
+    if (film) rptx_film_destroy(film);
+    if (map) rptx_photon_map_destroy(map);
+    return rc;
+}
+
+}  // extern "C"

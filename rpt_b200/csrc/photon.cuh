@@ -1,0 +1,578 @@
+// Photon integrators of the B200 core: device records and kernels replacing src/photon.rs of
+// the reference — photon emission and tracing (shoot_photon :724-799, trace_photon :803-946),
+// the photon-map structures (PhotonMap::new_* :193-305; the kd-tree 0.4.1 and bvh 0.6.0 crates
+// behind them) and the three radiance estimators (estimate_indirect :316-627) with the camera
+// pass (get_color_with_photon_map :950-985).
+//
+// Layout in HBM:
+//  * emission appends 104-byte PhotonRec rows (the reference's Photon, :25-34, plus a 64-bit
+//    key = photon index << 16 | depth that makes the list order canonical after a sort, so
+//    results do not depend on thread scheduling or on how many GPUs emitted the photons);
+//  * a point map keeps its photons in 63-bit Morton order as structure-of-arrays (f64 position
+//    triples read by the kNN search; direction / power / key touched only for the k winners)
+//    under an implicit complete binary tree of f32 boxes (32 B per node, two float4 loads)
+//    whose leaves are kPointLeaf consecutive photons;
+//  * photon spheres / beams sit under the same LBVH the object accelerator uses
+//    (bvh_build.cu), with their own f32 boxes computed exactly as the reference does
+//    (:76-105, :119-128) so the candidate set of BVH::traverse is reproduced.
+#pragma once
+#include <cooperative_groups.h>
+#include <cooperative_groups/reduce.h>
+
+#include "path.cuh"
+#include "shading.cuh"
+#include "trace.cuh"
+
+namespace rptx {
+
+namespace cg = cooperative_groups;
+
+struct PhotonRec {
+    double pos[3], dir[3], power[3], start[3];
+    uint64_t key;
+};
+static_assert(sizeof(PhotonRec) == 104, "PhotonRec is 13 x 8 bytes (rows of the C ABI)");
+
+constexpr double kPhotonRrDiffuse = 0.7;  // src/photon.rs:823
+constexpr double kBeamThin = 0.001;       // src/photon.rs:780
+constexpr double kBeamRadius = 3.0;       // src/photon.rs:277
+constexpr uint32_t kSphereKnn = 10;       // src/photon.rs:217
+constexpr int kPointLeaf = 8;
+
+RPTX_HD uint64_t photon_key(uint64_t photon_index, uint32_t depth) {
+    return (photon_index << 16) | (uint64_t)(depth < 65535u ? depth : 65535u);
+}
+
+struct PhotonSink {
+    PhotonRec* rows;
+    unsigned long long* count;  // keeps counting past cap (the host then grows the buffer and re-runs)
+    unsigned long long cap;
+};
+
+// one atomic per group of converged lanes
+RPTX_D void photon_deposit(const PhotonSink& s, d3 pos, d3 dir, d3 power, d3 start, uint64_t key) {
+    const cg::coalesced_group g = cg::coalesced_threads();
+    unsigned long long base = 0;
+    if (g.thread_rank() == 0) base = atomicAdd(s.count, (unsigned long long)g.size());
+    base = g.shfl(base, 0);
+    const unsigned long long i = base + g.thread_rank();
+    if (i >= s.cap) return;
+    PhotonRec* r = s.rows + i;
+    r->pos[0] = pos.x; r->pos[1] = pos.y; r->pos[2] = pos.z;
+    r->dir[0] = dir.x; r->dir[1] = dir.y; r->dir[2] = dir.z;
+    r->power[0] = power.x; r->power[1] = power.y; r->power[2] = power.z;
+    r->start[0] = start.x; r->start[1] = start.y; r->start[2] = start.z;
+    r->key = key;
+}
+
+struct EmitParams {
+    uint64_t seed;
+    uint64_t first, count;  // this call shoots photon indices [first, first + count)
+    double power;           // watts / photon_count (src/photon.rs:671)
+    int kind;               // PhotonRenderKind
+    uint32_t light_index;   // first Light::Object of the scene (src/photon.rs:727-729)
+};
+
+// shoot_photon + trace_photon as one walk per thread; persistent warps pull 32 photon indices
+// at a time.  The reference's recursion deposits a vertex only when the walk continues past it
+// (:842-866), which the loop reproduces by depositing right after a successful sample_f.
+__global__ void __launch_bounds__(128) k_photon_trace(const __grid_constant__ SceneDev sc, const MediumDev md, const EmitParams ep,
+                                                      PhotonSink surf, PhotonSink vol, unsigned long long* __restrict__ work_head,
+                                                      unsigned long long* __restrict__ stats) {
+    unsigned long long my_rays = 0;
+    for (;;) {
+        unsigned long long base = 0;
+        if ((threadIdx.x & 31u) == 0) base = atomicAdd(work_head, 32ull);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (base >= ep.count) break;
+        const unsigned long long i = base + (threadIdx.x & 31u);
+        if (i >= ep.count) continue;
+        const uint64_t pid = ep.first + i;
+        Rng rng = Rng::make(ep.seed, kDomainPhoton, pid, 0);
+        const Light& l = sc.lights[ep.light_index];
+        d3 pos, n;
+        double light_pdf;
+        sample_light_shape(sc, l, mk3(0, 0, 0), rng, &pos, &n, &light_pdf);
+        const double phi = 2.0 * kPi * rng.gen();
+        const double theta = acos(1.0 - rng.gen());
+        const double st = sin(theta);
+        const d3 hemi = mk3(st * cos(phi), cos(theta), st * sin(phi));
+        const Rot3 rot = rotation_from_y(n);
+        RayD ray;
+        ray.o = pos;
+        ray.d = rot_apply(rot, hemi);
+        d3 power = ep.power * mat_color(l.material);
+        for (uint32_t depth = 0;; depth++) {
+            const d3 wo = -normalize(ray.d);
+            Hit h;
+            h.t = CUDART_INF;
+            closest_hit<kClosest>(sc, ray, kEpsilon, 0.0, h);
+            my_rays++;
+            const bool hit = h.inst != kNoHit;
+            double dsamp = CUDART_INF;
+            if (md.kind != 0) dsamp = medium_sample_d(md, rng);
+            else if (!hit) break;
+            if (md.kind != 0 && (!hit || dsamp < h.t)) {
+                // trace_in_volume, src/photon.rs:877-927
+                const d3 collision = ray.o + dsamp * ray.d;
+                const d3 mc = md.color(collision);
+                const double scat = md.sigma_s, extinction = md.sigma_a + md.sigma_s;
+                const d3 attenuated = cmul(power, mc) * scat / extinction;
+                const double rr_prob = scat / extinction;
+                const bool go = rng.gen() < rr_prob;
+                d3 wi = mk3(0, 0, 0);
+                if (go) medium_sample_ph(rng, &wi);
+                if (ep.kind == 2) {  // beam-beam thinning, src/photon.rs:773-793
+                    Rng thin = Rng::make(ep.seed, kDomainThin, pid, depth);
+                    if (thin.gen() < kBeamThin) photon_deposit(vol, collision, wo, power / kBeamThin, ray.o, photon_key(pid, depth));
+                } else {
+                    photon_deposit(vol, collision, wo, power, ray.o, photon_key(pid, depth));
+                }
+                if (!go) break;
+                power = attenuated * md.phase / md.phase;  // phase(wo, wi) / ph_p, both the medium's constant
+                ray.o = collision;
+                ray.d = wi;
+            } else {
+                // trace_on_surface, src/photon.rs:813-874
+                uint32_t prim, inst;
+                const d3 hn = hit_normal(sc, ray, h, &prim, &inst);
+                const d3 world_pos = ray.o + h.t * ray.d;
+                const Material mat = sc.materials[h.obj];
+                if (!(rng.gen() < kPhotonRrDiffuse)) break;  // absorbed
+                d3 wi;
+                double pdf;
+                if (!mat_sample_f(mat, hn, wo, rng, &wi, &pdf)) break;  // total internal reflection
+                const d3 f = mat_bsdf(mat, hn, wo, wi);
+                const double wn = dot(wi, hn);
+                const double cosine_term = wn > 0.0 ? wn : 1.0;
+                const d3 attenuated = cmul(power, f) * cosine_term / pdf / kPhotonRrDiffuse;
+                if (!mat_is_mirror(mat)) photon_deposit(surf, world_pos, wo, power, world_pos, photon_key(pid, depth));
+                power = attenuated;
+                ray.o = world_pos;
+                ray.d = wi;
+            }
+        }
+    }
+    const cg::coalesced_group g = cg::coalesced_threads();
+    const unsigned long long tot = cg::reduce(g, my_rays, cg::plus<unsigned long long>());
+    if (g.thread_rank() == 0 && tot) atomicAdd(&stats[0], tot);
+}
+
+// ------------------------------------------------------------------ point map (kd-tree 0.4.1)
+
+struct PointMapDev {
+    uint32_t n;          // photons
+    uint32_t leaf_base;  // heap index of the first leaf node (= P - 1, P = leaves rounded up to 2^m)
+    const float4* node_box;  // [2P - 1][2]: (min xyz, -), (max xyz, -); empty nodes are inverted
+    const double *px, *py, *pz;  // Morton order
+    const double* dir;    // [n][3]
+    const double* power;  // [n][3]
+    const uint64_t* key;  // [n]
+};
+
+// k nearest so far: binary max-heap on the squared distance
+template <int KMAX>
+struct KnnHeap {
+    double d2[KMAX];
+    uint32_t idx[KMAX];
+    uint32_t size, k;
+    RPTX_D double worst() const { return size < k ? CUDART_INF : d2[0]; }
+    RPTX_D void push(double d, uint32_t id) {
+        if (size < k) {
+            uint32_t c = size++;
+            while (c > 0) {
+                const uint32_t p = (c - 1) >> 1;
+                if (!(d2[p] < d)) break;
+                d2[c] = d2[p]; idx[c] = idx[p];
+                c = p;
+            }
+            d2[c] = d; idx[c] = id;
+        } else if (d < d2[0]) {
+            sift_down(0, size, d, id);
+        }
+    }
+    RPTX_D void sift_down(uint32_t c, uint32_t n, double d, uint32_t id) {
+        for (;;) {
+            uint32_t l = 2 * c + 1;
+            if (l >= n) break;
+            if (l + 1 < n && d2[l + 1] > d2[l]) l++;
+            if (!(d2[l] > d)) break;
+            d2[c] = d2[l]; idx[c] = idx[l];
+            c = l;
+        }
+        d2[c] = d; idx[c] = id;
+    }
+    // heap -> ascending order in place (nearests() returns ascending)
+    RPTX_D void sort_ascending() {
+        for (uint32_t n = size; n > 1; n--) {
+            const double d = d2[n - 1];
+            const uint32_t id = idx[n - 1];
+            d2[n - 1] = d2[0]; idx[n - 1] = idx[0];
+            sift_down(0, n - 1, d, id);
+        }
+    }
+};
+
+constexpr double kBoxShrink = 0.99999999999999;  // rounding slack of the box lower bound
+
+RPTX_D double box_dist2(float4 mn, float4 mx, d3 q) {
+    const double dx = fmax(fmax((double)mn.x - q.x, q.x - (double)mx.x), 0.0);
+    const double dy = fmax(fmax((double)mn.y - q.y, q.y - (double)mx.y), 0.0);
+    const double dz = fmax(fmax((double)mn.z - q.z, q.z - (double)mx.z), 0.0);
+    return dx * dx + dy * dy + dz * dz;
+}
+
+// KdTree::nearests(q, k): exact k nearest by squared Euclidean distance
+template <int KMAX>
+RPTX_D void knn_query(const PointMapDev& m, d3 q, KnnHeap<KMAX>& h) {
+    h.size = 0;
+    if (m.n == 0 || h.k == 0) return;
+    uint32_t stack[32];
+    double stack_d[32];
+    int sp = 0;
+    uint32_t node = 0;
+    for (;;) {
+        bool have = true;
+        while (node < m.leaf_base) {
+            const uint32_t c0 = 2 * node + 1;
+            const float4 a0 = __ldg(m.node_box + 2 * c0), b0 = __ldg(m.node_box + 2 * c0 + 1);
+            const float4 a1 = __ldg(m.node_box + 2 * c0 + 2), b1 = __ldg(m.node_box + 2 * c0 + 3);
+            const double d0 = box_dist2(a0, b0, q), d1 = box_dist2(a1, b1, q);
+            const double w = h.worst();
+            const bool v0 = d0 * kBoxShrink <= w && d0 < CUDART_INF, v1 = d1 * kBoxShrink <= w && d1 < CUDART_INF;
+            if (v0 && v1) {
+                const bool first0 = d0 <= d1;
+                stack[sp] = first0 ? c0 + 1 : c0;
+                stack_d[sp] = first0 ? d1 : d0;
+                sp++;
+                node = first0 ? c0 : c0 + 1;
+            } else if (v0) {
+                node = c0;
+            } else if (v1) {
+                node = c0 + 1;
+            } else {
+                have = false;
+                break;
+            }
+        }
+        if (have) {
+            const uint32_t first = (node - m.leaf_base) * kPointLeaf;
+            const uint32_t last = min(first + (uint32_t)kPointLeaf, m.n);
+            for (uint32_t i = first; i < last; i++) {
+                const double dx = __ldg(m.px + i) - q.x, dy = __ldg(m.py + i) - q.y, dz = __ldg(m.pz + i) - q.z;
+                h.push(dx * dx + dy * dy + dz * dz, i);
+            }
+        }
+        for (;;) {
+            if (sp == 0) return;
+            sp--;
+            if (stack_d[sp] * kBoxShrink <= h.worst()) { node = stack[sp]; break; }
+        }
+    }
+}
+
+// ------------------------------------------------------------------ box BVH (bvh 0.6.0)
+
+struct Aabb32 {
+    float mn[3], mx[3];
+};
+
+// bvh::ray::Ray::new + intersects_aabb (Williams et al. slab test in f32)
+struct Ray32 {
+    float o[3], inv[3];
+    int sign[3];
+};
+RPTX_D Ray32 make_ray32(d3 origin, d3 dir) {
+    Ray32 r;
+    float d[3] = {(float)dir.x, (float)dir.y, (float)dir.z};
+    const float len = sqrtf(d[0] * d[0] + d[1] * d[1] + d[2] * d[2]);
+    r.o[0] = (float)origin.x; r.o[1] = (float)origin.y; r.o[2] = (float)origin.z;
+#pragma unroll
+    for (int i = 0; i < 3; i++) {
+        d[i] = d[i] / len;
+        r.inv[i] = 1.0f / d[i];
+        r.sign[i] = d[i] < 0.0f ? 1 : 0;
+    }
+    return r;
+}
+RPTX_D bool ray32_hits(const Ray32& r, const float* mn, const float* mx) {
+    float ray_min = ((r.sign[0] ? mx[0] : mn[0]) - r.o[0]) * r.inv[0];
+    float ray_max = ((r.sign[0] ? mn[0] : mx[0]) - r.o[0]) * r.inv[0];
+    const float y_min = ((r.sign[1] ? mx[1] : mn[1]) - r.o[1]) * r.inv[1];
+    const float y_max = ((r.sign[1] ? mn[1] : mx[1]) - r.o[1]) * r.inv[1];
+    if (ray_min > y_max || y_min > ray_max) return false;
+    if (y_min > ray_min) ray_min = y_min;
+    if (y_max < ray_max) ray_max = y_max;
+    const float z_min = ((r.sign[2] ? mx[2] : mn[2]) - r.o[2]) * r.inv[2];
+    const float z_max = ((r.sign[2] ? mn[2] : mx[2]) - r.o[2]) * r.inv[2];
+    if (ray_min > z_max || z_min > ray_max) return false;
+    if (z_max < ray_max) ray_max = z_max;
+    return ray_max > 0.0f;
+}
+
+struct BoxBvhDev {
+    uint32_t n;
+    int root_ref;
+    const BvhNode* nodes;  // child boxes are exact f32 unions of the item boxes (pad 0)
+    const Aabb32* boxes;   // per item, leaf order
+};
+
+// PhotonSphere (src/photon.rs:62-73), leaf order, structure-of-arrays
+struct SphereMapDev {
+    BoxBvhDev bvh;
+    const double* center;  // [n][3]
+    const double* radius;  // [n]
+    const double* dir;     // [n][3]
+    const double* power;   // [n][3]
+};
+// PhotonBeam (src/photon.rs:46-59), leaf order
+struct BeamMapDev {
+    BoxBvhDev bvh;
+    const double* start;  // [n][3]
+    const double* dirn;   // [n][3] normalised start -> end
+    const double* len;    // [n] |end - start|
+    const double* power;  // [n][3]
+};
+
+// BVH::traverse: call f(item) for every item whose own f32 box the ray hits.  Inner boxes are
+// exact unions, and the slab test is monotone under enclosure, so culling by them loses nothing.
+template <class F>
+RPTX_D void box_bvh_traverse(const BoxBvhDev& b, const Ray32& r, F&& f) {
+    if (b.n == 0) return;
+    if (b.n == 1) { f(0u); return; }  // a single-leaf root is returned untested
+    int stack[kStackSize];
+    int sp = 0;
+    int cur = b.root_ref;
+    for (;;) {
+        if (cur >= 0) {
+            const float4* np = reinterpret_cast<const float4*>(b.nodes + cur);
+            const float4 a = __ldg(np), bb = __ldg(np + 1), c = __ldg(np + 2), d = __ldg(np + 3);
+            const float lmn[3] = {a.x, a.y, a.z}, lmx[3] = {bb.x, bb.y, bb.z}, rmn[3] = {c.x, c.y, c.z}, rmx[3] = {d.x, d.y, d.z};
+            const bool hl = ray32_hits(r, lmn, lmx), hr = ray32_hits(r, rmn, rmx);
+            const int left = __float_as_int(a.w), right = __float_as_int(c.w);
+            if (hl && hr) { stack[sp++] = right; cur = left; continue; }
+            if (hl) { cur = left; continue; }
+            if (hr) { cur = right; continue; }
+        } else {
+            const uint32_t code = (uint32_t)(~cur);
+            const uint32_t first = code >> 3, count = (code & 7u) + 1u;
+            for (uint32_t i = first; i < first + count; i++) {
+                const Aabb32 bx = b.boxes[i];
+                if (ray32_hits(r, bx.mn, bx.mx)) f(i);
+            }
+        }
+        if (sp == 0) return;
+        cur = stack[--sp];
+    }
+}
+
+// ------------------------------------------------------------------ estimators
+
+struct PhotonMapDev {
+    int kind;  // PhotonRenderKind
+    PointMapDev surface, volume;
+    SphereMapDev spheres;
+    BeamMapDev beams;
+    uint32_t gather_size, gather_size_volume;
+};
+
+RPTX_D double k2_kernel(double sq) {  // src/photon.rs:466-469
+    const double tmp = 1.0 - sq;
+    return (3.0 / kPi) * tmp * tmp;
+}
+RPTX_D double transmittance(const MediumDev& md, double t) { return exp(-(md.extinction() * t)); }  // src/medium.rs:126-130
+
+struct GatherCounters {
+    unsigned long long knn, visibility, candidates;
+};
+
+// surface_estimate, src/photon.rs:327-375
+template <int KMAX>
+RPTX_D d3 surface_estimate(const SceneDev& sc, const PhotonMapDev& pm, const RayD& ray, d3 wo, double t_hit, d3 normal,
+                           const Material& mat, GatherCounters& ctr) {
+    const d3 world_pos = ray.o + t_hit * ray.d;
+    KnnHeap<KMAX> heap;
+    heap.k = pm.gather_size;
+    knn_query(pm.surface, world_pos, heap);
+    heap.sort_ascending();
+    ctr.knn++;
+    double max_d2 = 0.0;
+    for (uint32_t j = 0; j < heap.size; j++) max_d2 = fmax(max_d2, heap.d2[j]);
+    d3 color = mat_emittance(mat) * mat_color(mat);
+    for (uint32_t j = 0; j < heap.size; j++) {
+        const uint32_t i = heap.idx[j];
+        const d3 ppos = mk3(pm.surface.px[i], pm.surface.py[i], pm.surface.pz[i]);
+        const d3 disp = world_pos - ppos;
+        RayD vr;
+        vr.o = ppos;
+        vr.d = normalize(disp);
+        const double len = length(disp);
+        // the closest hit must not be nearer than the shading point: search below `len`, stop at the first find
+        Hit vh;
+        vh.t = len;
+        closest_hit<kAnyBelow>(sc, vr, kEpsilon, len, vh);
+        ctr.visibility++;
+        if (vh.inst != kNoHit && len > vh.t) continue;
+        const d3 pdir = mk3(pm.surface.dir[3 * (size_t)i], pm.surface.dir[3 * (size_t)i + 1], pm.surface.dir[3 * (size_t)i + 2]);
+        const d3 ppow = mk3(pm.surface.power[3 * (size_t)i], pm.surface.power[3 * (size_t)i + 1], pm.surface.power[3 * (size_t)i + 2]);
+        color = color + cmul(mat_bsdf(mat, normal, wo, pdir), ppow) * clampd(dot(pdir, normal), 0.0, 1.0);
+    }
+    return color * (1.0 / (kPi * max_d2));
+}
+
+// volume_estimate, src/photon.rs:379-594.  `hit` false = the camera ray left the scene.
+template <int KMAX>
+RPTX_D d3 volume_estimate(const SceneDev& sc, const MediumDev& md, const PhotonMapDev& pm, const RayD& ray, d3 wo, bool hit, double t_hit,
+                          d3 normal, const Material& mat, Rng& rng, GatherCounters& ctr) {
+    const double extinction = md.extinction();
+    if (pm.kind == 0) {
+        const double random = rng.gen_range(0.0, 1.0);
+        const double d = -log(random) / extinction;
+        const double tr = exp(-(extinction * d));
+        const double d_pdf = extinction * tr, d_cdf = 1.0 - tr;
+        if (!hit || d < t_hit) {
+            const d3 collision = ray.o + d * ray.d;
+            const d3 mc = md.color(collision);
+            KnnHeap<KMAX> heap;
+            heap.k = pm.gather_size_volume;
+            knn_query(pm.volume, collision, heap);
+            heap.sort_ascending();
+            ctr.knn++;
+            double max_d2 = 0.0;
+            for (uint32_t j = 0; j < heap.size; j++) max_d2 = fmax(max_d2, heap.d2[j]);
+            d3 color = mk3(0, 0, 0);
+            for (uint32_t j = 0; j < heap.size; j++) {
+                const size_t i = heap.idx[j];
+                const d3 ppow = mk3(pm.volume.power[3 * i], pm.volume.power[3 * i + 1], pm.volume.power[3 * i + 2]);
+                color = color + cmul(ppow, mc) * md.phase;
+            }
+            color = color / ((4.0 / 3.0) * kPi * pow(max_d2, 1.5));
+            color = color / extinction;
+            color = color * transmittance(md, d);
+            color = color / d_pdf;
+            return color;
+        }
+        return surface_estimate<KMAX>(sc, pm, ray, wo, t_hit, normal, mat, ctr) * transmittance(md, t_hit) / (1.0 - d_cdf);
+    }
+    const Ray32 r32 = make_ray32(ray.o, ray.d);
+    const d3 mc = md.color(mk3(0, 0, 0));
+    d3 volume_color = mk3(0, 0, 0);
+    if (pm.kind == 1) {
+        const SphereMapDev& sm = pm.spheres;
+        box_bvh_traverse(sm.bvh, r32, [&](uint32_t i) {
+            ctr.candidates++;
+            const d3 c = mk3(sm.center[3 * (size_t)i], sm.center[3 * (size_t)i + 1], sm.center[3 * (size_t)i + 2]);
+            const d3 origin_to_center = c - ray.o;
+            if (hit && length(origin_to_center) > t_hit) return;
+            const double radius = sm.radius[i];
+            const double radius_squared = radius * radius;
+            const double disk_distance = dot(origin_to_center, ray.d);
+            const double dn = length((ray.o + disk_distance * ray.d) - c);
+            const double distance_squared = dn * dn;
+            if (disk_distance > 0.0 && distance_squared < radius_squared) {
+                const double weight = k2_kernel(distance_squared / radius_squared) / radius_squared;
+                const double tr = exp(-extinction * disk_distance);
+                const d3 ppow = mk3(sm.power[3 * (size_t)i], sm.power[3 * (size_t)i + 1], sm.power[3 * (size_t)i + 2]);
+                volume_color = volume_color + tr * cmul(ppow, mc) * md.phase * weight * 1.0;
+            }
+        });
+        return volume_color;
+    }
+    const BeamMapDev& bm = pm.beams;
+    box_bvh_traverse(bm.bvh, r32, [&](uint32_t i) {
+        ctr.candidates++;
+        const size_t i3 = 3 * (size_t)i;
+        const d3 bstart = mk3(bm.start[i3], bm.start[i3 + 1], bm.start[i3 + 2]);
+        const d3 bdir = mk3(bm.dirn[i3], bm.dirn[i3 + 1], bm.dirn[i3 + 2]);
+        const d3 l = bstart - ray.o;
+        const d3 u = normalize(cross(l, bdir));
+        const d3 n = normalize(cross(bdir, u));
+        const double t = dot(n, l) / dot(n, ray.d);
+        const d3 query_collision = ray.o + t * ray.d;
+        if (hit && t >= t_hit) return;
+        const double dd = dot(ray.d, bdir);
+        const double inv_sin_theta = 1.0 / sqrt(fmax(0.0, 1.0 - dd * dd));
+        const double beam_t = dot(bdir, query_collision - bstart);
+        const double beam_len = bm.len[i];
+        if (beam_t < 0.0 || beam_t > beam_len) return;
+        const d3 beam_collision = bstart + beam_t * bdir;
+        const double dist = length(query_collision - beam_collision);
+        if (dist >= kBeamRadius) return;
+        const d3 ppow = mk3(bm.power[i3], bm.power[i3 + 1], bm.power[i3 + 2]);
+        const d3 color = extinction * cmul(ppow, mc) * md.phase * inv_sin_theta * transmittance(md, t) * transmittance(md, beam_t) *
+                         k2_kernel(dist / kBeamRadius) / (2.0 * kBeamRadius);
+        volume_color = volume_color + color;
+    });
+    return volume_color;
+}
+
+// estimate_indirect, src/photon.rs:316-627 (dispatch at :596-627)
+template <int KMAX>
+RPTX_D d3 estimate_indirect(const SceneDev& sc, const MediumDev& md, const PhotonMapDev& pm, const RayD& ray, Rng& rng,
+                            GatherCounters& ctr) {
+    const d3 wo = -normalize(ray.d);
+    Hit h;
+    h.t = CUDART_INF;
+    closest_hit<kClosest>(sc, ray, kEpsilon, 0.0, h);
+    const bool medium = md.kind != 0;
+    Material mat;
+    mat.kind = 0; mat.albedo[0] = mat.albedo[1] = mat.albedo[2] = 0.0; mat.emittance = 0.0; mat.shininess = 0.0; mat.ior = 1.0;
+    if (h.inst == kNoHit) {
+        if (!medium) return env_color(sc, ray.d);
+        return volume_estimate<KMAX>(sc, md, pm, ray, wo, false, CUDART_INF, mk3(0, 0, 0), mat, rng, ctr);
+    }
+    uint32_t prim, inst;
+    const d3 n = hit_normal(sc, ray, h, &prim, &inst);
+    mat = sc.materials[h.obj];
+    if (!medium) return surface_estimate<KMAX>(sc, pm, ray, wo, h.t, n, mat, ctr);
+    if (pm.kind == 0) return volume_estimate<KMAX>(sc, md, pm, ray, wo, true, h.t, n, mat, rng, ctr);
+    const d3 volume_color = volume_estimate<KMAX>(sc, md, pm, ray, wo, true, h.t, n, mat, rng, ctr);
+    const d3 surface_color = surface_estimate<KMAX>(sc, pm, ray, wo, h.t, n, mat, ctr) * transmittance(md, h.t);
+    return surface_color + volume_color;
+}
+
+struct GatherArgs {
+    Camera cam;
+    BatchParams bp;
+    uint32_t n_pixels, n_lanes;
+    double *ax, *ay, *az;  // [n_lanes][n_pixels] lane sums of the batch
+};
+
+// Camera pass (get_color_with_photon_map, src/photon.rs:950-985): one thread per (pixel, lane)
+// walks its share of the batch's samples and keeps their sum; k_batch_reduce then adds the lanes
+// in a fixed order.
+template <int KMAX>
+__global__ void __launch_bounds__(128) k_photon_gather(const __grid_constant__ SceneDev sc, const MediumDev md,
+                                                       const __grid_constant__ PhotonMapDev pm, const __grid_constant__ GatherArgs ga,
+                                                       unsigned long long* __restrict__ stats) {
+    const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
+    GatherCounters ctr = {0, 0, 0};
+    unsigned long long my_samples = 0;
+    if (slot < ga.n_pixels * ga.n_lanes) {
+        const uint32_t pixel = slot % ga.n_pixels, lane = slot / ga.n_pixels;
+        const uint32_t x = pixel % ga.bp.width, y = pixel / ga.bp.width;
+        d3 sum = mk3(0, 0, 0);
+        for (uint32_t j = lane; j < ga.bp.n_local; j += ga.n_lanes) {
+            const uint64_t s = ga.bp.batch_base + ga.bp.shard_index + (uint64_t)j * ga.bp.shard_count;
+            Rng rng = Rng::make(ga.bp.seed, kDomainGather, pixel, s);
+            RayD ray;
+            primary_ray(ga.cam, ga.bp.width, ga.bp.height, x, y, rng, &ray.o, &ray.d);
+            sum = sum + estimate_indirect<KMAX>(sc, md, pm, ray, rng, ctr);
+            my_samples++;
+        }
+        ga.ax[slot] = sum.x; ga.ay[slot] = sum.y; ga.az[slot] = sum.z;
+    }
+    const cg::coalesced_group g = cg::coalesced_threads();
+    const unsigned long long a = cg::reduce(g, my_samples, cg::plus<unsigned long long>());
+    const unsigned long long b = cg::reduce(g, ctr.knn, cg::plus<unsigned long long>());
+    const unsigned long long c = cg::reduce(g, ctr.visibility, cg::plus<unsigned long long>());
+    const unsigned long long d = cg::reduce(g, ctr.candidates, cg::plus<unsigned long long>());
+    if (g.thread_rank() == 0) {
+        if (a) atomicAdd(&stats[0], a);
+        if (b) atomicAdd(&stats[5], b);
+        if (c) atomicAdd(&stats[6], c);
+        if (d) atomicAdd(&stats[7], d);
+    }
+}
+
+}  // namespace rptx

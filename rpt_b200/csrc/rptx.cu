@@ -23,10 +23,7 @@ namespace {
         if (e_ != cudaSuccess) return ctx_fail(ctx, std::string(#call) + ": " + cudaGetErrorString(e_)); \
     } while (0)
 
-int ctx_fail(rptx_ctx* ctx, const std::string& msg) {
-    if (ctx) ctx->err = msg;
-    return 1;
-}
+using rptx_host::ctx_fail;
 
 // ---- small host linear algebra (same closed forms nalgebra uses) ----
 struct M4 { double m[4][4]; };
@@ -153,7 +150,7 @@ int grid_for(size_t n, int block) { return (int)std::max<size_t>(1, (n + block -
 void free_scene_device(rptx_scene* s) {
     cudaFree((void*)s->d_nodes); cudaFree((void*)s->d_instances); cudaFree((void*)s->d_tris);
     cudaFree((void*)s->d_tri_normals); cudaFree((void*)s->d_trif); s->d_trif = nullptr; cudaFree((void*)s->d_tri_orig); cudaFree((void*)s->d_materials);
-    cudaFree((void*)s->d_lights); cudaFree((void*)s->d_raw); cudaFree((void*)s->d_env);
+    cudaFree((void*)s->d_lights); cudaFree((void*)s->d_raw); cudaFree((void*)s->d_env); cudaFree((void*)s->d_cube_idx); s->d_cube_idx = nullptr;
     s->d_nodes = nullptr; s->d_instances = nullptr; s->d_tris = nullptr; s->d_tri_normals = nullptr;
     s->d_tri_orig = nullptr; s->d_materials = nullptr; s->d_lights = nullptr; s->d_raw = nullptr; s->d_env = nullptr;
     s->committed = false;
@@ -265,6 +262,15 @@ int lower_light(rptx_scene* s, const rptx_light& l, Light* out) {
     return 0;
 }
 
+}  // namespace
+
+namespace rptx_host {
+
+int ctx_fail(rptx_ctx* ctx, const std::string& msg) {
+    if (ctx) ctx->err = msg;
+    return 1;
+}
+
 MediumDev medium_dev(const rptx_scene* s) {
     MediumDev md;
     std::memset(&md, 0, sizeof(md));
@@ -292,15 +298,21 @@ SceneDev scene_dev(const rptx_scene* s) {
     sc.nodes = s->d_nodes; sc.instances = s->d_instances; sc.tris = s->d_tris; sc.trif = s->d_trif; sc.tri_normals = s->d_tri_normals;
     sc.tri_orig = s->d_tri_orig; sc.materials = s->d_materials; sc.lights = s->d_lights; sc.light_tris = s->d_raw;
     sc.tlas_root_ref = s->tlas_root_ref;
+    sc.cube_instances = s->d_cube_idx; sc.n_cube_instances = s->n_cubes;
     sc.n_bounded = s->n_bounded; sc.n_unbounded = s->n_unbounded;
     sc.n_lights = (uint32_t)s->lights.size(); sc.n_shadow_lights = s->n_shadow_lights;
+    sc.shadow_probe_mask = s->shadow_probe_mask;
     for (int k = 0; k < 3; k++) { sc.wmin[k] = s->wmin[k]; sc.wmax[k] = s->wmax[k]; sc.env_color[k] = s->env_color[k]; }
     sc.medium_kind = s->medium_kind; sc.sigma_a = s->sigma_a; sc.sigma_s = s->sigma_s;
     sc.env_is_hdri = s->env_is_hdri ? 1 : 0; sc.env_w = s->env_w; sc.env_h = s->env_h; sc.env_pixels = s->d_env;
     return sc;
 }
 
-}  // namespace
+
+}  // namespace rptx_host
+
+using rptx_host::medium_dev;
+using rptx_host::scene_dev;
 
 extern "C" {
 
@@ -549,6 +561,13 @@ int rptx_scene_commit(rptx_scene* s) {
     Instance* d_inst = nullptr;
     CK(upload(&d_inst, ordered, st));
     s->d_instances = d_inst;
+    std::vector<uint32_t> cubes;
+    for (uint32_t i = 0; i < s->n_bounded; i++)
+        if (ordered[i].kind == kCube) cubes.push_back(i);
+    uint32_t* d_cubes = nullptr;
+    CK(upload(&d_cubes, cubes, st));
+    s->d_cube_idx = d_cubes;
+    s->n_cubes = (uint32_t)cubes.size();
 
     // 3. materials, lights, environment
     std::vector<Material> mats;
@@ -558,10 +577,14 @@ int rptx_scene_commit(rptx_scene* s) {
     s->d_materials = d_mats;
     std::vector<Light> lights;
     s->n_shadow_lights = 0;
+    s->shadow_probe_mask = 0;
     for (const auto& l : s->lights) {
         Light r;
         if (lower_light(s, l, &r)) return 1;
-        if (l.kind == RPTX_LIGHT_POINT || l.kind == RPTX_LIGHT_OBJECT) s->n_shadow_lights++;
+        if (l.kind == RPTX_LIGHT_POINT || l.kind == RPTX_LIGHT_OBJECT) {
+            if (l.kind == RPTX_LIGHT_POINT && s->n_shadow_lights < 32) s->shadow_probe_mask |= 1u << s->n_shadow_lights;
+            s->n_shadow_lights++;
+        }
         lights.push_back(r);
     }
     Light* d_lights = nullptr;
@@ -579,13 +602,16 @@ int rptx_scene_commit(rptx_scene* s) {
 
 // ---------------------------------------------------------------- film / render loop
 
-static int film_alloc(rptx_film* f) {
+// gather_only: the film of a photon camera pass needs the lane sums and the Buffer, not the path pool
+static int film_alloc(rptx_film* f, bool gather_only) {
     rptx_ctx* ctx = f->ctx;
     PathPool& p = f->pool;
     const size_t ns = p.n_slots;
     std::vector<double**> dptrs = {&p.ox, &p.oy, &p.oz, &p.dx, &p.dy, &p.dz, &p.ht, &p.hnx, &p.hny, &p.hnz, &p.dirx, &p.diry, &p.dirz,
                                    &p.fx, &p.fy, &p.fz, &p.pdf, &p.abscos, &p.bx, &p.by, &p.bz, &p.lx, &p.ly, &p.lz, &p.ax, &p.ay, &p.az};
+    if (gather_only) dptrs = {&p.ax, &p.ay, &p.az};
     for (double** d : dptrs) { CK(cudaMalloc((void**)d, sizeof(double) * ns)); f->owned.push_back(*d); }
+    if (!gather_only) {
     std::vector<double**> sptrs = {&p.sdx, &p.sdy, &p.sdz, &p.sdist, &p.scx, &p.scy, &p.scz};
     for (double** d : sptrs) { CK(cudaMalloc((void**)d, sizeof(double) * ns * std::max<uint32_t>(p.n_shadow, 1))); f->owned.push_back(*d); }
     CK(cudaMalloc((void**)&p.stack, sizeof(double) * ns * 8 * std::max<uint32_t>(p.stack_depth, 1))); f->owned.push_back(p.stack);
@@ -596,6 +622,7 @@ static int film_alloc(rptx_film* f) {
     CK(cudaMalloc((void**)&p.flags, sizeof(uint32_t) * ns)); f->owned.push_back(p.flags);
     CK(cudaMalloc((void**)&f->q.cur, sizeof(uint32_t) * ns)); f->owned.push_back(f->q.cur);
     CK(cudaMalloc((void**)&f->q.next, sizeof(uint32_t) * ns)); f->owned.push_back(f->q.next);
+    }
     CK(cudaMalloc((void**)&f->q.counters, sizeof(uint32_t) * 8)); f->owned.push_back(f->q.counters);
     CK(cudaMalloc((void**)&f->q.stats, sizeof(unsigned long long) * 8)); f->owned.push_back(f->q.stats);
     CK(cudaMemsetAsync(f->q.stats, 0, sizeof(unsigned long long) * 8, ctx->stream));
@@ -610,10 +637,11 @@ static int film_alloc(rptx_film* f) {
     return 0;
 }
 
-int rptx_render_begin(rptx_ctx* ctx, rptx_scene* scene, const rptx_camera* camera, const rptx_params* params, rptx_film** out) {
+static int film_begin(rptx_ctx* ctx, rptx_scene* scene, const rptx_camera* camera, const rptx_params* params, bool gather_only,
+                      rptx_film** out) {
     if (!ctx || !out) return 1;
     *out = nullptr;
-    if (!scene || !camera || !params) return ctx_fail(ctx, "rptx_render_begin: null argument");
+    if (!scene || !camera || !params) return ctx_fail(ctx, "render begin: null argument");
     if (scene->ctx != ctx) return ctx_fail(ctx, "scene belongs to another context");
     if (!scene->committed) return ctx_fail(ctx, "scene not committed");
     if (params->width == 0 || params->height == 0) return ctx_fail(ctx, "empty image");
@@ -625,21 +653,32 @@ int rptx_render_begin(rptx_ctx* ctx, rptx_scene* scene, const rptx_camera* camer
     f->cam.direction = mk3(camera->direction[0], camera->direction[1], camera->direction[2]);
     f->cam.up = mk3(camera->up[0], camera->up[1], camera->up[2]);
     f->cam.fov = camera->fov; f->cam.aperture = camera->aperture; f->cam.focal_distance = camera->focal_distance;
+    f->cam.inv_tan_half_fov = 1.0 / std::tan(camera->fov / 2.0);
     PathPool& p = f->pool;
     std::memset(&p, 0, sizeof(p));
     const uint64_t n_pixels = (uint64_t)params->width * params->height;
     if (n_pixels >= (1ull << 31)) { delete f; return ctx_fail(ctx, "image too large"); }
     p.n_pixels = (uint32_t)n_pixels;
-    const uint64_t target = 1ull << 21;
+    // path tracing: ~2 M paths in flight; photon gather: ~0.5 M threads, each walking its samples
+    const uint64_t target = gather_only ? (1ull << 19) : (1ull << 21);
     uint64_t lanes = std::max<uint64_t>(1, target / n_pixels);
     lanes = std::min<uint64_t>(lanes, 4096);
+    if (gather_only) lanes = std::min<uint64_t>(lanes, std::max<uint32_t>(params->num_samples, 1));
     p.n_lanes = (uint32_t)lanes;
     p.n_slots = (uint32_t)(n_pixels * lanes);
     p.n_shadow = scene->n_shadow_lights;
     p.stack_depth = scene->medium_kind == RPTX_MEDIUM_NONE ? params->max_bounces + 1 : 1;
-    if (film_alloc(f)) { rptx_film_destroy(f); return 1; }
+    if (film_alloc(f, gather_only)) { rptx_film_destroy(f); return 1; }
     *out = f;
     return 0;
+}
+
+int rptx_render_begin(rptx_ctx* ctx, rptx_scene* scene, const rptx_camera* camera, const rptx_params* params, rptx_film** out) {
+    return film_begin(ctx, scene, camera, params, false, out);
+}
+
+int rptx_photon_gather_begin(rptx_ctx* ctx, rptx_scene* scene, const rptx_camera* camera, const rptx_params* params, rptx_film** out) {
+    return film_begin(ctx, scene, camera, params, true, out);
 }
 
 void rptx_film_destroy(rptx_film* f) {
@@ -704,6 +743,7 @@ int rptx_render_sample_trace(rptx_film* f, uint32_t iterations) {
     if (!f) return 1;
     rptx_ctx* ctx = f->ctx;
     if (iterations == 0) return ctx_fail(ctx, "iterations must be > 0");
+    if (!f->q.cur) return ctx_fail(ctx, "this film belongs to a photon gather pass (rptx_photon_gather_begin)");
     CK(cudaSetDevice(ctx->device));
     cudaStream_t st = ctx->stream;
     BatchParams bp;
@@ -826,6 +866,7 @@ int rptx_stats_get(const rptx_film* f, rptx_stats* out) {
     cudaMemcpy(st, f->q.stats, sizeof(st), cudaMemcpyDeviceToHost);
     *out = f->stats;
     out->path_samples = st[0]; out->extend_rays = st[1]; out->shadow_rays = st[2];
+    out->shadow_traced = st[3]; out->shadow_occlusion = st[4];
     out->kernel_launches = f->ctx->launches;
     return 0;
 }
@@ -883,10 +924,6 @@ int rptx_intersect_batch(rptx_scene* s, const double* o, const double* d, size_t
 #undef CKC
     cleanup();
     return rc;
-}
-
-int rptx_photon_render(rptx_ctx* ctx, rptx_scene*, const rptx_camera*, const rptx_params*, uint64_t, int32_t, uint8_t*, double*) {
-    return ctx_fail(ctx, "rptx_photon_render: photon integrators are not built yet");
 }
 
 }  // extern "C"

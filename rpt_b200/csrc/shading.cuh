@@ -271,7 +271,7 @@ RPTX_D void primary_ray(const Camera& cam, uint32_t width, uint32_t height, uint
     const double dx = rng.gen_range(-1.0 / dim, 1.0 / dim);
     const double dy = rng.gen_range(-1.0 / dim, 1.0 / dim);
     const double px = xn + dx, py = yn + dy;
-    const double dd = 1.0 / tan(cam.fov / 2.0);
+    const double dd = cam.inv_tan_half_fov;
     const d3 right = normalize(cross(cam.direction, cam.up));
     d3 origin = cam.eye;
     d3 new_dir = dd * cam.direction + px * right + py * cam.up;

@@ -42,7 +42,7 @@ RPTX_D RayF make_rayf(d3 o, d3 d) {
 
 // conservative f32 slab test; boxes are padded at build time (see bvh_build.cu)
 RPTX_D bool slab_f32(float bx0, float by0, float bz0, float bx1, float by1, float bz1, const RayF& r, float tbest,
-                     float* tnear) {
+                     float* tnear, float tlow = 0.0f) {
     const float t0x = (bx0 - r.ox) * r.ix, t1x = (bx1 - r.ox) * r.ix;
     const float t0y = (by0 - r.oy) * r.iy, t1y = (by1 - r.oy) * r.iy;
     const float t0z = (bz0 - r.oz) * r.iz, t1z = (bz1 - r.oz) * r.iz;
@@ -51,7 +51,7 @@ RPTX_D bool slab_f32(float bx0, float by0, float bz0, float bx1, float by1, floa
     tn = tn - fabsf(tn) * kSlabSlack;
     tf = tf + fabsf(tf) * kSlabSlack;
     *tnear = tn;
-    return tn <= tf && tf >= 0.0f && tn <= tbest;
+    return tn <= tf && tf >= tlow && tn <= tbest;
 }
 
 // f64 entry/exit of a ray against a padded box (fmin/fmax drop NaNs from 0/0)
@@ -179,11 +179,17 @@ RPTX_D bool tri_maybe_hit(const TriF* __restrict__ tf, float ox, float oy, float
 // the same inner-node code whether it is in the instance BVH or inside a mesh BVH; entering a
 // mesh pushes a sentinel, swaps the f32 ray for the mesh-local one and continues.
 // hit.t must be preset to the search bound (+inf for extend rays).
-// SHADOW: stop as soon as a hit below t_stop is accepted (the NEE test can only fail then).
+// MODE kAnyBelow: stop as soon as a hit below t_stop is accepted (occlusion query).
+// MODE kWindow: closest REPORTED hit with t >= t_stop (a primitive reports the t its reference
+// intersect() would, with the usual t_min; reports below t_stop are ignored); nodes that end
+// before t_stop are culled, so for a narrow window this is a point query.
 constexpr int kSentinel = 0x7fffffff;
+enum TraceMode : int { kClosest = 0, kAnyBelow = 1, kWindow = 2 };
 
-template <bool SHADOW>
+template <int MODE>
 RPTX_D void closest_hit(const SceneDev& sc, const RayD& ray, double t_min, double t_stop, Hit& hit) {
+    constexpr bool SHADOW = MODE == kAnyBelow;
+    constexpr bool WINDOW = MODE == kWindow;
     hit.inst = kNoHit; hit.obj = kNoHit; hit.prim = 0; hit.v = 0; hit.w = 0;
     // unbounded shapes (planes) cannot enter the BVH (src/renderer.rs:413-415)
     for (uint32_t i = 0; i < sc.n_unbounded; i++) {
@@ -192,16 +198,39 @@ RPTX_D void closest_hit(const SceneDev& sc, const RayD& ray, double t_min, doubl
         d3 lo = ray.o, ld = ray.d;
         if (in->has_transform) { lo = xform_point(in->inv, ray.o); ld = xform_dir(in->inv, ray.d); }
         double t;
-        if (plane_test(*in, lo, ld, t_min, &t) && accept(hit, t, in->object_id)) {
+        if (plane_test(*in, lo, ld, t_min, &t) && (!WINDOW || t >= t_stop) && accept(hit, t, in->object_id)) {
             hit.t = t; hit.inst = idx; hit.obj = in->object_id; hit.prim = 0;
             if (SHADOW && t < t_stop) return;
         }
     }
     if (sc.n_bounded == 0) return;
+    // Cube::intersect divides 0/0 for a ray lying exactly in a face plane (src/shape/cube.rs:24-25);
+    // the NaN then drops that slab from the test and a hit can be reported where the box is
+    // geometrically missed — which the BVH would cull.  Such rays (a direction component is exactly
+    // zero; e.g. photon visibility rays inside an axis-aligned wall) test those cubes directly.
+    if (sc.n_cube_instances && (ray.d.x == 0.0 || ray.d.y == 0.0 || ray.d.z == 0.0)) {
+        for (uint32_t c = 0; c < sc.n_cube_instances; c++) {
+            const uint32_t idx = sc.cube_instances[c];
+            const Instance* __restrict__ in = sc.instances + idx;
+            d3 lo = ray.o, ld = ray.d;
+            if (in->has_transform) { lo = xform_point(in->inv, ray.o); ld = xform_dir(in->inv, ray.d); }
+            const bool in_face = (ld.x == 0.0 && fabs(lo.x) == 0.5) || (ld.y == 0.0 && fabs(lo.y) == 0.5) || (ld.z == 0.0 && fabs(lo.z) == 0.5);
+            if (!in_face) continue;
+            double t;
+            uint32_t ccode = 0;
+            if (cube_test(lo, ld, t_min, &t, &ccode) && (!WINDOW || t >= t_stop) && accept(hit, t, in->object_id)) {
+                hit.t = t; hit.inst = idx; hit.obj = in->object_id; hit.prim = ccode;
+                if (SHADOW && t < t_stop) return;
+            }
+        }
+    }
     double t0, t1;
     clip_f64(sc.wmin, sc.wmax, ray.o, ray.d, &t0, &t1);
     if (!(t0 <= t1) || t1 < 0.0 || t0 > hit.t) return;
-    const double wshift = t0 > 0.0 ? t0 : 0.0;
+    if (WINDOW && t1 < t_stop) return;
+    // the f32 ray starts at the box entry (or at the window, whichever is later)
+    const double wshift = WINDOW ? fmax(fmax(t0, t_stop), 0.0) : (t0 > 0.0 ? t0 : 0.0);
+    const float tlow = WINDOW ? -1e-30f : 0.0f;  // window mode: shift >= t_stop, so "ends before the window" is tf < 0
     const RayF wrf = make_rayf(ray.o + wshift * ray.d, ray.d);
 
     int stack[kStackSize];
@@ -227,7 +256,7 @@ RPTX_D void closest_hit(const SceneDev& sc, const RayD& ray, double t_min, doubl
             TriRec tr;
             load_tri(tris + i, &tr);
             double t, v, w;
-            if (tri_test(tr, lo, ld, t_min, hit.t, cur_obj < hit.obj, &t, &v, &w)) {
+            if (tri_test(tr, lo, ld, t_min, hit.t, cur_obj < hit.obj, &t, &v, &w) && (!WINDOW || t >= t_stop)) {
                 hit.t = t; hit.inst = cur_inst; hit.obj = cur_obj; hit.prim = i; hit.v = v; hit.w = w;
                 improved = true;
                 if (SHADOW && t < t_stop) return true;
@@ -244,8 +273,8 @@ RPTX_D void closest_hit(const SceneDev& sc, const RayD& ray, double t_min, doubl
             const float4* np = reinterpret_cast<const float4*>(nodes + cur);
             const float4 a = __ldg(np), b = __ldg(np + 1), c = __ldg(np + 2), d = __ldg(np + 3);
             float tl, tr;
-            const bool hl = slab_f32(a.x, a.y, a.z, b.x, b.y, b.z, rf, tbest, &tl);
-            const bool hr = slab_f32(c.x, c.y, c.z, d.x, d.y, d.z, rf, tbest, &tr);
+            const bool hl = slab_f32(a.x, a.y, a.z, b.x, b.y, b.z, rf, tbest, &tl, tlow);
+            const bool hr = slab_f32(c.x, c.y, c.z, d.x, d.y, d.z, rf, tbest, &tr, tlow);
             const int left = __float_as_int(a.w), right = __float_as_int(c.w);
             if (hl && hr) {
                 const bool lf = tl <= tr;
@@ -299,8 +328,9 @@ RPTX_D void closest_hit(const SceneDev& sc, const RayD& ray, double t_min, doubl
                         double l0, l1v;
                         clip_f64(in->lmin, in->lmax, lo, ld, &l0, &l1v);
                         if (!(l0 <= l1v) || l1v < 0.0 || l0 > hit.t) continue;
+                        if (WINDOW && l1v < t_stop) continue;
                         // enter the mesh BVH (TLAS leaves hold one instance, so nothing is pending)
-                        shift = l0 > 0.0 ? l0 : 0.0;
+                        shift = WINDOW ? fmax(fmax(l0, t_stop), 0.0) : (l0 > 0.0 ? l0 : 0.0);
                         const d3 so = lo + shift * ld;
                         rf = make_rayf(so, ld);
                         fox = (float)so.x; foy = (float)so.y; foz = (float)so.z;
@@ -320,7 +350,7 @@ RPTX_D void closest_hit(const SceneDev& sc, const RayD& ray, double t_min, doubl
                     double t;
                     uint32_t ccode = 0;
                     const bool ok = kind == kSphere ? sphere_test(lo, ld, t_min, &t) : cube_test(lo, ld, t_min, &t, &ccode);
-                    if (ok && accept(hit, t, cur_obj)) {
+                    if (ok && (!WINDOW || t >= t_stop) && accept(hit, t, cur_obj)) {
                         hit.t = t; hit.inst = idx; hit.obj = cur_obj; hit.prim = ccode;
                         if (SHADOW && t < t_stop) return;
                         tbest = f32_up(hit.t - shift);
@@ -336,6 +366,32 @@ RPTX_D void closest_hit(const SceneDev& sc, const RayD& ray, double t_min, doubl
             if (stack_t[sp] <= tbest) { cur = stack[sp]; break; }
         }
     }
+}
+
+// NEE visibility as the reference defines it (src/renderer.rs:347-348, :395-396): the CLOSEST
+// hit of the shadow ray must lie within 1e-12 of the light sample.  Evaluated as (1) a probe of
+// the window [dist - 2e-12, dist + 2e-12]: the closest hit REPORTED there must pass the test —
+// a point query that fails at the root for lights floating in free space; (2) only then an
+// any-hit search for a report below the window.  Same verdict as the full closest-hit search.
+// probe_first is chosen per light at commit time (point lights: yes; emissive objects: no).
+RPTX_D bool nee_visible(const SceneDev& sc, const RayD& ray, double dist, bool probe_first, unsigned long long* n_occlusion) {
+    const double t_lo = dist - 2e-12;
+    Hit h;
+    h.t = dist + 2e-12;
+    if (!probe_first) {
+        // lights that are scene objects: the probe would nearly always succeed, so search the
+        // segment once, stopping at the first report below the window
+        (*n_occlusion)++;
+        closest_hit<kAnyBelow>(sc, ray, kEpsilon, t_lo, h);
+        return h.inst != kNoHit && fabs(h.t - dist) < kEpsilon;
+    }
+    closest_hit<kWindow>(sc, ray, kEpsilon, t_lo, h);
+    if (h.inst == kNoHit || !(fabs(h.t - dist) < kEpsilon)) return false;
+    (*n_occlusion)++;
+    Hit occ;
+    occ.t = t_lo;
+    closest_hit<kAnyBelow>(sc, ray, kEpsilon, t_lo, occ);
+    return occ.inst == kNoHit;
 }
 
 // normal of the accepted hit (the per-shape normal code of the reference + Transformed's M^-T)

@@ -143,6 +143,121 @@ class DeviceScene:
             pass
 
 
+ROW = A.PHOTON_ROW_F64
+
+
+def rows_keys(rows):
+    """u64 keys (photon index << 16 | depth) of [n,13] f64 photon rows."""
+    return np.ascontiguousarray(rows[:, 12]).view(np.uint64)
+
+
+class PhotonList:
+    """rptx_photons: the reference's PhotonList(surface, volume) (src/photon.rs:141-171) on the device."""
+
+    def __init__(self, ctx, h):
+        self.ctx, self.lib, self.h = ctx, ctx.lib, h
+
+    @staticmethod
+    def emit(dscene, params, photon_count, kind, first=0, count=None):
+        count = int(photon_count) - int(first) if count is None else int(count)
+        h = C.c_void_p()
+        rc = dscene.lib.rptx_photons_emit(dscene.ctx.h, dscene.h, C.byref(params), int(photon_count), int(first), count, int(kind), C.byref(h))
+        dscene.ctx.check(rc, "rptx_photons_emit")
+        return PhotonList(dscene.ctx, h)
+
+    @staticmethod
+    def empty(ctx):
+        h = C.c_void_p()
+        ctx.check(ctx.lib.rptx_photons_create(ctx.h, C.byref(h)), "rptx_photons_create")
+        return PhotonList(ctx, h)
+
+    def counts(self):
+        c = (C.c_uint64 * 2)()
+        self.ctx.check(self.lib.rptx_photons_count(self.h, c), "rptx_photons_count")
+        return int(c[0]), int(c[1])
+
+    def rows(self, which):
+        """Download one list as [n,13] f64 (column 12 holds the u64 key bits)."""
+        out = np.empty((self.counts()[which], ROW), np.float64)
+        self.ctx.check(self.lib.rptx_photons_download(self.h, which, out.ctypes.data_as(C.c_void_p)), "rptx_photons_download")
+        return out
+
+    def append_host(self, which, rows):
+        rows = np.ascontiguousarray(rows, np.float64).reshape(-1, ROW)
+        self.ctx.check(self.lib.rptx_photons_append_host(self.h, which, rows.ctypes.data_as(C.c_void_p), len(rows)), "rptx_photons_append_host")
+
+    def append_device(self, which, ptr, n):
+        self.ctx.check(self.lib.rptx_photons_append_device(self.h, which, C.c_void_p(int(ptr)), int(n)), "rptx_photons_append_device")
+
+    def device_tensor(self, which):
+        """torch view [n,13] f64 of one list's rows (for the NCCL all-gather)."""
+        from .dist import device_f64_view
+
+        n = self.counts()[which]
+        ptr = self.lib.rptx_photons_device_ptr(self.h, which)
+        return device_f64_view(ptr, n * ROW, f"cuda:{self.ctx.device}").view(n, ROW)
+
+    def stats(self):
+        e, r, ms = C.c_uint64(), C.c_uint64(), C.c_double()
+        self.ctx.check(self.lib.rptx_photons_stats(self.h, C.byref(e), C.byref(r), C.byref(ms)), "rptx_photons_stats")
+        return dict(emitted=e.value, rays=r.value, emit_ms=ms.value)
+
+    def close(self):
+        if self.h:
+            self.lib.rptx_photons_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class PhotonMap:
+    """rptx_photon_map: the reference's PhotonMap enum (src/photon.rs:185-189) on the device."""
+
+    def __init__(self, dscene, photons, kind):
+        self.ctx, self.lib, self.kind = dscene.ctx, dscene.lib, int(kind)
+        self.dscene = dscene
+        h = C.c_void_p()
+        self.ctx.check(self.lib.rptx_photon_map_build(self.ctx.h, dscene.h, photons.h, int(kind), C.byref(h)), "rptx_photon_map_build")
+        self.h = h
+
+    def stats(self):
+        c, ms = (C.c_uint64 * 3)(), C.c_double()
+        self.ctx.check(self.lib.rptx_photon_map_stats(self.h, c, C.byref(ms)), "rptx_photon_map_stats")
+        return dict(surface=int(c[0]), volume=int(c[1]), bvh_items=int(c[2]), build_ms=ms.value)
+
+    def knn(self, which, q, k):
+        """KdTree::nearests for host queries [n,3] -> (keys [n,k] u64, d2 [n,k], counts [n])."""
+        q = np.ascontiguousarray(q, np.float64).reshape(-1, 3)
+        n = len(q)
+        keys = np.empty((n, k), np.uint64)
+        d2 = np.empty((n, k), np.float64)
+        counts = np.empty(n, np.uint32)
+        rc = self.lib.rptx_photon_map_knn(self.h, which, _dp(q), n, k, keys.ctypes.data_as(A.U64P), _dp(d2), counts.ctypes.data_as(A.U32P))
+        self.ctx.check(rc, "rptx_photon_map_knn")
+        return keys, d2, counts
+
+    def spheres(self):
+        n = self.stats()["bvh_items"]
+        c, r = np.empty((n, 3), np.float64), np.empty(n, np.float64)
+        self.ctx.check(self.lib.rptx_photon_map_spheres(self.h, _dp(c), _dp(r)), "rptx_photon_map_spheres")
+        return c, r
+
+    def close(self):
+        if self.h:
+            self.lib.rptx_photon_map_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
 class Buffer:
     """What iterative_render's callback receives (src/buffer.rs:5-94): image(), variance()."""
 
@@ -162,14 +277,19 @@ class Buffer:
 class Film:
     """rptx_film: the device Buffer plus the path pool of one render."""
 
-    def __init__(self, dscene, camera, params):
+    def __init__(self, dscene, camera, params, gather_only=False):
         self.dscene, self.ctx, self.lib = dscene, dscene.ctx, dscene.lib
         self.params = params
         self.w, self.h_px = params.width, params.height
         h = C.c_void_p()
         cam = camera.lower()
-        self.ctx.check(self.lib.rptx_render_begin(self.ctx.h, dscene.h, C.byref(cam), C.byref(params), C.byref(h)), "rptx_render_begin")
+        begin = self.lib.rptx_photon_gather_begin if gather_only else self.lib.rptx_render_begin
+        self.ctx.check(begin(self.ctx.h, dscene.h, C.byref(cam), C.byref(params), C.byref(h)), "rptx_render_begin")
         self.h = h
+
+    def gather(self, photon_map, iterations):
+        """This rank's shard of `iterations` photon-map samples per pixel into the batch sums."""
+        self.ctx.check(self.lib.rptx_photon_gather_trace(self.h, photon_map.h, int(iterations)), "rptx_photon_gather_trace")
 
     def sample(self, iterations):
         self.ctx.check(self.lib.rptx_render_sample(self.h, int(iterations)), "rptx_render_sample")
@@ -291,7 +411,7 @@ class Renderer:
         return None if obj[0] == 0xFFFFFFFF else (float(t[0]), tuple(n[0]), int(obj[0]))
 
     def photon_render(self, photon_count, kind, want_mean=False):
-        """src/photon.rs:655-720"""
+        """src/photon.rs:655-720: emit -> build -> gather on one device."""
         ds = self.device_scene()
         p = self.params()
         out = np.empty((p.height, p.width, 3), np.uint8)
@@ -301,6 +421,19 @@ class Renderer:
                                        out.ctypes.data_as(A.U8P), _dp(mean) if want_mean else None)
         ds.ctx.check(rc, "rptx_photon_render")
         return (out, mean) if want_mean else out
+
+    # the three passes one by one (multi-GPU hosts shard pass 1 and pass 3; tests check each alone)
+    def emit_photons(self, photon_count, kind, first=0, count=None):
+        """PASS 1, src/photon.rs:663-675 -> PhotonList on the device."""
+        return PhotonList.emit(self.device_scene(), self.params(), photon_count, kind, first, count)
+
+    def build_photon_map(self, photons, kind):
+        """PASS 2, src/photon.rs:693-702."""
+        return PhotonMap(self.device_scene(), photons, kind)
+
+    def begin_gather(self):
+        """Film of PASS 3 (src/photon.rs:706-716); film.gather(map, n) then film.sample_commit(n)."""
+        return Film(self.device_scene(), self.camera, self.params(), gather_only=True)
 
     def photon_map_render(self, photon_count):
         return self.photon_render(photon_count, PhotonRenderKind.PhotonMap)

@@ -57,6 +57,15 @@ def lib():
             "orc_color_bytes": (None, [DP, U8P]),
             "orc_rng_u64": (C.c_uint64, [C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint32]),
             "orc_hardware_threads": (C.c_int, []),
+            "orc_photons_emit": (P, [P, C.POINTER(A.CameraDesc), C.POINTER(A.Params), C.c_uint64, C.c_uint64, C.c_uint64, C.c_int32, C.c_int]),
+            "orc_photons_destroy": (None, [P]),
+            "orc_photons_count": (None, [P, U64P]),
+            "orc_photons_rows": (None, [P, C.c_int32, DP]),
+            "orc_photon_map_build": (P, [P, DP, C.c_size_t, DP, C.c_size_t, C.c_int32]),
+            "orc_photon_map_destroy": (None, [P]),
+            "orc_photon_map_knn": (C.c_int, [P, C.c_int32, DP, C.c_size_t, C.c_uint32, U64P, DP, U32P]),
+            "orc_photon_map_spheres": (C.c_size_t, [P, DP, DP]),
+            "orc_photon_map_gather": (C.c_int, [P, C.POINTER(A.CameraDesc), C.POINTER(A.Params), C.c_int, U8P, DP, DP]),
             "orc_photon_render": (C.c_int, [P, C.POINTER(A.CameraDesc), C.POINTER(A.Params), C.c_uint64, C.c_int32, C.c_int, U8P, DP, U64P, DP]),
         }
         for name, (res, args) in sig.items():
@@ -138,9 +147,71 @@ class OracleScene:
                                           _dp(mean), counts, secs), "photon_render")
         return img, mean, tuple(counts), tuple(secs)
 
+    def emit_photons(self, camera, params, photon_count, kind, first=0, count=None, threads=0):
+        """PASS 1 -> (surface rows [n,13], volume rows [n,13]) sorted by key."""
+        count = photon_count - first if count is None else count
+        cam = camera.lower()
+        h = self.L.orc_photons_emit(self.h, C.byref(cam), C.byref(params), photon_count, first, count, kind, threads)
+        if not h:
+            raise RuntimeError(self.L.orc_last_error(self.h).decode())
+        c = (C.c_uint64 * 2)()
+        self.L.orc_photons_count(h, c)
+        out = []
+        for which in range(2):
+            rows = np.empty((c[which], 13), np.float64)
+            self.L.orc_photons_rows(h, which, _dp(rows))
+            out.append(sort_rows(rows))
+        self.L.orc_photons_destroy(h)
+        return out
+
     def __del__(self):
         try:
             self.L.orc_scene_destroy(self.h)
+        except Exception:
+            pass
+
+
+def sort_rows(rows):
+    """Canonical order of photon rows: ascending u64 key (column 12)."""
+    if len(rows) == 0:
+        return rows
+    return rows[np.argsort(np.ascontiguousarray(rows[:, 12]).view(np.uint64), kind="stable")]
+
+
+class OraclePhotonMap:
+    """PASS 2 + PASS 3 of the oracle over given photon rows."""
+
+    def __init__(self, oscene, surface_rows, volume_rows, kind):
+        self.L, self.oscene = oscene.L, oscene
+        s = np.ascontiguousarray(surface_rows, np.float64).reshape(-1, 13)
+        v = np.ascontiguousarray(volume_rows, np.float64).reshape(-1, 13)
+        self.h = self.L.orc_photon_map_build(oscene.h, _dp(s), len(s), _dp(v), len(v), kind)
+
+    def knn(self, which, q, k):
+        q = np.ascontiguousarray(q, np.float64).reshape(-1, 3)
+        n = len(q)
+        keys, d2, counts = np.empty((n, k), np.uint64), np.empty((n, k), np.float64), np.empty(n, np.uint32)
+        self.L.orc_photon_map_knn(self.h, which, _dp(q), n, k, keys.ctypes.data_as(U64P), _dp(d2), counts.ctypes.data_as(U32P))
+        return keys, d2, counts
+
+    def spheres(self):
+        n = self.L.orc_photon_map_spheres(self.h, None, None)
+        c, r = np.empty((n, 3), np.float64), np.empty(n, np.float64)
+        self.L.orc_photon_map_spheres(self.h, _dp(c), _dp(r))
+        return c, r
+
+    def gather(self, camera, params, threads=0):
+        w, h = params.width, params.height
+        mean = np.empty((h, w, 3), np.float64)
+        img = np.empty((h, w, 3), np.uint8)
+        sec = C.c_double()
+        cam = camera.lower()
+        self.L.orc_photon_map_gather(self.h, C.byref(cam), C.byref(params), threads, img.ctypes.data_as(U8P), _dp(mean), C.byref(sec))
+        return img, mean, sec.value
+
+    def __del__(self):
+        try:
+            self.L.orc_photon_map_destroy(self.h)
         except Exception:
             pass
 

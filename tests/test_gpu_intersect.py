@@ -64,14 +64,33 @@ def test_empty_and_degenerate():
     t, obj, *_ = ds.intersect_batch(np.zeros((0, 3)), np.zeros((0, 3)))
     assert len(t) == 0
     osc = orc.OracleScene(scene)
-    # axis-parallel rays, rays in wall planes, zero-length and NaN directions.  (A ray lying exactly
-    # in the plane of a cube face with a zero direction component is NOT in this list: the
-    # reference's slab code then divides 0/0 and reports a NaN-driven hit; the BVH culls that
-    # instance instead.  Documented deviation, DESIGN.md.)
+    # axis-parallel rays, rays in wall planes, zero-length and NaN directions
     o = np.array([[278, 273, -800], [0, 10, 5], [278, 0, 100], [100, 100, 100], [100, 100, 100], [556, 548.9, 559.2]], float)
     dd = np.array([[0, 0, 1], [1, 0, 0], [0, 0, 1], [0, 0, 0], [np.nan, 0, 1], [-1, -1, -1]], float)
     t, obj, prim, inst, _ = ds.intersect_batch(o, dd)
     to, objo, primo, insto, _ = osc.intersect_batch(o, dd)
     assert np.array_equal(obj, objo) and np.array_equal(prim, primo)
+    ok = objo != 0xFFFFFFFF
+    assert np.array_equal(t[ok], to[ok])
+
+
+def test_rays_in_cube_face_planes():
+    """A ray lying exactly in the plane of a cube face makes Cube::intersect divide 0/0
+    (src/shape/cube.rs:24-25); the NaN drops that slab from the test, so the reference reports
+    hits where the box is geometrically missed.  Photon visibility rays inside the floor do this
+    with the boxes standing on it (lampshade scene); closest_hit reproduces it."""
+    scene, cam, d = scenes.lampshade("photonphoton")
+    r = scenes.make_renderer(scene, cam, d)
+    ds = r.device_scene()
+    osc = orc.OracleScene(scene)
+    rng = np.random.default_rng(5)
+    n = 20000
+    o = np.stack([rng.uniform(0, 556, n), np.zeros(n), rng.uniform(0, 559, n)], axis=1)
+    a = rng.uniform(0, 2 * np.pi, n)
+    dd = np.stack([np.cos(a), np.zeros(n), np.sin(a)], axis=1)
+    t, obj, prim, inst, _ = ds.intersect_batch(o, dd)
+    to, objo, primo, insto, _ = osc.intersect_batch(o, dd)
+    assert (objo != 0xFFFFFFFF).mean() > 0.3
+    assert np.array_equal(obj, objo), (obj != objo).sum()
     ok = objo != 0xFFFFFFFF
     assert np.array_equal(t[ok], to[ok])
