@@ -99,6 +99,7 @@ struct __align__(16) Instance {
     Affine inv;        // inverse transform (world -> local), src/shape.rs:130
     Mat3 nrm;          // M^-T, src/shape.rs:133
     double lmin[3], lmax[3];  // local f64 bounds of the mesh (padded) for the entry clip
+    double bmin[3], bmax[3];  // exact local bounds (KdTree::bounds), see mesh_bounds_nan_reject
     double plane_n[3], plane_v;
     int kind;
     int has_transform;

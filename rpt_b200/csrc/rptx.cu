@@ -208,7 +208,7 @@ int lower_leaf(rptx_scene* s, const rptx_shape_desc& d, uint32_t object_id, uint
             in.kind = kMesh;
             in.root_ref = m.root_ref; in.node_base = m.node_base; in.tri_base = m.tri_base; in.ntri = (uint32_t)m.tris.size();
             in.lpad = m.pad;
-            for (int k = 0; k < 3; k++) { in.lmin[k] = m.bmin[k] - (double)m.pad; in.lmax[k] = m.bmax[k] + (double)m.pad; }
+            for (int k = 0; k < 3; k++) { in.lmin[k] = m.bmin[k] - (double)m.pad; in.lmax[k] = m.bmax[k] + (double)m.pad; in.bmin[k] = m.bmin[k]; in.bmax[k] = m.bmax[k]; }
             break;
         }
         default: return ctx_fail(ctx, "unsupported leaf shape kind");

@@ -175,6 +175,21 @@ RPTX_D bool tri_maybe_hit(const TriF* __restrict__ tf, float ox, float oy, float
     return true;  // includes NaN/inf cases (all comparisons false)
 }
 
+// KdTree::intersect first clips the ray against the tree's bounding box with NaN-ignoring
+// f64::min/max (src/kdtree.rs:57-71,133-137).  A ray lying exactly in a face plane of that box
+// (direction component 0, origin on the plane) divides 0/0 there; when the box has extent in
+// that dimension the slab collapses to (+inf,+inf) or (-inf,-inf) and the reference rejects the
+// whole mesh — although triangles touching that plane (a wall's bottom edge seen from inside the
+// floor) are geometrically hit.  Returns true when the reference would reject.
+RPTX_D bool mesh_bounds_nan_reject(const Instance* __restrict__ in, d3 lo, d3 ld) {
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+        const double d = comp(ld, k), o = comp(lo, k);
+        if (d == 0.0 && in->bmax[k] > in->bmin[k] && (o == in->bmin[k] || o == in->bmax[k])) return true;
+    }
+    return false;
+}
+
 // get_closest_hit over the two-level BVH as ONE loop (while-while): every lane of a warp runs
 // the same inner-node code whether it is in the instance BVH or inside a mesh BVH; entering a
 // mesh pushes a sentinel, swaps the f32 ray for the mesh-local one and continues.
@@ -315,6 +330,7 @@ RPTX_D void closest_hit(const SceneDev& sc, const RayD& ray, double t_min, doubl
                     lo = ray.o; ld = ray.d;
                     if (in->has_transform) { lo = xform_point(in->inv, ray.o); ld = xform_dir(in->inv, ray.d); }
                     if (kind == kMesh) {
+                        if ((ld.x == 0.0 || ld.y == 0.0 || ld.z == 0.0) && mesh_bounds_nan_reject(in, lo, ld)) continue;
                         cur_inst = idx;
                         tris = sc.tris + in->tri_base;
                         trif = sc.trif + in->tri_base;

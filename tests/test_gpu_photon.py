@@ -6,7 +6,7 @@ walk, which changes that walk's later deposits and thereby the k-nearest sets of
 near them.  So
   pass 1 (emission)  same seed -> same photon records, except for a small fraction of flipped walks;
   pass 2 (maps)      built from the ORACLE's photons -> kNN sets and sphere radii bit-exact;
-  pass 3 (gather)    same map, same seed -> per-pixel agreement to 1e-9 but for flipped samples;
+  pass 3 (gather)    same map, same seed -> per-pixel agreement to 1e-11;
   whole render       same seed -> relative RMSE within a stated tolerance.
 """
 import numpy as np
@@ -140,18 +140,14 @@ def test_gather_same_map_same_seed(variant):
     got = film.mean()
     _, want, _ = om.gather(cam, r.params())
     assert np.isfinite(want).all()
-    match = np.isclose(got, want, rtol=1e-9, atol=1e-14).all(axis=2).mean()
+    # Same map, same seed, bit-exact camera rays, kNN sets and visibility rays: only libm ulps
+    # (log/exp/pow) and summation order remain.  Getting here needed two NaN quirks of the
+    # reference reproduced (rays lying in a cube-face plane or in a mesh bounding-box plane,
+    # trace.cuh) — photon visibility rays run inside the floor plane all the time.
+    match = np.isclose(got, want, rtol=1e-11, atol=1e-300).all(axis=2).mean()
     rel_rmse = np.sqrt(np.mean((got - want) ** 2)) / np.mean(want)
-    # Flipped samples: every surface estimate casts gather_size visibility rays that start ON a
-    # surface with t_min = 1e-12 and end ON the shaded surface, where `|disp| > t_hit`
-    # (src/photon.rs:352-361) is decided in the last ulp -- the same epsilon fragility as NEE (see
-    # test_gpu_render.py), but up to 300 such rays per pixel here.  A flip moves the pixel by one
-    # photon's share (~1/(k*spp)), so pixels either agree to rounding or differ by a few 1e-3.
-    rel = np.abs(got - want).max(axis=2) / np.maximum(np.abs(want).max(axis=2), 1e-300)
-    np.savez(f"gpurun_out/diag_gather_{variant}.npz", got=got, want=want) if __import__("os").path.isdir("gpurun_out") else None
-    assert match >= (0.90 if variant == "photonphoton" else 0.97), (match, rel_rmse)
-    assert np.quantile(rel, 0.99) <= 5e-2, np.quantile(rel, [0.5, 0.9, 0.99, 1.0])
-    assert rel_rmse <= 2e-2, rel_rmse
+    assert match >= 0.995, (match, rel_rmse)
+    assert rel_rmse <= 1e-3, rel_rmse
     assert film.image().shape == (32, 32, 3)
     st = film.stats()
     assert st["path_samples"] == 32 * 32 * 3
@@ -203,7 +199,7 @@ def test_surface_only_scene_and_errors():
     film.gather(gm, 2); film.sample_commit(2)
     _, want, _ = om.gather(cam, r.params())
     got = film.mean()
-    assert np.isclose(got, want, rtol=1e-9, atol=1e-14).all(axis=2).mean() >= 0.90
+    assert np.isclose(got, want, rtol=1e-11, atol=1e-300).all(axis=2).mean() >= 0.995
     # photon mapping needs a Light::Object (src/photon.rs:798 panics)
     from rpt_b200 import Camera, Light, Material, Object, sphere
 
