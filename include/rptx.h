@@ -139,7 +139,10 @@ typedef struct rptx_stats {
     double   trace_ms;         /* of which: extend + shadow kernels (all ray queries) */
     double   extend_ms, shade_ms, connect_ms, shadow_ms; /* per-kernel CUDA-event sums of the last call */
     uint64_t photons_emitted, photons_surface, photons_volume;
-    uint64_t gather_queries;
+    uint64_t gather_queries;   /* kNN queries of the photon camera pass */
+    uint64_t gather_visibility; /* visibility rays of surface estimates */
+    uint64_t gather_candidates; /* sphere/beam candidates returned by the BVH */
+    uint64_t path_mode;        /* 0 wavefront kernels, 1 fused per-thread kernel, 2 photon gather film */
 } rptx_stats;
 
 int         rptx_abi_version(void);

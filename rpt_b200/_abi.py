@@ -103,6 +103,9 @@ class Stats(C.Structure):
         ("photons_surface", C.c_uint64),
         ("photons_volume", C.c_uint64),
         ("gather_queries", C.c_uint64),
+        ("gather_visibility", C.c_uint64),
+        ("gather_candidates", C.c_uint64),
+        ("path_mode", C.c_uint64),
     ]
 
 

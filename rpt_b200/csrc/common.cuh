@@ -9,6 +9,9 @@
 
 #define RPTX_HD __host__ __device__ __forceinline__
 #define RPTX_D __device__ __forceinline__
+// big bodies that kernels call from several sites: one copy each keeps the kernels inside the
+// instruction cache (the ray kernels were 100-400 KB of SASS when everything was inlined)
+#define RPTX_DN static __device__ __noinline__
 
 namespace rptx {
 

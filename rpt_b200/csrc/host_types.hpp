@@ -64,8 +64,11 @@ struct rptx_scene {
     double wmin[3] = {0, 0, 0}, wmax[3] = {0, 0, 0};
 };
 
+enum FilmMode : int { kFilmWavefront = 0, kFilmFused = 1, kFilmGather = 2 };
+
 struct rptx_film {
     rptx_ctx* ctx = nullptr;
+    int mode = kFilmWavefront;
     rptx_scene* scene = nullptr;
     rptx_params params;
     rptx::Camera cam;

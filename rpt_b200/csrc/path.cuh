@@ -28,7 +28,7 @@ struct PathPool {
     double *sdx, *sdy, *sdz, *sdist, *scx, *scy, *scz;  // [n_shadow][n_slots] NEE candidates
     // forward accumulation (medium mode): throughput and radiance
     double *bx, *by, *bz, *lx, *ly, *lz;
-    // per-level records for the clamped back-fold (surface mode): [stack_depth][8][n_slots]
+    // per-level records for the clamped back-fold (surface mode): [n_slots][stack_depth][8]
     double* stack;
     // lane film: sum of finished samples of this slot in the current batch
     double *ax, *ay, *az;

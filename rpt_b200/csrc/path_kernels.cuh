@@ -23,6 +23,13 @@ RPTX_D void stat_add(unsigned long long* __restrict__ dst, unsigned long long v)
     if (lane_id() == (uint32_t)(__ffs(active) - 1) && total) atomicAdd(dst, (unsigned long long)total);
 }
 
+// same for counts that may exceed 32 bits per warp
+RPTX_D void stat_add64(unsigned long long* __restrict__ dst, unsigned long long v) {
+    const unsigned active = __activemask();
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(active, v, o);
+    if (lane_id() == 0 && v) atomicAdd(dst, v);
+}
+
 // warp-ballot compaction: append `slot` of every lane with pred to q, one atomic per warp
 RPTX_D void queue_push(uint32_t* __restrict__ q, uint32_t* __restrict__ count, bool pred, uint32_t slot) {
     const unsigned active = __activemask();
@@ -100,12 +107,13 @@ __global__ void __launch_bounds__(kBlock) k_extend(const __grid_constant__ Scene
 }
 
 // NEE candidates of one vertex (Renderer::sample_lights / sample_lights_for_media).  Ambient
-// lights are added to `direct` here; every other light leaves a shadow job (direction,
-// distance, radiance if unoccluded) for k_connect.  Directional lights have dist = +inf, which
-// can never pass |t - dist| < 1e-12 (src/renderer.rs:396), so no job is emitted for them.
-template <bool SURFACE>
-RPTX_D void sample_lights_dev(const SceneDev& sc, const PathPool& p, uint32_t slot, const Material* mat, const MediumDev* md,
-                              d3 pos, d3 n, d3 wo, d3 mc, Rng& rng, d3* direct) {
+// lights are added to `direct` here; every other light hands a shadow job (k-th shadow-casting
+// light, direction, distance, radiance if unoccluded) to `job`.  Directional lights have
+// dist = +inf, which can never pass |t - dist| < 1e-12 (src/renderer.rs:396), so no job is
+// emitted for them (their RNG draws, if any, still happen).
+template <bool SURFACE, class Job>
+RPTX_D void sample_lights_each(const SceneDev& sc, const Material* mat, const MediumDev* md, d3 pos, d3 n, d3 wo, d3 mc, Rng& rng,
+                               d3* direct, Job&& job) {
     uint32_t k = 0;
     for (uint32_t li = 0; li < sc.n_lights; li++) {
         const Light& l = sc.lights[li];
@@ -124,12 +132,20 @@ RPTX_D void sample_lights_dev(const SceneDev& sc, const PathPool& p, uint32_t sl
         } else {
             c = (md->sigma_s / md->extinction()) * cmul(intensity, mc) * md->phase;
         }
+        job(k, wi, dist, c);
+        k++;
+    }
+}
+
+template <bool SURFACE>
+RPTX_D void sample_lights_dev(const SceneDev& sc, const PathPool& p, uint32_t slot, const Material* mat, const MediumDev* md,
+                              d3 pos, d3 n, d3 wo, d3 mc, Rng& rng, d3* direct) {
+    sample_lights_each<SURFACE>(sc, mat, md, pos, n, wo, mc, rng, direct, [&](uint32_t k, d3 wi, double dist, d3 c) {
         const size_t o = (size_t)k * p.n_slots + slot;
         p.sdx[o] = wi.x; p.sdy[o] = wi.y; p.sdz[o] = wi.z;
         p.sdist[o] = dist;
         p.scx[o] = c.x; p.scy[o] = c.y; p.scz[o] = c.z;
-        k++;
-    }
+    });
 }
 
 template <bool MEDIUM>
@@ -220,6 +236,8 @@ __global__ void __launch_bounds__(kBlock) k_shade(const __grid_constant__ SceneD
 // candidates are added to the vertex's direct light in light order.  A candidate whose
 // contribution is exactly zero (light sample facing away, bsdf 0) is not traced: adding it
 // cannot change the sum.
+// PROBE: the scene has point lights (probed at their sample first); all lights take that path then.
+template <bool PROBE>
 __global__ void __launch_bounds__(kBlock) k_shadow(const __grid_constant__ SceneDev sc, PathPool p, Queues q) {
     const uint32_t count = q.counters[0];
     unsigned long long my_queries = 0, my_traced = 0, my_occl = 0;
@@ -229,22 +247,23 @@ __global__ void __launch_bounds__(kBlock) k_shadow(const __grid_constant__ Scene
         base = __shfl_sync(0xffffffffu, base, 0);
         if (base >= count) break;
         const uint32_t i = base + lane_id();
-        if (i >= count) continue;
-        const uint32_t slot = q.cur[i];
-        if (!(p.flags[slot] & kFlagHasShadow)) continue;
+        const uint32_t slot = i < count ? q.cur[i] : 0u;
+        const bool has = i < count && (p.flags[slot] & kFlagHasShadow);
         d3 add = mk3(0, 0, 0);
         bool any = false;
         RayD ray;
-        ray.o = mk3(p.ox[slot], p.oy[slot], p.oz[slot]);
-        for (uint32_t k = 0; k < p.n_shadow; k++) {
+        ray.o = mk3(0, 0, 0);
+        if (has) ray.o = mk3(p.ox[slot], p.oy[slot], p.oz[slot]);
+        for (uint32_t k = 0; k < p.n_shadow; k++) {  // uniform trip count: the warp enters every traversal together
             const size_t off = (size_t)k * p.n_slots + slot;
-            my_queries++;
-            const d3 c = mk3(p.scx[off], p.scy[off], p.scz[off]);
-            if (c.x == 0.0 && c.y == 0.0 && c.z == 0.0) continue;
-            ray.d = mk3(p.sdx[off], p.sdy[off], p.sdz[off]);
-            const double dist = p.sdist[off];
-            my_traced++;
-            if (nee_visible(sc, ray, dist, k < 32 && ((sc.shadow_probe_mask >> k) & 1u), &my_occl)) {
+            d3 c = mk3(0, 0, 0);
+            if (has) { c = mk3(p.scx[off], p.scy[off], p.scz[off]); my_queries++; }
+            const bool job = has && !(c.x == 0.0 && c.y == 0.0 && c.z == 0.0);
+            double dist = 0.0;
+            ray.d = mk3(0, 0, 1);
+            if (job) { ray.d = mk3(p.sdx[off], p.sdy[off], p.sdz[off]); dist = p.sdist[off]; my_traced++; }
+            __syncwarp();
+            if (job && nee_visible<PROBE>(sc, ray, dist, &my_occl)) {
                 // direct += contribution, in light order like the reference's loop
                 if (!any) { add = mk3(p.dirx[slot], p.diry[slot], p.dirz[slot]); any = true; }
                 add = add + c;
@@ -252,9 +271,9 @@ __global__ void __launch_bounds__(kBlock) k_shadow(const __grid_constant__ Scene
         }
         if (any) { p.dirx[slot] = add.x; p.diry[slot] = add.y; p.dirz[slot] = add.z; }
     }
-    stat_add(&q.stats[2], my_queries);
-    stat_add(&q.stats[3], my_traced);
-    stat_add(&q.stats[4], my_occl);
+    stat_add64(&q.stats[2], my_queries);
+    stat_add64(&q.stats[3], my_traced);
+    stat_add64(&q.stats[4], my_occl);
 }
 
 // connect: finalise the vertex; finished paths are folded (surface mode), added to the slot's
@@ -282,21 +301,23 @@ __global__ void __launch_bounds__(kBlock) k_connect(PathPool p, Queues q, BatchP
                     p.bx[slot] = beta.x * p.fx[slot]; p.by[slot] = beta.y * p.fy[slot]; p.bz[slot] = beta.z * p.fz[slot];
                 }
             } else {
+                // per-slot stack, one 64-byte record per level: [slot][level]{direct, f, pdf, |cos|}.  Only the
+                // few lanes whose path ends fold, so a slot's levels are contiguous (4 x double2 per level).
+                double2* st = reinterpret_cast<double2*>(p.stack + ((size_t)slot * p.stack_depth) * 8);
                 if (!finished) {
-                    double* st = p.stack + (size_t)depth * 8 * p.n_slots + slot;
-                    const size_t ns = p.n_slots;
-                    st[0] = direct.x; st[ns] = direct.y; st[2 * ns] = direct.z;
-                    st[3 * ns] = p.fx[slot]; st[4 * ns] = p.fy[slot]; st[5 * ns] = p.fz[slot];
-                    st[6 * ns] = p.pdf[slot]; st[7 * ns] = p.abscos[slot];
+                    double2* r = st + (size_t)depth * 4;
+                    r[0] = make_double2(direct.x, direct.y);
+                    r[1] = make_double2(direct.z, p.fx[slot]);
+                    r[2] = make_double2(p.fy[slot], p.fz[slot]);
+                    r[3] = make_double2(p.pdf[slot], p.abscos[slot]);
                 } else {
                     L = direct;
                     for (int j = (int)depth - 1; j >= 0; j--) {
-                        const double* st = p.stack + (size_t)j * 8 * p.n_slots + slot;
-                        const size_t ns = p.n_slots;
-                        const d3 f = mk3(st[3 * ns], st[4 * ns], st[5 * ns]);
-                        const d3 ind = 1.0 / st[6 * ns] * cmul(f, L) * st[7 * ns];
-                        L = mk3(st[0] + fmin(ind.x, kFireflyClamp), st[ns] + fmin(ind.y, kFireflyClamp),
-                                st[2 * ns] + fmin(ind.z, kFireflyClamp));
+                        const double2* r = st + (size_t)j * 4;
+                        const double2 a = r[0], b = r[1], c = r[2], e = r[3];
+                        const d3 f = mk3(b.y, c.x, c.y);
+                        const d3 ind = 1.0 / e.x * cmul(f, L) * e.y;
+                        L = mk3(a.x + fmin(ind.x, kFireflyClamp), a.y + fmin(ind.y, kFireflyClamp), b.x + fmin(ind.z, kFireflyClamp));
                     }
                 }
             }
@@ -324,6 +345,167 @@ __global__ void k_wave_end(Queues q) {
     q.counters[1] = 0;
     q.counters[2] = 0;
     q.counters[3] = 0;
+}
+
+// ---- fused path kernel -------------------------------------------------------------------
+// For scenes whose whole accelerator sits in L1 (a dozen analytic objects: Cornell, lampshade)
+// the wavefront's per-vertex state round trip through HBM (~650 B) and its five launches per
+// wave cost more than the divergence they remove.  Here one thread owns a (pixel, lane) slot
+// and walks its samples' whole paths in registers: extend -> shade -> NEE -> next vertex,
+// regenerating the next sample in place.  Same arithmetic and RNG draw order as the wavefront
+// kernels; NEE contributions are added in the reference's light order.
+constexpr int kFusedMaxDepth = 16;
+
+struct FusedArgs {
+    Camera cam;
+    BatchParams bp;
+    uint32_t n_pixels, n_lanes;
+    double *ax, *ay, *az;  // [n_lanes][n_pixels] lane sums of the batch
+};
+
+struct PathCounters {
+    unsigned long long extend, queries, traced, occl;
+};
+
+template <bool SURFACE>
+RPTX_D void nee_inline(const SceneDev& sc, const Material* mat, const MediumDev* md, d3 pos, d3 n, d3 wo, d3 mc, Rng& rng, d3* direct,
+                       PathCounters& ctr) {
+    sample_lights_each<SURFACE>(sc, mat, md, pos, n, wo, mc, rng, direct, [&](uint32_t k, d3 wi, double dist, d3 c) {
+        ctr.queries++;
+        if (c.x == 0.0 && c.y == 0.0 && c.z == 0.0) return;
+        RayD sr;
+        sr.o = pos;
+        sr.d = wi;
+        ctr.traced++;
+        if (sc.shadow_probe_mask ? nee_visible<true>(sc, sr, dist, &ctr.occl) : nee_visible<false>(sc, sr, dist, &ctr.occl)) *direct = *direct + c;
+    });
+}
+
+// trace_ray, surface branch (src/renderer.rs:286-321)
+RPTX_D d3 path_radiance_surface(const SceneDev& sc, RayD ray, Rng& rng, uint32_t max_bounces, PathCounters& ctr) {
+    double st_dir[kFusedMaxDepth][3], st_f[kFusedMaxDepth][3], st_pdf[kFusedMaxDepth], st_ac[kFusedMaxDepth];
+    d3 direct = mk3(0, 0, 0);
+    uint32_t depth = 0;
+    for (;; depth++) {
+        Hit h;
+        h.t = CUDART_INF;
+        closest_hit<kClosest>(sc, ray, kEpsilon, 0.0, h);
+        ctr.extend++;
+        if (h.inst == kNoHit) { direct = env_color(sc, ray.d); break; }
+        uint32_t prim, inst;
+        const d3 n = hit_normal(sc, ray, h, &prim, &inst);
+        const d3 pos = ray.o + h.t * ray.d;
+        const Material mat = sc.materials[h.obj];
+        const d3 wo = -normalize(ray.d);
+        direct = depth == 0 ? mat_emittance(mat) * mat_color(mat) : mk3(0, 0, 0);
+        nee_inline<true>(sc, &mat, nullptr, pos, n, wo, mk3(0, 0, 0), rng, &direct, ctr);
+        if (!(depth < max_bounces)) break;
+        d3 wi;
+        double pdf;
+        if (!mat_sample_f(mat, n, wo, rng, &wi, &pdf)) break;
+        const d3 f = mat_bsdf(mat, n, wo, wi);
+        st_dir[depth][0] = direct.x; st_dir[depth][1] = direct.y; st_dir[depth][2] = direct.z;
+        st_f[depth][0] = f.x; st_f[depth][1] = f.y; st_f[depth][2] = f.z;
+        st_pdf[depth] = pdf;
+        st_ac[depth] = fabs(dot(wi, n));
+        ray.o = pos;
+        ray.d = wi;
+    }
+    d3 L = direct;
+    for (int j = (int)depth - 1; j >= 0; j--) {
+        const d3 f = mk3(st_f[j][0], st_f[j][1], st_f[j][2]);
+        const d3 ind = 1.0 / st_pdf[j] * cmul(f, L) * st_ac[j];
+        L = mk3(st_dir[j][0] + fmin(ind.x, kFireflyClamp), st_dir[j][1] + fmin(ind.y, kFireflyClamp), st_dir[j][2] + fmin(ind.z, kFireflyClamp));
+    }
+    return L;
+}
+
+// trace_ray, medium branch (src/renderer.rs:188-285)
+RPTX_D d3 path_radiance_medium(const SceneDev& sc, const MediumDev& md, RayD ray, Rng& rng, PathCounters& ctr) {
+    d3 beta = mk3(1, 1, 1), L = mk3(0, 0, 0);
+    for (uint32_t depth = 0;; depth++) {
+        const double dsamp = medium_sample_d(md, rng);
+        Hit h;
+        h.t = CUDART_INF;
+        closest_hit<kClosest>(sc, ray, kEpsilon, 0.0, h);
+        ctr.extend++;
+        const bool hit = h.inst != kNoHit;
+        const double max_dist = hit ? h.t : kBackgroundDist;
+        d3 direct = mk3(0, 0, 0), fc = mk3(0, 0, 0);
+        bool go = false;
+        if (dsamp < max_dist) {
+            const d3 wo = -normalize(ray.d);
+            const d3 collision = ray.o + dsamp * ray.d;
+            const d3 mc = md.color(collision);
+            if (depth == 0) direct = md.emission * mc;
+            nee_inline<false>(sc, nullptr, &md, collision, mk3(0, 0, 0), wo, mc, rng, &direct, ctr);
+            ray.o = collision;
+            if (rng.gen() < kRrMedium) {
+                d3 wi;
+                medium_sample_ph(rng, &wi);
+                const double ph_p = md.phase;
+                const double sa = md.sigma_s / md.extinction();
+                fc = mk3(((sa / ph_p) * mc.x * md.phase) / kRrMedium, ((sa / ph_p) * mc.y * md.phase) / kRrMedium,
+                         ((sa / ph_p) * mc.z * md.phase) / kRrMedium);
+                ray.d = wi;
+                go = true;
+            }
+        } else if (!hit) {
+            direct = env_color(sc, ray.d);
+        } else {
+            uint32_t prim, inst;
+            const d3 n = hit_normal(sc, ray, h, &prim, &inst);
+            const d3 pos = ray.o + h.t * ray.d;
+            const Material mat = sc.materials[h.obj];
+            const d3 wo = -normalize(ray.d);
+            if (depth == 0) direct = mat_emittance(mat) * mat_color(mat);
+            nee_inline<true>(sc, &mat, nullptr, pos, n, wo, mk3(0, 0, 0), rng, &direct, ctr);
+            ray.o = pos;
+            if (rng.gen() < kRrMedium) {
+                d3 wi;
+                double pdf;
+                if (mat_sample_f(mat, n, wo, rng, &wi, &pdf)) {
+                    const d3 f = mat_bsdf(mat, n, wo, wi);
+                    const double ac = fabs(dot(wi, n));
+                    const double s = 1.0 / (pdf * kRrMedium);
+                    fc = mk3(s * f.x * ac, s * f.y * ac, s * f.z * ac);
+                    ray.d = wi;
+                    go = true;
+                }
+            }
+        }
+        L = L + cmul(beta, direct);
+        if (!go) return L;
+        beta = mk3(beta.x * fc.x, beta.y * fc.y, beta.z * fc.z);
+    }
+}
+
+template <bool MEDIUM>
+__global__ void __launch_bounds__(kBlock) k_path_fused(const __grid_constant__ SceneDev sc, const MediumDev md,
+                                                        const __grid_constant__ FusedArgs fa, unsigned long long* __restrict__ stats) {
+    const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
+    PathCounters ctr = {0, 0, 0, 0};
+    unsigned long long my_paths = 0;
+    if (slot < fa.n_pixels * fa.n_lanes) {
+        const uint32_t pixel = slot % fa.n_pixels, lane = slot / fa.n_pixels;
+        const uint32_t x = pixel % fa.bp.width, y = pixel / fa.bp.width;
+        d3 sum = mk3(0, 0, 0);
+        for (uint32_t j = lane; j < fa.bp.n_local; j += fa.n_lanes) {
+            const uint64_t s = fa.bp.batch_base + fa.bp.shard_index + (uint64_t)j * fa.bp.shard_count;
+            Rng rng = Rng::make(fa.bp.seed, kDomainCamera, pixel, s);
+            RayD ray;
+            primary_ray(fa.cam, fa.bp.width, fa.bp.height, x, y, rng, &ray.o, &ray.d);
+            const d3 L = MEDIUM ? path_radiance_medium(sc, md, ray, rng, ctr) : path_radiance_surface(sc, ray, rng, fa.bp.max_bounces, ctr);
+            sum = sum + L;
+            my_paths++;
+        }
+        fa.ax[slot] = sum.x; fa.ay[slot] = sum.y; fa.az[slot] = sum.z;
+    }
+    stat_add64(&stats[0], my_paths);
+    stat_add64(&stats[1], ctr.extend);
+    stat_add64(&stats[2], ctr.queries);
+    stat_add64(&stats[3], ctr.traced);
+    stat_add64(&stats[4], ctr.occl);
 }
 
 // raw closest-hit batch (parity hook + kernel-only benchmark)

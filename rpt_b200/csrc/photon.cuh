@@ -94,9 +94,10 @@ __global__ void __launch_bounds__(128) k_photon_trace(const __grid_constant__ Sc
         double light_pdf;
         sample_light_shape(sc, l, mk3(0, 0, 0), rng, &pos, &n, &light_pdf);
         const double phi = 2.0 * kPi * rng.gen();
-        const double theta = acos(1.0 - rng.gen());
-        const double st = sin(theta);
-        const d3 hemi = mk3(st * cos(phi), cos(theta), st * sin(phi));
+        const double ct = 1.0 - rng.gen(), st = sin_from_cos(ct);  // theta = acos(1 - u), src/photon.rs:737
+        double sp, cp;
+        sincos(phi, &sp, &cp);
+        const d3 hemi = mk3(st * cp, ct, st * sp);
         const Rot3 rot = rotation_from_y(n);
         RayD ray;
         ray.o = pos;
@@ -224,7 +225,7 @@ RPTX_D double box_dist2(float4 mn, float4 mx, d3 q) {
 
 // KdTree::nearests(q, k): exact k nearest by squared Euclidean distance
 template <int KMAX>
-RPTX_D void knn_query(const PointMapDev& m, d3 q, KnnHeap<KMAX>& h) {
+RPTX_DN void knn_query(const PointMapDev& m, d3 q, KnnHeap<KMAX>& h) {
     h.size = 0;
     if (m.n == 0 || h.k == 0) return;
     uint32_t stack[32];
@@ -388,7 +389,7 @@ struct GatherCounters {
 
 // surface_estimate, src/photon.rs:327-375
 template <int KMAX>
-RPTX_D d3 surface_estimate(const SceneDev& sc, const PhotonMapDev& pm, const RayD& ray, d3 wo, double t_hit, d3 normal,
+RPTX_DN d3 surface_estimate(const SceneDev& sc, const PhotonMapDev& pm, const RayD& ray, d3 wo, double t_hit, d3 normal,
                            const Material& mat, GatherCounters& ctr) {
     const d3 world_pos = ray.o + t_hit * ray.d;
     KnnHeap<KMAX> heap;
@@ -422,7 +423,7 @@ RPTX_D d3 surface_estimate(const SceneDev& sc, const PhotonMapDev& pm, const Ray
 
 // volume_estimate, src/photon.rs:379-594.  `hit` false = the camera ray left the scene.
 template <int KMAX>
-RPTX_D d3 volume_estimate(const SceneDev& sc, const MediumDev& md, const PhotonMapDev& pm, const RayD& ray, d3 wo, bool hit, double t_hit,
+RPTX_DN d3 volume_estimate(const SceneDev& sc, const MediumDev& md, const PhotonMapDev& pm, const RayD& ray, d3 wo, bool hit, double t_hit,
                           d3 normal, const Material& mat, Rng& rng, GatherCounters& ctr) {
     const double extinction = md.extinction();
     if (pm.kind == 0) {
@@ -517,16 +518,16 @@ RPTX_D d3 estimate_indirect(const SceneDev& sc, const MediumDev& md, const Photo
     const bool medium = md.kind != 0;
     Material mat;
     mat.kind = 0; mat.albedo[0] = mat.albedo[1] = mat.albedo[2] = 0.0; mat.emittance = 0.0; mat.shininess = 0.0; mat.ior = 1.0;
-    if (h.inst == kNoHit) {
-        if (!medium) return env_color(sc, ray.d);
-        return volume_estimate<KMAX>(sc, md, pm, ray, wo, false, CUDART_INF, mk3(0, 0, 0), mat, rng, ctr);
+    const bool hit = h.inst != kNoHit;
+    d3 n = mk3(0, 0, 0);
+    if (hit) {
+        uint32_t prim, inst;
+        n = hit_normal(sc, ray, h, &prim, &inst);
+        mat = sc.materials[h.obj];
     }
-    uint32_t prim, inst;
-    const d3 n = hit_normal(sc, ray, h, &prim, &inst);
-    mat = sc.materials[h.obj];
-    if (!medium) return surface_estimate<KMAX>(sc, pm, ray, wo, h.t, n, mat, ctr);
-    if (pm.kind == 0) return volume_estimate<KMAX>(sc, md, pm, ray, wo, true, h.t, n, mat, rng, ctr);
-    const d3 volume_color = volume_estimate<KMAX>(sc, md, pm, ray, wo, true, h.t, n, mat, rng, ctr);
+    if (!medium) return hit ? surface_estimate<KMAX>(sc, pm, ray, wo, h.t, n, mat, ctr) : env_color(sc, ray.d);
+    const d3 volume_color = volume_estimate<KMAX>(sc, md, pm, ray, wo, hit, hit ? h.t : CUDART_INF, n, mat, rng, ctr);
+    if (!hit || pm.kind == 0) return volume_color;  // point-point: the surface term is inside (src/photon.rs:612-615)
     const d3 surface_color = surface_estimate<KMAX>(sc, pm, ray, wo, h.t, n, mat, ctr) * transmittance(md, h.t);
     return surface_color + volume_color;
 }

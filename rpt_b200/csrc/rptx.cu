@@ -3,6 +3,7 @@
 // path_kernels.cuh / trace.cuh / bvh_build.cu.
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <memory>
 #include <string>
@@ -602,8 +603,9 @@ int rptx_scene_commit(rptx_scene* s) {
 
 // ---------------------------------------------------------------- film / render loop
 
-// gather_only: the film of a photon camera pass needs the lane sums and the Buffer, not the path pool
-static int film_alloc(rptx_film* f, bool gather_only) {
+// the film of a photon camera pass or of the fused path kernel needs the lane sums and the Buffer, not the path pool
+static int film_alloc(rptx_film* f) {
+    const bool gather_only = f->mode != kFilmWavefront;
     rptx_ctx* ctx = f->ctx;
     PathPool& p = f->pool;
     const size_t ns = p.n_slots;
@@ -637,6 +639,19 @@ static int film_alloc(rptx_film* f, bool gather_only) {
     return 0;
 }
 
+// Path-tracing films pick their kernel set here: the fused per-thread kernel when the whole
+// accelerator is a handful of nodes (L1-resident), the wavefront otherwise.  RPTX_PATH_MODE =
+// wavefront | fused overrides (benchmarks compare both).
+static int choose_path_mode(const rptx_scene* s, const rptx_params* p) {
+    const bool fits = p->max_bounces + 1 <= (uint32_t)kFusedMaxDepth || s->medium_kind != RPTX_MEDIUM_NONE;
+    const char* env = std::getenv("RPTX_PATH_MODE");
+    if (env && std::strcmp(env, "wavefront") == 0) return kFilmWavefront;
+    if (env && std::strcmp(env, "fused") == 0 && fits) return kFilmFused;
+    size_t tris = 0;
+    for (const auto& m : s->meshes) tris += m.tris.size();
+    return (fits && tris <= 4096 && s->n_bounded + s->n_unbounded <= 64) ? kFilmFused : kFilmWavefront;
+}
+
 static int film_begin(rptx_ctx* ctx, rptx_scene* scene, const rptx_camera* camera, const rptx_params* params, bool gather_only,
                       rptx_film** out) {
     if (!ctx || !out) return 1;
@@ -649,6 +664,7 @@ static int film_begin(rptx_ctx* ctx, rptx_scene* scene, const rptx_camera* camer
     CK(cudaSetDevice(ctx->device));
     rptx_film* f = new rptx_film();
     f->ctx = ctx; f->scene = scene; f->params = *params;
+    f->mode = gather_only ? kFilmGather : choose_path_mode(scene, params);
     f->cam.eye = mk3(camera->eye[0], camera->eye[1], camera->eye[2]);
     f->cam.direction = mk3(camera->direction[0], camera->direction[1], camera->direction[2]);
     f->cam.up = mk3(camera->up[0], camera->up[1], camera->up[2]);
@@ -660,15 +676,16 @@ static int film_begin(rptx_ctx* ctx, rptx_scene* scene, const rptx_camera* camer
     if (n_pixels >= (1ull << 31)) { delete f; return ctx_fail(ctx, "image too large"); }
     p.n_pixels = (uint32_t)n_pixels;
     // path tracing: ~2 M paths in flight; photon gather: ~0.5 M threads, each walking its samples
-    const uint64_t target = gather_only ? (1ull << 19) : (1ull << 21);
+    // wavefront: ~2 M paths in flight; fused / photon gather: ~0.5 M threads, each walking its samples
+    const uint64_t target = f->mode == kFilmWavefront ? (1ull << 21) : (1ull << 19);
     uint64_t lanes = std::max<uint64_t>(1, target / n_pixels);
     lanes = std::min<uint64_t>(lanes, 4096);
-    if (gather_only) lanes = std::min<uint64_t>(lanes, std::max<uint32_t>(params->num_samples, 1));
+    if (f->mode != kFilmWavefront) lanes = std::min<uint64_t>(lanes, std::max<uint32_t>(params->num_samples, 1));
     p.n_lanes = (uint32_t)lanes;
     p.n_slots = (uint32_t)(n_pixels * lanes);
     p.n_shadow = scene->n_shadow_lights;
     p.stack_depth = scene->medium_kind == RPTX_MEDIUM_NONE ? params->max_bounces + 1 : 1;
-    if (film_alloc(f, gather_only)) { rptx_film_destroy(f); return 1; }
+    if (film_alloc(f)) { rptx_film_destroy(f); return 1; }
     *out = f;
     return 0;
 }
@@ -716,7 +733,10 @@ static int run_waves(rptx_film* f, const BatchParams& bp) {
         cudaEventRecord(f->evw[1], st);
         k_shade<MEDIUM><<<grid_for(active, kBlock), kBlock, 0, st>>>(sc, p, q, bp, md);
         cudaEventRecord(f->evw[2], st);
-        if (p.n_shadow) k_shadow<<<blocks, kBlock, 0, st>>>(sc, p, q);
+        if (p.n_shadow) {
+            if (sc.shadow_probe_mask) k_shadow<true><<<blocks, kBlock, 0, st>>>(sc, p, q);
+            else k_shadow<false><<<blocks, kBlock, 0, st>>>(sc, p, q);
+        }
         cudaEventRecord(f->evw[3], st);
         k_connect<MEDIUM><<<grid_for(active, kBlock), kBlock, 0, st>>>(p, q, bp, f->cam);
         cudaEventRecord(f->evw[4], st);
@@ -743,7 +763,7 @@ int rptx_render_sample_trace(rptx_film* f, uint32_t iterations) {
     if (!f) return 1;
     rptx_ctx* ctx = f->ctx;
     if (iterations == 0) return ctx_fail(ctx, "iterations must be > 0");
-    if (!f->q.cur) return ctx_fail(ctx, "this film belongs to a photon gather pass (rptx_photon_gather_begin)");
+    if (f->mode == kFilmGather) return ctx_fail(ctx, "this film belongs to a photon gather pass (rptx_photon_gather_begin)");
     CK(cudaSetDevice(ctx->device));
     cudaStream_t st = ctx->stream;
     BatchParams bp;
@@ -756,7 +776,23 @@ int rptx_render_sample_trace(rptx_film* f, uint32_t iterations) {
     PathPool& p = f->pool;
     const uint32_t full_lanes = p.n_lanes;
     p.n_lanes = std::max<uint32_t>(1, std::min(full_lanes, bp.n_local));
-    int rc = f->scene->medium_kind == RPTX_MEDIUM_NONE ? run_waves<false>(f, bp) : run_waves<true>(f, bp);
+    int rc = 0;
+    if (f->mode == kFilmFused) {
+        FusedArgs fa;
+        fa.cam = f->cam; fa.bp = bp; fa.n_pixels = p.n_pixels; fa.n_lanes = p.n_lanes;
+        fa.ax = p.ax; fa.ay = p.ay; fa.az = p.az;
+        const SceneDev sc = scene_dev(f->scene);
+        const MediumDev md = medium_dev(f->scene);
+        const size_t threads = (size_t)p.n_pixels * p.n_lanes;
+        if (f->scene->medium_kind == RPTX_MEDIUM_NONE) k_path_fused<false><<<grid_for(threads, kBlock), kBlock, 0, st>>>(sc, md, fa, f->q.stats);
+        else k_path_fused<true><<<grid_for(threads, kBlock), kBlock, 0, st>>>(sc, md, fa, f->q.stats);
+        ctx->launches++;
+        f->stats.waves++;
+        cudaError_t e = cudaGetLastError();
+        if (e != cudaSuccess) rc = ctx_fail(ctx, std::string("k_path_fused: ") + cudaGetErrorString(e));
+    } else {
+        rc = f->scene->medium_kind == RPTX_MEDIUM_NONE ? run_waves<false>(f, bp) : run_waves<true>(f, bp);
+    }
     if (rc == 0) {
         k_batch_reduce<<<grid_for(p.n_pixels, 128), 128, 0, st>>>(p, f->d_batch_sum);
         ctx->launches++;
@@ -867,6 +903,8 @@ int rptx_stats_get(const rptx_film* f, rptx_stats* out) {
     *out = f->stats;
     out->path_samples = st[0]; out->extend_rays = st[1]; out->shadow_rays = st[2];
     out->shadow_traced = st[3]; out->shadow_occlusion = st[4];
+    out->gather_queries = st[5]; out->gather_visibility = st[6]; out->gather_candidates = st[7];
+    out->path_mode = (uint64_t)f->mode;
     out->kernel_launches = f->ctx->launches;
     return 0;
 }

@@ -23,15 +23,23 @@ RPTX_D d3 rot_apply(const Rot3& r, d3 v) {
     return mk3(r.m[0] * v.x + r.m[1] * v.y + r.m[2] * v.z, r.m[3] * v.x + r.m[4] * v.y + r.m[5] * v.z,
                r.m[6] * v.x + r.m[7] * v.y + r.m[8] * v.z);
 }
-// nalgebra Rotation3::from_axis_angle
-RPTX_D Rot3 rot_from_axis_angle(d3 u, double angle) {
+// Trigonometry.  The reference goes through angles (theta = acos(x); cos(theta), sin(theta);
+// rotation_between = from_axis_angle(axis, acos(a.b))).  Here cos(acos(x)) is x, sin(acos(x)) is
+// sqrt(1 - x^2) and the sine of the angle between unit vectors is |a x b|: the same values to a
+// few ulps — the size of the CUDA-vs-glibc libm differences the parity tests already allow —
+// without the f64 acos/sin/cos code (each several KB of SASS; k_shade was 105-143 KB and
+// instruction-cache bound).
+RPTX_D double sin_from_cos(double c) { return sqrt(fmax(0.0, 1.0 - c * c)); }
+
+// nalgebra Rotation3::from_axis_angle with (sin, cos) of the angle
+RPTX_D Rot3 rot_identity() {
     Rot3 r;
-    if (angle == 0.0) {
-        r.m[0] = 1; r.m[1] = 0; r.m[2] = 0; r.m[3] = 0; r.m[4] = 1; r.m[5] = 0; r.m[6] = 0; r.m[7] = 0; r.m[8] = 1;
-        return r;
-    }
+    r.m[0] = 1; r.m[1] = 0; r.m[2] = 0; r.m[3] = 0; r.m[4] = 1; r.m[5] = 0; r.m[6] = 0; r.m[7] = 0; r.m[8] = 1;
+    return r;
+}
+RPTX_D Rot3 rot_from_axis_sincos(d3 u, double s, double c) {
+    Rot3 r;
     const double sqx = u.x * u.x, sqy = u.y * u.y, sqz = u.z * u.z;
-    const double s = sin(angle), c = cos(angle);
     const double omc = 1.0 - c;
     r.m[0] = sqx + (1.0 - sqx) * c;
     r.m[1] = u.x * u.y * omc - u.z * s;
@@ -53,12 +61,16 @@ RPTX_D bool rotation_between(d3 a, d3 b, Rot3* out) {
         const double sq = dot(c, c);
         const double eps = 2.220446049250313e-16;
         if (sq > eps * eps) {
-            *out = rot_from_axis_angle(c / sqrt(sq), acos(dot(na, nb)) * 1.0);
+            // angle = acos(na.nb): its cosine is the dot product and its sine follows from the
+            // cosine alone, as in the reference (|na x nb| would be MORE accurate for nearly
+            // (anti)parallel vectors, e.g. the (0,1,1e-8) fallback against -Y, and so differ from it)
+            const double cs = dot(na, nb);
+            *out = rot_from_axis_sincos(c / sqrt(sq), sin_from_cos(cs), cs);
             return true;
         }
         if (dot(na, nb) < 0.0) return false;
     }
-    *out = rot_from_axis_angle(mk3(1, 0, 0), 0.0);
+    *out = rot_identity();
     return true;
 }
 // the reference's +Y -> n rotation with its antiparallel fallback (src/material.rs:186-194)
@@ -69,15 +81,16 @@ RPTX_D Rot3 rotation_from_y(d3 n) {
 }
 
 // Material::sample_f.  false = None.
-RPTX_D bool mat_sample_f(const Material& m, d3 normal, d3 wo, Rng& rng, d3* wi, double* pdf) {
+RPTX_DN bool mat_sample_f(const Material& m, d3 normal, d3 wo, Rng& rng, d3* wi, double* pdf) {
     if (m.kind == 0) {
         const double r1 = rng.gen();
         const double r2 = rng.gen();
         const double phi = 2.0 * kPi * r1;
-        const double theta = acos(sqrt(r2));
-        const double ct = cos(theta), st = sin(theta);
+        const double ct = sqrt(r2), st = sin_from_cos(ct);  // theta = acos(sqrt(r2))
         *pdf = ct / kPi;
-        const d3 hemi = mk3(st * cos(phi), ct, st * sin(phi));
+        double sp, cp;
+        sincos(phi, &sp, &cp);
+        const d3 hemi = mk3(st * cp, ct, st * sp);
         const Rot3 rot = rotation_from_y(normal);
         *wi = normalize(rot_apply(rot, hemi));
         return true;
@@ -86,10 +99,11 @@ RPTX_D bool mat_sample_f(const Material& m, d3 normal, d3 wo, Rng& rng, d3* wi, 
         const double r1 = rng.gen();
         const double r2 = rng.gen();
         const double phi = 2.0 * kPi * r1;
-        const double theta = acos(pow(r2, 1.0 / (m.shininess + 1.0)));
-        const double ct = cos(theta), st = sin(theta);
+        const double ct = pow(r2, 1.0 / (m.shininess + 1.0)), st = sin_from_cos(ct);  // theta = acos(r2^(1/(s+1)))
         *pdf = (m.shininess + 1.0) / (2.0 * kPi) * pow(ct, m.shininess);
-        const d3 hemi = mk3(st * cos(phi), ct, st * sin(phi));
+        double sp, cp;
+        sincos(phi, &sp, &cp);
+        const d3 hemi = mk3(st * cp, ct, st * sp);
         const d3 reflected = -reflect_vec(wo, normal);
         // glm::quat_rotation(+Y, reflected) then quat_rotate_vec3
         double qw = 1.0;
@@ -103,9 +117,9 @@ RPTX_D bool mat_sample_f(const Material& m, d3 normal, d3 wo, Rng& rng, d3* wi, 
             if (sq > eps * eps) {
                 const double cs = dot(na, nb);
                 if (cs > -1.0 && cs < 1.0) {
-                    const double half = acos(cs) * 1.0 / 2.0;
-                    qw = cos(half);
-                    qv = (c / sqrt(sq)) * sin(half);
+                    // half = acos(cs) / 2: cos(half) = sqrt((1 + cs) / 2), sin(half) = sqrt((1 - cs) / 2)
+                    qw = sqrt((1.0 + cs) * 0.5);
+                    qv = (c / sqrt(sq)) * sqrt((1.0 - cs) * 0.5);
                 }
             }
         }
@@ -237,7 +251,7 @@ RPTX_D void sample_light_shape(const SceneDev& sc, const Light& l, d3 target, Rn
 }
 
 // Light::illuminate for non-ambient lights
-RPTX_D void illuminate(const SceneDev& sc, const Light& l, d3 pos, Rng& rng, d3* intensity, d3* wi, double* dist) {
+RPTX_DN void illuminate(const SceneDev& sc, const Light& l, d3 pos, Rng& rng, d3* intensity, d3* wi, double* dist) {
     const d3 color = mk3(l.color[0], l.color[1], l.color[2]);
     if (l.kind == 0) {  // Point
         const d3 disp = mk3(l.vec[0], l.vec[1], l.vec[2]) - pos;

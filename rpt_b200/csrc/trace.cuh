@@ -334,7 +334,7 @@ RPTX_D void closest_hit(const SceneDev& sc, const RayD& ray, double t_min, doubl
                         cur_inst = idx;
                         tris = sc.tris + in->tri_base;
                         trif = sc.trif + in->tri_base;
-                        if (in->root_ref < 0) {  // tiny mesh: no BLAS nodes, test its triangles here
+                        if (in->root_ref < 0) {  // one-leaf mesh (a polygon): test its triangles here, no BLAS entry
                             fox = (float)lo.x; foy = (float)lo.y; foz = (float)lo.z;
                             fdx = (float)ld.x; fdy = (float)ld.y; fdz = (float)ld.z;
                             const uint32_t c2 = (uint32_t)(~in->root_ref);
@@ -390,24 +390,22 @@ RPTX_D void closest_hit(const SceneDev& sc, const RayD& ray, double t_min, doubl
 // a point query that fails at the root for lights floating in free space; (2) only then an
 // any-hit search for a report below the window.  Same verdict as the full closest-hit search.
 // probe_first is chosen per light at commit time (point lights: yes; emissive objects: no).
-RPTX_D bool nee_visible(const SceneDev& sc, const RayD& ray, double dist, bool probe_first, unsigned long long* n_occlusion) {
+// PROBE = false: lights that are scene objects; the probe would nearly always succeed, so the
+// segment is searched once up to the window's far end, stopping at the first report below it.
+template <bool PROBE>
+RPTX_D bool nee_visible(const SceneDev& sc, const RayD& ray, double dist, unsigned long long* n_occlusion) {
     const double t_lo = dist - 2e-12;
     Hit h;
     h.t = dist + 2e-12;
-    if (!probe_first) {
-        // lights that are scene objects: the probe would nearly always succeed, so search the
-        // segment once, stopping at the first report below the window
-        (*n_occlusion)++;
-        closest_hit<kAnyBelow>(sc, ray, kEpsilon, t_lo, h);
-        return h.inst != kNoHit && fabs(h.t - dist) < kEpsilon;
+    if (PROBE) {
+        closest_hit<kWindow>(sc, ray, kEpsilon, t_lo, h);
+        if (h.inst == kNoHit || !(fabs(h.t - dist) < kEpsilon)) return false;
+        h.t = t_lo;
     }
-    closest_hit<kWindow>(sc, ray, kEpsilon, t_lo, h);
-    if (h.inst == kNoHit || !(fabs(h.t - dist) < kEpsilon)) return false;
     (*n_occlusion)++;
-    Hit occ;
-    occ.t = t_lo;
-    closest_hit<kAnyBelow>(sc, ray, kEpsilon, t_lo, occ);
-    return occ.inst == kNoHit;
+    closest_hit<kAnyBelow>(sc, ray, kEpsilon, t_lo, h);
+    if (PROBE) return h.inst == kNoHit;
+    return h.inst != kNoHit && fabs(h.t - dist) < kEpsilon;
 }
 
 // normal of the accepted hit (the per-shape normal code of the reference + Transformed's M^-T)

@@ -24,6 +24,13 @@ MIN_MATCH = 0.97
 MAX_REL_RMSE = 2e-2  # whole-image relative RMSE bound at equal seed (flipped samples only)
 
 
+@pytest.fixture(params=["wavefront", "fused"], autouse=True)
+def path_mode(request, monkeypatch):
+    """Every test here runs against both kernel sets (RPTX_PATH_MODE is read at render begin)."""
+    monkeypatch.setenv("RPTX_PATH_MODE", request.param)
+    return request.param
+
+
 def _same_seed(scene, cam, defaults, w, h, spp, batches=1, **over):
     r = scenes.make_renderer(scene, cam, defaults, width=w, height=h, num_samples=spp * batches, seed=11, **over)
     film = r.begin()
@@ -135,3 +142,21 @@ def test_render_api_and_errors():
     assert [s[0] for s in seen] == [2, 4, 5]
     with pytest.raises(RptxError):
         Renderer(scene, cam).width(0).height(16).render()
+
+
+def test_fused_equals_wavefront(monkeypatch):
+    """Same arithmetic, same RNG draw order: the two kernel sets give the same batch (NEE terms are
+    added in a different order only when several shadow-casting lights pass)."""
+    for name in ("cornell", "lampshade", "teapot"):
+        scene, cam, d = getattr(scenes, name)() if name != "lampshade" else scenes.lampshade("pathtrace")
+        means, modes = [], []
+        for mode in ("wavefront", "fused"):
+            monkeypatch.setenv("RPTX_PATH_MODE", mode)
+            f = scenes.make_renderer(scene, cam, d, width=40, height=30, num_samples=3, seed=9, max_bounces=3).begin()
+            f.sample(3)
+            means.append(f.mean())
+            modes.append(f.stats()["path_mode"])
+            st = f.stats()
+            assert st["path_samples"] == 40 * 30 * 3
+        assert modes == [0, 1]
+        assert np.allclose(means[0], means[1], rtol=1e-12, atol=1e-300), name
