@@ -37,6 +37,10 @@ EXTEND_BYTES_PER_RAY = 4 + 48 + 8 + 4 + 24
 
 
 _OVERRIDES = {}
+# photon workloads (BASELINE configs[3], configs[4]): a step = one photon_render (emit -> merge ->
+# build -> gather) of --photons photons per GPU at the example's camera pass; metric Mphotons/s
+PHOTON_KINDS = {"photonphoton": 0, "beamphoton": 1, "beambeam": 2}
+PHOTON_ROW_BYTES = 104
 
 
 def workload(name):
@@ -53,6 +57,8 @@ def workload(name):
         scene, cam, d = scenes.cornell()
     elif name == "lampshade":
         scene, cam, d = scenes.lampshade("pathtrace")
+    elif name in PHOTON_KINDS:
+        scene, cam, d = scenes.lampshade(name)
     else:
         raise SystemExit(f"unknown workload {name}")
     for k, v in _OVERRIDES.items():
@@ -130,6 +136,23 @@ def run_reference(args):
     scene, cam, d = workload(args.workload)
     from rpt_b200.scenes import make_renderer
 
+    if args.workload in PHOTON_KINDS:
+        n_total = int(args.photons) * args.gpus
+        if args.workload != "photonphoton":
+            d = dict(d, watts=(200000.0 / 13650.0) * n_total)
+        params = make_renderer(scene, cam, d).params()
+        kind = PHOTON_KINDS[args.workload]
+        t0 = time.perf_counter()
+        runs = [cpu_photons(scene, cam, params, kind, args.cpu_seconds) for _ in range(max(args.steps, 1))]
+        secs = time.perf_counter() - t0
+        last = runs[-1]
+        v = sum(x["value"] for x in runs) / len(runs)
+        last["value"] = v
+        print(json.dumps(dict(impl="reference", metric="Mphotons/s", value=v, unit="Mphotons/s", n_gpus=args.gpus, steps=args.steps, warmup=args.warmup,
+                              ms_per_step=1e3 * secs / max(args.steps, 1), higher_is_better=True, scaling="weak", vs_baseline=None, dtype="f64",
+                              data="synthetic", config=dict(workload=f"{args.workload}: bounded photon_render sample, see cpu_baseline.sample", photons=n_total),
+                              cpu_baseline=last, e2e=dict(value=v, unit="Mphotons/s", h2d_bytes_per_step=0, d2h_bytes_per_step=0))))
+        return
     params = make_renderer(scene, cam, d).params()
     for _ in range(args.warmup):
         cpu_sample(scene, cam, params, 0.5)
@@ -273,6 +296,127 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
+def run_photons(args):
+    import numpy as np
+    import torch
+
+    from rpt_b200 import Context
+    from rpt_b200 import dist as rd
+    from rpt_b200.scenes import make_renderer
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    dist = None
+    torch.cuda.set_device(local)
+    if world > 1:
+        import torch.distributed as dist
+
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    ctx = Context(local)
+    kind = PHOTON_KINDS[args.workload]
+    scene, cam, d = workload(args.workload)
+    n_total = int(args.photons) * world  # weak scaling
+    if args.workload != "photonphoton":
+        d = dict(d, watts=(200000.0 / 13650.0) * n_total)  # examples/volumetric_beambeam_lampshade.rs:139-148
+    w, h, spp = d["width"], d["height"], d["num_samples"]
+
+    def renderer(seed):
+        r = make_renderer(scene, cam, d, seed=seed)
+        r._ctx = ctx
+        return r.shard(world, rank)
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    r = renderer(0)
+    r.device_scene()
+    launches0 = 0
+    for _ in range(args.warmup):
+        film, pmap, tm = rd.photon_render(r, max(n_total // 50, 1000), kind)
+        launches0 = film.stats()["kernel_launches"]
+        film.close(); pmap.close()
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+    barrier()
+    t0 = time.perf_counter()
+    acc = dict(emit=0.0, merge=0.0, build=0.0, gather=0.0)
+    stats = None
+    for _ in range(args.steps):
+        film, pmap, tm = rd.photon_render(r, n_total, kind)
+        for k in acc:
+            acc[k] += tm[k]
+        stats = (tm["surface"], tm["volume"], film.stats(), pmap.stats())
+        img = film.image()
+        film.close(); pmap.close()
+    barrier()
+    wall = time.perf_counter() - t0
+    clk = clocks.stop() if rank == 0 else None
+    t = torch.tensor([wall], device=f"cuda:{local}", dtype=torch.float64)
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    step = float(t[0]) / args.steps
+    # e2e: from host scene description to host image, fresh scene every time
+    barrier()
+    t1 = time.perf_counter()
+    r2 = renderer(1)
+    film, pmap, _ = rd.photon_render(r2, n_total, kind)
+    img = film.image()
+    film.close(); pmap.close(); r2.device_scene().close()
+    barrier()
+    te = torch.tensor([time.perf_counter() - t1], device=f"cuda:{local}", dtype=torch.float64)
+    if dist is not None:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    if rank == 0:
+        peak, which = measured_peak_gbs()
+        ns, nv, fst, mst = stats
+        emit_s = acc["emit"] / 1e3 / args.steps
+        ach = PHOTON_ROW_BYTES * (ns + nv) / world / max(emit_s, 1e-12) / 1e9
+        cpu = None
+        if world == 1 and args.cpu_seconds > 0:
+            cpu = cpu_photons(scene, cam, r.params(), kind, args.cpu_seconds)
+        line = dict(metric="Mphotons/s", value=n_total / step / 1e6, unit="Mphotons/s", n_gpus=world, steps=args.steps, warmup=args.warmup,
+                    ms_per_step=1e3 * step, higher_is_better=True, scaling="weak", vs_baseline=None, dtype="f64", data="synthetic",
+                    config=dict(workload=f"{args.workload}: examples/volumetric_{args.workload}_lampshade.rs scene, {n_total} photons, camera pass {w}x{h} x {spp} spp, "
+                                         f"gather {d['gather_size']}/{d['gather_size_volume']}",
+                                photons=n_total, width=w, height=h, spp=spp, l2_policy="photon rows and maps (GBs) exceed the 126 MB L2",
+                                parallelism=f"photon-index-sharded emission + all-gather, sample-sharded gather x{world}"),
+                    e2e=dict(value=n_total / float(te[0]) / 1e6, unit="Mphotons/s", h2d_bytes_per_step=4096, d2h_bytes_per_step=int(w * h * 3),
+                             note="scene lowering + upload + BVH build + emit + merge + map build + gather + rgb8 image to host"),
+                    gpu_launches=int(fst["kernel_launches"] - launches0), clocks=clk,
+                    passes_ms={k: v / args.steps for k, v in acc.items()},
+                    photons=dict(surface=ns, volume=nv, bvh_items=mst["bvh_items"], gather_samples=w * h * spp * world,
+                                 knn_queries=fst["gather_queries"], visibility_rays=fst["gather_visibility"], candidates=fst["gather_candidates"]),
+                    roofline=dict(bound="hbm", kernel="k_photon_trace", achieved=ach, peak=peak, unit="GB/s", frac=ach / peak, traffic=None, peak_source=which,
+                                  note="104-byte deposit rows per emission second; the walk is issue-bound (12-object scene in L1), see DESIGN.md"),
+                    cpu_baseline=cpu)
+        print(json.dumps(line))
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def cpu_photons(scene, cam, params, kind, seconds):
+    """Oracle photon_render on a bounded photon count (calibrated to ~`seconds`), all host threads."""
+    import orc
+
+    osc = orc.OracleScene(scene)
+    n = 20000
+    t0 = time.perf_counter()
+    osc.photon_render(cam, params, n, kind)
+    dt = time.perf_counter() - t0
+    n2 = int(min(max(n * seconds / max(dt, 1e-6), n), 2_000_000))
+    t0 = time.perf_counter()
+    _, _, counts, secs = osc.photon_render(cam, params, n2, kind)
+    dt = time.perf_counter() - t0
+    return dict(value=n2 / dt / 1e6, unit="Mphotons/s", cores=orc.lib().orc_hardware_threads(), kind="port",
+                sample=f"photon_render of {n2} photons ({counts[0]} surface + {counts[1]} volume deposits) + camera pass {params.width}x{params.height}x{params.num_samples}: "
+                       f"emit {secs[0]:.2f} s, build {secs[1]:.2f} s, gather {secs[2]:.2f} s")
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -284,10 +428,13 @@ def main():
     ap.add_argument("--width", type=int, default=0, help="override (profiling runs only)")
     ap.add_argument("--height", type=int, default=0)
     ap.add_argument("--spp", type=int, default=0)
+    ap.add_argument("--photons", type=float, default=1e7, help="photons per GPU for the photon workloads")
     args = ap.parse_args()
     _OVERRIDES.update(width=args.width, height=args.height, num_samples=args.spp)
     if args.impl == "reference":
         run_reference(args)
+    elif args.workload in PHOTON_KINDS:
+        run_photons(args)
     else:
         run_ours(args)
 

@@ -29,31 +29,42 @@ __global__ void k_morton(const PrimBox* __restrict__ boxes, uint32_t n, float3 c
     keys[i] = ((uint64_t)code << 32) | (uint64_t)i;  // index makes every key unique
 }
 
+// SORTED = false: keys are (30-bit Morton << 32 | primitive index), unique, and a primitive's box is
+// boxes[key & 0xffffffff].  SORTED = true: keys are 63-bit Morton codes already sorted together with
+// their boxes (boxes[k] belongs to position k); equal keys are split by position (Karras 2012, sec. 4).
+template <bool SORTED>
 __device__ __forceinline__ int delta(const uint64_t* __restrict__ keys, int n, int i, int j) {
     if (j < 0 || j >= n) return -1;
-    return __clzll((long long)(keys[i] ^ keys[j]));
+    const uint64_t x = keys[i] ^ keys[j];
+    if (SORTED && x == 0) return 64 + __clz(i ^ j);
+    return __clzll((long long)x);
+}
+template <bool SORTED>
+__device__ __forceinline__ uint32_t box_of(const uint64_t* __restrict__ keys, int k) {
+    return SORTED ? (uint32_t)k : (uint32_t)(keys[k] & 0xffffffffu);
 }
 
 // Karras 2012: one thread per internal node
+template <bool SORTED>
 __global__ void k_hierarchy(const uint64_t* __restrict__ keys, int n, int* __restrict__ left, int* __restrict__ right,
                             int* __restrict__ first, int* __restrict__ last, int* __restrict__ parent_i,
                             int* __restrict__ parent_l) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n - 1) return;
-    const int d = (delta(keys, n, i, i + 1) - delta(keys, n, i, i - 1)) >= 0 ? 1 : -1;
-    const int dmin = delta(keys, n, i, i - d);
+    const int d = (delta<SORTED>(keys, n, i, i + 1) - delta<SORTED>(keys, n, i, i - 1)) >= 0 ? 1 : -1;
+    const int dmin = delta<SORTED>(keys, n, i, i - d);
     int lmax = 2;
-    while (delta(keys, n, i, i + lmax * d) > dmin) lmax *= 2;
+    while (delta<SORTED>(keys, n, i, i + lmax * d) > dmin) lmax *= 2;
     int l = 0;
     for (int t = lmax / 2; t >= 1; t /= 2)
-        if (delta(keys, n, i, i + (l + t) * d) > dmin) l += t;
+        if (delta<SORTED>(keys, n, i, i + (l + t) * d) > dmin) l += t;
     const int j = i + l * d;
-    const int dnode = delta(keys, n, i, j);
+    const int dnode = delta<SORTED>(keys, n, i, j);
     int s = 0;
     int t = l;
     do {
         t = (t + 1) / 2;
-        if (delta(keys, n, i, i + (s + t) * d) > dnode) s += t;
+        if (delta<SORTED>(keys, n, i, i + (s + t) * d) > dnode) s += t;
     } while (t > 1);
     const int gamma = i + s * d + min(d, 0);
     const int lo = min(i, j), hi = max(i, j);
@@ -82,6 +93,7 @@ __device__ __forceinline__ PrimBox load_cg(const PrimBox* p) {
 }
 
 // bottom-up refit: one thread per leaf, second arrival at a node merges its children
+template <bool SORTED>
 __global__ void k_refit(const PrimBox* __restrict__ boxes, const uint64_t* __restrict__ keys, int n, const int* __restrict__ left,
                         const int* __restrict__ right, const int* __restrict__ parent_i, const int* __restrict__ parent_l,
                         int* __restrict__ flags, PrimBox* __restrict__ ibox) {
@@ -93,13 +105,14 @@ __global__ void k_refit(const PrimBox* __restrict__ boxes, const uint64_t* __res
         if (atomicAdd(&flags[p], 1) == 0) return;
         __threadfence();
         const int lc = left[p], rc = right[p];
-        const PrimBox a = lc >= 0 ? load_cg(&ibox[lc]) : boxes[(uint32_t)(keys[~lc] & 0xffffffffu)];
-        const PrimBox b = rc >= 0 ? load_cg(&ibox[rc]) : boxes[(uint32_t)(keys[~rc] & 0xffffffffu)];
+        const PrimBox a = lc >= 0 ? load_cg(&ibox[lc]) : boxes[box_of<SORTED>(keys, ~lc)];
+        const PrimBox b = rc >= 0 ? load_cg(&ibox[rc]) : boxes[box_of<SORTED>(keys, ~rc)];
         ibox[p] = merge(a, b);
         p = parent_i[p];
     }
 }
 
+template <bool SORTED>
 __device__ __forceinline__ void child_out(int c, const PrimBox* __restrict__ boxes, const uint64_t* __restrict__ keys,
                                           const PrimBox* __restrict__ ibox, const int* __restrict__ first,
                                           const int* __restrict__ last, float pad, int leaf_max, float* mn, float* mx, int* ref) {
@@ -109,22 +122,23 @@ __device__ __forceinline__ void child_out(int c, const PrimBox* __restrict__ box
         const int sz = last[c] - first[c] + 1;
         *ref = (sz <= leaf_max) ? make_leaf_ref((uint32_t)first[c], (uint32_t)sz) : c;
     } else {
-        b = boxes[(uint32_t)(keys[~c] & 0xffffffffu)];
+        b = boxes[box_of<SORTED>(keys, ~c)];
         *ref = make_leaf_ref((uint32_t)(~c), 1u);
     }
 #pragma unroll
     for (int k = 0; k < 3; k++) { mn[k] = __fsub_rd(b.mn[k], pad); mx[k] = __fadd_ru(b.mx[k], pad); }
 }
 
+template <bool SORTED>
 __global__ void k_emit(const PrimBox* __restrict__ boxes, const uint64_t* __restrict__ keys, int n, const int* __restrict__ left,
                        const int* __restrict__ right, const int* __restrict__ first, const int* __restrict__ last,
                        const PrimBox* __restrict__ ibox, float pad, int leaf_max, BvhNode* __restrict__ nodes, uint32_t* __restrict__ perm) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) perm[i] = (uint32_t)(keys[i] & 0xffffffffu);
+    if (!SORTED && i < n) perm[i] = (uint32_t)(keys[i] & 0xffffffffu);
     if (i >= n - 1) return;
     BvhNode nd;
-    child_out(left[i], boxes, keys, ibox, first, last, pad, leaf_max, nd.lmin, nd.lmax, &nd.left);
-    child_out(right[i], boxes, keys, ibox, first, last, pad, leaf_max, nd.rmin, nd.rmax, &nd.right);
+    child_out<SORTED>(left[i], boxes, keys, ibox, first, last, pad, leaf_max, nd.lmin, nd.lmax, &nd.left);
+    child_out<SORTED>(right[i], boxes, keys, ibox, first, last, pad, leaf_max, nd.rmin, nd.rmax, &nd.right);
     nd.pad0 = 0; nd.pad1 = 0;
     nodes[i] = nd;
 }
@@ -168,11 +182,11 @@ int build_lbvh(const PrimBox* d_boxes, uint32_t n, float pad, int leaf_max, cons
         int* flags = ints + 6 * (size_t)n;
         RPTX_CK(cudaMemsetAsync(flags, 0, sizeof(int) * n, stream));
         if (n > 1) {
-            k_hierarchy<<<B, T, 0, stream>>>(keys_out, (int)n, left, right, first, last, parent_i, parent_l);
-            k_refit<<<B, T, 0, stream>>>(d_boxes, keys_out, (int)n, left, right, parent_i, parent_l, flags, ibox);
+            k_hierarchy<false><<<B, T, 0, stream>>>(keys_out, (int)n, left, right, first, last, parent_i, parent_l);
+            k_refit<false><<<B, T, 0, stream>>>(d_boxes, keys_out, (int)n, left, right, parent_i, parent_l, flags, ibox);
             (*launches) += 2;
         }
-        k_emit<<<B, T, 0, stream>>>(d_boxes, keys_out, (int)n, left, right, first, last, ibox, pad, leaf_max, d_nodes, d_perm);
+        k_emit<false><<<B, T, 0, stream>>>(d_boxes, keys_out, (int)n, left, right, first, last, ibox, pad, leaf_max, d_nodes, d_perm);
         (*launches)++;
         RPTX_CK(cudaGetLastError());
         RPTX_CK(cudaStreamSynchronize(stream));
@@ -181,6 +195,44 @@ int build_lbvh(const PrimBox* d_boxes, uint32_t n, float pad, int leaf_max, cons
 fail:
 #undef RPTX_CK
     cudaFree(keys_in); cudaFree(keys_out); cudaFree(ints); cudaFree(ibox); cudaFree(tmp);
+    return (int)e;
+}
+
+// LBVH over items that are ALREADY sorted by a 63-bit Morton key (photon point maps).
+int build_lbvh_sorted(const uint64_t* d_keys, const PrimBox* d_boxes, uint32_t n, float pad, int leaf_max, BvhNode* d_nodes, int* root_ref,
+                      cudaStream_t stream, uint64_t* launches) {
+    if (n == 0) { *root_ref = 0; return 0; }
+    cudaError_t e;
+    int* ints = nullptr;
+    PrimBox* ibox = nullptr;
+#define RPTX_CK(x) do { e = (x); if (e != cudaSuccess) goto fail; } while (0)
+    RPTX_CK(cudaMalloc(&ints, sizeof(int) * (size_t)n * 7));
+    RPTX_CK(cudaMalloc(&ibox, sizeof(PrimBox) * n));
+    {
+        const int T = 128;
+        const int B = (int)((n + T - 1) / T);
+        int* left = ints;
+        int* right = ints + n;
+        int* first = ints + 2 * (size_t)n;
+        int* last = ints + 3 * (size_t)n;
+        int* parent_i = ints + 4 * (size_t)n;
+        int* parent_l = ints + 5 * (size_t)n;
+        int* flags = ints + 6 * (size_t)n;
+        RPTX_CK(cudaMemsetAsync(flags, 0, sizeof(int) * n, stream));
+        if (n > 1) {
+            k_hierarchy<true><<<B, T, 0, stream>>>(d_keys, (int)n, left, right, first, last, parent_i, parent_l);
+            k_refit<true><<<B, T, 0, stream>>>(d_boxes, d_keys, (int)n, left, right, parent_i, parent_l, flags, ibox);
+            (*launches) += 2;
+        }
+        k_emit<true><<<B, T, 0, stream>>>(d_boxes, d_keys, (int)n, left, right, first, last, ibox, pad, leaf_max, d_nodes, nullptr);
+        (*launches)++;
+        RPTX_CK(cudaGetLastError());
+        RPTX_CK(cudaStreamSynchronize(stream));
+        *root_ref = (n <= (uint32_t)leaf_max) ? make_leaf_ref(0u, n) : 0;
+    }
+fail:
+#undef RPTX_CK
+    cudaFree(ints); cudaFree(ibox);
     return (int)e;
 }
 

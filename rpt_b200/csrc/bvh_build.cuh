@@ -20,4 +20,9 @@ struct LbvhScratch;  // opaque
 int build_lbvh(const PrimBox* d_boxes, uint32_t n, float pad, int leaf_max, const double cmin[3], const double cmax[3],
                BvhNode* d_nodes, uint32_t* d_perm, int* root_ref, cudaStream_t stream, uint64_t* launches);
 
+// Same hierarchy over items already sorted by 63-bit Morton keys (d_keys[k], d_boxes[k] = item in
+// slot k; equal keys allowed).  d_nodes: room for max(n-1,1) nodes.
+int build_lbvh_sorted(const uint64_t* d_keys, const PrimBox* d_boxes, uint32_t n, float pad, int leaf_max, BvhNode* d_nodes, int* root_ref,
+                      cudaStream_t stream, uint64_t* launches);
+
 }  // namespace rptx

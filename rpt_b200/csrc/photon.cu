@@ -4,6 +4,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -116,30 +117,16 @@ __global__ void k_rows_gather(const PhotonRec* __restrict__ rows, const uint32_t
     key[i] = r.key;
 }
 
-// leaves of the implicit tree: f32 boxes (rounded outward) of kPointLeaf consecutive photons
-__global__ void k_point_leaves(const double* __restrict__ px, const double* __restrict__ py, const double* __restrict__ pz, uint32_t n,
-                               uint32_t n_leaf_slots, uint32_t leaf_base, float4* __restrict__ node_box) {
-    const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
-    if (j >= n_leaf_slots) return;
-    float mn[3] = {CUDART_INF_F, CUDART_INF_F, CUDART_INF_F}, mx[3] = {-CUDART_INF_F, -CUDART_INF_F, -CUDART_INF_F};
-    const uint64_t first = (uint64_t)j * kPointLeaf;
-    for (uint64_t i = first; i < first + kPointLeaf && i < n; i++) {
-        mn[0] = fminf(mn[0], __double2float_rd(px[i])); mx[0] = fmaxf(mx[0], __double2float_ru(px[i]));
-        mn[1] = fminf(mn[1], __double2float_rd(py[i])); mx[1] = fmaxf(mx[1], __double2float_ru(py[i]));
-        mn[2] = fminf(mn[2], __double2float_rd(pz[i])); mx[2] = fmaxf(mx[2], __double2float_ru(pz[i]));
-    }
-    node_box[2 * (size_t)(leaf_base + j)] = make_float4(mn[0], mn[1], mn[2], 0.f);
-    node_box[2 * (size_t)(leaf_base + j) + 1] = make_float4(mx[0], mx[1], mx[2], 0.f);
-}
-
-// one level of inner nodes [first, first + count): union of the two children
-__global__ void k_point_level(uint32_t first, uint32_t count, float4* __restrict__ node_box) {
-    const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
-    if (j >= count) return;
-    const size_t node = first + j, c0 = 2 * node + 1;
-    const float4 a0 = node_box[2 * c0], b0 = node_box[2 * c0 + 1], a1 = node_box[2 * c0 + 2], b1 = node_box[2 * c0 + 3];
-    node_box[2 * node] = make_float4(fminf(a0.x, a1.x), fminf(a0.y, a1.y), fminf(a0.z, a1.z), 0.f);
-    node_box[2 * node + 1] = make_float4(fmaxf(b0.x, b1.x), fmaxf(b0.y, b1.y), fmaxf(b0.z, b1.z), 0.f);
+// f32 boxes (rounded outward) of the Morton-ordered photons, for the LBVH refit
+__global__ void k_point_boxes(const double* __restrict__ px, const double* __restrict__ py, const double* __restrict__ pz, uint32_t n,
+                              PrimBox* __restrict__ boxes) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    PrimBox b;
+    b.mn[0] = __double2float_rd(px[i]); b.mx[0] = __double2float_ru(px[i]);
+    b.mn[1] = __double2float_rd(py[i]); b.mx[1] = __double2float_ru(py[i]);
+    b.mn[2] = __double2float_rd(pz[i]); b.mx[2] = __double2float_ru(pz[i]);
+    boxes[i] = b;
 }
 
 // radius of a photon sphere = distance to its 10th nearest volume photon, itself included
@@ -324,56 +311,52 @@ int build_point_map(rptx_ctx* ctx, const PhotonRec* rows, const uint32_t* d_cano
     cudaStream_t st = ctx->stream;
     out->dev = PointMapDev{};
     out->dev.n = n;
+    if (n >= (1u << 28)) return ctx_fail(ctx, "photon map exceeds 2^28 records per list");
     double *px = nullptr, *py = nullptr, *pz = nullptr, *dir = nullptr, *power = nullptr;
     uint64_t* key = nullptr;
+    BvhNode* nodes = nullptr;
     CK(dev_alloc(&px, n, &out->owned)); CK(dev_alloc(&py, n, &out->owned)); CK(dev_alloc(&pz, n, &out->owned));
     CK(dev_alloc(&dir, 3 * (size_t)n, &out->owned)); CK(dev_alloc(&power, 3 * (size_t)n, &out->owned));
     CK(dev_alloc(&key, n, &out->owned));
-    const uint32_t n_leaf = (n + kPointLeaf - 1) / kPointLeaf;
-    uint32_t P = 1;
-    while (P < std::max<uint32_t>(n_leaf, 1)) P <<= 1;
-    float4* node_box = nullptr;
-    CK(dev_alloc(&node_box, 2 * (size_t)(2 * P - 1), &out->owned));
-    out->dev.leaf_base = P - 1;
-    out->dev.node_box = node_box;
+    CK(dev_alloc(&nodes, std::max<uint32_t>(n, 1), &out->owned));
+    out->dev.nodes = nodes;
     out->dev.px = px; out->dev.py = py; out->dev.pz = pz; out->dev.dir = dir; out->dev.power = power; out->dev.key = key;
-    if (n > 0) {
-        const int blocks = std::min(grid_for(n, 256), 1184);
-        double* d_b = nullptr;
-        CK(dev_alloc(&d_b, (size_t)blocks * 6, nullptr));
-        k_rows_bounds<<<blocks, 256, 0, st>>>(rows, n, d_b);
-        ctx->launches++;
-        double mn[3], mx[3];
-        const int rc0 = reduce_bounds(ctx, d_b, blocks, mn, mx);
-        cudaFree(d_b);
-        if (rc0) return rc0;
-        uint64_t *k0 = nullptr, *k1 = nullptr;
-        uint32_t* i1 = nullptr;
+    if (n == 0) return 0;
+    const int blocks = std::min(grid_for(n, 256), 1184);
+    double* d_b = nullptr;
+    CK(dev_alloc(&d_b, (size_t)blocks * 6, nullptr));
+    k_rows_bounds<<<blocks, 256, 0, st>>>(rows, n, d_b);
+    ctx->launches++;
+    double mn[3], mx[3];
+    const int rc0 = reduce_bounds(ctx, d_b, blocks, mn, mx);
+    cudaFree(d_b);
+    if (rc0) return rc0;
+    uint64_t *k0 = nullptr, *k1 = nullptr;
+    uint32_t* i1 = nullptr;
+    PrimBox* boxes = nullptr;
+    int rc = 0;
+    auto body = [&]() -> int {
         CK(dev_alloc(&k0, n, nullptr)); CK(dev_alloc(&k1, n, nullptr)); CK(dev_alloc(&i1, n, nullptr));
         const double3 dmn = make_double3(mn[0], mn[1], mn[2]);
         const double3 inv = make_double3(mx[0] > mn[0] ? 1.0 / (mx[0] - mn[0]) : 0.0, mx[1] > mn[1] ? 1.0 / (mx[1] - mn[1]) : 0.0,
                                          mx[2] > mn[2] ? 1.0 / (mx[2] - mn[2]) : 0.0);
         k_rows_morton<<<grid_for(n, 256), 256, 0, st>>>(rows, d_canon, n, dmn, inv, k0);
         ctx->launches++;
-        const int rc = sort_pairs(ctx, k0, k1, const_cast<uint32_t*>(d_canon), i1, n, 63);
-        if (rc == 0) {
-            k_rows_gather<<<grid_for(n, 256), 256, 0, st>>>(rows, i1, n, px, py, pz, dir, power, key);
-            ctx->launches++;
-        }
-        cudaError_t e = cudaStreamSynchronize(st);
-        cudaFree(k0); cudaFree(k1); cudaFree(i1);
-        if (rc) return rc;
-        if (e != cudaSuccess) return ctx_fail(ctx, std::string("point map gather: ") + cudaGetErrorString(e));
-    }
-    k_point_leaves<<<grid_for(P, 256), 256, 0, st>>>(px, py, pz, n, P, P - 1, node_box);
-    ctx->launches++;
-    for (uint32_t level = P / 2; level >= 1; level /= 2) {
-        k_point_level<<<grid_for(level, 256), 256, 0, st>>>(level - 1, level, node_box);
+        if (int r = sort_pairs(ctx, k0, k1, const_cast<uint32_t*>(d_canon), i1, n, 63)) return r;
+        k_rows_gather<<<grid_for(n, 256), 256, 0, st>>>(rows, i1, n, px, py, pz, dir, power, key);
         ctx->launches++;
-    }
-    CK(cudaGetLastError());
-    CK(cudaStreamSynchronize(st));
-    return 0;
+        cudaFree(k0); k0 = nullptr;
+        cudaFree(i1); i1 = nullptr;
+        CK(dev_alloc(&boxes, n, nullptr));
+        k_point_boxes<<<grid_for(n, 256), 256, 0, st>>>(px, py, pz, n, boxes);
+        ctx->launches++;
+        const int e = build_lbvh_sorted(k1, boxes, n, 0.0f, kPointLeaf, nodes, &out->dev.root_ref, st, &ctx->launches);
+        if (e != 0) return ctx_fail(ctx, std::string("point map LBVH: ") + cudaGetErrorString((cudaError_t)e));
+        return 0;
+    };
+    rc = body();
+    cudaFree(k0); cudaFree(k1); cudaFree(i1); cudaFree(boxes);
+    return rc;
 }
 
 // BVH::build over item boxes (bvh 0.6.0): LBVH with exact f32 unions.  perm[k] = item in leaf slot k.
@@ -735,7 +718,13 @@ int rptx_photon_gather_trace(rptx_film* f, rptx_photon_map* m, uint32_t iteratio
     const SceneDev sc = rptx_host::scene_dev(f->scene);
     const MediumDev md = rptx_host::medium_dev(f->scene);
     CK(cudaEventRecord(f->ev0, st));
-    if (kmax <= 32) launch_gather<32>(sc, md, pm, ga, f->q.stats, st);
+    const bool warp_mode = m->kind == RPTX_PHOTON_MAP && kmax <= kWarpKnnMaxK && !std::getenv("RPTX_GATHER_PER_THREAD");
+    if (warp_mode) {
+        // one warp per slot: ~64 K slots keep every SM busy for several rounds
+        ga.n_lanes = std::max<uint32_t>(1, std::min<uint32_t>(ga.n_lanes, std::max<uint32_t>(1, 65536u / ga.n_pixels)));
+        const size_t warps = (size_t)ga.n_pixels * ga.n_lanes;
+        k_photon_gather_warp<<<grid_for(warps, 4), 128, 0, st>>>(sc, md, pm, ga, f->q.stats);
+    } else if (kmax <= 32) launch_gather<32>(sc, md, pm, ga, f->q.stats, st);
     else if (kmax <= 128) launch_gather<128>(sc, md, pm, ga, f->q.stats, st);
     else launch_gather<1024>(sc, md, pm, ga, f->q.stats, st);
     k_lane_reduce<<<grid_for(ga.n_pixels, 128), 128, 0, st>>>(ga.ax, ga.ay, ga.az, ga.n_pixels, ga.n_lanes, f->d_batch_sum);

@@ -10,8 +10,9 @@
 //    results do not depend on thread scheduling or on how many GPUs emitted the photons);
 //  * a point map keeps its photons in 63-bit Morton order as structure-of-arrays (f64 position
 //    triples read by the kNN search; direction / power / key touched only for the k winners)
-//    under an implicit complete binary tree of f32 boxes (32 B per node, two float4 loads)
-//    whose leaves are kPointLeaf consecutive photons;
+//    under a Karras LBVH built on those codes (64-byte nodes holding both children's f32 boxes,
+//    leaves of <= kPointLeaf consecutive photons).  Splitting at Morton-cell boundaries matters:
+//    an implicit equal-count tree over the same order visited 8x more nodes per query;
 //  * photon spheres / beams sit under the same LBVH the object accelerator uses
 //    (bvh_build.cu), with their own f32 boxes computed exactly as the reference does
 //    (:76-105, :119-128) so the candidate set of BVH::traverse is reproduced.
@@ -162,14 +163,15 @@ __global__ void __launch_bounds__(128) k_photon_trace(const __grid_constant__ Sc
 // ------------------------------------------------------------------ point map (kd-tree 0.4.1)
 
 struct PointMapDev {
-    uint32_t n;          // photons
-    uint32_t leaf_base;  // heap index of the first leaf node (= P - 1, P = leaves rounded up to 2^m)
-    const float4* node_box;  // [2P - 1][2]: (min xyz, -), (max xyz, -); empty nodes are inverted
+    uint32_t n;           // photons
+    int root_ref;         // LBVH root (leaf ref when n <= kPointLeaf)
+    const BvhNode* nodes; // Karras LBVH over the 63-bit Morton order: 64 B, both children's f32 boxes (rounded outward)
     const double *px, *py, *pz;  // Morton order
     const double* dir;    // [n][3]
     const double* power;  // [n][3]
     const uint64_t* key;  // [n]
 };
+constexpr int kKnnStack = 96;  // Karras depth <= 63 key bits + 32 tie-break bits
 
 // k nearest so far: binary max-heap on the squared distance
 template <int KMAX>
@@ -228,37 +230,36 @@ template <int KMAX>
 RPTX_DN void knn_query(const PointMapDev& m, d3 q, KnnHeap<KMAX>& h) {
     h.size = 0;
     if (m.n == 0 || h.k == 0) return;
-    uint32_t stack[32];
-    double stack_d[32];
+    int stack[kKnnStack];
+    double stack_d[kKnnStack];
     int sp = 0;
-    uint32_t node = 0;
+    int cur = m.root_ref;
     for (;;) {
-        bool have = true;
-        while (node < m.leaf_base) {
-            const uint32_t c0 = 2 * node + 1;
-            const float4 a0 = __ldg(m.node_box + 2 * c0), b0 = __ldg(m.node_box + 2 * c0 + 1);
-            const float4 a1 = __ldg(m.node_box + 2 * c0 + 2), b1 = __ldg(m.node_box + 2 * c0 + 3);
-            const double d0 = box_dist2(a0, b0, q), d1 = box_dist2(a1, b1, q);
+        while (cur >= 0) {
+            const float4* np = reinterpret_cast<const float4*>(m.nodes + cur);
+            const float4 a = __ldg(np), b = __ldg(np + 1), c = __ldg(np + 2), d = __ldg(np + 3);
+            const double d0 = box_dist2(a, b, q), d1 = box_dist2(c, d, q);
+            const int left = __float_as_int(a.w), right = __float_as_int(c.w);
             const double w = h.worst();
-            const bool v0 = d0 * kBoxShrink <= w && d0 < CUDART_INF, v1 = d1 * kBoxShrink <= w && d1 < CUDART_INF;
+            const bool v0 = d0 * kBoxShrink <= w, v1 = d1 * kBoxShrink <= w;
             if (v0 && v1) {
                 const bool first0 = d0 <= d1;
-                stack[sp] = first0 ? c0 + 1 : c0;
+                stack[sp] = first0 ? right : left;
                 stack_d[sp] = first0 ? d1 : d0;
                 sp++;
-                node = first0 ? c0 : c0 + 1;
+                cur = first0 ? left : right;
             } else if (v0) {
-                node = c0;
+                cur = left;
             } else if (v1) {
-                node = c0 + 1;
+                cur = right;
             } else {
-                have = false;
+                cur = 0x7fffffff;  // nothing to visit below this node
                 break;
             }
         }
-        if (have) {
-            const uint32_t first = (node - m.leaf_base) * kPointLeaf;
-            const uint32_t last = min(first + (uint32_t)kPointLeaf, m.n);
+        if (cur < 0) {
+            const uint32_t code = (uint32_t)(~cur);
+            const uint32_t first = code >> 3, last = first + (code & 7u) + 1u;
             for (uint32_t i = first; i < last; i++) {
                 const double dx = __ldg(m.px + i) - q.x, dy = __ldg(m.py + i) - q.y, dz = __ldg(m.pz + i) - q.z;
                 h.push(dx * dx + dy * dy + dz * dz, i);
@@ -267,7 +268,7 @@ RPTX_DN void knn_query(const PointMapDev& m, d3 q, KnnHeap<KMAX>& h) {
         for (;;) {
             if (sp == 0) return;
             sp--;
-            if (stack_d[sp] * kBoxShrink <= h.worst()) { node = stack[sp]; break; }
+            if (stack_d[sp] * kBoxShrink <= h.worst()) { cur = stack[sp]; break; }
         }
     }
 }
@@ -532,6 +533,203 @@ RPTX_D d3 estimate_indirect(const SceneDev& sc, const MediumDev& md, const Photo
     return surface_color + volume_color;
 }
 
+// ------------------------------------------------------------------ warp-cooperative gather
+// The per-thread kNN above spends its time in heap sift loops over local memory with 2-3 of 32
+// lanes active (profiles/r1_v2_summary.md).  For the point-point estimator (k = 30..100) a whole
+// warp owns one camera sample instead: all lanes walk the tree together (uniform control flow),
+// a "warp leaf" is 32 consecutive photons tested one per lane, accepted candidates are appended
+// to a shared-memory list by ballot, and when the list is full a bitonic sort keeps the k best
+// and tightens the radius.  The k visibility rays of the surface estimate then run 32 at a time.
+constexpr int kWarpCand = 256;       // candidate list capacity per warp (>= k + 32)
+constexpr uint32_t kWarpKnnMaxK = 128;
+
+struct WarpKnnSmem {
+    double d2[kWarpCand];
+    uint32_t idx[kWarpCand];
+    double stack_d[kKnnStack];
+    uint32_t stack[kKnnStack];
+};
+
+// ascending bitonic sort of the first n (power of two, <= kWarpCand) candidates by d2
+RPTX_D void warp_sort_candidates(WarpKnnSmem& sm, uint32_t n, uint32_t lane) {
+    for (uint32_t size = 2; size <= n; size <<= 1) {
+        for (uint32_t stride = size >> 1; stride > 0; stride >>= 1) {
+            for (uint32_t t = lane; t < (n >> 1); t += 32) {
+                const uint32_t lo = 2 * t - (t & (stride - 1));  // index of the lower partner
+                const uint32_t hi = lo + stride;
+                const bool up = (lo & size) == 0;
+                const double a = sm.d2[lo], b = sm.d2[hi];
+                if ((a > b) == up) {
+                    sm.d2[lo] = b; sm.d2[hi] = a;
+                    const uint32_t ia = sm.idx[lo];
+                    sm.idx[lo] = sm.idx[hi]; sm.idx[hi] = ia;
+                }
+            }
+            __syncwarp();
+        }
+    }
+}
+
+// keep the k smallest of the `count` candidates (sorted ascending); returns the new count
+RPTX_D uint32_t warp_compact_candidates(WarpKnnSmem& sm, uint32_t count, uint32_t k, uint32_t lane) {
+    uint32_t n = 2;
+    while (n < count) n <<= 1;
+    for (uint32_t i = count + lane; i < n; i += 32) { sm.d2[i] = CUDART_INF; sm.idx[i] = 0xffffffffu; }
+    __syncwarp();
+    warp_sort_candidates(sm, n, lane);
+    return count < k ? count : k;
+}
+
+// KdTree::nearests(q, k) by a whole warp; every lane passes the same q and k (k <= kWarpKnnMaxK).
+// On return sm.d2 / sm.idx hold the result in ascending order; returns its size.
+RPTX_D uint32_t warp_knn(const PointMapDev& m, d3 q, uint32_t k, WarpKnnSmem& sm) {
+    const uint32_t lane = threadIdx.x & 31u;
+    if (m.n == 0 || k == 0) return 0;
+    uint32_t count = 0, sp = 0;
+    int cur = m.root_ref;
+    double worst = CUDART_INF;
+    for (;;) {
+        while (cur >= 0) {
+            const float4* np = reinterpret_cast<const float4*>(m.nodes + cur);
+            const float4 a = __ldg(np), b = __ldg(np + 1), c = __ldg(np + 2), d = __ldg(np + 3);
+            const double d0 = box_dist2(a, b, q), d1 = box_dist2(c, d, q);
+            const int left = __float_as_int(a.w), right = __float_as_int(c.w);
+            const bool v0 = d0 * kBoxShrink <= worst, v1 = d1 * kBoxShrink <= worst;
+            if (v0 && v1) {
+                const bool first0 = d0 <= d1;
+                if (lane == 0) { sm.stack[sp] = (uint32_t)(first0 ? right : left); sm.stack_d[sp] = first0 ? d1 : d0; }
+                sp++;
+                cur = first0 ? left : right;
+            } else if (v0) {
+                cur = left;
+            } else if (v1) {
+                cur = right;
+            } else {
+                cur = 0x7fffffff;
+                break;
+            }
+        }
+        if (cur < 0) {
+            if (count + 32 > (uint32_t)kWarpCand) {
+                count = warp_compact_candidates(sm, count, k, lane);
+                if (count == k) worst = sm.d2[k - 1];
+            }
+            const uint32_t code = (uint32_t)(~cur);
+            const uint32_t first = code >> 3, n_here = (code & 7u) + 1u;
+            const uint32_t i = first + lane;
+            double dd = CUDART_INF;
+            if (lane < n_here) {
+                const double dx = __ldg(m.px + i) - q.x, dy = __ldg(m.py + i) - q.y, dz = __ldg(m.pz + i) - q.z;
+                dd = dx * dx + dy * dy + dz * dz;
+            }
+            const bool take = lane < n_here && dd < worst;
+            const unsigned mask = __ballot_sync(0xffffffffu, take);
+            if (take) {
+                const uint32_t at = count + __popc(mask & ((1u << lane) - 1u));
+                sm.d2[at] = dd; sm.idx[at] = i;
+            }
+            count += __popc(mask);
+        }
+        __syncwarp();
+        for (;;) {
+            if (sp == 0) return warp_compact_candidates(sm, count, k, lane);
+            sp--;
+            if (sm.stack_d[sp] * kBoxShrink <= worst) { cur = (int)sm.stack[sp]; break; }
+        }
+        __syncwarp();  // every lane has read the popped entry before lane 0 may overwrite the slot
+    }
+}
+
+RPTX_D d3 warp_sum(d3 v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        v.x += __shfl_xor_sync(0xffffffffu, v.x, o);
+        v.y += __shfl_xor_sync(0xffffffffu, v.y, o);
+        v.z += __shfl_xor_sync(0xffffffffu, v.z, o);
+    }
+    return v;
+}
+
+// surface_estimate (src/photon.rs:327-375) by a warp: lanes share the kNN, then take the photons'
+// visibility rays 32 at a time.  All lanes return the same colour.
+RPTX_D d3 warp_surface_estimate(const SceneDev& sc, const PhotonMapDev& pm, const RayD& ray, d3 wo, double t_hit, d3 normal,
+                                const Material& mat, WarpKnnSmem& sm, GatherCounters& ctr) {
+    const uint32_t lane = threadIdx.x & 31u;
+    const d3 world_pos = ray.o + t_hit * ray.d;
+    const uint32_t count = warp_knn(pm.surface, world_pos, pm.gather_size, sm);
+    if (lane == 0) ctr.knn++;
+    const double max_d2 = count ? fmax(0.0, sm.d2[count - 1]) : 0.0;
+    d3 part = mk3(0, 0, 0);
+    for (uint32_t j = lane; j < count; j += 32) {
+        const uint32_t i = sm.idx[j];
+        const d3 ppos = mk3(pm.surface.px[i], pm.surface.py[i], pm.surface.pz[i]);
+        const d3 disp = world_pos - ppos;
+        RayD vr;
+        vr.o = ppos;
+        vr.d = normalize(disp);
+        const double len = length(disp);
+        Hit vh;
+        vh.t = len;
+        closest_hit<kAnyBelow>(sc, vr, kEpsilon, len, vh);
+        ctr.visibility++;
+        if (vh.inst != kNoHit && len > vh.t) continue;
+        const d3 pdir = mk3(pm.surface.dir[3 * (size_t)i], pm.surface.dir[3 * (size_t)i + 1], pm.surface.dir[3 * (size_t)i + 2]);
+        const d3 ppow = mk3(pm.surface.power[3 * (size_t)i], pm.surface.power[3 * (size_t)i + 1], pm.surface.power[3 * (size_t)i + 2]);
+        part = part + cmul(mat_bsdf(mat, normal, wo, pdir), ppow) * clampd(dot(pdir, normal), 0.0, 1.0);
+    }
+    __syncwarp();
+    const d3 color = mat_emittance(mat) * mat_color(mat) + warp_sum(part);
+    return color * (1.0 / (kPi * max_d2));
+}
+
+// estimate_indirect for the point-point map (PhotonRenderKind::PhotonMap) by a warp
+RPTX_D d3 warp_estimate_point_point(const SceneDev& sc, const MediumDev& md, const PhotonMapDev& pm, const RayD& ray, Rng& rng,
+                                    WarpKnnSmem& sm, GatherCounters& ctr) {
+    const uint32_t lane = threadIdx.x & 31u;
+    const d3 wo = -normalize(ray.d);
+    Hit h;
+    h.t = CUDART_INF;
+    closest_hit<kClosest>(sc, ray, kEpsilon, 0.0, h);
+    const bool medium = md.kind != 0;
+    const bool hit = h.inst != kNoHit;
+    Material mat;
+    mat.kind = 0; mat.albedo[0] = mat.albedo[1] = mat.albedo[2] = 0.0; mat.emittance = 0.0; mat.shininess = 0.0; mat.ior = 1.0;
+    d3 n = mk3(0, 0, 0);
+    if (hit) {
+        uint32_t prim, inst;
+        n = hit_normal(sc, ray, h, &prim, &inst);
+        mat = sc.materials[h.obj];
+    }
+    if (!medium) return hit ? warp_surface_estimate(sc, pm, ray, wo, h.t, n, mat, sm, ctr) : env_color(sc, ray.d);
+    // volume_estimate, point-point branch (src/photon.rs:386-437)
+    const double extinction = md.extinction();
+    const double random = rng.gen_range(0.0, 1.0);
+    const double d = -log(random) / extinction;
+    const double tr = exp(-(extinction * d));
+    const double d_pdf = extinction * tr, d_cdf = 1.0 - tr;
+    if (!hit || d < h.t) {
+        const d3 collision = ray.o + d * ray.d;
+        const d3 mc = md.color(collision);
+        const uint32_t count = warp_knn(pm.volume, collision, pm.gather_size_volume, sm);
+        if (lane == 0) ctr.knn++;
+        const double max_d2 = count ? fmax(0.0, sm.d2[count - 1]) : 0.0;
+        d3 part = mk3(0, 0, 0);
+        for (uint32_t j = lane; j < count; j += 32) {
+            const size_t i = sm.idx[j];
+            const d3 ppow = mk3(pm.volume.power[3 * i], pm.volume.power[3 * i + 1], pm.volume.power[3 * i + 2]);
+            part = part + cmul(ppow, mc) * md.phase;
+        }
+        __syncwarp();
+        d3 color = warp_sum(part);
+        color = color / ((4.0 / 3.0) * kPi * pow(max_d2, 1.5));
+        color = color / extinction;
+        color = color * transmittance(md, d);
+        color = color / d_pdf;
+        return color;
+    }
+    return warp_surface_estimate(sc, pm, ray, wo, h.t, n, mat, sm, ctr) * transmittance(md, h.t) / (1.0 - d_cdf);
+}
+
 struct GatherArgs {
     Camera cam;
     BatchParams bp;
@@ -573,6 +771,42 @@ __global__ void __launch_bounds__(128) k_photon_gather(const __grid_constant__ S
         if (b) atomicAdd(&stats[5], b);
         if (c) atomicAdd(&stats[6], c);
         if (d) atomicAdd(&stats[7], d);
+    }
+}
+
+// Camera pass for the point-point map: one warp per (pixel, lane) slot walks that slot's samples.
+__global__ void __launch_bounds__(128) k_photon_gather_warp(const __grid_constant__ SceneDev sc, const MediumDev md,
+                                                            const __grid_constant__ PhotonMapDev pm, const __grid_constant__ GatherArgs ga,
+                                                            unsigned long long* __restrict__ stats) {
+    __shared__ WarpKnnSmem smem[4];
+    WarpKnnSmem& sm = smem[threadIdx.x >> 5];
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t slot = blockIdx.x * 4 + (threadIdx.x >> 5);
+    GatherCounters ctr = {0, 0, 0};
+    unsigned long long my_samples = 0;
+    if (slot < ga.n_pixels * ga.n_lanes) {
+        const uint32_t pixel = slot % ga.n_pixels, slane = slot / ga.n_pixels;
+        const uint32_t x = pixel % ga.bp.width, y = pixel / ga.bp.width;
+        d3 sum = mk3(0, 0, 0);
+        for (uint32_t j = slane; j < ga.bp.n_local; j += ga.n_lanes) {
+            const uint64_t s = ga.bp.batch_base + ga.bp.shard_index + (uint64_t)j * ga.bp.shard_count;
+            Rng rng = Rng::make(ga.bp.seed, kDomainGather, pixel, s);
+            RayD ray;
+            primary_ray(ga.cam, ga.bp.width, ga.bp.height, x, y, rng, &ray.o, &ray.d);
+            sum = sum + warp_estimate_point_point(sc, md, pm, ray, rng, sm, ctr);
+            if (lane == 0) my_samples++;
+            __syncwarp();
+        }
+        if (lane == 0) { ga.ax[slot] = sum.x; ga.ay[slot] = sum.y; ga.az[slot] = sum.z; }
+    }
+    __syncwarp();
+    const unsigned long long a = __reduce_add_sync(0xffffffffu, (unsigned)my_samples);
+    const unsigned long long b = __reduce_add_sync(0xffffffffu, (unsigned)ctr.knn);
+    const unsigned long long c = __reduce_add_sync(0xffffffffu, (unsigned)ctr.visibility);
+    if (lane == 0) {
+        if (a) { atomicAdd(&stats[0], a); atomicAdd(&stats[1], a); }
+        if (b) atomicAdd(&stats[5], b);
+        if (c) atomicAdd(&stats[6], c);
     }
 }
 

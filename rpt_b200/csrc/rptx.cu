@@ -647,9 +647,12 @@ static int choose_path_mode(const rptx_scene* s, const rptx_params* p) {
     const char* env = std::getenv("RPTX_PATH_MODE");
     if (env && std::strcmp(env, "wavefront") == 0) return kFilmWavefront;
     if (env && std::strcmp(env, "fused") == 0 && fits) return kFilmFused;
+    // measured (profiles/r1_v2_summary.md): the fused kernel wins only for one-vertex paths on small
+    // scenes (teapot, max_bounces 0: +33 %); with bounces the wavefront's compaction wins 3-7x
     size_t tris = 0;
     for (const auto& m : s->meshes) tris += m.tris.size();
-    return (fits && tris <= 4096 && s->n_bounded + s->n_unbounded <= 64) ? kFilmFused : kFilmWavefront;
+    const bool one_vertex = s->medium_kind == RPTX_MEDIUM_NONE && p->max_bounces == 0;
+    return (one_vertex && tris <= 4096 && s->n_bounded + s->n_unbounded <= 64) ? kFilmFused : kFilmWavefront;
 }
 
 static int film_begin(rptx_ctx* ctx, rptx_scene* scene, const rptx_camera* camera, const rptx_params* params, bool gather_only,

@@ -76,3 +76,49 @@ def device_f64_view(ptr, n, device):
         __cuda_array_interface__ = dict(shape=(int(n),), typestr="<f8", data=(int(ptr), False), version=3)
 
     return torch.as_tensor(_V(), device=device)
+
+
+def merge_photons(local, empty, group=None):
+    """PhotonList::merge (src/photon.rs:153-160,675) across ranks: all-gather the ragged row lists
+    of `local` (protocol: device_tensor(which) -> [n,13] f64 tensor) into `empty`
+    (protocol: append_tensor(which, rows)).  World size 1 returns `local` itself."""
+    world, _ = world_rank(group)
+    if world == 1:
+        return local
+    for which in (0, 1):
+        rows, _ = all_gather_ragged(local.device_tensor(which), group)
+        empty.append_tensor(which, rows)
+    return empty
+
+
+def photon_render(renderer, photon_count, kind, group=None):
+    """photon_render (src/photon.rs:655-720) across ranks: emit this rank's photon range, merge
+    the lists, build the (identical) map everywhere, gather this rank's sample shard, all-reduce
+    the batch sums, commit.  Returns (film, map, timings_ms); `renderer` must already carry
+    .shard(world, rank)."""
+    import time
+
+    from .renderer import PhotonList
+
+    world, rank = world_rank(group)
+    lo, hi = photon_range(photon_count, world, rank)
+    t0 = time.perf_counter()
+    local = renderer.emit_photons(photon_count, kind, first=lo, count=hi - lo)
+    t1 = time.perf_counter()
+    full = merge_photons(local, PhotonList.empty(renderer.device_scene().ctx) if world > 1 else None, group)
+    t2 = time.perf_counter()
+    pmap = renderer.build_photon_map(full, kind)
+    t3 = time.perf_counter()
+    film = renderer.begin_gather()
+    n = renderer._p["num_samples"]
+    film.gather(pmap, n)
+    all_reduce_sum_(film.batch_sum_tensor(), group)
+    if film.batch_sum_tensor().is_cuda:
+        torch.cuda.current_stream().synchronize()
+    film.sample_commit(n)
+    t4 = time.perf_counter()
+    counts = full.counts()
+    if full is not local:
+        local.close()
+    full.close()
+    return film, pmap, dict(emit=1e3 * (t1 - t0), merge=1e3 * (t2 - t1), build=1e3 * (t3 - t2), gather=1e3 * (t4 - t3), surface=counts[0], volume=counts[1])

@@ -189,6 +189,17 @@ class PhotonList:
     def append_device(self, which, ptr, n):
         self.ctx.check(self.lib.rptx_photons_append_device(self.h, which, C.c_void_p(int(ptr)), int(n)), "rptx_photons_append_device")
 
+    def append_tensor(self, which, rows):
+        """Append a [n,13] f64 torch tensor (device rows stay on the device)."""
+        rows = rows.contiguous()
+        if rows.is_cuda:
+            import torch
+
+            torch.cuda.current_stream(rows.device).synchronize()
+            self.append_device(which, rows.data_ptr(), rows.shape[0])
+        else:
+            self.append_host(which, rows.numpy())
+
     def device_tensor(self, which):
         """torch view [n,13] f64 of one list's rows (for the NCCL all-gather)."""
         from .dist import device_f64_view

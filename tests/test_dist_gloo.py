@@ -46,6 +46,50 @@ class OracleShardFilm:
         self.base += iterations
 
 
+class OraclePhotonList:
+    """Test double with the PhotonList protocol used by rd.merge_photons."""
+
+    def __init__(self, rows_s=None, rows_v=None):
+        self.rows = [np.zeros((0, 13)) if rows_s is None else rows_s, np.zeros((0, 13)) if rows_v is None else rows_v]
+
+    def device_tensor(self, which):
+        return torch.from_numpy(np.ascontiguousarray(self.rows[which]))
+
+    def append_tensor(self, which, rows):
+        self.rows[which] = np.concatenate([self.rows[which], rows.numpy()])
+
+
+def _photon_worker(rank, world, port, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        scene, cam, d = scenes.lampshade("photonphoton")
+        r = scenes.make_renderer(scene, cam, d, width=8, height=8, num_samples=2, seed=4)
+        osc = orc.OracleScene(scene)
+        lo, hi = rd.photon_range(3001, world, rank)
+        s, v = osc.emit_photons(cam, r.params(), 3001, 0, first=lo, count=hi - lo, threads=1)
+        full = rd.merge_photons(OraclePhotonList(s, v), OraclePhotonList())
+        out[rank] = (full.rows[0], full.rows[1])
+    finally:
+        dist.destroy_process_group()
+
+
+def test_photon_lists_merge_to_the_unsharded_emission():
+    """Rank r shoots photon_range(N, 2, r); the all-gathered lists are the single-rank emission."""
+    world = 2
+    mgr = mp.Manager()
+    out = mgr.dict()
+    mp.spawn(_photon_worker, args=(world, _free_port(), out), nprocs=world, join=True)
+    scene, cam, d = scenes.lampshade("photonphoton")
+    r = scenes.make_renderer(scene, cam, d, width=8, height=8, num_samples=2, seed=4)
+    ws, wv = orc.OracleScene(scene).emit_photons(cam, r.params(), 3001, 0, threads=1)
+    for rank in range(world):
+        s, v = out[rank]
+        assert np.array_equal(orc.sort_rows(s).view(np.uint64), ws.view(np.uint64))
+        assert np.array_equal(orc.sort_rows(v).view(np.uint64), wv.view(np.uint64))
+    assert np.array_equal(out[0][0], out[1][0])  # same order on every rank (rank-major)
+
+
 def _free_port():
     with socket.socket() as s:
         s.bind(("127.0.0.1", 0))

@@ -153,6 +153,23 @@ def test_gather_same_map_same_seed(variant):
     assert st["path_samples"] == 32 * 32 * 3
 
 
+def test_gather_warp_and_per_thread_kernels_agree(monkeypatch):
+    """The point-point camera pass has a warp-cooperative kernel (default, k <= 128) and the
+    per-thread one (larger k, and the beam kinds): same kNN sets, different summation order."""
+    scene, cam, r, osc = _setup("photonphoton", w=24, h=24, spp=3)
+    ph = r.emit_photons(30000, 0)
+    gm = r.build_photon_map(ph, 0)
+    means = []
+    for per_thread in (False, True):
+        if per_thread:
+            monkeypatch.setenv("RPTX_GATHER_PER_THREAD", "1")
+        f = r.begin_gather()
+        f.gather(gm, 3); f.sample_commit(3)
+        means.append(f.mean())
+        assert f.stats()["gather_queries"] == 24 * 24 * 3
+    assert np.allclose(means[0], means[1], rtol=1e-11, atol=1e-300)
+
+
 def test_gather_shards_sum_to_whole():
     import torch
 
