@@ -7,7 +7,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "librptx.so")
+# RPTX_LIBRARY: developer knob for A/B builds of the same ABI (tools/); the product is librptx.so next to this file
+LIB_PATH = os.environ.get("RPTX_LIBRARY") or os.path.join(_HERE, "librptx.so")
 
 SHAPE_SPHERE, SHAPE_PLANE, SHAPE_CUBE, SHAPE_MESH, SHAPE_GROUP = range(5)
 MAT_LAMBERTIAN, MAT_PHONG, MAT_MIRROR, MAT_TRANSMISSIVE = range(4)

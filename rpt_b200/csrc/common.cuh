@@ -31,7 +31,36 @@ RPTX_HD d3 operator-(d3 a, d3 b) { return mk3(a.x - b.x, a.y - b.y, a.z - b.z); 
 RPTX_HD d3 operator-(d3 a) { return mk3(-a.x, -a.y, -a.z); }
 RPTX_HD d3 operator*(d3 a, double s) { return mk3(a.x * s, a.y * s, a.z * s); }
 RPTX_HD d3 operator*(double s, d3 a) { return mk3(s * a.x, s * a.y, s * a.z); }
-RPTX_HD d3 operator/(d3 a, double s) { return mk3(a.x / s, a.y / s, a.z / s); }
+// a / s, componentwise, IEEE results.  On the device a ZERO numerator is kept away from the divider: nvcc's
+// inlined f64 division sends every quotient of zero magnitude to its ~90-instruction slow path, and
+// axis-aligned normals (two zero components) made that 23 % of k_shade's instructions on the Cornell box.
+// 0 / s for finite non-zero s is a zero whose sign is sign(a) ^ sign(s), i.e. a * s.
+RPTX_HD double div_component(double a, double s, bool s_regular) {
+    const bool z = s_regular && a == 0.0;
+    double num = z ? 1.0 : a;
+#ifdef __CUDA_ARCH__
+    asm("" : "+d"(num));  // opaque: otherwise nvcc divides a / s anyway (slow path included) and selects afterwards
+#endif
+    const double q = num / s;
+    return z ? a * s : q;
+}
+// scalar form, for quotients whose numerator is often exactly zero (a ray leaving a wall at coordinate 0
+// has dot(pn, v1 - o) == 0 against that wall's own triangles)
+RPTX_HD double fdiv(double a, double b) {
+#ifdef __CUDA_ARCH__
+    return div_component(a, b, fabs(b) > 0.0 && fabs(b) < CUDART_INF);
+#else
+    return a / b;
+#endif
+}
+RPTX_HD d3 operator/(d3 a, double s) {
+#ifdef __CUDA_ARCH__
+    const bool reg = fabs(s) > 0.0 && fabs(s) < CUDART_INF;
+    return mk3(div_component(a.x, s, reg), div_component(a.y, s, reg), div_component(a.z, s, reg));
+#else
+    return mk3(a.x / s, a.y / s, a.z / s);
+#endif
+}
 RPTX_HD double dot(d3 a, d3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
 RPTX_HD d3 cross(d3 a, d3 b) { return mk3(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x); }
 RPTX_HD d3 cmul(d3 a, d3 b) { return mk3(a.x * b.x, a.y * b.y, a.z * b.z); }
@@ -141,6 +170,8 @@ struct Camera {
     double inv_tan_half_fov;  // 1 / tan(fov / 2) (src/camera.rs:66), evaluated once on the host
 };
 
+constexpr uint32_t kSmallSceneMax = 16;
+
 struct SceneDev {
     const BvhNode* nodes;       // node pool: TLAS first, then BLASes
     const Instance* instances;  // sorted in TLAS leaf order, then unbounded ones
@@ -155,6 +186,11 @@ struct SceneDev {
     uint32_t n_cube_instances;
     int tlas_root_ref;
     uint32_t n_bounded, n_unbounded, n_lights, n_shadow_lights;
+    int small_scene;             // <= kSmallSceneMax instances, <= 64 triangles, every mesh a single leaf: closest_hit_small applies
+    const uint8_t* small_slots;  // [<= 64] triangle slot -> instance << 3 | triangle within its mesh leaf
+    const float4* small_boxes;   // [n_bounded][2] padded f32 box of each bounded instance
+    uint32_t small_kind_mask[3]; // instances of kSphere / kPlane / kCube, bit = instance index
+    uint32_t small_unbounded_mask;
     uint32_t shadow_probe_mask;  // bit k: k-th shadow-casting light is probed at its sample first (trace.cuh nee_visible)
     double wmin[3], wmax[3];    // padded world bounds of the bounded instances
     int medium_kind;

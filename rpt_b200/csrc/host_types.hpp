@@ -59,6 +59,11 @@ struct rptx_scene {
     const double* d_env = nullptr;
     const uint32_t* d_cube_idx = nullptr;
     uint32_t n_cubes = 0;
+    int small_scene = 0;
+    uint8_t* d_small_slots = nullptr;
+    float4* d_small_boxes = nullptr;
+    uint32_t small_kind_mask[3] = {0, 0, 0};
+    uint32_t small_unbounded_mask = 0;
     int tlas_root_ref = 0;
     uint32_t n_bounded = 0, n_unbounded = 0, n_shadow_lights = 0, shadow_probe_mask = 0;
     double wmin[3] = {0, 0, 0}, wmax[3] = {0, 0, 0};

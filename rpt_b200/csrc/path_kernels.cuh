@@ -10,6 +10,17 @@
 #include "shading.cuh"
 #include "trace.cuh"
 
+// resident blocks per SM asked of ptxas for the three heavy wavefront kernels (register cap = 65536 / (128 * n))
+#ifndef RPTX_OCC_EXTEND
+#define RPTX_OCC_EXTEND 4
+#endif
+#ifndef RPTX_OCC_SHADE
+#define RPTX_OCC_SHADE 1
+#endif
+#ifndef RPTX_OCC_SHADOW
+#define RPTX_OCC_SHADOW 4
+#endif
+
 namespace rptx {
 
 constexpr int kBlock = 128;
@@ -75,7 +86,8 @@ __global__ void __launch_bounds__(kBlock) k_generate(PathPool p, Queues q, Batch
 }
 
 // extend: persistent warps pull 32 rays at a time from the queue
-__global__ void __launch_bounds__(kBlock) k_extend(const __grid_constant__ SceneDev sc, PathPool p, Queues q) {
+template <bool SMALL>
+__global__ void __launch_bounds__(kBlock, RPTX_OCC_EXTEND) k_extend(const __grid_constant__ SceneDev sc, PathPool p, Queues q) {
     const uint32_t count = q.counters[0];
     for (;;) {
         uint32_t base = 0;
@@ -90,7 +102,7 @@ __global__ void __launch_bounds__(kBlock) k_extend(const __grid_constant__ Scene
             ray.d = mk3(p.dx[slot], p.dy[slot], p.dz[slot]);
             Hit h;
             h.t = CUDART_INF;
-            closest_hit<kClosest>(sc, ray, kEpsilon, 0.0, h);
+            closest_hit_sel<kClosest, SMALL>(sc, ray, kEpsilon, 0.0, h);
             if (h.inst != kNoHit) {
                 uint32_t prim, inst;
                 const d3 n = hit_normal(sc, ray, h, &prim, &inst);
@@ -149,7 +161,7 @@ RPTX_D void sample_lights_dev(const SceneDev& sc, const PathPool& p, uint32_t sl
 }
 
 template <bool MEDIUM>
-__global__ void __launch_bounds__(kBlock) k_shade(const __grid_constant__ SceneDev sc, PathPool p, Queues q, BatchParams bp,
+__global__ void __launch_bounds__(kBlock, RPTX_OCC_SHADE) k_shade(const __grid_constant__ SceneDev sc, PathPool p, Queues q, BatchParams bp,
                                                    MediumDev md) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= q.counters[0]) return;
@@ -237,8 +249,8 @@ __global__ void __launch_bounds__(kBlock) k_shade(const __grid_constant__ SceneD
 // contribution is exactly zero (light sample facing away, bsdf 0) is not traced: adding it
 // cannot change the sum.
 // PROBE: the scene has point lights (probed at their sample first); all lights take that path then.
-template <bool PROBE>
-__global__ void __launch_bounds__(kBlock) k_shadow(const __grid_constant__ SceneDev sc, PathPool p, Queues q) {
+template <bool PROBE, bool SMALL>
+__global__ void __launch_bounds__(kBlock, RPTX_OCC_SHADOW) k_shadow(const __grid_constant__ SceneDev sc, PathPool p, Queues q) {
     const uint32_t count = q.counters[0];
     unsigned long long my_queries = 0, my_traced = 0, my_occl = 0;
     for (;;) {
@@ -263,7 +275,7 @@ __global__ void __launch_bounds__(kBlock) k_shadow(const __grid_constant__ Scene
             ray.d = mk3(0, 0, 1);
             if (job) { ray.d = mk3(p.sdx[off], p.sdy[off], p.sdz[off]); dist = p.sdist[off]; my_traced++; }
             __syncwarp();
-            if (job && nee_visible<PROBE>(sc, ray, dist, &my_occl)) {
+            if (job && nee_visible<PROBE, SMALL>(sc, ray, dist, &my_occl)) {
                 // direct += contribution, in light order like the reference's loop
                 if (!any) { add = mk3(p.dirx[slot], p.diry[slot], p.dirz[slot]); any = true; }
                 add = add + c;

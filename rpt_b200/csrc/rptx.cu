@@ -152,6 +152,7 @@ void free_scene_device(rptx_scene* s) {
     cudaFree((void*)s->d_nodes); cudaFree((void*)s->d_instances); cudaFree((void*)s->d_tris);
     cudaFree((void*)s->d_tri_normals); cudaFree((void*)s->d_trif); s->d_trif = nullptr; cudaFree((void*)s->d_tri_orig); cudaFree((void*)s->d_materials);
     cudaFree((void*)s->d_lights); cudaFree((void*)s->d_raw); cudaFree((void*)s->d_env); cudaFree((void*)s->d_cube_idx); s->d_cube_idx = nullptr;
+    cudaFree(s->d_small_slots); s->d_small_slots = nullptr; cudaFree(s->d_small_boxes); s->d_small_boxes = nullptr;
     s->d_nodes = nullptr; s->d_instances = nullptr; s->d_tris = nullptr; s->d_tri_normals = nullptr;
     s->d_tri_orig = nullptr; s->d_materials = nullptr; s->d_lights = nullptr; s->d_raw = nullptr; s->d_env = nullptr;
     s->committed = false;
@@ -303,6 +304,10 @@ SceneDev scene_dev(const rptx_scene* s) {
     sc.n_bounded = s->n_bounded; sc.n_unbounded = s->n_unbounded;
     sc.n_lights = (uint32_t)s->lights.size(); sc.n_shadow_lights = s->n_shadow_lights;
     sc.shadow_probe_mask = s->shadow_probe_mask;
+    sc.small_scene = s->small_scene;
+    sc.small_slots = s->d_small_slots; sc.small_boxes = s->d_small_boxes;
+    for (int k = 0; k < 3; k++) sc.small_kind_mask[k] = s->small_kind_mask[k];
+    sc.small_unbounded_mask = s->small_unbounded_mask;
     for (int k = 0; k < 3; k++) { sc.wmin[k] = s->wmin[k]; sc.wmax[k] = s->wmax[k]; sc.env_color[k] = s->env_color[k]; }
     sc.medium_kind = s->medium_kind; sc.sigma_a = s->sigma_a; sc.sigma_s = s->sigma_s;
     sc.env_is_hdri = s->env_is_hdri ? 1 : 0; sc.env_w = s->env_w; sc.env_h = s->env_h; sc.env_pixels = s->d_env;
@@ -537,11 +542,14 @@ int rptx_scene_commit(rptx_scene* s) {
     s->n_bounded = (uint32_t)bounded.size();
     s->n_unbounded = (uint32_t)unbounded.size();
     std::vector<Instance> ordered;
+    float wpad_used = 0.0f;
+    std::vector<std::array<double, 6>> wboxes_ordered;  // world bounds of the bounded instances, TLAS order
     s->tlas_root_ref = 0;
     if (!bounded.empty()) {
         double e_abs = 0.0;
         for (int k = 0; k < 3; k++) e_abs = std::fmax(e_abs, std::fmax(std::fabs(wmn[k]), std::fabs(wmx[k])));
         const float wpad = f32_upf(std::fmax(e_abs, 1e-30) * (1.0 / 2097152.0));
+        wpad_used = wpad;
         for (const auto& b : wboxes) {
             PrimBox pb;
             for (int k = 0; k < 3; k++) { pb.mn[k] = f32_down(b[k]); pb.mx[k] = f32_upf(b[3 + k]); }
@@ -555,7 +563,7 @@ int rptx_scene_commit(rptx_scene* s) {
         std::vector<uint32_t> perm(boxes.size());
         CK(cudaMemcpy(perm.data(), d_perm, sizeof(uint32_t) * perm.size(), cudaMemcpyDeviceToHost));
         cudaFree(d_boxes); cudaFree(d_perm);
-        for (uint32_t k : perm) ordered.push_back(bounded[k]);
+        for (uint32_t k : perm) { ordered.push_back(bounded[k]); wboxes_ordered.push_back(wboxes[k]); }
         for (int k = 0; k < 3; k++) { s->wmin[k] = wmn[k] - 2.0 * (double)wpad; s->wmax[k] = wmx[k] + 2.0 * (double)wpad; }
     }
     ordered.insert(ordered.end(), unbounded.begin(), unbounded.end());
@@ -565,6 +573,38 @@ int rptx_scene_commit(rptx_scene* s) {
     std::vector<uint32_t> cubes;
     for (uint32_t i = 0; i < s->n_bounded; i++)
         if (ordered[i].kind == kCube) cubes.push_back(i);
+    // small scenes: candidate tables of closest_hit_small (trace.cuh)
+    {
+        s->small_scene = ordered.size() <= kSmallSceneMax;
+        std::vector<uint8_t> slots;
+        std::vector<float4> sboxes;
+        for (int k = 0; k < 3; k++) s->small_kind_mask[k] = 0;
+        s->small_unbounded_mask = 0;
+        const float spad = wpad_used;
+        for (uint32_t i = 0; i < ordered.size() && s->small_scene; i++) {
+            const Instance& in = ordered[i];
+            if (in.kind == kMesh) {
+                if (in.root_ref >= 0) { s->small_scene = 0; break; }
+                const uint32_t count = ((uint32_t)(~in.root_ref) & 7u) + 1u;
+                for (uint32_t j = 0; j < count; j++) slots.push_back((uint8_t)(i << 3 | j));
+            } else {
+                s->small_kind_mask[in.kind] |= 1u << i;
+                if (i >= s->n_bounded) s->small_unbounded_mask |= 1u << i;
+            }
+            if (i < s->n_bounded) {
+                const auto& wb = wboxes_ordered[i];
+                sboxes.push_back(make_float4(f32_down(wb[0]) - spad, f32_down(wb[1]) - spad, f32_down(wb[2]) - spad, 0.0f));
+                sboxes.push_back(make_float4(f32_upf(wb[3]) + spad, f32_upf(wb[4]) + spad, f32_upf(wb[5]) + spad, 0.0f));
+            }
+        }
+        if (slots.size() > 64) s->small_scene = 0;
+        if (s->small_scene) {
+            uint8_t* d_slots = nullptr; float4* d_sboxes = nullptr;
+            CK(upload(&d_slots, slots, st));
+            CK(upload(&d_sboxes, sboxes, st));
+            s->d_small_slots = d_slots; s->d_small_boxes = d_sboxes;
+        }
+    }
     uint32_t* d_cubes = nullptr;
     CK(upload(&d_cubes, cubes, st));
     s->d_cube_idx = d_cubes;
@@ -727,18 +767,25 @@ static int run_waves(rptx_film* f, const BatchParams& bp) {
     k_generate<MEDIUM><<<grid_for(p.n_slots, kBlock), kBlock, 0, st>>>(p, q, bp, f->cam);
     ctx->launches++;
     const int persistent_blocks = ctx->sm_count * 8;
+    const bool small = sc.small_scene != 0 && !getenv("RPTX_NO_SMALL_SCENE");
     uint32_t* h_count = (uint32_t*)ctx->h_pinned;
     uint32_t active = std::min<uint64_t>(p.n_slots, (uint64_t)p.n_pixels * std::min(p.n_lanes, bp.n_local));
     while (active > 0) {
         const int blocks = (int)std::min<uint64_t>(persistent_blocks, grid_for(active, kBlock));
         cudaEventRecord(f->evw[0], st);
-        k_extend<<<blocks, kBlock, 0, st>>>(sc, p, q);
+        if (small) k_extend<true><<<blocks, kBlock, 0, st>>>(sc, p, q);
+        else k_extend<false><<<blocks, kBlock, 0, st>>>(sc, p, q);
         cudaEventRecord(f->evw[1], st);
         k_shade<MEDIUM><<<grid_for(active, kBlock), kBlock, 0, st>>>(sc, p, q, bp, md);
         cudaEventRecord(f->evw[2], st);
         if (p.n_shadow) {
-            if (sc.shadow_probe_mask) k_shadow<true><<<blocks, kBlock, 0, st>>>(sc, p, q);
-            else k_shadow<false><<<blocks, kBlock, 0, st>>>(sc, p, q);
+            if (small) {
+                if (sc.shadow_probe_mask) k_shadow<true, true><<<blocks, kBlock, 0, st>>>(sc, p, q);
+                else k_shadow<false, true><<<blocks, kBlock, 0, st>>>(sc, p, q);
+            } else {
+                if (sc.shadow_probe_mask) k_shadow<true, false><<<blocks, kBlock, 0, st>>>(sc, p, q);
+                else k_shadow<false, false><<<blocks, kBlock, 0, st>>>(sc, p, q);
+            }
         }
         cudaEventRecord(f->evw[3], st);
         k_connect<MEDIUM><<<grid_for(active, kBlock), kBlock, 0, st>>>(p, q, bp, f->cam);

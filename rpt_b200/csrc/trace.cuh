@@ -71,7 +71,7 @@ RPTX_D bool tri_test(const TriRec& tr, d3 o, d3 d, double t_min, double t_max, b
     const double cosine = dot(pn, d);
     if (fabs(cosine) < 1e-8) return false;
     const d3 v1 = mk3(tr.v1[0], tr.v1[1], tr.v1[2]);
-    const double time = dot(pn, v1 - o) / cosine;
+    const double time = fdiv(dot(pn, v1 - o), cosine);
     if (time < t_min || !(time < t_max || (allow_eq && time == t_max))) return false;
     const d3 d0 = mk3(tr.d0[0], tr.d0[1], tr.d0[2]), d1 = mk3(tr.d1[0], tr.d1[1], tr.d1[2]);
     const d3 d2 = (o + time * d) - v1;
@@ -116,8 +116,8 @@ RPTX_D bool cube_test(d3 o, d3 d, double t_min, double* t, uint32_t* code) {
 #pragma unroll
     for (int dim = 0; dim < 3; dim++) {
         const double oo = comp(o, dim), dd = comp(d, dim);
-        double x1 = (-0.5 - oo) / dd;
-        double x2 = (0.5 - oo) / dd;
+        double x1 = fdiv(-0.5 - oo, dd);
+        double x2 = fdiv(0.5 - oo, dd);
         uint32_t c1 = dim * 2, c2 = dim * 2 + 1;
         if (x1 > x2) { const double s = x1; x1 = x2; x2 = s; const uint32_t cs = c1; c1 = c2; c2 = cs; }
         lo[dim] = x1; hi[dim] = x2; lc[dim] = c1; hc[dim] = c2;
@@ -384,6 +384,106 @@ RPTX_D void closest_hit(const SceneDev& sc, const RayD& ray, double t_min, doubl
     }
 }
 
+// Scenes of a few analytic shapes and polygons (Cornell box, lampshade; SceneDev::small_scene):
+// no hierarchy.  Two phases keep the warp together where the hierarchy cannot:
+//   1. every lane walks the instance list in the same order and only runs the f32 pre-tests
+//      (conservative triangle test, padded instance box), collecting its candidates in bit masks;
+//   2. each lane pops ITS candidates and runs the exact f64 test, so in one pass of the loop the
+//      lanes work on different primitives of the same kind.  With the hierarchy (or a plain list
+//      walk) an exact triangle test ran with 3-5 live lanes: a warp's rays end on different walls.
+// Same result as closest_hit: the pre-tests are the ones the hierarchy uses (a culled primitive
+// is provably missed), accept() does not depend on the visiting order, and triangles of one mesh
+// are still taken in ascending order.
+template <int MODE>
+RPTX_D void closest_hit_small(const SceneDev& sc, const RayD& ray, double t_min, double t_stop, Hit& hit) {
+    constexpr bool SHADOW = MODE == kAnyBelow;
+    constexpr bool WINDOW = MODE == kWindow;
+    hit.inst = kNoHit; hit.obj = kNoHit; hit.prim = 0; hit.v = 0; hit.w = 0;
+    // ---- phase 1: candidates ----
+    unsigned long long tri_cand = 0;
+    uint32_t box_cand = sc.small_unbounded_mask;
+    {
+        // f32 ray from the world-box entry, as in closest_hit; a ray with a zero direction component takes
+        // every analytic instance (Cube::intersect's 0/0 quirk reports hits outside the box)
+        double t0, t1;
+        clip_f64(sc.wmin, sc.wmax, ray.o, ray.d, &t0, &t1);
+        const bool world = sc.n_bounded != 0 && (t0 <= t1) && !(t1 < 0.0) && !(WINDOW && t1 < t_stop);
+        const bool axis = ray.d.x == 0.0 || ray.d.y == 0.0 || ray.d.z == 0.0;
+        const double wshift = WINDOW ? fmax(fmax(t0, t_stop), 0.0) : (t0 > 0.0 ? t0 : 0.0);
+        const float tlow = WINDOW ? -1e-30f : 0.0f;
+        const RayF rf = make_rayf(ray.o + wshift * ray.d, ray.d);
+        float tbest = f32_up(hit.t - wshift);
+        tbest = tbest + fabsf(tbest) * kSlabSlack;
+        uint32_t slot = 0;
+        for (uint32_t idx = 0; idx < sc.n_bounded; idx++) {
+            const Instance* __restrict__ in = sc.instances + idx;
+            if (in->kind != kMesh) {  // warp-uniform
+                const float4 a = __ldg(sc.small_boxes + 2 * idx), b = __ldg(sc.small_boxes + 2 * idx + 1);
+                float tn;
+                if (axis || (world && slab_f32(a.x, a.y, a.z, b.x, b.y, b.z, rf, tbest, &tn, tlow))) box_cand |= 1u << idx;
+                continue;
+            }
+            const uint32_t code = (uint32_t)(~in->root_ref);
+            const uint32_t first = code >> 3, count = (code & 7u) + 1u;
+            d3 lo = ray.o, ld = ray.d;
+            if (in->has_transform) { lo = xform_point(in->inv, ray.o); ld = xform_dir(in->inv, ray.d); }
+            const bool rejected = (ld.x == 0.0 || ld.y == 0.0 || ld.z == 0.0) && mesh_bounds_nan_reject(in, lo, ld);
+            const float fox = (float)lo.x, foy = (float)lo.y, foz = (float)lo.z;
+            const float fdx = (float)ld.x, fdy = (float)ld.y, fdz = (float)ld.z;
+            const TriF* __restrict__ trif = sc.trif + in->tri_base + first;
+            for (uint32_t i = 0; i < count; i++, slot++)
+                if (!rejected && tri_maybe_hit(trif + i, fox, foy, foz, fdx, fdy, fdz)) tri_cand |= 1ull << slot;
+        }
+    }
+    // ---- phase 2: exact tests, each lane on its own candidates ----
+    while (tri_cand) {
+        const int k = __ffsll((long long)tri_cand) - 1;
+        tri_cand &= tri_cand - 1;
+        const uint32_t e = sc.small_slots[k];
+        const uint32_t idx = e >> 3;
+        const Instance* __restrict__ in = sc.instances + idx;
+        const uint32_t obj = in->object_id;
+        d3 lo = ray.o, ld = ray.d;
+        if (in->has_transform) { lo = xform_point(in->inv, ray.o); ld = xform_dir(in->inv, ray.d); }
+        const uint32_t i = ((uint32_t)(~in->root_ref) >> 3) + (e & 7u);
+        TriRec tr;
+        load_tri(sc.tris + in->tri_base + i, &tr);
+        double t, v, w;
+        if (tri_test(tr, lo, ld, t_min, hit.t, obj < hit.obj, &t, &v, &w) && (!WINDOW || t >= t_stop)) {
+            hit.t = t; hit.inst = idx; hit.obj = obj; hit.prim = i; hit.v = v; hit.w = w;
+            if (SHADOW && t < t_stop) return;
+        }
+    }
+#pragma unroll
+    for (int kind = 0; kind < 3; kind++) {  // kSphere, kPlane, kCube
+        uint32_t m = box_cand & sc.small_kind_mask[kind];
+        while (m) {
+            const uint32_t idx = (uint32_t)__ffs((int)m) - 1u;
+            m &= m - 1u;
+            const Instance* __restrict__ in = sc.instances + idx;
+            const uint32_t obj = in->object_id;
+            d3 lo = ray.o, ld = ray.d;
+            if (in->has_transform) { lo = xform_point(in->inv, ray.o); ld = xform_dir(in->inv, ray.d); }
+            double t;
+            uint32_t ccode = 0;
+            bool ok;
+            if (kind == kSphere) ok = sphere_test(lo, ld, t_min, &t);
+            else if (kind == kCube) ok = cube_test(lo, ld, t_min, &t, &ccode);
+            else ok = plane_test(*in, lo, ld, t_min, &t);
+            if (ok && (!WINDOW || t >= t_stop) && accept(hit, t, obj)) {
+                hit.t = t; hit.inst = idx; hit.obj = obj; hit.prim = ccode;
+                if (SHADOW && t < t_stop) return;
+            }
+        }
+    }
+}
+
+template <int MODE, bool SMALL>
+RPTX_D void closest_hit_sel(const SceneDev& sc, const RayD& ray, double t_min, double t_stop, Hit& hit) {
+    if (SMALL) closest_hit_small<MODE>(sc, ray, t_min, t_stop, hit);
+    else closest_hit<MODE>(sc, ray, t_min, t_stop, hit);
+}
+
 // NEE visibility as the reference defines it (src/renderer.rs:347-348, :395-396): the CLOSEST
 // hit of the shadow ray must lie within 1e-12 of the light sample.  Evaluated as (1) a probe of
 // the window [dist - 2e-12, dist + 2e-12]: the closest hit REPORTED there must pass the test —
@@ -392,18 +492,18 @@ RPTX_D void closest_hit(const SceneDev& sc, const RayD& ray, double t_min, doubl
 // probe_first is chosen per light at commit time (point lights: yes; emissive objects: no).
 // PROBE = false: lights that are scene objects; the probe would nearly always succeed, so the
 // segment is searched once up to the window's far end, stopping at the first report below it.
-template <bool PROBE>
+template <bool PROBE, bool SMALL = false>
 RPTX_D bool nee_visible(const SceneDev& sc, const RayD& ray, double dist, unsigned long long* n_occlusion) {
     const double t_lo = dist - 2e-12;
     Hit h;
     h.t = dist + 2e-12;
     if (PROBE) {
-        closest_hit<kWindow>(sc, ray, kEpsilon, t_lo, h);
+        closest_hit_sel<kWindow, SMALL>(sc, ray, kEpsilon, t_lo, h);
         if (h.inst == kNoHit || !(fabs(h.t - dist) < kEpsilon)) return false;
         h.t = t_lo;
     }
     (*n_occlusion)++;
-    closest_hit<kAnyBelow>(sc, ray, kEpsilon, t_lo, h);
+    closest_hit_sel<kAnyBelow, SMALL>(sc, ray, kEpsilon, t_lo, h);
     if (PROBE) return h.inst == kNoHit;
     return h.inst != kNoHit && fabs(h.t - dist) < kEpsilon;
 }

@@ -160,3 +160,22 @@ def test_fused_equals_wavefront(monkeypatch):
             assert st["path_samples"] == 40 * 30 * 3
         assert modes == [0, 1]
         assert np.allclose(means[0], means[1], rtol=1e-12, atol=1e-300), name
+
+
+def test_list_walk_equals_hierarchy(monkeypatch):
+    """Small scenes skip the TLAS and walk the instance list (closest_hit_small); the hits, and so
+    the batch, are identical bit for bit to the hierarchy's."""
+    monkeypatch.setenv("RPTX_PATH_MODE", "wavefront")
+    for name in ("cornell", "lampshade"):
+        scene, cam, d = scenes.cornell() if name == "cornell" else scenes.lampshade("pathtrace")
+        means = []
+        for off in (False, True):
+            if off:
+                monkeypatch.setenv("RPTX_NO_SMALL_SCENE", "1")
+            else:
+                monkeypatch.delenv("RPTX_NO_SMALL_SCENE", raising=False)
+            f = scenes.make_renderer(scene, cam, d, width=64, height=48, num_samples=4, seed=11, max_bounces=4).begin()
+            f.sample(4)
+            means.append(f.mean())
+        monkeypatch.delenv("RPTX_NO_SMALL_SCENE", raising=False)
+        assert np.array_equal(means[0], means[1]), name
