@@ -16,6 +16,11 @@ struct rptx_ctx {
     void* h_pinned = nullptr;
     uint64_t launches = 0;
     std::string err;
+    // Path-state arena: one slab per film (tens of GB for a wavefront pool), handed back here when the film is
+    // destroyed and reused by the next film of this context, so a render loop maps its HBM once
+    // (cudaMalloc of 23 GB costs ~50 ms; iterative_render / repeated render() calls would pay it every time).
+    void* spare_arena = nullptr;
+    size_t spare_arena_bytes = 0;
 };
 
 struct HostMesh {
@@ -73,6 +78,8 @@ enum FilmMode : int { kFilmWavefront = 0, kFilmFused = 1, kFilmGather = 2 };
 
 struct rptx_film {
     rptx_ctx* ctx = nullptr;
+    void* arena = nullptr;
+    size_t arena_bytes = 0;
     int mode = kFilmWavefront;
     rptx_scene* scene = nullptr;
     rptx_params params;

@@ -340,11 +340,18 @@ int rptx_ctx_create(int device_id, rptx_ctx** out) {
     CK(cudaGetDeviceProperties(&prop, device_id));
     ctx->sm_count = prop.multiProcessorCount;
     CK(cudaMallocHost((void**)&ctx->h_pinned, 64));
+    {  // batch means come from the stream-ordered pool; keep what it has mapped across synchronisations
+        cudaMemPool_t pool;
+        CK(cudaDeviceGetDefaultMemPool(&pool, device_id));
+        uint64_t keep = 1ull << 30;
+        CK(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep));
+    }
     return 0;
 }
 
 void rptx_ctx_destroy(rptx_ctx* ctx) {
     if (!ctx) return;
+    if (ctx->spare_arena) cudaFree(ctx->spare_arena);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     if (ctx->h_pinned) cudaFreeHost(ctx->h_pinned);
     delete ctx;
@@ -644,33 +651,62 @@ int rptx_scene_commit(rptx_scene* s) {
 // ---------------------------------------------------------------- film / render loop
 
 // the film of a photon camera pass or of the fused path kernel needs the lane sums and the Buffer, not the path pool
-static int film_alloc(rptx_film* f) {
+// Per-slot path state is carved from one slab (ctx->spare_arena when a previous film left one that is large
+// enough).  256-byte alignment per array.
+extern "C++" {
+namespace {
+struct Carver {
+    char* base;
+    size_t off = 0;
+    template <class T>
+    void take(T** out, size_t n) {
+        off = (off + 255) & ~(size_t)255;
+        if (base) *out = reinterpret_cast<T*>(base + off);
+        off += n * sizeof(T);
+    }
+};
+}  // namespace
+}  // extern "C++"
+
+static void film_carve(rptx_film* f, Carver& c) {
     const bool gather_only = f->mode != kFilmWavefront;
-    rptx_ctx* ctx = f->ctx;
     PathPool& p = f->pool;
     const size_t ns = p.n_slots;
     std::vector<double**> dptrs = {&p.ox, &p.oy, &p.oz, &p.dx, &p.dy, &p.dz, &p.ht, &p.hnx, &p.hny, &p.hnz, &p.dirx, &p.diry, &p.dirz,
                                    &p.fx, &p.fy, &p.fz, &p.pdf, &p.abscos, &p.bx, &p.by, &p.bz, &p.lx, &p.ly, &p.lz, &p.ax, &p.ay, &p.az};
     if (gather_only) dptrs = {&p.ax, &p.ay, &p.az};
-    for (double** d : dptrs) { CK(cudaMalloc((void**)d, sizeof(double) * ns)); f->owned.push_back(*d); }
+    for (double** d : dptrs) c.take(d, ns);
     if (!gather_only) {
-    std::vector<double**> sptrs = {&p.sdx, &p.sdy, &p.sdz, &p.sdist, &p.scx, &p.scy, &p.scz};
-    for (double** d : sptrs) { CK(cudaMalloc((void**)d, sizeof(double) * ns * std::max<uint32_t>(p.n_shadow, 1))); f->owned.push_back(*d); }
-    CK(cudaMalloc((void**)&p.stack, sizeof(double) * ns * 8 * std::max<uint32_t>(p.stack_depth, 1))); f->owned.push_back(p.stack);
-    CK(cudaMalloc((void**)&p.hobj, sizeof(uint32_t) * ns)); f->owned.push_back(p.hobj);
-    CK(cudaMalloc((void**)&p.rng, sizeof(uint64_t) * ns)); f->owned.push_back(p.rng);
-    CK(cudaMalloc((void**)&p.sample_j, sizeof(uint32_t) * ns)); f->owned.push_back(p.sample_j);
-    CK(cudaMalloc((void**)&p.depth, sizeof(uint32_t) * ns)); f->owned.push_back(p.depth);
-    CK(cudaMalloc((void**)&p.flags, sizeof(uint32_t) * ns)); f->owned.push_back(p.flags);
-    CK(cudaMalloc((void**)&f->q.cur, sizeof(uint32_t) * ns)); f->owned.push_back(f->q.cur);
-    CK(cudaMalloc((void**)&f->q.next, sizeof(uint32_t) * ns)); f->owned.push_back(f->q.next);
+        std::vector<double**> sptrs = {&p.sdx, &p.sdy, &p.sdz, &p.sdist, &p.scx, &p.scy, &p.scz};
+        for (double** d : sptrs) c.take(d, ns * std::max<uint32_t>(p.n_shadow, 1));
+        c.take(&p.stack, ns * 8 * std::max<uint32_t>(p.stack_depth, 1));
+        c.take(&p.hobj, ns); c.take(&p.rng, ns); c.take(&p.sample_j, ns); c.take(&p.depth, ns); c.take(&p.flags, ns);
+        c.take(&f->q.cur, ns); c.take(&f->q.next, ns);
     }
-    CK(cudaMalloc((void**)&f->q.counters, sizeof(uint32_t) * 8)); f->owned.push_back(f->q.counters);
-    CK(cudaMalloc((void**)&f->q.stats, sizeof(unsigned long long) * 8)); f->owned.push_back(f->q.stats);
-    CK(cudaMemsetAsync(f->q.stats, 0, sizeof(unsigned long long) * 8, ctx->stream));
+    c.take(&f->q.counters, 8);
+    c.take(&f->q.stats, 8);
     const size_t n3 = (size_t)p.n_pixels * 3;
-    CK(cudaMalloc((void**)&f->d_batch_sum, sizeof(double) * n3)); f->owned.push_back(f->d_batch_sum);
-    CK(cudaMalloc((void**)&f->d_film_sum, sizeof(double) * n3)); f->owned.push_back(f->d_film_sum);
+    c.take(&f->d_batch_sum, n3);
+    c.take(&f->d_film_sum, n3);
+}
+
+static int film_alloc(rptx_film* f) {
+    rptx_ctx* ctx = f->ctx;
+    Carver size_pass{nullptr};
+    film_carve(f, size_pass);
+    const size_t need = size_pass.off + 256;
+    if (ctx->spare_arena && ctx->spare_arena_bytes >= need) {
+        f->arena = ctx->spare_arena; f->arena_bytes = ctx->spare_arena_bytes;
+        ctx->spare_arena = nullptr; ctx->spare_arena_bytes = 0;
+    } else {
+        if (ctx->spare_arena) { cudaFree(ctx->spare_arena); ctx->spare_arena = nullptr; ctx->spare_arena_bytes = 0; }
+        CK(cudaMalloc(&f->arena, need));
+        f->arena_bytes = need;
+    }
+    Carver carve{static_cast<char*>(f->arena)};
+    film_carve(f, carve);
+    const size_t n3 = (size_t)f->pool.n_pixels * 3;
+    CK(cudaMemsetAsync(f->q.stats, 0, sizeof(unsigned long long) * 8, ctx->stream));
     CK(cudaMemsetAsync(f->d_film_sum, 0, sizeof(double) * n3, ctx->stream));
     CK(cudaMemsetAsync(f->d_batch_sum, 0, sizeof(double) * n3, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
@@ -718,16 +754,31 @@ static int film_begin(rptx_ctx* ctx, rptx_scene* scene, const rptx_camera* camer
     const uint64_t n_pixels = (uint64_t)params->width * params->height;
     if (n_pixels >= (1ull << 31)) { delete f; return ctx_fail(ctx, "image too large"); }
     p.n_pixels = (uint32_t)n_pixels;
-    // path tracing: ~2 M paths in flight; photon gather: ~0.5 M threads, each walking its samples
-    // wavefront: ~2 M paths in flight; fused / photon gather: ~0.5 M threads, each walking its samples
-    const uint64_t target = f->mode == kFilmWavefront ? (1ull << 21) : (1ull << 19);
-    uint64_t lanes = std::max<uint64_t>(1, target / n_pixels);
-    lanes = std::min<uint64_t>(lanes, 4096);
-    if (f->mode != kFilmWavefront) lanes = std::min<uint64_t>(lanes, std::max<uint32_t>(params->num_samples, 1));
-    p.n_lanes = (uint32_t)lanes;
-    p.n_slots = (uint32_t)(n_pixels * lanes);
     p.n_shadow = scene->n_shadow_lights;
     p.stack_depth = scene->medium_kind == RPTX_MEDIUM_NONE ? params->max_bounces + 1 : 1;
+    // Paths in flight.  Wavefront: as many as a quarter of the free HBM holds, up to 32 M (~0.7 KB per slot on
+    // the Cornell box).  The pool size is not about occupancy (2 M paths already fill the GPU) but about
+    // coherence: a slot that regenerates mid-batch puts depth-0 and depth-5 vertices into the same warps, so
+    // the fewer regenerations, the closer every wave is to one bounce depth of neighbouring pixels.  Measured
+    // (profiles/r1_v2_summary.md): 2 M -> 32 M slots is +40 % on cornell, +26 % on lampshade, +9 % on fractal.
+    // Fused / photon gather: ~0.5 M threads, each walking its samples.
+    uint64_t target = 1ull << 19;
+    if (f->mode == kFilmWavefront) {
+        const uint64_t slot_bytes = 248 + 56ull * std::max<uint32_t>(p.n_shadow, 1) + 64ull * std::max<uint32_t>(p.stack_depth, 1);
+        size_t free_b = 0, total_b = 0;
+        CK(cudaMemGetInfo(&free_b, &total_b));
+        target = 1ull << 25;
+        while (target > (1ull << 21) && target * slot_bytes > free_b / 4) target >>= 1;
+    }
+    if (const char* e = std::getenv("RPTX_POOL_LOG2")) {  // developer knob: paths in flight
+        const int v = std::atoi(e);
+        if (v >= 10 && v <= 26) target = 1ull << v;
+    }
+    uint64_t lanes = std::max<uint64_t>(1, target / n_pixels);
+    lanes = std::min<uint64_t>(lanes, 4096);
+    lanes = std::min<uint64_t>(lanes, std::max<uint32_t>(params->num_samples, 1));
+    p.n_lanes = (uint32_t)lanes;
+    p.n_slots = (uint32_t)(n_pixels * lanes);
     if (film_alloc(f)) { rptx_film_destroy(f); return 1; }
     *out = f;
     return 0;
@@ -746,6 +797,16 @@ void rptx_film_destroy(rptx_film* f) {
     cudaSetDevice(f->ctx->device);
     for (void* p : f->owned) cudaFree(p);
     for (double* b : f->batches) cudaFree(b);
+    if (f->arena) {  // the slab goes back to the context for the next film (one spare at most, the larger one)
+        cudaStreamSynchronize(f->ctx->stream);
+        rptx_ctx* c = f->ctx;
+        if (f->arena_bytes > c->spare_arena_bytes) {
+            if (c->spare_arena) cudaFree(c->spare_arena);
+            c->spare_arena = f->arena; c->spare_arena_bytes = f->arena_bytes;
+        } else {
+            cudaFree(f->arena);
+        }
+    }
     if (f->d_batch_ptrs) cudaFree(f->d_batch_ptrs);
     if (f->ev0) cudaEventDestroy(f->ev0);
     if (f->ev1) cudaEventDestroy(f->ev1);
@@ -866,7 +927,7 @@ int rptx_render_sample_commit(rptx_film* f, uint32_t iterations) {
     cudaStream_t st = ctx->stream;
     const size_t n3 = (size_t)f->pool.n_pixels * 3;
     double* mean = nullptr;
-    CK(cudaMalloc((void**)&mean, sizeof(double) * n3));
+    CK(cudaMallocAsync((void**)&mean, sizeof(double) * n3, st));  // stream-ordered pool: no device-wide lock on the hot path
     f->batches.push_back(mean);
     const double exposure = std::pow(2.0, f->params.exposure_value);
     k_batch_commit<<<grid_for(n3, 256), 256, 0, st>>>(f->d_batch_sum, n3, (double)iterations, exposure, mean, f->d_film_sum);
