@@ -80,6 +80,8 @@ struct rptx_film {
     rptx_ctx* ctx = nullptr;
     void* arena = nullptr;
     size_t arena_bytes = 0;
+    char* d_select_tmp = nullptr;  // cub::DeviceSelect scratch of the queue compaction
+    size_t select_tmp_bytes = 0;
     int mode = kFilmWavefront;
     rptx_scene* scene = nullptr;
     rptx_params params;
@@ -90,6 +92,9 @@ struct rptx_film {
     double* d_batch_sum = nullptr;
     double* d_film_sum = nullptr;
     std::vector<double*> batches;  // one mean image per Renderer::sample call, as Buffer keeps them
+    std::vector<double*> pooled_means;  // those of `batches` that came from cudaMallocAsync
+    double* d_mean_slots = nullptr;     // the first n_mean_slots batch means live in the arena
+    uint32_t n_mean_slots = 0;
     double** d_batch_ptrs = nullptr;
     uint64_t next_sample = 0;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;

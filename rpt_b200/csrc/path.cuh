@@ -39,6 +39,7 @@ enum PathFlags : uint32_t { kFlagTerminate = 1u, kFlagHasShadow = 2u };
 struct Queues {
     uint32_t* cur;        // slot ids to process this wave
     uint32_t* next;       // slot ids alive after this wave
+    uint8_t* keep;        // [i] whether cur[i] stays in flight (k_connect); next = the kept entries of cur, order preserved
     uint32_t* counters;   // [0] cur count, [1] next count, [2] extend work head, [3] connect work head
     unsigned long long* stats;  // [0] paths started, [1] extend rays, [2] shadow rays
 };

@@ -80,8 +80,11 @@ __global__ void __launch_bounds__(kBlock) k_generate(PathPool p, Queues q, Batch
     p.ax[slot] = 0.0; p.ay[slot] = 0.0; p.az[slot] = 0.0;
     const uint32_t lane = slot / p.n_pixels;
     const bool active = lane < p.n_lanes && lane < bp.n_local;
-    if (active) start_path<MEDIUM>(p, bp, cam, slot, lane);
-    queue_push(q.cur, &q.counters[0], active, slot);
+    if (active) {  // the active slots are a prefix: the first queue is the identity, i.e. in slot order
+        start_path<MEDIUM>(p, bp, cam, slot, lane);
+        q.cur[slot] = slot;
+    }
+    if (slot == 0) q.counters[0] = p.n_pixels * min(p.n_lanes, bp.n_local);
     stat_add(&q.stats[0], active ? 1ull : 0ull);
 }
 
@@ -289,7 +292,60 @@ __global__ void __launch_bounds__(kBlock, RPTX_OCC_SHADOW) k_shadow(const __grid
 }
 
 // connect: finalise the vertex; finished paths are folded (surface mode), added to the slot's
-// lane film and the slot regenerates its next sample; survivors are compacted into the next queue.
+// lane film and the slot regenerates its next sample.  Returns whether the slot stays in flight.
+// The queue is then compacted IN ORDER (cub::DeviceSelect::Flagged on q.keep, rptx.cu): it starts
+// as the identity and a regenerated path keeps its slot, so every wave's queue is sorted by slot.
+// A warp's 32 entries are then as close in memory as the survivors allow (coalesced SoA access)
+// and belong to neighbouring pixels.  An atomic append per warp (the previous scheme) shuffled
+// the warps' chunks every wave: k_shade was 1.6x slower after a few regenerations.
+template <bool MEDIUM>
+RPTX_D bool connect_vertex(const PathPool& p, const BatchParams& bp, const Camera& cam, uint32_t slot, d3 direct, unsigned long long* n_started) {
+    const uint32_t flags = p.flags[slot];
+    const uint32_t depth = p.depth[slot];
+    const bool finished = (flags & kFlagTerminate) != 0;
+    d3 L;
+    if (MEDIUM) {
+        const d3 beta = mk3(p.bx[slot], p.by[slot], p.bz[slot]);
+        L = mk3(p.lx[slot], p.ly[slot], p.lz[slot]) + cmul(beta, direct);
+        if (!finished) {
+            p.lx[slot] = L.x; p.ly[slot] = L.y; p.lz[slot] = L.z;
+            p.bx[slot] = beta.x * p.fx[slot]; p.by[slot] = beta.y * p.fy[slot]; p.bz[slot] = beta.z * p.fz[slot];
+        }
+    } else {
+        // per-slot stack, one 64-byte record per level: [slot][level]{direct, f, pdf, |cos|}.  Only the
+        // few lanes whose path ends fold, so a slot's levels are contiguous (4 x double2 per level).
+        double2* st = reinterpret_cast<double2*>(p.stack + ((size_t)slot * p.stack_depth) * 8);
+        if (!finished) {
+            double2* r = st + (size_t)depth * 4;
+            r[0] = make_double2(direct.x, direct.y);
+            r[1] = make_double2(direct.z, p.fx[slot]);
+            r[2] = make_double2(p.fy[slot], p.fz[slot]);
+            r[3] = make_double2(p.pdf[slot], p.abscos[slot]);
+        } else {
+            L = direct;
+            for (int j = (int)depth - 1; j >= 0; j--) {
+                const double2* r = st + (size_t)j * 4;
+                const double2 a = r[0], b = r[1], c = r[2], e = r[3];
+                const d3 f = mk3(b.y, c.x, c.y);
+                const d3 ind = 1.0 / e.x * cmul(f, L) * e.y;
+                L = mk3(a.x + fmin(ind.x, kFireflyClamp), a.y + fmin(ind.y, kFireflyClamp), b.x + fmin(ind.z, kFireflyClamp));
+            }
+        }
+    }
+    if (finished) {
+        p.ax[slot] += L.x; p.ay[slot] += L.y; p.az[slot] += L.z;
+        const uint32_t jn = p.sample_j[slot] + p.n_lanes;
+        if (jn < bp.n_local) {
+            start_path<MEDIUM>(p, bp, cam, slot, jn);
+            (*n_started)++;
+            return true;
+        }
+        return false;
+    }
+    p.depth[slot] = depth + 1;
+    return true;
+}
+
 template <bool MEDIUM>
 __global__ void __launch_bounds__(kBlock) k_connect(PathPool p, Queues q, BatchParams bp, Camera cam) {
     const uint32_t count = q.counters[0];
@@ -300,53 +356,9 @@ __global__ void __launch_bounds__(kBlock) k_connect(PathPool p, Queues q, BatchP
         uint32_t slot = 0;
         if (i < count) {
             slot = q.cur[i];
-            const uint32_t flags = p.flags[slot];
-            const d3 direct = mk3(p.dirx[slot], p.diry[slot], p.dirz[slot]);
-            const uint32_t depth = p.depth[slot];
-            bool finished = (flags & kFlagTerminate) != 0;
-            d3 L;
-            if (MEDIUM) {
-                const d3 beta = mk3(p.bx[slot], p.by[slot], p.bz[slot]);
-                L = mk3(p.lx[slot], p.ly[slot], p.lz[slot]) + cmul(beta, direct);
-                if (!finished) {
-                    p.lx[slot] = L.x; p.ly[slot] = L.y; p.lz[slot] = L.z;
-                    p.bx[slot] = beta.x * p.fx[slot]; p.by[slot] = beta.y * p.fy[slot]; p.bz[slot] = beta.z * p.fz[slot];
-                }
-            } else {
-                // per-slot stack, one 64-byte record per level: [slot][level]{direct, f, pdf, |cos|}.  Only the
-                // few lanes whose path ends fold, so a slot's levels are contiguous (4 x double2 per level).
-                double2* st = reinterpret_cast<double2*>(p.stack + ((size_t)slot * p.stack_depth) * 8);
-                if (!finished) {
-                    double2* r = st + (size_t)depth * 4;
-                    r[0] = make_double2(direct.x, direct.y);
-                    r[1] = make_double2(direct.z, p.fx[slot]);
-                    r[2] = make_double2(p.fy[slot], p.fz[slot]);
-                    r[3] = make_double2(p.pdf[slot], p.abscos[slot]);
-                } else {
-                    L = direct;
-                    for (int j = (int)depth - 1; j >= 0; j--) {
-                        const double2* r = st + (size_t)j * 4;
-                        const double2 a = r[0], b = r[1], c = r[2], e = r[3];
-                        const d3 f = mk3(b.y, c.x, c.y);
-                        const d3 ind = 1.0 / e.x * cmul(f, L) * e.y;
-                        L = mk3(a.x + fmin(ind.x, kFireflyClamp), a.y + fmin(ind.y, kFireflyClamp), b.x + fmin(ind.z, kFireflyClamp));
-                    }
-                }
-            }
-            if (finished) {
-                p.ax[slot] += L.x; p.ay[slot] += L.y; p.az[slot] += L.z;
-                const uint32_t jn = p.sample_j[slot] + p.n_lanes;
-                if (jn < bp.n_local) {
-                    start_path<MEDIUM>(p, bp, cam, slot, jn);
-                    my_started++;
-                    alive = true;
-                }
-            } else {
-                p.depth[slot] = depth + 1;
-                alive = true;
-            }
+            alive = connect_vertex<MEDIUM>(p, bp, cam, slot, mk3(p.dirx[slot], p.diry[slot], p.dirz[slot]), &my_started);
+            q.keep[i] = alive ? 1 : 0;
         }
-        queue_push(q.next, &q.counters[1], alive, slot);
     }
     stat_add(&q.stats[0], my_started);
 }

@@ -4,6 +4,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdlib>
+#include <cub/cub.cuh>
 #include <cstring>
 #include <memory>
 #include <string>
@@ -681,17 +682,25 @@ static void film_carve(rptx_film* f, Carver& c) {
         for (double** d : sptrs) c.take(d, ns * std::max<uint32_t>(p.n_shadow, 1));
         c.take(&p.stack, ns * 8 * std::max<uint32_t>(p.stack_depth, 1));
         c.take(&p.hobj, ns); c.take(&p.rng, ns); c.take(&p.sample_j, ns); c.take(&p.depth, ns); c.take(&p.flags, ns);
-        c.take(&f->q.cur, ns); c.take(&f->q.next, ns);
+        c.take(&f->q.cur, ns); c.take(&f->q.next, ns); c.take(&f->q.keep, ns);
+        c.take(&f->d_select_tmp, f->select_tmp_bytes);
     }
     c.take(&f->q.counters, 8);
     c.take(&f->q.stats, 8);
     const size_t n3 = (size_t)p.n_pixels * 3;
     c.take(&f->d_batch_sum, n3);
     c.take(&f->d_film_sum, n3);
+    // room for the first batch means (Buffer keeps every batch for variance()); later ones come from the stream-ordered pool
+    f->n_mean_slots = std::min<uint32_t>(std::max<uint32_t>(f->params.num_samples, 1), 16);
+    c.take(&f->d_mean_slots, n3 * f->n_mean_slots);
 }
 
 static int film_alloc(rptx_film* f) {
     rptx_ctx* ctx = f->ctx;
+    if (f->mode == kFilmWavefront) {
+        uint32_t* u = nullptr; uint8_t* b = nullptr;
+        CK(cub::DeviceSelect::Flagged(nullptr, f->select_tmp_bytes, u, b, u, u, (int)f->pool.n_slots, ctx->stream));
+    }
     Carver size_pass{nullptr};
     film_carve(f, size_pass);
     const size_t need = size_pass.off + 256;
@@ -796,7 +805,7 @@ void rptx_film_destroy(rptx_film* f) {
     if (!f) return;
     cudaSetDevice(f->ctx->device);
     for (void* p : f->owned) cudaFree(p);
-    for (double* b : f->batches) cudaFree(b);
+    for (double* b : f->pooled_means) cudaFree(b);
     if (f->arena) {  // the slab goes back to the context for the next film (one spare at most, the larger one)
         cudaStreamSynchronize(f->ctx->stream);
         rptx_ctx* c = f->ctx;
@@ -839,20 +848,27 @@ static int run_waves(rptx_film* f, const BatchParams& bp) {
         cudaEventRecord(f->evw[1], st);
         k_shade<MEDIUM><<<grid_for(active, kBlock), kBlock, 0, st>>>(sc, p, q, bp, md);
         cudaEventRecord(f->evw[2], st);
-        if (p.n_shadow) {
-            if (small) {
-                if (sc.shadow_probe_mask) k_shadow<true, true><<<blocks, kBlock, 0, st>>>(sc, p, q);
-                else k_shadow<false, true><<<blocks, kBlock, 0, st>>>(sc, p, q);
-            } else {
-                if (sc.shadow_probe_mask) k_shadow<true, false><<<blocks, kBlock, 0, st>>>(sc, p, q);
-                else k_shadow<false, false><<<blocks, kBlock, 0, st>>>(sc, p, q);
+        {
+            if (p.n_shadow) {
+                if (small) {
+                    if (sc.shadow_probe_mask) k_shadow<true, true><<<blocks, kBlock, 0, st>>>(sc, p, q);
+                    else k_shadow<false, true><<<blocks, kBlock, 0, st>>>(sc, p, q);
+                } else {
+                    if (sc.shadow_probe_mask) k_shadow<true, false><<<blocks, kBlock, 0, st>>>(sc, p, q);
+                    else k_shadow<false, false><<<blocks, kBlock, 0, st>>>(sc, p, q);
+                }
             }
+            cudaEventRecord(f->evw[3], st);
+            k_connect<MEDIUM><<<grid_for(active, kBlock), kBlock, 0, st>>>(p, q, bp, f->cam);
+            {  // next = kept entries of cur, in order; the count lands in counters[1]
+                size_t bytes = f->select_tmp_bytes;
+                CK(cub::DeviceSelect::Flagged(f->d_select_tmp, bytes, q.cur, q.keep, q.next, q.counters + 1, (int)active, st));
+            }
+            cudaEventRecord(f->evw[4], st);
+            ctx->launches += p.n_shadow ? 6 : 5;  // + the two kernels of the select
         }
-        cudaEventRecord(f->evw[3], st);
-        k_connect<MEDIUM><<<grid_for(active, kBlock), kBlock, 0, st>>>(p, q, bp, f->cam);
-        cudaEventRecord(f->evw[4], st);
         k_wave_end<<<1, 1, 0, st>>>(q);
-        ctx->launches += p.n_shadow ? 5 : 4;
+        ctx->launches++;
         f->stats.waves++;
         std::swap(q.cur, q.next);
         CK(cudaMemcpyAsync(h_count, q.counters, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
@@ -927,7 +943,12 @@ int rptx_render_sample_commit(rptx_film* f, uint32_t iterations) {
     cudaStream_t st = ctx->stream;
     const size_t n3 = (size_t)f->pool.n_pixels * 3;
     double* mean = nullptr;
-    CK(cudaMallocAsync((void**)&mean, sizeof(double) * n3, st));  // stream-ordered pool: no device-wide lock on the hot path
+    if (f->batches.size() < f->n_mean_slots) {
+        mean = f->d_mean_slots + f->batches.size() * n3;
+    } else {
+        CK(cudaMallocAsync((void**)&mean, sizeof(double) * n3, st));  // stream-ordered pool: no device-wide lock on the hot path
+        f->pooled_means.push_back(mean);
+    }
     f->batches.push_back(mean);
     const double exposure = std::pow(2.0, f->params.exposure_value);
     k_batch_commit<<<grid_for(n3, 256), 256, 0, st>>>(f->d_batch_sum, n3, (double)iterations, exposure, mean, f->d_film_sum);
