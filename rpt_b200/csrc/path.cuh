@@ -11,6 +11,7 @@ namespace rptx {
 struct PathPool {
     uint32_t n_slots, n_pixels, n_lanes, n_shadow;  // n_shadow = non-ambient, non-directional lights
     uint32_t stack_depth;                           // max_bounces + 1 (surface mode only)
+    uint32_t width, tiled;                          // tiled: slots walk the image in 8x4-pixel tiles (pool_pixel)
     // current segment
     double *ox, *oy, *oz, *dx, *dy, *dz;
     // closest hit of the segment
@@ -33,6 +34,18 @@ struct PathPool {
     // lane film: sum of finished samples of this slot in the current batch
     double *ax, *ay, *az;
 };
+
+// Pixel owned by a slot.  Wavefront films whose size allows it map 32 consecutive slots to an 8x4-pixel
+// tile rather than to 32 pixels of one row: a warp's primary rays then span a squarer footprint (fewer
+// warps straddle a silhouette, closer traversal lengths).  The RNG is keyed by the PIXEL, so the image
+// does not depend on the mapping.
+RPTX_HD uint32_t pool_pixel(const PathPool& p, uint32_t slot) {
+    const uint32_t r = slot % p.n_pixels;
+    if (!p.tiled) return r;
+    const uint32_t tile = r >> 5, in = r & 31u, tiles_x = p.width >> 3;
+    const uint32_t tx = tile % tiles_x, ty = tile / tiles_x;
+    return (ty * 4u + (in >> 3)) * p.width + tx * 8u + (in & 7u);
+}
 
 enum PathFlags : uint32_t { kFlagTerminate = 1u, kFlagHasShadow = 2u };
 

@@ -55,7 +55,7 @@ RPTX_D void queue_push(uint32_t* __restrict__ q, uint32_t* __restrict__ count, b
 
 template <bool MEDIUM>
 RPTX_D void start_path(const PathPool& p, const BatchParams& bp, const Camera& cam, uint32_t slot, uint32_t j) {
-    const uint32_t pixel = slot % p.n_pixels;
+    const uint32_t pixel = pool_pixel(p, slot);
     const uint32_t x = pixel % bp.width, y = pixel / bp.width;
     const uint64_t s = bp.batch_base + bp.shard_index + (uint64_t)j * bp.shard_count;
     Rng rng = Rng::make(bp.seed, kDomainCamera, pixel, s);
@@ -560,11 +560,12 @@ __global__ void __launch_bounds__(kBlock) k_intersect_batch(const __grid_constan
 
 // batch_sum[pixel] = sum over lanes of the lane films (fixed order)
 __global__ void k_batch_reduce(PathPool p, double* __restrict__ batch_sum) {
-    const uint32_t pixel = blockIdx.x * blockDim.x + threadIdx.x;
-    if (pixel >= p.n_pixels) return;
+    const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= p.n_pixels) return;
+    const uint32_t pixel = pool_pixel(p, r);
     double x = 0, y = 0, z = 0;
     for (uint32_t l = 0; l < p.n_lanes; l++) {
-        const size_t s = (size_t)l * p.n_pixels + pixel;
+        const size_t s = (size_t)l * p.n_pixels + r;
         x += p.ax[s]; y += p.ay[s]; z += p.az[s];
     }
     batch_sum[3 * (size_t)pixel] = x; batch_sum[3 * (size_t)pixel + 1] = y; batch_sum[3 * (size_t)pixel + 2] = z;

@@ -763,6 +763,8 @@ static int film_begin(rptx_ctx* ctx, rptx_scene* scene, const rptx_camera* camer
     const uint64_t n_pixels = (uint64_t)params->width * params->height;
     if (n_pixels >= (1ull << 31)) { delete f; return ctx_fail(ctx, "image too large"); }
     p.n_pixels = (uint32_t)n_pixels;
+    p.width = params->width;
+    p.tiled = f->mode == kFilmWavefront && params->width % 8 == 0 && params->height % 4 == 0 && !std::getenv("RPTX_LINEAR_PIXELS");
     p.n_shadow = scene->n_shadow_lights;
     p.stack_depth = scene->medium_kind == RPTX_MEDIUM_NONE ? params->max_bounces + 1 : 1;
     // Paths in flight.  Wavefront: as many as a quarter of the free HBM holds, up to 32 M (~0.7 KB per slot on
