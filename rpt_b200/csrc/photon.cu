@@ -422,7 +422,8 @@ int emit_once(rptx_ctx* ctx, rptx_scene* scene, const EmitParams& ep, PhotonRec*
     const SceneDev sc = rptx_host::scene_dev(scene);
     const MediumDev md = rptx_host::medium_dev(scene);
     const int blocks = (int)std::min<uint64_t>((uint64_t)ctx->sm_count * 8, (ep.count + 127) / 128);
-    k_photon_trace<<<std::max(blocks, 1), 128, 0, st>>>(sc, md, ep, surf, vol, d_ctr + 2, d_ctr + 3);
+    if (sc.small_scene) k_photon_trace<true><<<std::max(blocks, 1), 128, 0, st>>>(sc, md, ep, surf, vol, d_ctr + 2, d_ctr + 3);
+    else k_photon_trace<false><<<std::max(blocks, 1), 128, 0, st>>>(sc, md, ep, surf, vol, d_ctr + 2, d_ctr + 3);
     ctx->launches++;
     unsigned long long h[4] = {0, 0, 0, 0};
     cudaError_t e = cudaGetLastError();

@@ -74,47 +74,70 @@ struct EmitParams {
     uint32_t light_index;   // first Light::Object of the scene (src/photon.rs:727-729)
 };
 
-// shoot_photon + trace_photon as one walk per thread; persistent warps pull 32 photon indices
-// at a time.  The reference's recursion deposits a vertex only when the walk continues past it
-// (:842-866), which the loop reproduces by depositing right after a successful sample_f.
+// shoot_photon + trace_photon as one walk per lane.  Persistent warps; every pass of the loop is one segment
+// of each live lane's photon, and a lane whose photon ended takes the next photon index at the top of the
+// loop (one atomic per warp for all idle lanes, once at least kRefillLanes are idle), so lanes do not
+// wait for the longest walk among 32.  Rows leave in arbitrary order; their key (photon index, depth)
+// restores the canonical one (photon.cu canonical_order).  The reference's recursion deposits a vertex
+// only when the walk continues past it (:842-866), which the loop reproduces by depositing right after a
+// successful sample_f.
+constexpr int kRefillLanes = 8;
+
+template <bool SMALL>
 __global__ void __launch_bounds__(128) k_photon_trace(const __grid_constant__ SceneDev sc, const MediumDev md, const EmitParams ep,
                                                       PhotonSink surf, PhotonSink vol, unsigned long long* __restrict__ work_head,
                                                       unsigned long long* __restrict__ stats) {
+    const uint32_t lane = threadIdx.x & 31u;
     unsigned long long my_rays = 0;
+    bool alive = false, exhausted = false;
+    uint64_t pid = 0;
+    uint32_t depth = 0;
+    Rng rng = Rng::make(ep.seed, kDomainPhoton, 0, 0);
+    RayD ray;
+    ray.o = mk3(0, 0, 0); ray.d = mk3(0, 0, 1);
+    d3 power = mk3(0, 0, 0);
     for (;;) {
-        unsigned long long base = 0;
-        if ((threadIdx.x & 31u) == 0) base = atomicAdd(work_head, 32ull);
-        base = __shfl_sync(0xffffffffu, base, 0);
-        if (base >= ep.count) break;
-        const unsigned long long i = base + (threadIdx.x & 31u);
-        if (i >= ep.count) continue;
-        const uint64_t pid = ep.first + i;
-        Rng rng = Rng::make(ep.seed, kDomainPhoton, pid, 0);
-        const Light& l = sc.lights[ep.light_index];
-        d3 pos, n;
-        double light_pdf;
-        sample_light_shape(sc, l, mk3(0, 0, 0), rng, &pos, &n, &light_pdf);
-        const double phi = 2.0 * kPi * rng.gen();
-        const double ct = 1.0 - rng.gen(), st = sin_from_cos(ct);  // theta = acos(1 - u), src/photon.rs:737
-        double sp, cp;
-        sincos(phi, &sp, &cp);
-        const d3 hemi = mk3(st * cp, ct, st * sp);
-        const Rot3 rot = rotation_from_y(n);
-        RayD ray;
-        ray.o = pos;
-        ray.d = rot_apply(rot, hemi);
-        d3 power = ep.power * mat_color(l.material);
-        for (uint32_t depth = 0;; depth++) {
+        const unsigned idle = __ballot_sync(0xffffffffu, !alive);
+        if (!exhausted && (__popc(idle) >= kRefillLanes || idle == 0xffffffffu)) {
+            unsigned long long base = 0;
+            if (lane == 0) base = atomicAdd(work_head, (unsigned long long)__popc(idle));
+            base = __shfl_sync(0xffffffffu, base, 0);
+            exhausted = base + (unsigned long long)__popc(idle) >= ep.count;
+            const unsigned long long i = base + (unsigned long long)__popc(idle & ((1u << lane) - 1u));
+            if (!alive && i < ep.count) {
+                pid = ep.first + i;
+                rng = Rng::make(ep.seed, kDomainPhoton, pid, 0);
+                const Light& l = sc.lights[ep.light_index];
+                d3 pos, n;
+                double light_pdf;
+                sample_light_shape(sc, l, mk3(0, 0, 0), rng, &pos, &n, &light_pdf);
+                const double phi = 2.0 * kPi * rng.gen();
+                const double ct = 1.0 - rng.gen(), st = sin_from_cos(ct);  // theta = acos(1 - u), src/photon.rs:737
+                double sp, cp;
+                sincos(phi, &sp, &cp);
+                const d3 hemi = mk3(st * cp, ct, st * sp);
+                const Rot3 rot = rotation_from_y(n);
+                ray.o = pos;
+                ray.d = rot_apply(rot, hemi);
+                power = ep.power * mat_color(l.material);
+                depth = 0;
+                alive = true;
+            }
+        }
+        if (__ballot_sync(0xffffffffu, alive) == 0) break;
+        if (alive) {
             const d3 wo = -normalize(ray.d);
             Hit h;
             h.t = CUDART_INF;
-            closest_hit<kClosest>(sc, ray, kEpsilon, 0.0, h);
+            closest_hit_sel<kClosest, SMALL>(sc, ray, kEpsilon, 0.0, h);
             my_rays++;
             const bool hit = h.inst != kNoHit;
             double dsamp = CUDART_INF;
             if (md.kind != 0) dsamp = medium_sample_d(md, rng);
-            else if (!hit) break;
-            if (md.kind != 0 && (!hit || dsamp < h.t)) {
+            else if (!hit) alive = false;
+            if (!alive) {
+                // left the scene (no medium)
+            } else if (md.kind != 0 && (!hit || dsamp < h.t)) {
                 // trace_in_volume, src/photon.rs:877-927
                 const d3 collision = ray.o + dsamp * ray.d;
                 const d3 mc = md.color(collision);
@@ -130,34 +153,42 @@ __global__ void __launch_bounds__(128) k_photon_trace(const __grid_constant__ Sc
                 } else {
                     photon_deposit(vol, collision, wo, power, ray.o, photon_key(pid, depth));
                 }
-                if (!go) break;
-                power = attenuated * md.phase / md.phase;  // phase(wo, wi) / ph_p, both the medium's constant
-                ray.o = collision;
-                ray.d = wi;
+                if (!go) {
+                    alive = false;
+                } else {
+                    power = attenuated * md.phase / md.phase;  // phase(wo, wi) / ph_p, both the medium's constant
+                    ray.o = collision;
+                    ray.d = wi;
+                }
             } else {
                 // trace_on_surface, src/photon.rs:813-874
                 uint32_t prim, inst;
                 const d3 hn = hit_normal(sc, ray, h, &prim, &inst);
                 const d3 world_pos = ray.o + h.t * ray.d;
                 const Material mat = sc.materials[h.obj];
-                if (!(rng.gen() < kPhotonRrDiffuse)) break;  // absorbed
                 d3 wi;
                 double pdf;
-                if (!mat_sample_f(mat, hn, wo, rng, &wi, &pdf)) break;  // total internal reflection
-                const d3 f = mat_bsdf(mat, hn, wo, wi);
-                const double wn = dot(wi, hn);
-                const double cosine_term = wn > 0.0 ? wn : 1.0;
-                const d3 attenuated = cmul(power, f) * cosine_term / pdf / kPhotonRrDiffuse;
-                if (!mat_is_mirror(mat)) photon_deposit(surf, world_pos, wo, power, world_pos, photon_key(pid, depth));
-                power = attenuated;
-                ray.o = world_pos;
-                ray.d = wi;
+                if (!(rng.gen() < kPhotonRrDiffuse)) {
+                    alive = false;  // absorbed
+                } else if (!mat_sample_f(mat, hn, wo, rng, &wi, &pdf)) {
+                    alive = false;  // total internal reflection
+                } else {
+                    const d3 f = mat_bsdf(mat, hn, wo, wi);
+                    const double wn = dot(wi, hn);
+                    const double cosine_term = wn > 0.0 ? wn : 1.0;
+                    const d3 attenuated = cmul(power, f) * cosine_term / pdf / kPhotonRrDiffuse;
+                    if (!mat_is_mirror(mat)) photon_deposit(surf, world_pos, wo, power, world_pos, photon_key(pid, depth));
+                    power = attenuated;
+                    ray.o = world_pos;
+                    ray.d = wi;
+                }
             }
+            depth++;
         }
+        __syncwarp();
     }
-    const cg::coalesced_group g = cg::coalesced_threads();
-    const unsigned long long tot = cg::reduce(g, my_rays, cg::plus<unsigned long long>());
-    if (g.thread_rank() == 0 && tot) atomicAdd(&stats[0], tot);
+    const unsigned long long tot = __reduce_add_sync(0xffffffffu, (unsigned)my_rays) ;
+    if (lane == 0 && tot) atomicAdd(&stats[0], tot);
 }
 
 // ------------------------------------------------------------------ point map (kd-tree 0.4.1)

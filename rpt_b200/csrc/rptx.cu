@@ -305,7 +305,7 @@ SceneDev scene_dev(const rptx_scene* s) {
     sc.n_bounded = s->n_bounded; sc.n_unbounded = s->n_unbounded;
     sc.n_lights = (uint32_t)s->lights.size(); sc.n_shadow_lights = s->n_shadow_lights;
     sc.shadow_probe_mask = s->shadow_probe_mask;
-    sc.small_scene = s->small_scene;
+    sc.small_scene = s->small_scene && !std::getenv("RPTX_NO_SMALL_SCENE");
     sc.small_slots = s->d_small_slots; sc.small_boxes = s->d_small_boxes;
     for (int k = 0; k < 3; k++) sc.small_kind_mask[k] = s->small_kind_mask[k];
     sc.small_unbounded_mask = s->small_unbounded_mask;
@@ -839,7 +839,7 @@ static int run_waves(rptx_film* f, const BatchParams& bp) {
     k_generate<MEDIUM><<<grid_for(p.n_slots, kBlock), kBlock, 0, st>>>(p, q, bp, f->cam);
     ctx->launches++;
     const int persistent_blocks = ctx->sm_count * 8;
-    const bool small = sc.small_scene != 0 && !getenv("RPTX_NO_SMALL_SCENE");
+    const bool small = sc.small_scene != 0;
     uint32_t* h_count = (uint32_t*)ctx->h_pinned;
     uint32_t active = std::min<uint64_t>(p.n_slots, (uint64_t)p.n_pixels * std::min(p.n_lanes, bp.n_local));
     while (active > 0) {

@@ -31,6 +31,10 @@ def run(variant, kind, n, w, h, spp, oracle=False):
 if __name__ == "__main__":
     sizes = [int(float(x)) for x in sys.argv[1].split(",")]
     kinds = dict(photonphoton=0, beamphoton=1, beambeam=2)
+    import io, contextlib
+    for v, k in kinds.items():  # warm-up: module load, allocator pools
+        with contextlib.redirect_stdout(io.StringIO()):
+            run(v, k, 20000, 32, 32, 2)
     for n in sizes:
         for v, k in kinds.items():
             if v == "beamphoton" and n > 2e7: continue
