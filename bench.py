@@ -34,6 +34,9 @@ METRIC = "Mpath-samples/s"
 # algorithmic HBM bytes of one extend-kernel ray (DESIGN.md "k_extend"): queue entry 4 B +
 # ray origin/direction 48 B read; t 8 B + object id 4 B + normal 24 B written
 EXTEND_BYTES_PER_RAY = 4 + 48 + 8 + 4 + 24
+# dram__bytes_read.sum + dram__bytes_write.sum of one k_extend launch / its rays, from the committed
+# `ncu --set full` capture of the same command (profiles/r1_v2_summary.md); None where not captured
+EXTEND_DRAM_BYTES_PER_RAY = {"fractal_teapots": 88.2, "cornell": 148.7}
 
 
 _OVERRIDES = {}
@@ -220,6 +223,7 @@ def run_ours(args):
     for _ in range(args.warmup):
         step()
     launches0 = film.stats()["kernel_launches"]
+    waves0 = film.stats()["waves"]
     clocks = ClockSampler(local)
     if rank == 0:
         clocks.start()
@@ -251,7 +255,7 @@ def run_ours(args):
     # e2e: the user-facing call from HOST data: lower + upload scene, GPU BVH build, render, image to host
     h2d = sum(v.nbytes + (0 if n is None else n.nbytes) for v, n in r.device_scene().low.meshes)
     e2e_t = 0.0
-    n_e2e = max(1, min(args.steps, 2))
+    n_e2e = max(1, min(args.steps, 3))
     film.close()  # its path-state slab returns to the context, as it does between a user's successive render() calls
     for _ in range(n_e2e):
         barrier()
@@ -284,9 +288,13 @@ def run_ours(args):
                     e2e=dict(value=e2e_val, unit=METRIC, h2d_bytes_per_step=int(h2d), d2h_bytes_per_step=int(w * h * 3),
                              note="Renderer -> scene lowering + upload + GPU BVH build + path pool alloc + render + rgb8 image to host"),
                     gpu_launches=int(launches), clocks=clk,
-                    roofline=dict(bound="hbm", kernel="k_extend", achieved=ach, peak=peak, unit="GB/s", frac=ach / peak, traffic=None,
+                    roofline=dict(bound="hbm", kernel="k_extend", achieved=ach, peak=peak, unit="GB/s", frac=ach / peak,
+                                  traffic=(EXTEND_DRAM_BYTES_PER_RAY[args.workload] * rays_e / max(st["waves"] - waves0, 1)
+                                           if args.workload in EXTEND_DRAM_BYTES_PER_RAY else None),
+                                  launches=int(st["waves"] - waves0), algorithmic_bytes_per_launch=EXTEND_BYTES_PER_RAY * rays_e / max(st["waves"] - waves0, 1),
                                   peak_source=which,
-                                  note="closest-hit traversal is issue/latency-bound, not HBM-bound (scene is L2-resident): see DESIGN.md and profiles/"),
+                                  note="per launch (one wave); closest-hit traversal is issue-bound (62 % of issue slots, 16-23 of 32 lanes), "
+                                       "not HBM-bound: the scene stays in L2 and DRAM traffic equals the path-state bytes; see DESIGN.md and profiles/"),
                     rays_per_s=dict(extend=rays_e / max(ext_ms / 1e3, 1e-12), shadow=rays_s / max(sdw_ms / 1e3, 1e-12),
                                     total_step=(rays_e + rays_s) / step_time),
                     kernel_ms_per_step=dict(extend=ext_ms / args.steps, shade=shd_ms / args.steps, shadow=sdw_ms / args.steps, connect=con_ms / args.steps,

@@ -3,6 +3,7 @@
 // path_kernels.cuh / trace.cuh / bvh_build.cu.
 #include <algorithm>
 #include <cmath>
+#include <cstdio>
 #include <cstdlib>
 #include <cub/cub.cuh>
 #include <cstring>
@@ -708,6 +709,7 @@ static int film_alloc(rptx_film* f) {
         f->arena = ctx->spare_arena; f->arena_bytes = ctx->spare_arena_bytes;
         ctx->spare_arena = nullptr; ctx->spare_arena_bytes = 0;
     } else {
+        if (std::getenv("RPTX_TRACE_ALLOC")) fprintf(stderr, "[rptx] film slab: need %zu B, spare %zu B -> cudaMalloc\n", need, ctx->spare_arena_bytes);
         if (ctx->spare_arena) { cudaFree(ctx->spare_arena); ctx->spare_arena = nullptr; ctx->spare_arena_bytes = 0; }
         CK(cudaMalloc(&f->arena, need));
         f->arena_bytes = need;
@@ -815,6 +817,7 @@ void rptx_film_destroy(rptx_film* f) {
             if (c->spare_arena) cudaFree(c->spare_arena);
             c->spare_arena = f->arena; c->spare_arena_bytes = f->arena_bytes;
         } else {
+            if (std::getenv("RPTX_TRACE_ALLOC")) fprintf(stderr, "[rptx] film slab: %zu B freed (spare holds %zu B)\n", f->arena_bytes, c->spare_arena_bytes);
             cudaFree(f->arena);
         }
     }
