@@ -177,7 +177,7 @@ def config_of(args, d):
     return dict(workload=f"{args.workload}: examples/{args.workload.split('_mb')[0]}.rs scene, {d['width']}x{d['height']}, {d['num_samples']} spp, "
                          f"max_bounces {d['max_bounces']}",
                 width=d["width"], height=d["height"], spp=d["num_samples"], max_bounces=d["max_bounces"],
-                l2_policy="per-step path state (>= 1.4 GB) and film exceed the 126 MB L2; no explicit flush",
+                l2_policy="per-step path state (13-23 GB: up to 33.5 M paths in flight) and film exceed the 126 MB L2; no explicit flush",
                 parallelism=f"sample-sharded x{args.gpus}")
 
 
