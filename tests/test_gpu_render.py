@@ -179,3 +179,4 @@ def test_list_walk_equals_hierarchy(monkeypatch):
             means.append(f.mean())
         monkeypatch.delenv("RPTX_NO_SMALL_SCENE", raising=False)
         assert np.array_equal(means[0], means[1]), name
+
