@@ -163,12 +163,56 @@ RPTX_D void sample_lights_dev(const SceneDev& sc, const PathPool& p, uint32_t sl
     });
 }
 
+// shade: one thread per queue entry.  The three kinds of vertex (medium collision, surface hit, miss) run
+// different code, and a warp of 32 consecutive queue entries holds all three (lampshade: 12 of 32 lanes live
+// per instruction).  So each block first classifies its kShadeBlock entries (the class needs t, the hit
+// object and, with a medium, the free-flight draw) and re-deals them to its threads sorted by class
+// (stable counting sort through shared memory): all but two or three of its warps then run one kind only.
+// The entries stay within kShadeBlock queue positions of where they were, so the state accesses stay local.
+constexpr int kShadeBlock = 256;
+
 template <bool MEDIUM>
-__global__ void __launch_bounds__(kBlock, RPTX_OCC_SHADE) k_shade(const __grid_constant__ SceneDev sc, PathPool p, Queues q, BatchParams bp,
-                                                   MediumDev md) {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= q.counters[0]) return;
-    const uint32_t slot = q.cur[i];
+__global__ void __launch_bounds__(kShadeBlock, 2) k_shade(const __grid_constant__ SceneDev sc, PathPool p, Queues q, BatchParams bp,
+                                                          MediumDev md) {
+    __shared__ uint32_t s_slot[kShadeBlock];
+    __shared__ uint32_t s_cnt[3][kShadeBlock / 32];
+    uint32_t slot;
+    {
+        const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+        const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
+        uint32_t cls = 3, slot0 = 0;  // 0 medium collision, 1 surface, 2 miss, 3 no entry
+        if (i < q.counters[0]) {
+            slot0 = q.cur[i];
+            const bool hit0 = p.hobj[slot0] != kNoHit;
+            cls = hit0 ? 1u : 2u;
+            if (MEDIUM) {
+                Rng r0;
+                r0.state = p.rng[slot0];
+                const double d0 = medium_sample_d(md, r0);
+                if (d0 < (hit0 ? p.ht[slot0] : kBackgroundDist)) cls = 0;
+            }
+        }
+        uint32_t rank = 0;
+#pragma unroll
+        for (uint32_t c = 0; c < 3; c++) {
+            const unsigned m = __ballot_sync(0xffffffffu, cls == c);
+            if (cls == c) rank = (uint32_t)__popc(m & ((1u << lane) - 1u));
+            if (lane == 0) s_cnt[c][warp] = (uint32_t)__popc(m);
+        }
+        __syncthreads();
+        uint32_t before = 0, total = 0;
+#pragma unroll
+        for (uint32_t c = 0; c < 3; c++)
+            for (uint32_t w = 0; w < kShadeBlock / 32; w++) {
+                const uint32_t n = s_cnt[c][w];
+                total += n;
+                if (c < cls || (c == cls && w < warp)) before += n;
+            }
+        if (cls < 3) s_slot[before + rank] = slot0;
+        __syncthreads();
+        if (threadIdx.x >= total) return;
+        slot = s_slot[threadIdx.x];
+    }
     const d3 o = mk3(p.ox[slot], p.oy[slot], p.oz[slot]);
     const d3 d = mk3(p.dx[slot], p.dy[slot], p.dz[slot]);
     const double t = p.ht[slot];

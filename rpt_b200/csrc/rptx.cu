@@ -851,7 +851,7 @@ static int run_waves(rptx_film* f, const BatchParams& bp) {
         if (small) k_extend<true><<<blocks, kBlock, 0, st>>>(sc, p, q);
         else k_extend<false><<<blocks, kBlock, 0, st>>>(sc, p, q);
         cudaEventRecord(f->evw[1], st);
-        k_shade<MEDIUM><<<grid_for(active, kBlock), kBlock, 0, st>>>(sc, p, q, bp, md);
+        k_shade<MEDIUM><<<grid_for(active, kShadeBlock), kShadeBlock, 0, st>>>(sc, p, q, bp, md);
         cudaEventRecord(f->evw[2], st);
         {
             if (p.n_shadow) {

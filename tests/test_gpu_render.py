@@ -180,3 +180,42 @@ def test_list_walk_equals_hierarchy(monkeypatch):
         monkeypatch.delenv("RPTX_NO_SMALL_SCENE", raising=False)
         assert np.array_equal(means[0], means[1]), name
 
+
+def test_tiled_slots_equal_row_major(monkeypatch):
+    """Slots walk the image in 8x4 tiles when the size allows it; the RNG is keyed by the pixel, so the
+    batch is the one the row-major walk produces, bit for bit."""
+    monkeypatch.setenv("RPTX_PATH_MODE", "wavefront")
+    scene, cam, d = scenes.cornell()
+    means = []
+    for linear in (False, True):
+        if linear:
+            monkeypatch.setenv("RPTX_LINEAR_PIXELS", "1")
+        else:
+            monkeypatch.delenv("RPTX_LINEAR_PIXELS", raising=False)
+        f = scenes.make_renderer(scene, cam, d, width=64, height=48, num_samples=3, seed=2, max_bounces=3).begin()
+        f.sample(3)
+        means.append(f.mean())
+    monkeypatch.delenv("RPTX_LINEAR_PIXELS", raising=False)
+    assert np.array_equal(means[0], means[1])
+
+
+def test_film_slab_is_recycled_and_pool_size_does_not_matter(monkeypatch):
+    """A second film of the same context reuses the first one's slab; the number of paths in flight
+    (RPTX_POOL_LOG2) changes scheduling only: same batch."""
+    monkeypatch.setenv("RPTX_PATH_MODE", "wavefront")
+    scene, cam, d = scenes.lampshade("pathtrace")
+    means = []
+    for log2 in (None, "12", None):
+        if log2:
+            monkeypatch.setenv("RPTX_POOL_LOG2", log2)
+        else:
+            monkeypatch.delenv("RPTX_POOL_LOG2", raising=False)
+        r = scenes.make_renderer(scene, cam, d, width=56, height=40, num_samples=6, seed=4, max_bounces=4)
+        f = r.begin()
+        f.sample(2)
+        f.sample(4)
+        means.append(f.mean())
+        f.close()
+    monkeypatch.delenv("RPTX_POOL_LOG2", raising=False)
+    assert np.array_equal(means[0], means[2])
+    assert np.allclose(means[0], means[1], rtol=1e-12, atol=1e-300)  # lane sums are added in a different order
