@@ -263,13 +263,21 @@ def run_ours(args):
         rr = make_renderer(scene, cam, d, seed=1)
         rr._ctx = ctx
         rr.shard(world, rank)
+        rr.device_scene()
+        t2 = time.perf_counter()
         f2 = rr.begin()
+        t3 = time.perf_counter()
         rd.sample_batch(f2, batch)
+        t4 = time.perf_counter()
         img = f2.image()
         barrier()
-        e2e_t += time.perf_counter() - t1
+        t5 = time.perf_counter()
+        e2e_t += t5 - t1
         assert img.shape == (h, w, 3)
         f2.close(); rr.device_scene().close()
+        if rank == 0:
+            print("e2e ms: scene %.1f begin %.1f sample %.1f image %.1f close %.1f" % (
+                1e3 * (t2 - t1), 1e3 * (t3 - t2), 1e3 * (t4 - t3), 1e3 * (t5 - t4), 1e3 * (time.perf_counter() - t5)), file=sys.stderr)
     te = torch.tensor([e2e_t / n_e2e], device=f"cuda:{local}", dtype=torch.float64)
     if dist is not None:
         dist.all_reduce(te, op=dist.ReduceOp.MAX)

@@ -91,6 +91,7 @@ struct rptx_film {
     std::vector<void*> owned;
     double* d_batch_sum = nullptr;
     double* d_film_sum = nullptr;
+    double* d_scratch = nullptr;
     std::vector<double*> batches;  // one mean image per Renderer::sample call, as Buffer keeps them
     std::vector<double*> pooled_means;  // those of `batches` that came from cudaMallocAsync
     double* d_mean_slots = nullptr;     // the first n_mean_slots batch means live in the arena
@@ -101,6 +102,12 @@ struct rptx_film {
     cudaEvent_t evw[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};  // per-wave kernel boundaries
     rptx_stats stats = {};
 };
+
+// Stream-ordered allocation for everything that is created and destroyed per call (scene buffers, BVH build
+// scratch): cudaMalloc / cudaFree take a device-wide lock and, with a 20 GB film slab mapped, stalled for
+// 20-460 ms at random in the end-to-end loop; the pool (release threshold set in rptx_ctx_create) does neither.
+inline cudaError_t rptx_alloc_async(void** p, size_t bytes, cudaStream_t st) { return cudaMallocAsync(p, bytes ? bytes : 16, st); }
+inline void rptx_free_async(const void* p, cudaStream_t st) { if (p) cudaFreeAsync(const_cast<void*>(p), st); }
 
 // host helpers shared by rptx.cu and photon.cu
 namespace rptx_host {

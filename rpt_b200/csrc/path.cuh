@@ -11,6 +11,8 @@ namespace rptx {
 struct PathPool {
     uint32_t n_slots, n_pixels, n_lanes, n_shadow;  // n_shadow = non-ambient, non-directional lights
     uint32_t stack_depth;                           // max_bounces + 1 (surface mode only)
+    uint32_t rec_stride;                            // doubles per level record: 8, or 4 when max_bounces == 0 (only `direct` is kept)
+    uint32_t record_mode;                           // surface mode: the vertex is assembled in its stack record (k_shade/k_shadow)
     uint32_t width, tiled;                          // tiled: slots walk the image in 8x4-pixel tiles (pool_pixel)
     // current segment
     double *ox, *oy, *oz, *dx, *dy, *dz;
@@ -24,8 +26,8 @@ struct PathPool {
     uint32_t* depth;
     uint32_t* flags;
     // vertex being assembled
-    double *dirx, *diry, *dirz;                  // direct light of the current vertex
-    double *fx, *fy, *fz, *pdf, *abscos;          // continuation weights
+    double *dirx, *diry, *dirz;                  // direct light of the current vertex (medium mode)
+    double *fx, *fy, *fz;                        // continuation weight (medium mode)
     double *sdx, *sdy, *sdz, *sdist, *scx, *scy, *scz;  // [n_shadow][n_slots] NEE candidates
     // forward accumulation (medium mode): throughput and radiance
     double *bx, *by, *bz, *lx, *ly, *lz;

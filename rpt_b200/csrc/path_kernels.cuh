@@ -222,6 +222,8 @@ __global__ void __launch_bounds__(kShadeBlock, 2) k_shade(const __grid_constant_
     rng.state = p.rng[slot];
     uint32_t flags = 0;
     d3 direct = mk3(0, 0, 0);
+    d3 rec_f = mk3(0, 0, 0);
+    double rec_pdf = 0.0, rec_ac = 0.0;
 
     double dsamp = 0.0;
     if (MEDIUM) dsamp = medium_sample_d(md, rng);
@@ -275,9 +277,7 @@ __global__ void __launch_bounds__(kShadeBlock, 2) k_shade(const __grid_constant_
                     const double s = 1.0 / (pdf * kRrMedium);
                     p.fx[slot] = s * f.x * ac; p.fy[slot] = s * f.y * ac; p.fz[slot] = s * f.z * ac;
                 } else {
-                    p.fx[slot] = f.x; p.fy[slot] = f.y; p.fz[slot] = f.z;
-                    p.pdf[slot] = pdf;
-                    p.abscos[slot] = ac;
+                    rec_f = f; rec_pdf = pdf; rec_ac = ac;
                 }
                 p.dx[slot] = wi.x; p.dy[slot] = wi.y; p.dz[slot] = wi.z;
             } else {
@@ -286,7 +286,20 @@ __global__ void __launch_bounds__(kShadeBlock, 2) k_shade(const __grid_constant_
         }
         if (!go) flags |= kFlagTerminate;
     }
-    p.dirx[slot] = direct.x; p.diry[slot] = direct.y; p.dirz[slot] = direct.z;
+    if (MEDIUM) {
+        p.dirx[slot] = direct.x; p.diry[slot] = direct.y; p.dirz[slot] = direct.z;
+    } else {
+        // surface mode assembles the vertex directly in its level record of the clamp stack
+        // ([slot][depth]{direct, f, pdf, |cos|}, 64 B): k_shadow adds the visible light samples to `direct`
+        // there and k_connect has nothing to copy.  A vertex that ends the path only needs `direct`.
+        double2* r = reinterpret_cast<double2*>(p.stack + ((size_t)slot * p.stack_depth + depth) * p.rec_stride);
+        r[0] = make_double2(direct.x, direct.y);
+        r[1] = make_double2(direct.z, rec_f.x);
+        if (!(flags & kFlagTerminate)) {
+            r[2] = make_double2(rec_f.y, rec_f.z);
+            r[3] = make_double2(rec_pdf, rec_ac);
+        }
+    }
     p.flags[slot] = flags;
     p.rng[slot] = rng.state;
 }
@@ -310,6 +323,8 @@ __global__ void __launch_bounds__(kBlock, RPTX_OCC_SHADOW) k_shadow(const __grid
         const bool has = i < count && (p.flags[slot] & kFlagHasShadow);
         d3 add = mk3(0, 0, 0);
         bool any = false;
+        double2* rec = nullptr;
+        double keep_fx = 0.0;
         RayD ray;
         ray.o = mk3(0, 0, 0);
         if (has) ray.o = mk3(p.ox[slot], p.oy[slot], p.oz[slot]);
@@ -324,11 +339,24 @@ __global__ void __launch_bounds__(kBlock, RPTX_OCC_SHADOW) k_shadow(const __grid
             __syncwarp();
             if (job && nee_visible<PROBE, SMALL>(sc, ray, dist, &my_occl)) {
                 // direct += contribution, in light order like the reference's loop
-                if (!any) { add = mk3(p.dirx[slot], p.diry[slot], p.dirz[slot]); any = true; }
+                if (!any) {
+                    if (p.record_mode) {
+                        rec = reinterpret_cast<double2*>(p.stack + ((size_t)slot * p.stack_depth + p.depth[slot]) * p.rec_stride);
+                        const double2 a = rec[0], b = rec[1];
+                        add = mk3(a.x, a.y, b.x);
+                        keep_fx = b.y;
+                    } else {
+                        add = mk3(p.dirx[slot], p.diry[slot], p.dirz[slot]);
+                    }
+                    any = true;
+                }
                 add = add + c;
             }
         }
-        if (any) { p.dirx[slot] = add.x; p.diry[slot] = add.y; p.dirz[slot] = add.z; }
+        if (any) {
+            if (p.record_mode) { rec[0] = make_double2(add.x, add.y); rec[1] = make_double2(add.z, keep_fx); }
+            else { p.dirx[slot] = add.x; p.diry[slot] = add.y; p.dirz[slot] = add.z; }
+        }
     }
     stat_add64(&q.stats[2], my_queries);
     stat_add64(&q.stats[3], my_traced);
@@ -358,17 +386,14 @@ RPTX_D bool connect_vertex(const PathPool& p, const BatchParams& bp, const Camer
     } else {
         // per-slot stack, one 64-byte record per level: [slot][level]{direct, f, pdf, |cos|}.  Only the
         // few lanes whose path ends fold, so a slot's levels are contiguous (4 x double2 per level).
-        double2* st = reinterpret_cast<double2*>(p.stack + ((size_t)slot * p.stack_depth) * 8);
-        if (!finished) {
-            double2* r = st + (size_t)depth * 4;
-            r[0] = make_double2(direct.x, direct.y);
-            r[1] = make_double2(direct.z, p.fx[slot]);
-            r[2] = make_double2(p.fy[slot], p.fz[slot]);
-            r[3] = make_double2(p.pdf[slot], p.abscos[slot]);
-        } else {
-            L = direct;
+        // (k_shade assembled this level's record, k_shadow added the visible light samples to it)
+        const double2* st = reinterpret_cast<const double2*>(p.stack + ((size_t)slot * p.stack_depth) * p.rec_stride);
+        if (finished) {
+            const size_t lvl = p.rec_stride >> 1;  // double2 per level
+            const double2 d0 = st[(size_t)depth * lvl], d1 = st[(size_t)depth * lvl + 1];
+            L = mk3(d0.x, d0.y, d1.x);
             for (int j = (int)depth - 1; j >= 0; j--) {
-                const double2* r = st + (size_t)j * 4;
+                const double2* r = st + (size_t)j * lvl;
                 const double2 a = r[0], b = r[1], c = r[2], e = r[3];
                 const d3 f = mk3(b.y, c.x, c.y);
                 const d3 ind = 1.0 / e.x * cmul(f, L) * e.y;
@@ -400,7 +425,8 @@ __global__ void __launch_bounds__(kBlock) k_connect(PathPool p, Queues q, BatchP
         uint32_t slot = 0;
         if (i < count) {
             slot = q.cur[i];
-            alive = connect_vertex<MEDIUM>(p, bp, cam, slot, mk3(p.dirx[slot], p.diry[slot], p.dirz[slot]), &my_started);
+            const d3 direct = MEDIUM ? mk3(p.dirx[slot], p.diry[slot], p.dirz[slot]) : mk3(0, 0, 0);
+            alive = connect_vertex<MEDIUM>(p, bp, cam, slot, direct, &my_started);
             q.keep[i] = alive ? 1 : 0;
         }
     }

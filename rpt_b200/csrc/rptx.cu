@@ -142,7 +142,7 @@ cudaError_t copy_h2d(void* dst, const void* src, size_t bytes, cudaStream_t st) 
 template <class T>
 cudaError_t upload(T** dst, const std::vector<T>& src, cudaStream_t st) {
     *dst = nullptr;
-    cudaError_t e = cudaMalloc((void**)dst, std::max<size_t>(src.size(), 1) * sizeof(T));
+    cudaError_t e = rptx_alloc_async((void**)dst, std::max<size_t>(src.size(), 1) * sizeof(T), st);
     if (e != cudaSuccess) return e;
     if (!src.empty()) e = copy_h2d(*dst, src.data(), src.size() * sizeof(T), st);
     return e;
@@ -151,10 +151,10 @@ cudaError_t upload(T** dst, const std::vector<T>& src, cudaStream_t st) {
 int grid_for(size_t n, int block) { return (int)std::max<size_t>(1, (n + block - 1) / block); }
 
 void free_scene_device(rptx_scene* s) {
-    cudaFree((void*)s->d_nodes); cudaFree((void*)s->d_instances); cudaFree((void*)s->d_tris);
-    cudaFree((void*)s->d_tri_normals); cudaFree((void*)s->d_trif); s->d_trif = nullptr; cudaFree((void*)s->d_tri_orig); cudaFree((void*)s->d_materials);
-    cudaFree((void*)s->d_lights); cudaFree((void*)s->d_raw); cudaFree((void*)s->d_env); cudaFree((void*)s->d_cube_idx); s->d_cube_idx = nullptr;
-    cudaFree(s->d_small_slots); s->d_small_slots = nullptr; cudaFree(s->d_small_boxes); s->d_small_boxes = nullptr;
+    rptx_free_async((void*)s->d_nodes, s->ctx->stream); rptx_free_async((void*)s->d_instances, s->ctx->stream); rptx_free_async((void*)s->d_tris, s->ctx->stream);
+    rptx_free_async((void*)s->d_tri_normals, s->ctx->stream); rptx_free_async((void*)s->d_trif, s->ctx->stream); s->d_trif = nullptr; rptx_free_async((void*)s->d_tri_orig, s->ctx->stream); rptx_free_async((void*)s->d_materials, s->ctx->stream);
+    rptx_free_async((void*)s->d_lights, s->ctx->stream); rptx_free_async((void*)s->d_raw, s->ctx->stream); rptx_free_async((void*)s->d_env, s->ctx->stream); rptx_free_async((void*)s->d_cube_idx, s->ctx->stream); s->d_cube_idx = nullptr;
+    rptx_free_async(s->d_small_slots, s->ctx->stream); s->d_small_slots = nullptr; rptx_free_async(s->d_small_boxes, s->ctx->stream); s->d_small_boxes = nullptr;
     s->d_nodes = nullptr; s->d_instances = nullptr; s->d_tris = nullptr; s->d_tri_normals = nullptr;
     s->d_tri_orig = nullptr; s->d_materials = nullptr; s->d_lights = nullptr; s->d_raw = nullptr; s->d_env = nullptr;
     s->committed = false;
@@ -486,15 +486,15 @@ int rptx_scene_commit(rptx_scene* s) {
     CK(upload(&d_raw, raw_all, st));
     s->d_raw = d_raw;
     BvhNode* d_nodes = nullptr;
-    CK(cudaMalloc((void**)&d_nodes, sizeof(BvhNode) * node_total));
+    CK(rptx_alloc_async((void**)&d_nodes, sizeof(BvhNode) * node_total, st));
     CK(cudaMemsetAsync(d_nodes, 0, sizeof(BvhNode) * node_total, st));
     s->d_nodes = d_nodes;
     TriRec* d_tris = nullptr; TriNormals* d_tn = nullptr; uint32_t* d_orig = nullptr; TriF* d_trif = nullptr;
-    CK(cudaMalloc((void**)&d_trif, sizeof(TriF) * std::max<uint32_t>(tri_total, 1)));
+    CK(rptx_alloc_async((void**)&d_trif, sizeof(TriF) * std::max<uint32_t>(tri_total, 1), st));
     s->d_trif = d_trif;
-    CK(cudaMalloc((void**)&d_tris, sizeof(TriRec) * std::max<uint32_t>(tri_total, 1)));
-    CK(cudaMalloc((void**)&d_tn, sizeof(TriNormals) * std::max<uint32_t>(tri_total, 1)));
-    CK(cudaMalloc((void**)&d_orig, sizeof(uint32_t) * std::max<uint32_t>(tri_total, 1)));
+    CK(rptx_alloc_async((void**)&d_tris, sizeof(TriRec) * std::max<uint32_t>(tri_total, 1), st));
+    CK(rptx_alloc_async((void**)&d_tn, sizeof(TriNormals) * std::max<uint32_t>(tri_total, 1), st));
+    CK(rptx_alloc_async((void**)&d_orig, sizeof(uint32_t) * std::max<uint32_t>(tri_total, 1), st));
     s->d_tris = d_tris; s->d_tri_normals = d_tn; s->d_tri_orig = d_orig;
 
     for (auto& m : s->meshes) {
@@ -505,20 +505,20 @@ int rptx_scene_commit(rptx_scene* s) {
             ctx->launches++;
         }
         PrimBox* d_boxes = nullptr; uint32_t* d_perm = nullptr;
-        CK(cudaMalloc((void**)&d_boxes, sizeof(PrimBox) * n));
-        CK(cudaMalloc((void**)&d_perm, sizeof(uint32_t) * n));
+        CK(rptx_alloc_async((void**)&d_boxes, sizeof(PrimBox) * n, st));
+        CK(rptx_alloc_async((void**)&d_perm, sizeof(uint32_t) * n, st));
         k_tri_boxes<<<grid_for(n, 128), 128, 0, st>>>(d_raw + m.raw_base, n, d_boxes);
         ctx->launches++;
         double e_abs = 0.0;
         for (int k = 0; k < 3; k++) e_abs = std::fmax(e_abs, std::fmax(std::fabs(m.bmin[k]), std::fabs(m.bmax[k])));
         m.pad = f32_upf(std::fmax(e_abs, 1e-30) * (1.0 / 2097152.0));  // E * 2^-21
         const int rc = build_lbvh(d_boxes, n, m.pad, kLeafMax, m.bmin, m.bmax, d_nodes + m.node_base, d_perm, &m.root_ref, st, &ctx->launches);
-        if (rc != 0) { cudaFree(d_boxes); cudaFree(d_perm); return ctx_fail(ctx, std::string("BLAS build: ") + cudaGetErrorString((cudaError_t)rc)); }
+        if (rc != 0) { rptx_free_async(d_boxes, st); rptx_free_async(d_perm, st); return ctx_fail(ctx, std::string("BLAS build: ") + cudaGetErrorString((cudaError_t)rc)); }
         k_tri_prepare<<<grid_for(n, 128), 128, 0, st>>>(d_raw + m.raw_base, d_perm, n, d_tris + m.tri_base, d_trif + m.tri_base, d_tn + m.tri_base,
                                                          d_orig + m.tri_base);
         ctx->launches++;
         CK(cudaStreamSynchronize(st));
-        cudaFree(d_boxes); cudaFree(d_perm);
+        rptx_free_async(d_boxes, st); rptx_free_async(d_perm, st);
     }
     if (!s->meshes.empty()) {
         // light sampling reads face normals from the raw pool: pull the computed ones back
@@ -566,12 +566,12 @@ int rptx_scene_commit(rptx_scene* s) {
         }
         PrimBox* d_boxes = nullptr; uint32_t* d_perm = nullptr;
         CK(upload(&d_boxes, boxes, st));
-        CK(cudaMalloc((void**)&d_perm, sizeof(uint32_t) * boxes.size()));
+        CK(rptx_alloc_async((void**)&d_perm, sizeof(uint32_t) * boxes.size(), st));
         const int rc = build_lbvh(d_boxes, (uint32_t)boxes.size(), wpad, 1, wmn, wmx, d_nodes, d_perm, &s->tlas_root_ref, st, &ctx->launches);
-        if (rc != 0) { cudaFree(d_boxes); cudaFree(d_perm); return ctx_fail(ctx, std::string("TLAS build: ") + cudaGetErrorString((cudaError_t)rc)); }
+        if (rc != 0) { rptx_free_async(d_boxes, st); rptx_free_async(d_perm, st); return ctx_fail(ctx, std::string("TLAS build: ") + cudaGetErrorString((cudaError_t)rc)); }
         std::vector<uint32_t> perm(boxes.size());
         CK(cudaMemcpy(perm.data(), d_perm, sizeof(uint32_t) * perm.size(), cudaMemcpyDeviceToHost));
-        cudaFree(d_boxes); cudaFree(d_perm);
+        rptx_free_async(d_boxes, st); rptx_free_async(d_perm, st);
         for (uint32_t k : perm) { ordered.push_back(bounded[k]); wboxes_ordered.push_back(wboxes[k]); }
         for (int k = 0; k < 3; k++) { s->wmin[k] = wmn[k] - 2.0 * (double)wpad; s->wmax[k] = wmx[k] + 2.0 * (double)wpad; }
     }
@@ -674,14 +674,18 @@ static void film_carve(rptx_film* f, Carver& c) {
     const bool gather_only = f->mode != kFilmWavefront;
     PathPool& p = f->pool;
     const size_t ns = p.n_slots;
-    std::vector<double**> dptrs = {&p.ox, &p.oy, &p.oz, &p.dx, &p.dy, &p.dz, &p.ht, &p.hnx, &p.hny, &p.hnz, &p.dirx, &p.diry, &p.dirz,
-                                   &p.fx, &p.fy, &p.fz, &p.pdf, &p.abscos, &p.bx, &p.by, &p.bz, &p.lx, &p.ly, &p.lz, &p.ax, &p.ay, &p.az};
+    std::vector<double**> dptrs = {&p.ox, &p.oy, &p.oz, &p.dx, &p.dy, &p.dz, &p.ht, &p.hnx, &p.hny, &p.hnz, &p.ax, &p.ay, &p.az};
     if (gather_only) dptrs = {&p.ax, &p.ay, &p.az};
     for (double** d : dptrs) c.take(d, ns);
     if (!gather_only) {
         std::vector<double**> sptrs = {&p.sdx, &p.sdy, &p.sdz, &p.sdist, &p.scx, &p.scy, &p.scz};
         for (double** d : sptrs) c.take(d, ns * std::max<uint32_t>(p.n_shadow, 1));
-        c.take(&p.stack, ns * 8 * std::max<uint32_t>(p.stack_depth, 1));
+        if (p.record_mode) {  // surface mode: the vertex lives in its 64-byte level record
+            c.take(&p.stack, ns * p.rec_stride * std::max<uint32_t>(p.stack_depth, 1));
+        } else {              // medium mode: forward accumulation
+            std::vector<double**> mptrs = {&p.dirx, &p.diry, &p.dirz, &p.fx, &p.fy, &p.fz, &p.bx, &p.by, &p.bz, &p.lx, &p.ly, &p.lz};
+            for (double** d : mptrs) c.take(d, ns);
+        }
         c.take(&p.hobj, ns); c.take(&p.rng, ns); c.take(&p.sample_j, ns); c.take(&p.depth, ns); c.take(&p.flags, ns);
         c.take(&f->q.cur, ns); c.take(&f->q.next, ns); c.take(&f->q.keep, ns);
         c.take(&f->d_select_tmp, f->select_tmp_bytes);
@@ -691,6 +695,7 @@ static void film_carve(rptx_film* f, Carver& c) {
     const size_t n3 = (size_t)p.n_pixels * 3;
     c.take(&f->d_batch_sum, n3);
     c.take(&f->d_film_sum, n3);
+    c.take(&f->d_scratch, n3);  // read-back staging (rgb8 image, mean): no cudaMalloc / cudaFree on the read-back calls
     // room for the first batch means (Buffer keeps every batch for variance()); later ones come from the stream-ordered pool
     f->n_mean_slots = std::min<uint32_t>(std::max<uint32_t>(f->params.num_samples, 1), 16);
     c.take(&f->d_mean_slots, n3 * f->n_mean_slots);
@@ -769,6 +774,8 @@ static int film_begin(rptx_ctx* ctx, rptx_scene* scene, const rptx_camera* camer
     p.tiled = f->mode == kFilmWavefront && params->width % 8 == 0 && params->height % 4 == 0 && !std::getenv("RPTX_LINEAR_PIXELS");
     p.n_shadow = scene->n_shadow_lights;
     p.stack_depth = scene->medium_kind == RPTX_MEDIUM_NONE ? params->max_bounces + 1 : 1;
+    p.record_mode = scene->medium_kind == RPTX_MEDIUM_NONE;
+    p.rec_stride = p.stack_depth == 1 ? 4 : 8;
     // Paths in flight.  Wavefront: as many as a quarter of the free HBM holds, up to 32 M (~0.7 KB per slot on
     // the Cornell box).  The pool size is not about occupancy (2 M paths already fill the GPU) but about
     // coherence: a slot that regenerates mid-batch puts depth-0 and depth-5 vertices into the same warps, so
@@ -777,7 +784,7 @@ static int film_begin(rptx_ctx* ctx, rptx_scene* scene, const rptx_camera* camer
     // Fused / photon gather: ~0.5 M threads, each walking its samples.
     uint64_t target = 1ull << 19;
     if (f->mode == kFilmWavefront) {
-        const uint64_t slot_bytes = 248 + 56ull * std::max<uint32_t>(p.n_shadow, 1) + 64ull * std::max<uint32_t>(p.stack_depth, 1);
+        const uint64_t slot_bytes = 137 + 56ull * std::max<uint32_t>(p.n_shadow, 1) + (p.record_mode ? 64ull * std::max<uint32_t>(p.stack_depth, 1) : 96ull);
         size_t free_b = 0, total_b = 0;
         CK(cudaMemGetInfo(&free_b, &total_b));
         target = 1ull << 25;
@@ -977,14 +984,13 @@ int rptx_film_image_rgb8(rptx_film* f, uint8_t* out) {
     if (f->batches.empty()) return ctx_fail(ctx, "Pixel found with no samples");  // src/buffer.rs:89
     CK(cudaSetDevice(ctx->device));
     const uint32_t w = f->params.width, h = f->params.height;
-    uint8_t* d_out = nullptr;
-    CK(cudaMalloc((void**)&d_out, (size_t)w * h * 3));
+    uint8_t* d_out = reinterpret_cast<uint8_t*>(f->d_scratch);
     dim3 blk(16, 16), grd((w + 15) / 16, (h + 15) / 16);
     k_image<<<grd, blk, 0, ctx->stream>>>(f->d_film_sum, w, h, f->params.filter_radius, (uint32_t)f->batches.size(), d_out);
     ctx->launches++;
     cudaError_t e = cudaMemcpyAsync(out, d_out, (size_t)w * h * 3, cudaMemcpyDeviceToHost, ctx->stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
-    cudaFree(d_out);
+    
     if (e != cudaSuccess) return ctx_fail(ctx, cudaGetErrorString(e));
     return 0;
 }
@@ -996,18 +1002,18 @@ int rptx_film_variance(rptx_film* f, double* out) {
     CK(cudaSetDevice(ctx->device));
     const uint32_t nb = (uint32_t)f->batches.size();
     if (nb == 0) { *out = NAN; return 0; }
-    if (f->d_batch_ptrs) { cudaFree(f->d_batch_ptrs); f->d_batch_ptrs = nullptr; }
-    CK(cudaMalloc((void**)&f->d_batch_ptrs, sizeof(double*) * nb));
+    if (f->d_batch_ptrs) { rptx_free_async(f->d_batch_ptrs, ctx->stream); f->d_batch_ptrs = nullptr; }
+    CK(rptx_alloc_async((void**)&f->d_batch_ptrs, sizeof(double*) * nb, ctx->stream));
     CK(copy_h2d(f->d_batch_ptrs, f->batches.data(), sizeof(double*) * nb, ctx->stream));
     double* d_acc = nullptr;
-    CK(cudaMalloc((void**)&d_acc, sizeof(double)));
+    CK(rptx_alloc_async((void**)&d_acc, sizeof(double), ctx->stream));
     CK(cudaMemsetAsync(d_acc, 0, sizeof(double), ctx->stream));
     k_variance<<<ctx->sm_count * 4, 256, 0, ctx->stream>>>(f->d_batch_ptrs, nb, f->d_film_sum, f->pool.n_pixels, d_acc);
     ctx->launches++;
     double acc = 0.0;
     cudaError_t e = cudaMemcpyAsync(&acc, d_acc, sizeof(double), cudaMemcpyDeviceToHost, ctx->stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
-    cudaFree(d_acc);
+    rptx_free_async(d_acc, ctx->stream);
     if (e != cudaSuccess) return ctx_fail(ctx, cudaGetErrorString(e));
     *out = acc / (double)f->pool.n_pixels;
     return 0;
@@ -1020,13 +1026,12 @@ int rptx_film_mean(rptx_film* f, double* out) {
     if (f->batches.empty()) return ctx_fail(ctx, "no batches rendered");
     CK(cudaSetDevice(ctx->device));
     const size_t n3 = (size_t)f->pool.n_pixels * 3;
-    double* d_out = nullptr;
-    CK(cudaMalloc((void**)&d_out, sizeof(double) * n3));
+    double* d_out = f->d_scratch;
     k_film_mean<<<grid_for(n3, 256), 256, 0, ctx->stream>>>(f->d_film_sum, n3, (double)f->batches.size(), d_out);
     ctx->launches++;
     cudaError_t e = cudaMemcpyAsync(out, d_out, sizeof(double) * n3, cudaMemcpyDeviceToHost, ctx->stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
-    cudaFree(d_out);
+    
     if (e != cudaSuccess) return ctx_fail(ctx, cudaGetErrorString(e));
     return 0;
 }
