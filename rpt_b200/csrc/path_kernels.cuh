@@ -176,7 +176,11 @@ __global__ void __launch_bounds__(kShadeBlock, 2) k_shade(const __grid_constant_
                                                           MediumDev md) {
     __shared__ uint32_t s_slot[kShadeBlock];
     __shared__ uint32_t s_cnt[3][kShadeBlock / 32];
+    __shared__ double s_dsamp[MEDIUM ? kShadeBlock : 1];      // the free-flight draw travels with the entry
+    __shared__ uint64_t s_rng[MEDIUM ? kShadeBlock : 1];
     uint32_t slot;
+    double dsamp = 0.0;
+    Rng rng;
     {
         const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
         const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
@@ -186,10 +190,9 @@ __global__ void __launch_bounds__(kShadeBlock, 2) k_shade(const __grid_constant_
             const bool hit0 = p.hobj[slot0] != kNoHit;
             cls = hit0 ? 1u : 2u;
             if (MEDIUM) {
-                Rng r0;
-                r0.state = p.rng[slot0];
-                const double d0 = medium_sample_d(md, r0);
-                if (d0 < (hit0 ? p.ht[slot0] : kBackgroundDist)) cls = 0;
+                rng.state = p.rng[slot0];
+                dsamp = medium_sample_d(md, rng);
+                if (dsamp < (hit0 ? p.ht[slot0] : kBackgroundDist)) cls = 0;
             }
         }
         uint32_t rank = 0;
@@ -208,25 +211,26 @@ __global__ void __launch_bounds__(kShadeBlock, 2) k_shade(const __grid_constant_
                 total += n;
                 if (c < cls || (c == cls && w < warp)) before += n;
             }
-        if (cls < 3) s_slot[before + rank] = slot0;
+        if (cls < 3) {
+            s_slot[before + rank] = slot0;
+            if (MEDIUM) { s_dsamp[before + rank] = dsamp; s_rng[before + rank] = rng.state; }
+        }
         __syncthreads();
         if (threadIdx.x >= total) return;
         slot = s_slot[threadIdx.x];
+        if (MEDIUM) { dsamp = s_dsamp[threadIdx.x]; rng.state = s_rng[threadIdx.x]; }
     }
     const d3 o = mk3(p.ox[slot], p.oy[slot], p.oz[slot]);
     const d3 d = mk3(p.dx[slot], p.dy[slot], p.dz[slot]);
     const double t = p.ht[slot];
     const uint32_t obj = p.hobj[slot];
     const uint32_t depth = p.depth[slot];
-    Rng rng;
-    rng.state = p.rng[slot];
+    if (!MEDIUM) rng.state = p.rng[slot];
     uint32_t flags = 0;
     d3 direct = mk3(0, 0, 0);
     d3 rec_f = mk3(0, 0, 0);
     double rec_pdf = 0.0, rec_ac = 0.0;
 
-    double dsamp = 0.0;
-    if (MEDIUM) dsamp = medium_sample_d(md, rng);
     const bool hit = obj != kNoHit;
     const double max_dist = hit ? t : kBackgroundDist;
 
