@@ -13,6 +13,7 @@
 
 #include "../../include/rptx.h"
 #include "bvh_build.cuh"
+#include "bvh_sah.hpp"
 #include "host_types.hpp"
 #include "path_kernels.cuh"
 
@@ -467,7 +468,8 @@ int rptx_scene_commit(rptx_scene* s) {
     free_scene_device(s);
     cudaStream_t st = ctx->stream;
 
-    // 1. meshes: upload raw triangles, build one BLAS per mesh on the device
+    // 1. meshes: upload raw triangles, build one BLAS per mesh (host SAH for small meshes, GPU LBVH otherwise)
+    const bool lbvh_only = std::getenv("RPTX_LBVH_ONLY") != nullptr;  // developer knob: the GPU LBVH for every tree
     std::vector<RawTri> raw_all;
     uint32_t tri_total = 0, node_total = 0;
     for (auto& m : s->meshes) {
@@ -505,15 +507,32 @@ int rptx_scene_commit(rptx_scene* s) {
             ctx->launches++;
         }
         PrimBox* d_boxes = nullptr; uint32_t* d_perm = nullptr;
-        CK(rptx_alloc_async((void**)&d_boxes, sizeof(PrimBox) * n, st));
-        CK(rptx_alloc_async((void**)&d_perm, sizeof(uint32_t) * n, st));
-        k_tri_boxes<<<grid_for(n, 128), 128, 0, st>>>(d_raw + m.raw_base, n, d_boxes);
-        ctx->launches++;
         double e_abs = 0.0;
         for (int k = 0; k < 3; k++) e_abs = std::fmax(e_abs, std::fmax(std::fabs(m.bmin[k]), std::fabs(m.bmax[k])));
         m.pad = f32_upf(std::fmax(e_abs, 1e-30) * (1.0 / 2097152.0));  // E * 2^-21
-        const int rc = build_lbvh(d_boxes, n, m.pad, kLeafMax, m.bmin, m.bmax, d_nodes + m.node_base, d_perm, &m.root_ref, st, &ctx->launches);
-        if (rc != 0) { rptx_free_async(d_boxes, st); rptx_free_async(d_perm, st); return ctx_fail(ctx, std::string("BLAS build: ") + cudaGetErrorString((cudaError_t)rc)); }
+        if (n <= rptx_host::kSahMaxPrims && !lbvh_only) {
+            // small mesh: binned SAH on the host (bvh_sah.hpp), same node format, same padding
+            std::vector<PrimBox> hb(n);
+            for (uint32_t i = 0; i < n; i++)
+                for (int k = 0; k < 3; k++) {
+                    const double* v = m.tris[i].v;
+                    hb[i].mn[k] = f32_down(std::fmin(std::fmin(v[k], v[3 + k]), v[6 + k]));
+                    hb[i].mx[k] = f32_upf(std::fmax(std::fmax(v[k], v[3 + k]), v[6 + k]));
+                }
+            std::vector<BvhNode> hn;
+            std::vector<uint32_t> hp;
+            rptx_host::build_sah_host(hb, m.pad, kLeafMax, hn, hp, &m.root_ref);
+            if (!hn.empty()) CK(copy_h2d(d_nodes + m.node_base, hn.data(), sizeof(BvhNode) * hn.size(), st));
+            CK(upload(&d_perm, hp, st));
+            CK(cudaStreamSynchronize(st));  // hn / hp go out of scope
+        } else {
+            CK(rptx_alloc_async((void**)&d_boxes, sizeof(PrimBox) * n, st));
+            CK(rptx_alloc_async((void**)&d_perm, sizeof(uint32_t) * n, st));
+            k_tri_boxes<<<grid_for(n, 128), 128, 0, st>>>(d_raw + m.raw_base, n, d_boxes);
+            ctx->launches++;
+            const int rc = build_lbvh(d_boxes, n, m.pad, kLeafMax, m.bmin, m.bmax, d_nodes + m.node_base, d_perm, &m.root_ref, st, &ctx->launches);
+            if (rc != 0) { rptx_free_async(d_boxes, st); rptx_free_async(d_perm, st); return ctx_fail(ctx, std::string("BLAS build: ") + cudaGetErrorString((cudaError_t)rc)); }
+        }
         k_tri_prepare<<<grid_for(n, 128), 128, 0, st>>>(d_raw + m.raw_base, d_perm, n, d_tris + m.tri_base, d_trif + m.tri_base, d_tn + m.tri_base,
                                                          d_orig + m.tri_base);
         ctx->launches++;
@@ -564,14 +583,22 @@ int rptx_scene_commit(rptx_scene* s) {
             for (int k = 0; k < 3; k++) { pb.mn[k] = f32_down(b[k]); pb.mx[k] = f32_upf(b[3 + k]); }
             boxes.push_back(pb);
         }
-        PrimBox* d_boxes = nullptr; uint32_t* d_perm = nullptr;
-        CK(upload(&d_boxes, boxes, st));
-        CK(rptx_alloc_async((void**)&d_perm, sizeof(uint32_t) * boxes.size(), st));
-        const int rc = build_lbvh(d_boxes, (uint32_t)boxes.size(), wpad, 1, wmn, wmx, d_nodes, d_perm, &s->tlas_root_ref, st, &ctx->launches);
-        if (rc != 0) { rptx_free_async(d_boxes, st); rptx_free_async(d_perm, st); return ctx_fail(ctx, std::string("TLAS build: ") + cudaGetErrorString((cudaError_t)rc)); }
         std::vector<uint32_t> perm(boxes.size());
-        CK(cudaMemcpy(perm.data(), d_perm, sizeof(uint32_t) * perm.size(), cudaMemcpyDeviceToHost));
-        rptx_free_async(d_boxes, st); rptx_free_async(d_perm, st);
+        if (boxes.size() <= rptx_host::kSahMaxPrims && !lbvh_only) {
+            std::vector<BvhNode> hn;
+            rptx_host::build_sah_host(boxes, wpad, 1, hn, perm, &s->tlas_root_ref);
+            if (!hn.empty()) CK(copy_h2d(d_nodes, hn.data(), sizeof(BvhNode) * hn.size(), st));
+            CK(cudaStreamSynchronize(st));
+        } else {
+            PrimBox* d_boxes = nullptr; uint32_t* d_perm = nullptr;
+            CK(upload(&d_boxes, boxes, st));
+            CK(rptx_alloc_async((void**)&d_perm, sizeof(uint32_t) * boxes.size(), st));
+            const int rc = build_lbvh(d_boxes, (uint32_t)boxes.size(), wpad, 1, wmn, wmx, d_nodes, d_perm, &s->tlas_root_ref, st, &ctx->launches);
+            if (rc != 0) { rptx_free_async(d_boxes, st); rptx_free_async(d_perm, st); return ctx_fail(ctx, std::string("TLAS build: ") + cudaGetErrorString((cudaError_t)rc)); }
+            CK(cudaMemcpyAsync(perm.data(), d_perm, sizeof(uint32_t) * perm.size(), cudaMemcpyDeviceToHost, st));
+            CK(cudaStreamSynchronize(st));
+            rptx_free_async(d_boxes, st); rptx_free_async(d_perm, st);
+        }
         for (uint32_t k : perm) { ordered.push_back(bounded[k]); wboxes_ordered.push_back(wboxes[k]); }
         for (int k = 0; k < 3; k++) { s->wmin[k] = wmn[k] - 2.0 * (double)wpad; s->wmax[k] = wmx[k] + 2.0 * (double)wpad; }
     }

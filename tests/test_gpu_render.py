@@ -219,3 +219,25 @@ def test_film_slab_is_recycled_and_pool_size_does_not_matter(monkeypatch):
     monkeypatch.delenv("RPTX_POOL_LOG2", raising=False)
     assert np.array_equal(means[0], means[2])
     assert np.allclose(means[0], means[1], rtol=1e-12, atol=1e-300)  # lane sums are added in a different order
+
+
+def test_sah_trees_equal_lbvh_trees(monkeypatch):
+    """Small meshes and the instance level get a host-built SAH tree, larger ones the GPU LBVH (RPTX_LBVH_ONLY forces
+    it everywhere).  The accelerator only orders the search: same hits, same batch, bit for bit."""
+    monkeypatch.setenv("RPTX_PATH_MODE", "wavefront")
+    for name in ("teapot", "fractal_teapots"):
+        scene, cam, d = getattr(scenes, name)()
+        means = []
+        for lbvh in (False, True):
+            if lbvh:
+                monkeypatch.setenv("RPTX_LBVH_ONLY", "1")
+            else:
+                monkeypatch.delenv("RPTX_LBVH_ONLY", raising=False)
+            r = scenes.make_renderer(scene, cam, d, width=96, height=64, num_samples=2, seed=5, max_bounces=2)
+            f = r.begin()
+            f.sample(2)
+            means.append(f.mean())
+            f.close()
+            r.device_scene().close()
+        monkeypatch.delenv("RPTX_LBVH_ONLY", raising=False)
+        assert np.array_equal(means[0], means[1]), name
