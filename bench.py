@@ -36,7 +36,7 @@ METRIC = "Mpath-samples/s"
 EXTEND_BYTES_PER_RAY = 4 + 48 + 8 + 4 + 24
 # dram__bytes_read.sum + dram__bytes_write.sum of one k_extend launch / its rays, from the committed
 # `ncu --set full` capture of the same command (profiles/r1_v2_summary.md); None where not captured
-EXTEND_DRAM_BYTES_PER_RAY = {"fractal_teapots": 88.2, "cornell": 148.7}
+EXTEND_DRAM_BYTES_PER_RAY = {"fractal_teapots": 88.1, "cornell": 148.7}
 
 
 _OVERRIDES = {}
