@@ -17,6 +17,9 @@ namespace rptx_host {
 
 constexpr uint32_t kSahMaxPrims = 1u << 16;
 constexpr int kSahBins = 16;
+// SAH splits down to this depth, halving below: depth <= 20 + 16 per tree, <= 74 pending entries for TLAS + sentinel + BLAS
+// (trace.cuh kStackSize = 80).  Real meshes stay far below (teapot: 13).
+constexpr uint32_t kSahFreeDepth = 20;
 
 struct SahBox {
     float mn[3], mx[3];
@@ -118,7 +121,7 @@ inline void build_sah_host(const std::vector<rptx::PrimBox>& boxes, float pad, i
         } else {
             nl = t.count / 2;  // all centroids coincide: any split is as good
         }
-        if (nl == 0 || nl == t.count || t.depth >= 40) nl = t.count / 2;  // bounded depth: halving from here on
+        if (nl == 0 || nl == t.count || t.depth >= kSahFreeDepth) nl = t.count / 2;  // bounded depth: halving from here on
         const uint32_t nr = t.count - nl;
         const SahBox lb = range_box(t.first, nl), rb = range_box(t.first + nl, nr);
         int refs[2];

@@ -29,7 +29,7 @@ struct RayF {
 };
 
 constexpr float kSlabSlack = 1e-6f;
-constexpr int kStackSize = 64;
+constexpr int kStackSize = 80;  // >= worst-case pending entries of two SAH levels (bvh_sah.hpp)
 
 RPTX_D float f32_up(double x) { return __double2float_ru(x); }
 

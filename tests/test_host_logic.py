@@ -122,3 +122,17 @@ def test_benchmark_scenes_have_the_reference_inventory():
     assert len(low.meshes) == 1 and (d["width"], d["height"], d["num_samples"]) == (1920, 1080, 256)
     s, _, d = scenes.lampshade("pathtrace")
     assert len(s.objects) == 12 and len(s.media) == 1 and (d["width"], d["height"], d["num_samples"]) == (1920, 1080, 1024)
+
+
+def test_sah_builder_invariants(tmp_path):
+    """rpt_b200/csrc/bvh_sah.hpp on the CPU: permutation, containment, leaf size, bounded depth (tests/native/sah_check.cu)."""
+    import shutil
+    import subprocess
+
+    nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
+    exe = tmp_path / "sah_check"
+    src = os.path.join(os.path.dirname(os.path.abspath(__file__)), "native", "sah_check.cu")
+    subprocess.check_call([nvcc, "-std=c++17", "-O2", "-Wno-deprecated-gpu-targets", "-x", "cu", "-o", str(exe), src])
+    out = subprocess.run([str(exe)], capture_output=True, text=True)
+    assert out.returncode == 0, out.stdout[-2000:]
+    assert "FAIL" not in out.stdout and out.stdout.count("ok ") >= 18
