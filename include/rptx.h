@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define RPTX_ABI_VERSION 1
+#define RPTX_ABI_VERSION 2
 
 /* ---- shapes: src/shape.rs:19-26 (trait Shape), :102-109 (Transformed<T>) ---- */
 enum {
@@ -34,7 +34,8 @@ enum {
     RPTX_SHAPE_PLANE  = 1, /* x.normal = value, src/shape/plane.rs:7-13 */
     RPTX_SHAPE_CUBE   = 2, /* unit cube [-.5,.5]^3, src/shape/cube.rs:9 */
     RPTX_SHAPE_MESH   = 3, /* Mesh = KdTree<Triangle>, src/shape/mesh.rs:103 */
-    RPTX_SHAPE_GROUP  = 4  /* KdTree<Box<dyn Bounded>> of transformed children, src/kdtree.rs:103 */
+    RPTX_SHAPE_GROUP  = 4, /* KdTree<Box<dyn Bounded>> of transformed children, src/kdtree.rs:103 */
+    RPTX_SHAPE_MONOMIAL = 5 /* y = height * (x^2 + z^2)^2, x^2 + z^2 <= 1, src/shape/monomial_surface.rs:8-19 */
 };
 
 typedef struct rptx_shape_desc {
@@ -45,7 +46,9 @@ typedef struct rptx_shape_desc {
     uint32_t n_children;        /* GROUP */
     double   plane_normal[3];   /* PLANE */
     double   plane_value;       /* PLANE */
-    const struct rptx_shape_desc* children; /* GROUP: n_children leaf shapes (SPHERE/CUBE/MESH) */
+    double   mono_height;       /* MONOMIAL: MonomialSurface::height */
+    double   mono_exp;          /* MONOMIAL: MonomialSurface::exp (must be 4: the reference's intersect hard-codes it) */
+    const struct rptx_shape_desc* children; /* GROUP: n_children leaf shapes (SPHERE/CUBE/MESH/MONOMIAL) */
 } rptx_shape_desc;
 
 /* ---- materials: src/material.rs:8-23 ---- */

@@ -58,6 +58,7 @@ std::shared_ptr<const Shape> build_shape(OScene* s, const rptx_shape_desc* d, bo
         case RPTX_SHAPE_PLANE:
             base = std::make_shared<Plane>(Vec3(d->plane_normal[0], d->plane_normal[1], d->plane_normal[2]), d->plane_value);
             break;
+        case RPTX_SHAPE_MONOMIAL: base = std::make_shared<MonomialSurface>(d->mono_height, d->mono_exp); break;
         case RPTX_SHAPE_MESH:
             if (d->mesh_id >= s->meshes.size()) { s->err = "bad mesh id"; return nullptr; }
             base = s->meshes[d->mesh_id];

@@ -51,6 +51,18 @@ struct Rng {
             if (a * a + b * b <= 1.0) { *x = a; *y = b; return; }
         }
     }
+    // rand_distr::UnitCircle (0.4.0): x1, x2 uniform in (-1,1) until x1^2 + x2^2 < 1, then
+    // ((x1^2 - x2^2) / sum, 2 x1 x2 / sum)
+    void unit_circle(double* x, double* y) {
+        double x1, x2, sum;
+        do {
+            x1 = gen_range(-1.0, 1.0);
+            x2 = gen_range(-1.0, 1.0);
+            sum = x1 * x1 + x2 * x2;
+        } while (sum >= 1.0);
+        *x = (x1 * x1 - x2 * x2) / sum;
+        *y = 2.0 * x1 * x2 / sum;
+    }
 };
 
 }  // namespace orc

@@ -1,5 +1,5 @@
 // ORACLE — TEST INFRASTRUCTURE ONLY (see vec.hpp header).
-// Restates src/shape.rs, src/shape/{sphere,plane,cube,mesh}.rs and src/kdtree.rs of the
+// Restates src/shape.rs, src/shape/{sphere,plane,cube,mesh,monomial_surface}.rs and src/kdtree.rs of the
 // reference.  Additions the reference lacks: HitRecord carries the triangle index
 // (prim_id) and the group-child index (inst_id) of the winning primitive so that ray
 // sets can be compared id-for-id.
@@ -125,6 +125,82 @@ struct Plane : Shape {
     void sample(const Vec3&, Rng&, Vec3*, Vec3*, double*) const override { assert(!"unimplemented"); }
     bool bounded() const override { return false; }
     BoundingBox bounding_box() const override { return {}; }
+};
+
+// src/shape/monomial_surface.rs:8-190 — y = height * (x^2 + z^2)^2 over the unit disc.  powi(2)/powi(3) are
+// restated as the multiplication chains LLVM emits for constant integer powers.
+struct MonomialSurface : Shape {
+    double height, exp;
+    MonomialSurface(double h, double e) : height(h), exp(e) {}
+    BoundingBox bounding_box() const override { return {Vec3(-1.0, 0.0, -1.0), Vec3(1.0, height, 1.0)}; }
+    bool intersect(const Ray& ray, double t_min, HitRecord& rec) const override {
+        double b_min, b_max;
+        bounding_box().intersect(ray, &b_min, &b_max);
+        if (std::fmax(b_min, t_min) > std::fmin(b_max, rec.time)) return false;  // :23-26
+        auto dist = [&](double t) {
+            const double x = ray.origin.x + t * ray.dir.x;
+            const double y = ray.origin.y + t * ray.dir.y;
+            const double z = ray.origin.z + t * ray.dir.z;
+            const double s = x * x + z * z;
+            return y - height * (s * s);
+        };
+        const double coef0 = ray.origin.x * ray.origin.x + ray.origin.z * ray.origin.z;
+        const double coef1 = 2. * (ray.origin.x * ray.dir.x + ray.origin.z * ray.dir.z);
+        const double coef2 = ray.dir.x * ray.dir.x + ray.dir.z * ray.dir.z;
+        auto deriv = [&](double t) {
+            const double dy = 2. * coef0 * coef1 + 2. * t * (coef1 * coef1 + 2. * coef0 * coef2) +
+                              3. * (t * t) * 2. * coef1 * coef2 + 4. * (t * t * t) * coef2 * coef2;
+            return ray.dir.y - height * dy;
+        };
+        auto deriv2 = [&](double t) {
+            const double dy = 2. * (coef1 * coef1 + 2. * coef0 * coef2) + 3. * 2. * t * 2. * coef1 * coef2 +
+                              4. * 3. * (t * t) * coef2 * coef2;
+            return -height * dy;
+        };
+        double t_max;
+        const bool maximize = dist(t_min) < 0.0;
+        if (maximize) {  // Newton steps toward the maximum of dist, :51-67
+            double cur_x = (b_min + b_max) / 2.;
+            for (int i = 0; i < 10; i++) {
+                const double f = dist(cur_x);
+                if (f > 0.) break;
+                const double der = deriv(cur_x);
+                const double der2 = deriv2(cur_x);
+                cur_x -= der / der2;
+            }
+            t_max = cur_x;
+            if (t_max < t_min) return false;
+        } else {
+            t_max = 10000.;
+        }
+        if ((dist(t_min) < 0.0) == (dist(t_max) < 0.0)) return false;
+        double l = t_min, r = t_max;
+        for (int i = 0; i < 60; i++) {  // bisection, :75-82
+            const double m = (l + r) / 2.0;
+            if ((dist(m) >= 0.0) == maximize) r = m;
+            else l = m;
+        }
+        if (r > rec.time) return false;
+        const Vec3 pos = ray.at(r);
+        if (pos.x * pos.x + pos.z * pos.z > 1.0) return false;
+        rec.time = r;
+        rec.normal = normalize(Vec3(height * 4.0 * pos.x * (pos.x * pos.x + pos.z * pos.z), -1.0,
+                                    height * 4.0 * pos.z * (pos.x * pos.x + pos.z * pos.z)));
+        if (dot(rec.normal, ray.dir) > 0.0) rec.normal = -rec.normal;
+        rec.prim_id = 0;
+        return true;
+    }
+    // :109-124; rand_distr::UnitCircle = von Neumann's rejection method, gen::<bool>() restated as U < 0.5
+    void sample(const Vec3&, Rng& rng, Vec3* v, Vec3* n, double* p) const override {
+        double x, z;
+        rng.unit_circle(&x, &z);
+        const Vec3 pos(x, height * std::pow(x * x + z * z, exp / 2.), z);
+        Vec3 normal = normalize(Vec3(height * 4. * pos.x * (pos.x * pos.x + pos.z * pos.z), -1.,
+                                     height * 4. * pos.z * (pos.x * pos.x + pos.z * pos.z)));
+        const double AREA = 6.3406654362;
+        if (rng.gen() < 0.5) normal = -normal;
+        *v = pos; *n = normal; *p = 1. / (2. * AREA);
+    }
 };
 
 // src/shape/cube.rs:9-90

@@ -10,7 +10,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 # RPTX_LIBRARY: developer knob for A/B builds of the same ABI (tools/); the product is librptx.so next to this file
 LIB_PATH = os.environ.get("RPTX_LIBRARY") or os.path.join(_HERE, "librptx.so")
 
-SHAPE_SPHERE, SHAPE_PLANE, SHAPE_CUBE, SHAPE_MESH, SHAPE_GROUP = range(5)
+SHAPE_SPHERE, SHAPE_PLANE, SHAPE_CUBE, SHAPE_MESH, SHAPE_GROUP, SHAPE_MONOMIAL = range(6)
 MAT_LAMBERTIAN, MAT_PHONG, MAT_MIRROR, MAT_TRANSMISSIVE = range(4)
 LIGHT_POINT, LIGHT_AMBIENT, LIGHT_DIRECTIONAL, LIGHT_OBJECT = range(4)
 MEDIUM_NONE, MEDIUM_HOMOGENEOUS_ISOTROPIC, MEDIUM_COLORED_GLOWING_FOG = range(3)
@@ -29,6 +29,8 @@ ShapeDesc._fields_ = [
     ("n_children", C.c_uint32),
     ("plane_normal", C.c_double * 3),
     ("plane_value", C.c_double),
+    ("mono_height", C.c_double),
+    ("mono_exp", C.c_double),
     ("children", C.POINTER(ShapeDesc)),
 ]
 
@@ -185,6 +187,6 @@ def load():
                 "or `make -C rpt_b200/csrc`. rpt_b200 has no CPU fallback."
             )
         _lib = bind(C.CDLL(LIB_PATH))
-        if _lib.rptx_abi_version() != 1:
+        if _lib.rptx_abi_version() != 2:
             raise ImportError("librptx.so ABI version mismatch")
     return _lib

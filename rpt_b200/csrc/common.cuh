@@ -125,14 +125,14 @@ struct RawTri {  // upload format
     double v[9], n[9];
 };
 
-enum InstKind : int { kSphere = 0, kPlane = 1, kCube = 2, kMesh = 3 };
+enum InstKind : int { kSphere = 0, kPlane = 1, kCube = 2, kMesh = 3, kMonomial = 4 };
 
 struct __align__(16) Instance {
     Affine inv;        // inverse transform (world -> local), src/shape.rs:130
     Mat3 nrm;          // M^-T, src/shape.rs:133
     double lmin[3], lmax[3];  // local f64 bounds of the mesh (padded) for the entry clip
     double bmin[3], bmax[3];  // exact local bounds (KdTree::bounds), see mesh_bounds_nan_reject
-    double plane_n[3], plane_v;
+    double plane_n[3], plane_v;  // PLANE; MONOMIAL: plane_v = height, plane_n[0] = exp
     int kind;
     int has_transform;
     uint32_t object_id, inst_id;
@@ -153,7 +153,7 @@ struct Material {
 
 struct Light {
     int kind;
-    int shape_kind;      // OBJECT lights: kSphere/kCube/kMesh
+    int shape_kind;      // OBJECT lights: kSphere/kCube/kMesh/kMonomial (vec[0] = height, vec[1] = exp)
     int has_transform;
     uint32_t tri_base, ntri;  // OBJECT mesh lights: ORIGINAL-order raw triangles (light pool)
     int pad;

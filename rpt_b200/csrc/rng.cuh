@@ -47,6 +47,17 @@ struct Rng {
             if (a * a + b * b <= 1.0) { *x = a; *y = b; return; }
         }
     }
+    // rand_distr::UnitCircle
+    RPTX_HD void unit_circle(double* x, double* y) {
+        double x1, x2, sum;
+        do {
+            x1 = gen_range(-1.0, 1.0);
+            x2 = gen_range(-1.0, 1.0);
+            sum = x1 * x1 + x2 * x2;
+        } while (sum >= 1.0);
+        *x = (x1 * x1 - x2 * x2) / sum;
+        *y = 2.0 * x1 * x2 / sum;
+    }
 };
 
 }  // namespace rptx

@@ -174,6 +174,10 @@ Material to_material(const rptx_material& m) {
 bool local_bounds(const rptx_scene* s, const rptx_shape_desc& d, double mn[3], double mx[3]) {
     if (d.kind == RPTX_SHAPE_SPHERE) { for (int k = 0; k < 3; k++) { mn[k] = -1; mx[k] = 1; } return true; }
     if (d.kind == RPTX_SHAPE_CUBE) { for (int k = 0; k < 3; k++) { mn[k] = -0.5; mx[k] = 0.5; } return true; }
+    if (d.kind == RPTX_SHAPE_MONOMIAL) {  // src/shape/monomial_surface.rs:175-181
+        mn[0] = -1; mn[1] = 0; mn[2] = -1; mx[0] = 1; mx[1] = d.mono_height; mx[2] = 1;
+        return true;
+    }
     if (d.kind == RPTX_SHAPE_MESH) {
         const HostMesh& m = s->meshes[d.mesh_id];
         for (int k = 0; k < 3; k++) { mn[k] = m.bmin[k]; mx[k] = m.bmax[k]; }
@@ -201,6 +205,12 @@ int lower_leaf(rptx_scene* s, const rptx_shape_desc& d, uint32_t object_id, uint
     switch (d.kind) {
         case RPTX_SHAPE_SPHERE: in.kind = kSphere; break;
         case RPTX_SHAPE_CUBE: in.kind = kCube; break;
+        case RPTX_SHAPE_MONOMIAL:
+            if (d.mono_exp != 4.0) return ctx_fail(ctx, "MonomialSurface: exp must be 4 (src/shape/monomial_surface.rs:17)");
+            if (!(d.mono_height > 0.0)) return ctx_fail(ctx, "MonomialSurface: height must be positive");
+            in.kind = kMonomial;
+            in.plane_v = d.mono_height; in.plane_n[0] = d.mono_exp;
+            break;
         case RPTX_SHAPE_PLANE:
             in.kind = kPlane;
             for (int k = 0; k < 3; k++) in.plane_n[k] = d.plane_normal[k];
@@ -261,7 +271,8 @@ int lower_light(rptx_scene* s, const rptx_light& l, Light* out) {
             r.ntri = (uint32_t)s->meshes[d.mesh_id].tris.size();
         } else if (d.kind == RPTX_SHAPE_CUBE) r.shape_kind = kCube;
         else if (d.kind == RPTX_SHAPE_SPHERE) r.shape_kind = kSphere;
-        else return ctx_fail(ctx, "object lights must be mesh, cube or sphere (Plane::sample is unimplemented, src/shape/plane.rs:34)");
+        else if (d.kind == RPTX_SHAPE_MONOMIAL) { r.shape_kind = kMonomial; r.vec[0] = d.mono_height; r.vec[1] = d.mono_exp; }
+        else return ctx_fail(ctx, "object lights must be mesh, cube, sphere or monomial surface (Plane::sample is unimplemented, src/shape/plane.rs:34)");
     }
     *out = r;
     return 0;
@@ -415,10 +426,10 @@ int rptx_scene_add_object(rptx_scene* s, const rptx_shape_desc* shape, const rpt
         if (shape->n_children == 0 || !shape->children) return ctx_fail(ctx, "empty group");
         o.children.assign(shape->children, shape->children + shape->n_children);
         for (const auto& c : o.children)
-            if (c.kind != RPTX_SHAPE_SPHERE && c.kind != RPTX_SHAPE_CUBE && c.kind != RPTX_SHAPE_MESH)
-                return ctx_fail(ctx, "group children must be bounded leaf shapes (sphere, cube, mesh)");
+            if (c.kind != RPTX_SHAPE_SPHERE && c.kind != RPTX_SHAPE_CUBE && c.kind != RPTX_SHAPE_MESH && c.kind != RPTX_SHAPE_MONOMIAL)
+                return ctx_fail(ctx, "group children must be bounded leaf shapes (sphere, cube, mesh, monomial surface)");
         o.desc.children = nullptr;
-    } else if (shape->kind < RPTX_SHAPE_SPHERE || shape->kind > RPTX_SHAPE_GROUP) {
+    } else if (shape->kind < RPTX_SHAPE_SPHERE || shape->kind > RPTX_SHAPE_MONOMIAL) {
         return ctx_fail(ctx, "unknown shape kind");
     }
     if (shape->kind == RPTX_SHAPE_MESH && shape->mesh_id >= s->meshes.size()) return ctx_fail(ctx, "unknown mesh id");
@@ -623,6 +634,9 @@ int rptx_scene_commit(rptx_scene* s) {
                 if (in.root_ref >= 0) { s->small_scene = 0; break; }
                 const uint32_t count = ((uint32_t)(~in.root_ref) & 7u) + 1u;
                 for (uint32_t j = 0; j < count; j++) slots.push_back((uint8_t)(i << 3 | j));
+            } else if (in.kind == kMonomial) {
+                s->small_scene = 0;  // the root finder is too long for the in-step candidate walk
+                break;
             } else {
                 s->small_kind_mask[in.kind] |= 1u << i;
                 if (i >= s->n_bounded) s->small_unbounded_mask |= 1u << i;

@@ -223,6 +223,15 @@ RPTX_D void sample_light_shape(const SceneDev& sc, const Light& l, d3 target, Rn
         else if (f == 4) { lv = mk3(0.5, a, b); ln = mk3(1, 0, 0); }
         else { lv = mk3(-0.5, a, b); ln = mk3(-1, 0, 0); }
         lp = 1.0 / 6.0;
+    } else if (l.shape_kind == kMonomial) {  // src/shape/monomial_surface.rs:109-124
+        double x, z;
+        rng.unit_circle(&x, &z);
+        const double h = l.vec[0];
+        lv = mk3(x, h * pow(x * x + z * z, l.vec[1] / 2.), z);
+        const double s = lv.x * lv.x + lv.z * lv.z;
+        ln = normalize(mk3(h * 4. * lv.x * s, -1., h * 4. * lv.z * s));
+        if (rng.gen() < 0.5) ln = -ln;
+        lp = 1. / (2. * 6.3406654362);
     } else {  // sphere, src/shape/sphere.rs:53-65
         double x, y;
         rng.unit_disc(&x, &y);

@@ -148,6 +148,59 @@ RPTX_D bool plane_test(const Instance& in, d3 o, d3 d, double t_min, double* t) 
     return false;
 }
 
+// MonomialSurface::intersect, src/shape/monomial_surface.rs:22-107: y = h (x^2 + z^2)^2 over the unit disc.
+// Same operation order as the reference (powi(2), powi(3) are multiplication chains); t_best is the
+// record's current time (the reference rejects r > record.time).
+RPTX_DN bool monomial_test(double h, d3 o, d3 d, double t_min, double t_best, double* t_out) {
+    // BoundingBox::intersect (src/kdtree.rs:57-71) on (-1,0,-1)-(1,h,1); fmin/fmax drop NaNs like f64::min/max
+    double b_min, b_max;
+    {
+        const double x1 = (-1.0 - o.x) / d.x, x2 = (1.0 - o.x) / d.x;
+        const double y1 = (0.0 - o.y) / d.y, y2 = (h - o.y) / d.y;
+        const double z1 = (-1.0 - o.z) / d.z, z2 = (1.0 - o.z) / d.z;
+        b_min = fmax(fmax(fmin(x1, x2), fmin(y1, y2)), fmin(z1, z2));
+        b_max = fmin(fmin(fmax(x1, x2), fmax(y1, y2)), fmax(z1, z2));
+    }
+    if (fmax(b_min, t_min) > fmin(b_max, t_best)) return false;
+    auto dist = [&](double t) {
+        const double x = o.x + t * d.x, y = o.y + t * d.y, z = o.z + t * d.z;
+        const double s = x * x + z * z;
+        return y - h * (s * s);
+    };
+    const double coef0 = o.x * o.x + o.z * o.z;
+    const double coef1 = 2. * (o.x * d.x + o.z * d.z);
+    const double coef2 = d.x * d.x + d.z * d.z;
+    double t_max;
+    const bool maximize = dist(t_min) < 0.0;
+    if (maximize) {
+        double cur = (b_min + b_max) / 2.;
+        for (int i = 0; i < 10; i++) {
+            if (dist(cur) > 0.) break;
+            const double der = d.y - h * (2. * coef0 * coef1 + 2. * cur * (coef1 * coef1 + 2. * coef0 * coef2) +
+                                          3. * (cur * cur) * 2. * coef1 * coef2 + 4. * (cur * cur * cur) * coef2 * coef2);
+            const double der2 = -h * (2. * (coef1 * coef1 + 2. * coef0 * coef2) + 3. * 2. * cur * 2. * coef1 * coef2 +
+                                      4. * 3. * (cur * cur) * coef2 * coef2);
+            cur -= der / der2;
+        }
+        t_max = cur;
+        if (t_max < t_min) return false;
+    } else {
+        t_max = 10000.;
+    }
+    if ((dist(t_min) < 0.0) == (dist(t_max) < 0.0)) return false;
+    double l = t_min, r = t_max;
+    for (int i = 0; i < 60; i++) {
+        const double m = (l + r) / 2.0;
+        if ((dist(m) >= 0.0) == maximize) r = m;
+        else l = m;
+    }
+    if (r > t_best) return false;
+    const double px = o.x + r * d.x, pz = o.z + r * d.z;
+    if (px * px + pz * pz > 1.0) return false;
+    *t_out = r;
+    return true;
+}
+
 // Conservative f32 Moller-Trumbore pre-test.  Returns false only when the ray provably misses
 // the triangle: every comparison carries an absolute error bound built from L1 norms of the
 // operands (an f32 dot/cross of vectors with relative input error ~2^-23 is off by at most a
@@ -368,7 +421,10 @@ RPTX_D void closest_hit(const SceneDev& sc, const RayD& ray, double t_min, doubl
                     }
                     double t;
                     uint32_t ccode = 0;
-                    const bool ok = kind == kSphere ? sphere_test(lo, ld, t_min, &t) : cube_test(lo, ld, t_min, &t, &ccode);
+                    bool ok;
+                    if (kind == kSphere) ok = sphere_test(lo, ld, t_min, &t);
+                    else if (kind == kCube) ok = cube_test(lo, ld, t_min, &t, &ccode);
+                    else ok = monomial_test(in->plane_v, lo, ld, t_min, hit.t, &t);
                     if (ok && (!WINDOW || t >= t_stop) && accept(hit, t, cur_obj)) {
                         hit.t = t; hit.inst = idx; hit.obj = cur_obj; hit.prim = ccode;
                         if (SHADOW && t < t_stop) return;
@@ -531,6 +587,11 @@ RPTX_D d3 hit_normal(const SceneDev& sc, const RayD& ray, const Hit& hit, uint32
         *prim_orig = sc.tri_orig[in->tri_base + hit.prim];
     } else if (in->kind == kSphere) {
         n = normalize(lo + hit.t * ld);
+    } else if (in->kind == kMonomial) {  // src/shape/monomial_surface.rs:94-104 (two-sided)
+        const d3 pos = lo + hit.t * ld;
+        const double h = in->plane_v, s = pos.x * pos.x + pos.z * pos.z;
+        n = normalize(mk3(h * 4.0 * pos.x * s, -1.0, h * 4.0 * pos.z * s));
+        if (dot(n, ld) > 0.0) n = -n;
     } else if (in->kind == kCube) {
         const uint32_t axis = hit.prim >> 1;
         const double s = (hit.prim & 1u) ? 1.0 : -1.0;

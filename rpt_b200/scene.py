@@ -133,6 +133,15 @@ class Cube(Shape):
     kind = A.SHAPE_CUBE
 
 
+class MonomialSurface(Shape):
+    """src/shape/monomial_surface.rs:8-19: y = height * sqrt(x^2 + z^2)^exp over the unit disc (exp must be 4)."""
+
+    kind = A.SHAPE_MONOMIAL
+
+    def __init__(self, height, exp):
+        self.height, self.exp = float(height), float(exp)
+
+
 class Plane(Shape):
     kind = A.SHAPE_PLANE
     bounded = False
@@ -206,6 +215,11 @@ def sphere():
 
 def cube():
     return Cube()
+
+
+def monomial_surface(height, exp):
+    """src/shape.rs:292-295"""
+    return MonomialSurface(height, exp)
 
 
 def plane(normal, value):

@@ -155,6 +155,23 @@ def lampshade(variant="pathtrace"):
     return scene, _cornell_camera(), defaults
 
 
+def monomial_glass(environment=(0.6, 0.7, 0.9)):
+    """examples/monomial_glass.rs:29-82.  The example downloads its HDRI; a solid environment colour (or an
+    Hdri passed in) stands in for it."""
+    from .scene import monomial_surface
+
+    scene = Scene()
+    scene.environment = environment
+    scene.add(Object(monomial_surface(2.0, 4.0).translate((0.0, -1.0, 0.0))).material(Material.metallic(hex_color(0xFFFFFF), 0.0001)))
+    scene.add(Object(cube().rotate_y(math.pi / 6.0).scale((0.5, 0.3, 0.4)).translate((0.4, -0.8, 4.0))).material(Material.specular(hex_color(0xFF00FF), 0.5)))
+    scene.add(Object(sphere().scale((0.5, 0.5, 0.5)).translate((1.5, -0.5, 1.0))).material(Material.specular(hex_color(0x0000FF), 0.1)))
+    scene.add(Object(sphere().scale((0.5, 0.5, 0.5)).translate((-1.5, -0.5, 1.0))).material(Material.specular(hex_color(0x00FF00), 0.1)))
+    scene.add(Object(plane((0.0, 1.0, 0.0), -1.0)).material(Material.specular(hex_color(0xAAAAAA), 0.5)))
+    scene.add(Light.Ambient((0.01, 0.01, 0.01)))
+    scene.add(Light.Point((100.0, 100.0, 100.0), (0.0, 5.0, 5.0)))
+    return scene, Camera(), dict(width=800, height=600, max_bounces=1, num_samples=100)
+
+
 def make_renderer(scene, camera, defaults, **overrides):
     """Renderer builder preloaded with a workload's parameters."""
     from .renderer import Renderer

@@ -6,7 +6,7 @@ import math
 import numpy as np
 
 from . import _abi as A
-from .scene import Cube, KdTree, Mesh, Plane, Shape, Sphere, Transformed, _dot, _normalize, _sub, vec3
+from .scene import Cube, KdTree, Mesh, MonomialSurface, Plane, Shape, Sphere, Transformed, _dot, _normalize, _sub, vec3
 
 
 class Material:
@@ -199,6 +199,9 @@ def _lower_shape(low, shape, allow_group=True):
         d.kind = A.SHAPE_SPHERE
     elif isinstance(base, Cube):
         d.kind = A.SHAPE_CUBE
+    elif isinstance(base, MonomialSurface):
+        d.kind = A.SHAPE_MONOMIAL
+        d.mono_height, d.mono_exp = base.height, base.exp
     elif isinstance(base, Plane):
         d.kind = A.SHAPE_PLANE
         d.plane_normal[:] = base.normal

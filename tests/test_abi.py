@@ -27,12 +27,12 @@ def test_library_exports_every_declared_symbol():
     lib = C.CDLL(A.LIB_PATH)
     for name in _header_symbols():
         assert hasattr(lib, name), f"librptx.so does not export {name}"
-    assert A.load().rptx_abi_version() == 1
+    assert A.load().rptx_abi_version() == 2
 
 
 def test_struct_layouts_match_the_header():
     # sizes follow from the C declarations in include/rptx.h (natural alignment, LP64)
-    assert C.sizeof(A.ShapeDesc) == 4 + 4 + 128 + 4 + 4 + 24 + 8 + 8
+    assert C.sizeof(A.ShapeDesc) == 4 + 4 + 128 + 4 + 4 + 24 + 8 + 16 + 8
     assert C.sizeof(A.MaterialDesc) == 8 + 24 + 24
     assert C.sizeof(A.LightDesc) == 8 + 48 + C.sizeof(A.ShapeDesc) + C.sizeof(A.MaterialDesc)
     assert C.sizeof(A.CameraDesc) == 96

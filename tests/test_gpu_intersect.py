@@ -57,6 +57,28 @@ def test_fractal_teapots_rays():
     _check(scene, cam, d, 96, 54, 1, 300000, extra_random=20000, max_bounces=3)
 
 
+def test_monomial_surface_rays():
+    """MonomialSurface::intersect (src/shape/monomial_surface.rs:22-107): Newton + 60 bisection steps, bit-exact t;
+    rays from the example's camera paths, random rays, rays starting inside the bowl and axis-parallel rays."""
+    scene, cam, d = scenes.monomial_glass()
+    _check(scene, cam, d, 64, 48, 2, 400000, extra_random=20000, max_bounces=3)
+    r = scenes.make_renderer(scene, cam, d)
+    ds, osc = r.device_scene(), orc.OracleScene(scene)
+    rng = np.random.default_rng(11)
+    n = 20000
+    o = np.stack([rng.uniform(-1, 1, n), rng.uniform(-1, 1.5, n), rng.uniform(-1, 1, n)], axis=1)
+    dd = rng.normal(size=(n, 3))
+    dd[: n // 4, rng.integers(0, 3)] = 0.0  # a zero direction component: 0/0 and x/0 in the bounding-box clip
+    dd /= np.linalg.norm(dd, axis=1, keepdims=True)
+    t, obj, prim, inst, nrm = ds.intersect_batch(o, dd)
+    to, objo, primo, insto, nrmo = osc.intersect_batch(o, dd)
+    assert (objo == 0).mean() > 0.2, "the surface itself should be hit often from inside its box"
+    assert np.array_equal(obj, objo), (obj != objo).sum()
+    ok = objo != 0xFFFFFFFF
+    assert np.array_equal(t[ok], to[ok])
+    assert np.allclose(nrm[ok], nrmo[ok], rtol=0, atol=1e-12)
+
+
 def test_empty_and_degenerate():
     scene, cam, d = scenes.cornell()
     r = scenes.make_renderer(scene, cam, d)

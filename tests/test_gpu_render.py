@@ -241,3 +241,22 @@ def test_sah_trees_equal_lbvh_trees(monkeypatch):
             r.device_scene().close()
         monkeypatch.delenv("RPTX_LBVH_ONLY", raising=False)
         assert np.array_equal(means[0], means[1]), name
+
+
+def test_monomial_glass_same_seed():
+    """examples/monomial_glass.rs (MonomialSurface + Phong materials + plane, solid environment): same-seed parity,
+    and the same scene lit by the surface itself as a Light::Object (MonomialSurface::sample, :109-124)."""
+    from rpt_b200 import Light, Material, Object, hex_color, monomial_surface
+
+    scene, cam, d = scenes.monomial_glass()
+    film, of, match, rmse = _same_seed(scene, cam, d, 80, 60, 4, max_bounces=2)
+    assert match >= MIN_MATCH, match
+    assert rmse <= MAX_REL_RMSE, rmse
+    scene, cam, d = scenes.monomial_glass(environment=(0.0, 0.0, 0.0))
+    glow = Object(monomial_surface(2.0, 4.0).translate((0.0, -1.0, 0.0))).material(Material.light(hex_color(0xFFFFFF), 5.0))
+    scene.objects[0] = glow
+    scene.add(Light.Object(glow))
+    film, of, match, rmse = _same_seed(scene, cam, d, 80, 60, 4, max_bounces=1)
+    assert match >= MIN_MATCH, match
+    assert rmse <= MAX_REL_RMSE, rmse
+    assert film.mean().mean() > 1e-3

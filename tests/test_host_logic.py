@@ -103,6 +103,65 @@ def test_load_obj_semantics():
     assert np.allclose(m.normals[2], [[0, 0, 1]] * 3)  # face normal filled in for the corner-less face
 
 
+def test_load_stl_binary_and_ascii(tmp_path):
+    """src/io.rs:264-364: binary = 80-byte header, u32 count, 50-byte records (f32 normal + 3 vertices + u16), values
+    widened from f32, facet normal on all three corners; ASCII = `solid `, then facets until end of file."""
+    import struct
+
+    from rpt_b200 import load_stl
+
+    tris = [((0, 0, 1), (0, 0, 0), (1, 0, 0), (0, 1, 0)), ((1, 0, 0), (0.1, 0.2, 0.3), (0, 1, 0), (0, 0, 1))]
+    blob = b"\0" * 80 + struct.pack("<I", len(tris))
+    for t in tris:
+        blob += struct.pack("<12f", *[c for v in t for c in v]) + b"\0\0"
+    p = tmp_path / "b.stl"
+    p.write_bytes(blob)
+    m = load_stl(str(p))
+    assert len(m) == 2
+    assert np.array_equal(m.vertices[1][0], np.array([0.1, 0.2, 0.3], np.float32).astype(np.float64))
+    assert np.array_equal(m.normals[0], [[0, 0, 1]] * 3) and np.array_equal(m.normals[1], [[1, 0, 0]] * 3)
+    body = "solid t\n" + "".join(
+        f"facet normal {n[0]} {n[1]} {n[2]}\nouter loop\nvertex {a[0]} {a[1]} {a[2]}\nvertex {b[0]} {b[1]} {b[2]}\n"
+        f"vertex {c[0]} {c[1]} {c[2]}\nendloop\nendfacet\n" for n, a, b, c in tris)
+    m2 = load_stl(io.BytesIO(body.encode()))
+    assert len(m2) == 2 and np.array_equal(m2.vertices[1][0], [0.1, 0.2, 0.3]) and np.array_equal(m2.normals[1], [[1, 0, 0]] * 3)
+    # the reference's ASCII loop treats EVERY remaining line as a facet (src/io.rs:294-299): `endsolid` is malformed
+    with pytest.raises(ValueError, match="facet normal"):
+        load_stl(io.BytesIO((body + "endsolid t\n").encode()))
+    with pytest.raises(ValueError, match="too short"):
+        load_stl(io.BytesIO(b"solid"))
+    with pytest.raises(ValueError, match="could not determine format"):
+        load_stl(io.BytesIO(b"not an stl file at all"))
+
+
+def test_load_obj_with_mtl_groups_by_usemtl():
+    """src/io.rs:84-150,203-258: default material per `newmtl`; one Object per run of a material; unknown names are
+    InvalidData; any MTL property line hits the reference's `panic!("MTL loading not implemented")`."""
+    from rpt_b200 import load_mtl, load_obj_with_mtl
+
+    obj = "v 0 0 0\nv 1 0 0\nv 1 1 0\nv 0 1 0\nf 1 2 3\nusemtl a\nf 1 2 3 4\nusemtl a\nf 1 3 4\nusemtl b\nf 2 3 4\n"
+    objs = load_obj_with_mtl(io.StringIO(obj), io.StringIO("# lib\nnewmtl a\nnewmtl b\n"))
+    assert [len(o.shape) for o in objs] == [1, 3, 1]
+    assert all(o.mat.kind == Material.default().kind for o in objs)
+    with pytest.raises(ValueError, match="usemtl c"):
+        load_obj_with_mtl(io.StringIO(obj.replace("usemtl b", "usemtl c")), io.StringIO("newmtl a\nnewmtl b\n"))
+    with pytest.raises(RuntimeError, match="not implemented"):
+        load_mtl(io.StringIO("newmtl a\nKd 1 0 0\n"))
+    with pytest.raises(ValueError, match="newmtl"):
+        load_mtl(io.StringIO("Kd 1 0 0\n"))
+
+
+def test_monomial_surface_lowering():
+    """src/shape.rs:292-295 -> RPTX_SHAPE_MONOMIAL with height / exp in the POD record."""
+    from rpt_b200 import monomial_surface
+
+    s, _, _ = scenes.monomial_glass()
+    low = lower_scene(s)
+    d = low.objects[0][0]
+    assert d.kind == A.SHAPE_MONOMIAL and d.mono_height == 2.0 and d.mono_exp == 4.0 and d.has_transform == 1
+    assert monomial_surface(1.0, 4.0).kind == A.SHAPE_MONOMIAL
+
+
 def test_teapot_fixture_is_the_reference_asset():
     z = np.load(os.path.join(HERE, "golden", "teapot_tris.npz"))
     assert z["vertices"].shape == (2256, 3, 3) and z["normals"].shape == (2256, 3, 3)

@@ -8,7 +8,7 @@ import math
 import numpy as np
 
 import orc
-from rpt_b200 import Camera, Light, Material, Medium, Object, Scene, cube, hex_color, polygon, scenes, sphere, plane
+from rpt_b200 import Camera, Light, Material, Medium, Object, Scene, cube, hex_color, monomial_surface, polygon, scenes, sphere, plane
 
 
 def _scene(*nodes):
@@ -145,3 +145,31 @@ def test_medium_free_flight_statistics():
     # continue w.p. 0.8 => mean segments = 1/(1 - .8647*.8) = 3.243
     per_path = c["extend_rays"] / (8 * 8 * 50)
     assert abs(per_path - 1.0 / (1.0 - (1 - math.exp(-2.0)) * 0.8)) < 0.15, per_path
+
+
+def test_monomial_surface_known_answers():
+    """src/shape/monomial_surface.rs:22-107 on y = 2 (x^2+z^2)^2: the axis ray from above meets the apex at
+    t = 3 with normal +y (two-sided flip); a horizontal ray at height y0 enters at radius (y0/2)^(1/4); rays
+    outside the unit disc miss (second equation, :88-91); the surface satisfies its own equation at every hit."""
+    osc = orc.OracleScene(_scene(Object(monomial_surface(2.0, 4.0))))
+    y0 = 0.5
+    r0 = (y0 / 2.0) ** 0.25
+    o = [[0, 3, 0], [-3, y0, 0], [0, 3, 1.5], [0.3, 3, -0.2], [0, -1, 0]]
+    d = [[0, -1, 0], [1, 0, 0], [0, -1, 0], [0, -1, 0], [0, 1, 0]]
+    t, obj, prim, inst, n = osc.intersect_batch(o, d)
+    assert abs(t[0] - 3.0) < 1e-9 and np.allclose(n[0], [0, 1, 0], atol=1e-12)
+    assert abs(t[1] - (3.0 - r0)) < 1e-9 and n[1][0] < 0 and abs(np.linalg.norm(n[1]) - 1) < 1e-12
+    assert np.isinf(t[2]) and obj[2] == 0xFFFFFFFF
+    s = 0.3 ** 2 + 0.2 ** 2
+    assert abs(t[3] - (3.0 - 2.0 * s * s)) < 1e-9
+    assert abs(t[4] - 1.0) < 1e-9 and np.allclose(n[4], [0, -1, 0], atol=1e-12)
+    rng = np.random.default_rng(3)
+    o = np.stack([rng.uniform(-2, 2, 4000), rng.uniform(2.5, 4, 4000), rng.uniform(-2, 2, 4000)], axis=1)
+    dd = np.stack([rng.uniform(-0.5, 0.5, 4000), -np.ones(4000), rng.uniform(-0.5, 0.5, 4000)], axis=1)
+    t, obj, *_ = osc.intersect_batch(o, dd)
+    hit = obj == 0
+    assert 0.05 < hit.mean() < 0.9
+    p = o[hit] + t[hit, None] * dd[hit]
+    s = p[:, 0] ** 2 + p[:, 2] ** 2
+    assert (s <= 1.0).all() and np.abs(p[:, 1] - 2.0 * s * s).max() < 1e-9
+
