@@ -311,55 +311,96 @@ __global__ void __launch_bounds__(kShadeBlock, 2) k_shade(const __grid_constant_
 // shadow: NEE visibility of the vertex's light samples (nee_visible, trace.cuh).  Passing
 // candidates are added to the vertex's direct light in light order.  A candidate whose
 // contribution is exactly zero (light sample facing away, bsdf 0) is not traced: adding it
-// cannot change the sum.
+// cannot change the sum.  About half of the Cornell / lampshade vertices have no job, and a warp of
+// 32 consecutive queue entries ran its traversal with 16 live lanes.  So a block pulls kShadowChunk
+// entries at a time, keeps the ones with a job (ballot ranks + per-warp counts, queue order kept) and
+// deals them to its threads densely: every warp but the last runs with 32 live lanes.
 // PROBE: the scene has point lights (probed at their sample first); all lights take that path then.
+constexpr int kShadowPer = 2;                        // queue entries classified per thread and pull
+constexpr int kShadowChunk = kShadowPer * kBlock;
+
 template <bool PROBE, bool SMALL>
 __global__ void __launch_bounds__(kBlock, RPTX_OCC_SHADOW) k_shadow(const __grid_constant__ SceneDev sc, PathPool p, Queues q) {
+    __shared__ uint32_t s_base;
+    __shared__ uint32_t s_cnt[kShadowPer * (kBlock / 32)];
+    __shared__ uint32_t s_slot[kShadowChunk];
+    __shared__ double s_c[3][kShadowChunk];
     const uint32_t count = q.counters[0];
+    const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
     unsigned long long my_queries = 0, my_traced = 0, my_occl = 0;
     for (;;) {
-        uint32_t base = 0;
-        if (lane_id() == 0) base = atomicAdd(&q.counters[3], 32u);
-        base = __shfl_sync(0xffffffffu, base, 0);
+        __syncthreads();  // the previous chunk's readers of s_base / s_slot are done
+        if (threadIdx.x == 0) s_base = atomicAdd(&q.counters[3], (uint32_t)kShadowChunk);
+        __syncthreads();
+        const uint32_t base = s_base;
         if (base >= count) break;
-        const uint32_t i = base + lane_id();
-        const uint32_t slot = i < count ? q.cur[i] : 0u;
-        const bool has = i < count && (p.flags[slot] & kFlagHasShadow);
-        d3 add = mk3(0, 0, 0);
-        bool any = false;
-        double2* rec = nullptr;
-        double keep_fx = 0.0;
-        RayD ray;
-        ray.o = mk3(0, 0, 0);
-        if (has) ray.o = mk3(p.ox[slot], p.oy[slot], p.oz[slot]);
-        for (uint32_t k = 0; k < p.n_shadow; k++) {  // uniform trip count: the warp enters every traversal together
-            const size_t off = (size_t)k * p.n_slots + slot;
-            d3 c = mk3(0, 0, 0);
-            if (has) { c = mk3(p.scx[off], p.scy[off], p.scz[off]); my_queries++; }
-            const bool job = has && !(c.x == 0.0 && c.y == 0.0 && c.z == 0.0);
-            double dist = 0.0;
-            ray.d = mk3(0, 0, 1);
-            if (job) { ray.d = mk3(p.sdx[off], p.sdy[off], p.sdz[off]); dist = p.sdist[off]; my_traced++; }
-            __syncwarp();
-            if (job && nee_visible<PROBE, SMALL>(sc, ray, dist, &my_occl)) {
-                // direct += contribution, in light order like the reference's loop
-                if (!any) {
-                    if (p.record_mode) {
-                        rec = reinterpret_cast<double2*>(p.stack + ((size_t)slot * p.stack_depth + p.depth[slot]) * p.rec_stride);
-                        const double2 a = rec[0], b = rec[1];
-                        add = mk3(a.x, a.y, b.x);
-                        keep_fx = b.y;
-                    } else {
-                        add = mk3(p.dirx[slot], p.diry[slot], p.dirz[slot]);
-                    }
-                    any = true;
-                }
-                add = add + c;
-            }
+        uint32_t slot[kShadowPer];
+        bool has[kShadowPer];
+#pragma unroll
+        for (int r = 0; r < kShadowPer; r++) {
+            const uint32_t i = base + (uint32_t)r * kBlock + threadIdx.x;
+            slot[r] = i < count ? q.cur[i] : 0u;
+            has[r] = i < count && (p.flags[slot[r]] & kFlagHasShadow);
         }
-        if (any) {
-            if (p.record_mode) { rec[0] = make_double2(add.x, add.y); rec[1] = make_double2(add.z, keep_fx); }
-            else { p.dirx[slot] = add.x; p.diry[slot] = add.y; p.dirz[slot] = add.z; }
+        for (uint32_t k = 0; k < p.n_shadow; k++) {  // light order; the adds of light k are visible before light k + 1 starts
+            if (k) __syncthreads();
+            uint32_t rank[kShadowPer];
+            bool job[kShadowPer];
+            d3 c[kShadowPer];
+#pragma unroll
+            for (int r = 0; r < kShadowPer; r++) {
+                c[r] = mk3(0, 0, 0);
+                if (has[r]) {
+                    const size_t off = (size_t)k * p.n_slots + slot[r];
+                    c[r] = mk3(p.scx[off], p.scy[off], p.scz[off]);
+                    my_queries++;
+                }
+                job[r] = has[r] && !(c[r].x == 0.0 && c[r].y == 0.0 && c[r].z == 0.0);
+                const unsigned m = __ballot_sync(0xffffffffu, job[r]);
+                rank[r] = (uint32_t)__popc(m & ((1u << lane) - 1u));
+                if (lane == 0) s_cnt[r * (kBlock / 32) + warp] = (uint32_t)__popc(m);
+            }
+            __syncthreads();
+            uint32_t total = 0, before[kShadowPer];
+#pragma unroll
+            for (int r = 0; r < kShadowPer; r++) before[r] = 0;
+#pragma unroll
+            for (uint32_t w = 0; w < kShadowPer * (kBlock / 32); w++) {
+                const uint32_t n = s_cnt[w];
+#pragma unroll
+                for (int r = 0; r < kShadowPer; r++)
+                    if (w < r * (kBlock / 32) + warp) before[r] += n;
+                total += n;
+            }
+#pragma unroll
+            for (int r = 0; r < kShadowPer; r++)
+                if (job[r]) {
+                    const uint32_t at = before[r] + rank[r];
+                    s_slot[at] = slot[r];
+                    s_c[0][at] = c[r].x; s_c[1][at] = c[r].y; s_c[2][at] = c[r].z;
+                }
+            __syncthreads();
+            for (uint32_t j = threadIdx.x; j < total; j += kBlock) {
+                const uint32_t js = s_slot[j];
+                const d3 cj = mk3(s_c[0][j], s_c[1][j], s_c[2][j]);
+                const size_t off = (size_t)k * p.n_slots + js;
+                RayD ray;
+                ray.o = mk3(p.ox[js], p.oy[js], p.oz[js]);
+                ray.d = mk3(p.sdx[off], p.sdy[off], p.sdz[off]);
+                const double dist = p.sdist[off];
+                my_traced++;
+                if (nee_visible<PROBE, SMALL>(sc, ray, dist, &my_occl)) {
+                    // direct += contribution, in light order like the reference's loop
+                    if (p.record_mode) {
+                        double2* rec = reinterpret_cast<double2*>(p.stack + ((size_t)js * p.stack_depth + p.depth[js]) * p.rec_stride);
+                        const double2 a = rec[0], b = rec[1];
+                        rec[0] = make_double2(a.x + cj.x, a.y + cj.y);
+                        rec[1] = make_double2(b.x + cj.z, b.y);
+                    } else {
+                        p.dirx[js] += cj.x; p.diry[js] += cj.y; p.dirz[js] += cj.z;
+                    }
+                }
+            }
         }
     }
     stat_add64(&q.stats[2], my_queries);
