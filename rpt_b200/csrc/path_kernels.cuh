@@ -15,7 +15,10 @@
 #define RPTX_OCC_EXTEND 4
 #endif
 #ifndef RPTX_OCC_SHADE
-#define RPTX_OCC_SHADE 1
+#define RPTX_OCC_SHADE 5
+#endif
+#ifndef RPTX_SHADE_BLOCK
+#define RPTX_SHADE_BLOCK 128
 #endif
 #ifndef RPTX_OCC_SHADOW
 #define RPTX_OCC_SHADOW 4
@@ -34,6 +37,7 @@ namespace rptx {
 constexpr int kBlock = 128;
 
 RPTX_D uint32_t lane_id() { return threadIdx.x & 31u; }
+RPTX_D void prefetch_l2(const void* ptr) { asm volatile("prefetch.global.L2 [%0];" ::"l"(ptr)); }
 
 // one atomic per warp for the run counters (a per-thread atomic on one address serialises)
 RPTX_D void stat_add(unsigned long long* __restrict__ dst, unsigned long long v) {
@@ -177,10 +181,10 @@ RPTX_D void sample_lights_dev(const SceneDev& sc, const PathPool& p, uint32_t sl
 // object and, with a medium, the free-flight draw) and re-deals them to its threads sorted by class
 // (stable counting sort through shared memory): all but two or three of its warps then run one kind only.
 // The entries stay within kShadeBlock queue positions of where they were, so the state accesses stay local.
-constexpr int kShadeBlock = 256;
+constexpr int kShadeBlock = RPTX_SHADE_BLOCK;
 
 template <bool MEDIUM>
-__global__ void __launch_bounds__(kShadeBlock, 2) k_shade(const __grid_constant__ SceneDev sc, PathPool p, Queues q, BatchParams bp,
+__global__ void __launch_bounds__(kShadeBlock, RPTX_OCC_SHADE) k_shade(const __grid_constant__ SceneDev sc, PathPool p, Queues q, BatchParams bp,
                                                           MediumDev md) {
     __shared__ uint32_t s_slot[kShadeBlock];
     __shared__ uint32_t s_cnt[3][kShadeBlock / 32];
@@ -195,6 +199,15 @@ __global__ void __launch_bounds__(kShadeBlock, 2) k_shade(const __grid_constant_
         uint32_t cls = 3, slot0 = 0;  // 0 medium collision, 1 surface, 2 miss, 3 no entry
         if (i < q.counters[0]) {
             slot0 = q.cur[i];
+#ifndef RPTX_NO_SHADE_PREFETCH
+            // the entry is dealt to another thread of this block below: start its state on the way to L2 now, so
+            // that the loads after the re-deal do not add a third DRAM round trip (queue -> hit object -> state)
+            prefetch_l2(p.ox + slot0); prefetch_l2(p.oy + slot0); prefetch_l2(p.oz + slot0);
+            prefetch_l2(p.dx + slot0); prefetch_l2(p.dy + slot0); prefetch_l2(p.dz + slot0);
+            prefetch_l2(p.hnx + slot0); prefetch_l2(p.hny + slot0); prefetch_l2(p.hnz + slot0);
+            prefetch_l2(p.depth + slot0);
+            if (!MEDIUM) { prefetch_l2(p.rng + slot0); prefetch_l2(p.ht + slot0); }
+#endif
             const bool hit0 = p.hobj[slot0] != kNoHit;
             cls = hit0 ? 1u : 2u;
             if (MEDIUM) {
