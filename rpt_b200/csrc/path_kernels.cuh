@@ -17,11 +17,14 @@
 #ifndef RPTX_OCC_SHADE
 #define RPTX_OCC_SHADE 5
 #endif
+#ifndef RPTX_OCC_FINAL
+#define RPTX_OCC_FINAL 6
+#endif
 #ifndef RPTX_SHADE_BLOCK
 #define RPTX_SHADE_BLOCK 128
 #endif
 #ifndef RPTX_OCC_SHADOW
-#define RPTX_OCC_SHADOW 4
+#define RPTX_OCC_SHADOW 6
 #endif
 // the small-scene variants (closest_hit_small: no traversal stack) are bound by the latency of dependent L1 hits at 16
 // warps per SM: 7 / 8 blocks (72 / 64 registers, 90-190 B of spills) measured best (cornell extend 39.2 -> 33.9 ms, shadow 37.3 -> 28.0)
@@ -539,6 +542,58 @@ RPTX_D void nee_inline(const SceneDev& sc, const Material* mat, const MediumDev*
         ctr.traced++;
         if (sc.shadow_probe_mask ? nee_visible<true>(sc, sr, dist, &ctr.occl) : nee_visible<false>(sc, sr, dist, &ctr.occl)) *direct = *direct + c;
     });
+}
+
+// One-vertex paths (surface mode with max_bounces == 0 - the reference's builder default, examples/teapot.rs and
+// fractal_teapots.rs): the vertex k_extend found ends the path.  Shading, NEE visibility, the film add and the
+// regeneration of the slot's next sample then run in ONE kernel and nothing of the vertex goes through HBM
+// (k_shade + k_shadow + k_connect write and re-read ~400 B per vertex for it).  Same arithmetic, same RNG draws and
+// the same light order as the three kernels.
+template <bool PROBE, bool SMALL>
+__global__ void __launch_bounds__(kBlock, RPTX_OCC_FINAL) k_shade_final(const __grid_constant__ SceneDev sc, PathPool p, Queues q, BatchParams bp, Camera cam) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned long long my_started = 0, my_queries = 0, my_traced = 0, my_occl = 0;
+    if (i < q.counters[0]) {
+        const uint32_t slot = q.cur[i];
+        const d3 o = mk3(p.ox[slot], p.oy[slot], p.oz[slot]);
+        const d3 d = mk3(p.dx[slot], p.dy[slot], p.dz[slot]);
+        const uint32_t obj = p.hobj[slot];
+        Rng rng;
+        rng.state = p.rng[slot];
+        d3 direct;
+        if (obj == kNoHit) {
+            direct = env_color(sc, d);
+        } else {
+            const double t = p.ht[slot];
+            const d3 n = mk3(p.hnx[slot], p.hny[slot], p.hnz[slot]);
+            const d3 pos = o + t * d;
+            const Material mat = sc.materials[obj];
+            const d3 wo = -normalize(d);
+            direct = mat_emittance(mat) * mat_color(mat);  // depth 0, src/renderer.rs:295-299
+            sample_lights_each<true>(sc, &mat, nullptr, pos, n, wo, mk3(0, 0, 0), rng, &direct, [&](uint32_t, d3 wi, double dist, d3 c) {
+                my_queries++;
+                if (c.x == 0.0 && c.y == 0.0 && c.z == 0.0) return;
+                RayD sr;
+                sr.o = pos;
+                sr.d = wi;
+                my_traced++;
+                if (nee_visible<PROBE, SMALL>(sc, sr, dist, &my_occl)) direct = direct + c;
+            });
+        }
+        p.ax[slot] += direct.x; p.ay[slot] += direct.y; p.az[slot] += direct.z;
+        const uint32_t jn = p.sample_j[slot] + p.n_lanes;
+        bool alive = false;
+        if (jn < bp.n_local) {
+            start_path<false>(p, bp, cam, slot, jn);
+            my_started++;
+            alive = true;
+        }
+        q.keep[i] = alive ? 1 : 0;
+    }
+    stat_add(&q.stats[0], my_started);
+    stat_add64(&q.stats[2], my_queries);
+    stat_add64(&q.stats[3], my_traced);
+    stat_add64(&q.stats[4], my_occl);
 }
 
 // trace_ray, surface branch (src/renderer.rs:286-321)

@@ -532,7 +532,9 @@ int rptx_scene_commit(rptx_scene* s) {
                 }
             std::vector<BvhNode> hn;
             std::vector<uint32_t> hp;
-            rptx_host::build_sah_host(hb, m.pad, kLeafMax, hn, hp, &m.root_ref);
+            int leaf_max = kLeafMax;
+            if (const char* e = std::getenv("RPTX_SAH_LEAF")) leaf_max = std::min(8, std::max(1, std::atoi(e)));  // developer knob
+            rptx_host::build_sah_host(hb, m.pad, leaf_max, hn, hp, &m.root_ref);
             if (!hn.empty()) CK(copy_h2d(d_nodes + m.node_base, hn.data(), sizeof(BvhNode) * hn.size(), st));
             CK(upload(&d_perm, hp, st));
             CK(cudaStreamSynchronize(st));  // hn / hp go out of scope
@@ -891,6 +893,7 @@ static int run_waves(rptx_film* f, const BatchParams& bp) {
     ctx->launches++;
     const int persistent_blocks = ctx->sm_count * 8;
     const bool small = sc.small_scene != 0;
+    const bool one_vertex = !MEDIUM && bp.max_bounces == 0 && !std::getenv("RPTX_NO_ONE_VERTEX");  // k_shade_final
     uint32_t* h_count = (uint32_t*)ctx->h_pinned;
     uint32_t active = std::min<uint64_t>(p.n_slots, (uint64_t)p.n_pixels * std::min(p.n_lanes, bp.n_local));
     while (active > 0) {
@@ -899,6 +902,25 @@ static int run_waves(rptx_film* f, const BatchParams& bp) {
         if (small) k_extend<true><<<blocks, kBlock, 0, st>>>(sc, p, q);
         else k_extend<false><<<blocks, kBlock, 0, st>>>(sc, p, q);
         cudaEventRecord(f->evw[1], st);
+        if (one_vertex) {
+            // the vertex ends the path: shade + NEE visibility + film add + regeneration in one kernel
+            const int g = (int)grid_for(active, kBlock);
+            if (small) {
+                if (sc.shadow_probe_mask) k_shade_final<true, true><<<g, kBlock, 0, st>>>(sc, p, q, bp, f->cam);
+                else k_shade_final<false, true><<<g, kBlock, 0, st>>>(sc, p, q, bp, f->cam);
+            } else {
+                if (sc.shadow_probe_mask) k_shade_final<true, false><<<g, kBlock, 0, st>>>(sc, p, q, bp, f->cam);
+                else k_shade_final<false, false><<<g, kBlock, 0, st>>>(sc, p, q, bp, f->cam);
+            }
+            cudaEventRecord(f->evw[2], st);
+            cudaEventRecord(f->evw[3], st);
+            {
+                size_t bytes = f->select_tmp_bytes;
+                CK(cub::DeviceSelect::Flagged(f->d_select_tmp, bytes, q.cur, q.keep, q.next, q.counters + 1, (int)active, st));
+            }
+            cudaEventRecord(f->evw[4], st);
+            ctx->launches += 4;
+        } else {
         k_shade<MEDIUM><<<grid_for(active, kShadeBlock), kShadeBlock, 0, st>>>(sc, p, q, bp, md);
         cudaEventRecord(f->evw[2], st);
         {
@@ -919,6 +941,7 @@ static int run_waves(rptx_film* f, const BatchParams& bp) {
             }
             cudaEventRecord(f->evw[4], st);
             ctx->launches += p.n_shadow ? 6 : 5;  // + the two kernels of the select
+        }
         }
         k_wave_end<<<1, 1, 0, st>>>(q);
         ctx->launches++;

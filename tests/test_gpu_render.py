@@ -260,3 +260,28 @@ def test_monomial_glass_same_seed():
     assert match >= MIN_MATCH, match
     assert rmse <= MAX_REL_RMSE, rmse
     assert film.mean().mean() > 1e-3
+
+
+def test_one_vertex_kernel_equals_three_kernels(monkeypatch):
+    """max_bounces == 0 (the reference's builder default): k_shade_final does shade + NEE visibility + film add +
+    regeneration in one kernel.  Same batch and the same ray counters as k_shade + k_shadow + k_connect, bit for bit,
+    on a BVH scene with point / directional / ambient lights and on a small scene with an area light; several samples
+    per slot so that regeneration runs."""
+    monkeypatch.setenv("RPTX_PATH_MODE", "wavefront")
+    monkeypatch.setenv("RPTX_POOL_LOG2", "12")
+    for make, size in ((scenes.fractal_teapots, (96, 56)), (scenes.cornell, (64, 48)), (scenes.monomial_glass, (64, 48))):
+        scene, cam, d = make()
+        out = []
+        for three in (False, True):
+            if three:
+                monkeypatch.setenv("RPTX_NO_ONE_VERTEX", "1")
+            else:
+                monkeypatch.delenv("RPTX_NO_ONE_VERTEX", raising=False)
+            f = scenes.make_renderer(scene, cam, d, width=size[0], height=size[1], num_samples=5, seed=4, max_bounces=0).begin()
+            f.sample(5)
+            st = f.stats()
+            out.append((f.mean(), st["extend_rays"], st["shadow_rays"], st["shadow_traced"], st["path_samples"]))
+        monkeypatch.delenv("RPTX_NO_ONE_VERTEX", raising=False)
+        assert np.array_equal(out[0][0], out[1][0]), make.__name__
+        assert out[0][1:] == out[1][1:], (make.__name__, out[0][1:], out[1][1:])
+        assert out[0][4] == size[0] * size[1] * 5
