@@ -338,6 +338,7 @@ RPTX_D void closest_hit(const SceneDev& sc, const RayD& ray, double t_min, doubl
     };
 
     int cur = sc.tlas_root_ref;
+    float cur_t = 0.0f;  // f32 entry time (relative to wshift) of the node `cur`, from its parent's slab test
     for (;;) {
         // ---- inner nodes (same code for both levels) ----
         while (cur >= 0 && cur != kSentinel) {
@@ -353,17 +354,18 @@ RPTX_D void closest_hit(const SceneDev& sc, const RayD& ray, double t_min, doubl
                 stack_t[sp] = lf ? tr : tl;
                 sp++;
                 cur = lf ? left : right;
+                cur_t = lf ? tl : tr;
             } else if (hl) {
-                cur = left;
+                cur = left; cur_t = tl;
             } else if (hr) {
-                cur = right;
+                cur = right; cur_t = tr;
             } else {
                 cur = kSentinel + 0;  // placeholder, replaced by the pop below
                 // pop
                 for (;;) {
                     if (sp == 0) return;
                     sp--;
-                    if (stack_t[sp] <= tbest) { cur = stack[sp]; break; }
+                    if (stack_t[sp] <= tbest) { cur = stack[sp]; cur_t = stack_t[sp]; break; }
                 }
             }
         }
@@ -397,10 +399,20 @@ RPTX_D void closest_hit(const SceneDev& sc, const RayD& ray, double t_min, doubl
                             if (test_tris(c2 >> 3, (c2 & 7u) + 1u)) return;
                             continue;
                         }
+#ifdef RPTX_BLAS_CLIP
                         double l0, l1v;
                         clip_f64(in->lmin, in->lmax, lo, ld, &l0, &l1v);
                         if (!(l0 <= l1v) || l1v < 0.0 || l0 > hit.t) continue;
                         if (WINDOW && l1v < t_stop) continue;
+#else
+                        // The local f32 ray starts where the ray entered the instance's WORLD box: that time is the
+                        // leaf's entry time of the slab test that led here (the parameter is the same in local space:
+                        // the direction is not renormalised).  It lies at or before the local box entry and within
+                        // the preimage of the world box, so |origin| stays within a few E of the mesh and its f32
+                        // rounding inside the boxes' padding; an f64 clip against the local box (three divisions and
+                        // as many instructions as a dozen node visits) only repeated what the BLAS root test does.
+                        const double l0 = wshift + (double)cur_t;
+#endif
                         // enter the mesh BVH (TLAS leaves hold one instance, so nothing is pending)
                         shift = WINDOW ? fmax(fmax(l0, t_stop), 0.0) : (l0 > 0.0 ? l0 : 0.0);
                         const d3 so = lo + shift * ld;
@@ -438,7 +450,7 @@ RPTX_D void closest_hit(const SceneDev& sc, const RayD& ray, double t_min, doubl
         for (;;) {
             if (sp == 0) return;
             sp--;
-            if (stack_t[sp] <= tbest) { cur = stack[sp]; break; }
+            if (stack_t[sp] <= tbest) { cur = stack[sp]; cur_t = stack_t[sp]; break; }
         }
     }
 }
