@@ -45,10 +45,12 @@ struct BoxBvhHost {
 
 int grid_for(size_t n, int block) { return (int)std::max<size_t>(1, (n + block - 1) / block); }
 
+// Everything here comes from the stream-ordered pool on the library's stream: cudaMalloc / cudaFree
+// next to a mapped multi-GB film slab or photon list stall for 20-460 ms at random (profiles/r1_v2_summary.md).
 template <class T>
-cudaError_t dev_alloc(T** p, size_t n, std::vector<void*>* owned) {
+cudaError_t dev_alloc(rptx_ctx* ctx, T** p, size_t n, std::vector<void*>* owned) {
     *p = nullptr;
-    cudaError_t e = cudaMalloc((void**)p, std::max<size_t>(n, 1) * sizeof(T));
+    cudaError_t e = rptx_alloc_async((void**)p, std::max<size_t>(n, 1) * sizeof(T), ctx->stream);
     if (e == cudaSuccess && owned) owned->push_back(*p);
     return e;
 }
@@ -274,11 +276,11 @@ int sort_pairs(rptx_ctx* ctx, uint64_t* keys_in, uint64_t* keys_out, uint32_t* v
     size_t tmp_bytes = 0;
     CK(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys_in, keys_out, vals_in, vals_out, (int)n, 0, end_bit, ctx->stream));
     void* tmp = nullptr;
-    CK(cudaMalloc(&tmp, std::max<size_t>(tmp_bytes, 16)));
+    CK(rptx_alloc_async(&tmp, std::max<size_t>(tmp_bytes, 16), ctx->stream));
     cudaError_t e = cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, keys_in, keys_out, vals_in, vals_out, (int)n, 0, end_bit, ctx->stream);
     ctx->launches += 4;
     if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
-    cudaFree(tmp);
+    rptx_free_async(tmp, ctx->stream);
     if (e != cudaSuccess) return ctx_fail(ctx, std::string("radix sort: ") + cudaGetErrorString(e));
     return 0;
 }
@@ -287,21 +289,21 @@ int sort_pairs(rptx_ctx* ctx, uint64_t* keys_in, uint64_t* keys_out, uint32_t* v
 int canonical_order(rptx_ctx* ctx, const PhotonRec* rows, uint32_t n, uint32_t** d_idx_out) {
     uint64_t *k0 = nullptr, *k1 = nullptr;
     uint32_t *i0 = nullptr, *i1 = nullptr;
-    CK(dev_alloc(&k0, n, nullptr));
-    CK(dev_alloc(&k1, n, nullptr));
-    CK(dev_alloc(&i0, n, nullptr));
-    CK(dev_alloc(&i1, n, nullptr));
+    CK(dev_alloc(ctx, &k0, n, nullptr));
+    CK(dev_alloc(ctx, &k1, n, nullptr));
+    CK(dev_alloc(ctx, &i0, n, nullptr));
+    CK(dev_alloc(ctx, &i1, n, nullptr));
     k_rows_keys<<<grid_for(n, 256), 256, 0, ctx->stream>>>(rows, n, k0, i0);
     ctx->launches++;
     const int rc = sort_pairs(ctx, k0, k1, i0, i1, n, 64);
-    cudaFree(k0); cudaFree(k1); cudaFree(i0);
-    if (rc) { cudaFree(i1); return rc; }
+    rptx_free_async(k0, ctx->stream); rptx_free_async(k1, ctx->stream); rptx_free_async(i0, ctx->stream);
+    if (rc) { rptx_free_async(i1, ctx->stream); return rc; }
     *d_idx_out = i1;
     return 0;
 }
 
-void free_owned(std::vector<void*>& owned) {
-    for (void* p : owned) cudaFree(p);
+void free_owned(rptx_ctx* ctx, std::vector<void*>& owned) {
+    for (void* p : owned) rptx_free_async(p, ctx->stream);
     owned.clear();
 }
 
@@ -315,28 +317,28 @@ int build_point_map(rptx_ctx* ctx, const PhotonRec* rows, const uint32_t* d_cano
     double *px = nullptr, *py = nullptr, *pz = nullptr, *dir = nullptr, *power = nullptr;
     uint64_t* key = nullptr;
     BvhNode* nodes = nullptr;
-    CK(dev_alloc(&px, n, &out->owned)); CK(dev_alloc(&py, n, &out->owned)); CK(dev_alloc(&pz, n, &out->owned));
-    CK(dev_alloc(&dir, 3 * (size_t)n, &out->owned)); CK(dev_alloc(&power, 3 * (size_t)n, &out->owned));
-    CK(dev_alloc(&key, n, &out->owned));
-    CK(dev_alloc(&nodes, std::max<uint32_t>(n, 1), &out->owned));
+    CK(dev_alloc(ctx, &px, n, &out->owned)); CK(dev_alloc(ctx, &py, n, &out->owned)); CK(dev_alloc(ctx, &pz, n, &out->owned));
+    CK(dev_alloc(ctx, &dir, 3 * (size_t)n, &out->owned)); CK(dev_alloc(ctx, &power, 3 * (size_t)n, &out->owned));
+    CK(dev_alloc(ctx, &key, n, &out->owned));
+    CK(dev_alloc(ctx, &nodes, std::max<uint32_t>(n, 1), &out->owned));
     out->dev.nodes = nodes;
     out->dev.px = px; out->dev.py = py; out->dev.pz = pz; out->dev.dir = dir; out->dev.power = power; out->dev.key = key;
     if (n == 0) return 0;
     const int blocks = std::min(grid_for(n, 256), 1184);
     double* d_b = nullptr;
-    CK(dev_alloc(&d_b, (size_t)blocks * 6, nullptr));
+    CK(dev_alloc(ctx, &d_b, (size_t)blocks * 6, nullptr));
     k_rows_bounds<<<blocks, 256, 0, st>>>(rows, n, d_b);
     ctx->launches++;
     double mn[3], mx[3];
     const int rc0 = reduce_bounds(ctx, d_b, blocks, mn, mx);
-    cudaFree(d_b);
+    rptx_free_async(d_b, ctx->stream);
     if (rc0) return rc0;
     uint64_t *k0 = nullptr, *k1 = nullptr;
     uint32_t* i1 = nullptr;
     PrimBox* boxes = nullptr;
     int rc = 0;
     auto body = [&]() -> int {
-        CK(dev_alloc(&k0, n, nullptr)); CK(dev_alloc(&k1, n, nullptr)); CK(dev_alloc(&i1, n, nullptr));
+        CK(dev_alloc(ctx, &k0, n, nullptr)); CK(dev_alloc(ctx, &k1, n, nullptr)); CK(dev_alloc(ctx, &i1, n, nullptr));
         const double3 dmn = make_double3(mn[0], mn[1], mn[2]);
         const double3 inv = make_double3(mx[0] > mn[0] ? 1.0 / (mx[0] - mn[0]) : 0.0, mx[1] > mn[1] ? 1.0 / (mx[1] - mn[1]) : 0.0,
                                          mx[2] > mn[2] ? 1.0 / (mx[2] - mn[2]) : 0.0);
@@ -345,9 +347,9 @@ int build_point_map(rptx_ctx* ctx, const PhotonRec* rows, const uint32_t* d_cano
         if (int r = sort_pairs(ctx, k0, k1, const_cast<uint32_t*>(d_canon), i1, n, 63)) return r;
         k_rows_gather<<<grid_for(n, 256), 256, 0, st>>>(rows, i1, n, px, py, pz, dir, power, key);
         ctx->launches++;
-        cudaFree(k0); k0 = nullptr;
-        cudaFree(i1); i1 = nullptr;
-        CK(dev_alloc(&boxes, n, nullptr));
+        rptx_free_async(k0, ctx->stream); k0 = nullptr;
+        rptx_free_async(i1, ctx->stream); i1 = nullptr;
+        CK(dev_alloc(ctx, &boxes, n, nullptr));
         k_point_boxes<<<grid_for(n, 256), 256, 0, st>>>(px, py, pz, n, boxes);
         ctx->launches++;
         const int e = build_lbvh_sorted(k1, boxes, n, 0.0f, kPointLeaf, nodes, &out->dev.root_ref, st, &ctx->launches);
@@ -355,7 +357,7 @@ int build_point_map(rptx_ctx* ctx, const PhotonRec* rows, const uint32_t* d_cano
         return 0;
     };
     rc = body();
-    cudaFree(k0); cudaFree(k1); cudaFree(i1); cudaFree(boxes);
+    rptx_free_async(k0, ctx->stream); rptx_free_async(k1, ctx->stream); rptx_free_async(i1, ctx->stream); rptx_free_async(boxes, ctx->stream);
     return rc;
 }
 
@@ -365,26 +367,26 @@ int build_box_bvh(rptx_ctx* ctx, const Aabb32* d_boxes, uint32_t n, BoxBvhHost* 
     out->dev.n = n;
     *d_perm_out = nullptr;
     BvhNode* nodes = nullptr;
-    CK(dev_alloc(&nodes, std::max<uint32_t>(n, 1), &out->owned));
+    CK(dev_alloc(ctx, &nodes, std::max<uint32_t>(n, 1), &out->owned));
     out->dev.nodes = nodes;
     if (n == 0) return 0;
     const int blocks = std::min(grid_for(n, 256), 1184);
     double* d_b = nullptr;
-    CK(dev_alloc(&d_b, (size_t)blocks * 6, nullptr));
+    CK(dev_alloc(ctx, &d_b, (size_t)blocks * 6, nullptr));
     k_box_bounds<<<blocks, 256, 0, ctx->stream>>>(d_boxes, n, d_b);
     ctx->launches++;
     double mn[3], mx[3];
     const int rc0 = reduce_bounds(ctx, d_b, blocks, mn, mx);
-    cudaFree(d_b);
+    rptx_free_async(d_b, ctx->stream);
     if (rc0) return rc0;
     for (int k = 0; k < 3; k++)
         if (!(mn[k] <= mx[k])) { mn[k] = 0.0; mx[k] = 1.0; }
     uint32_t* perm = nullptr;
-    CK(dev_alloc(&perm, n, nullptr));
+    CK(dev_alloc(ctx, &perm, n, nullptr));
     static_assert(sizeof(PrimBox) == sizeof(Aabb32), "box layouts match");
     const int rc = build_lbvh(reinterpret_cast<const PrimBox*>(d_boxes), n, 0.0f, kLeafMax, mn, mx, nodes, perm, &out->dev.root_ref, ctx->stream,
                               &ctx->launches);
-    if (rc != 0) { cudaFree(perm); return ctx_fail(ctx, std::string("photon BVH build: ") + cudaGetErrorString((cudaError_t)rc)); }
+    if (rc != 0) { rptx_free_async(perm, ctx->stream); return ctx_fail(ctx, std::string("photon BVH build: ") + cudaGetErrorString((cudaError_t)rc)); }
     *d_perm_out = perm;
     return 0;
 }
@@ -416,7 +418,7 @@ int emit_once(rptx_ctx* ctx, rptx_scene* scene, const EmitParams& ep, PhotonRec*
               uint64_t counts[3]) {
     cudaStream_t st = ctx->stream;
     unsigned long long* d_ctr = nullptr;  // [0] surface count, [1] volume count, [2] work head, [3] rays
-    CK(cudaMalloc((void**)&d_ctr, sizeof(unsigned long long) * 4));
+    CK(rptx_alloc_async((void**)&d_ctr, sizeof(unsigned long long) * 4, st));
     CK(cudaMemsetAsync(d_ctr, 0, sizeof(unsigned long long) * 4, st));
     PhotonSink surf{d_surf, d_ctr, cap_s}, vol{d_vol, d_ctr + 1, cap_v};
     const SceneDev sc = rptx_host::scene_dev(scene);
@@ -429,7 +431,7 @@ int emit_once(rptx_ctx* ctx, rptx_scene* scene, const EmitParams& ep, PhotonRec*
     cudaError_t e = cudaGetLastError();
     if (e == cudaSuccess) e = cudaMemcpyAsync(h, d_ctr, sizeof(h), cudaMemcpyDeviceToHost, st);
     if (e == cudaSuccess) e = cudaStreamSynchronize(st);
-    cudaFree(d_ctr);
+    rptx_free_async(d_ctr, ctx->stream);
     if (e != cudaSuccess) return ctx_fail(ctx, std::string("photon emission: ") + cudaGetErrorString(e));
     counts[0] = h[0]; counts[1] = h[1]; counts[2] = h[3];
     return 0;
@@ -457,7 +459,7 @@ int rptx_photons_create(rptx_ctx* ctx, rptx_photons** out) {
 void rptx_photons_destroy(rptx_photons* p) {
     if (!p) return;
     cudaSetDevice(p->ctx->device);
-    cudaFree(p->d_rows[0]); cudaFree(p->d_rows[1]);
+    rptx_free_async(p->d_rows[0], p->ctx->stream); rptx_free_async(p->d_rows[1], p->ctx->stream);
     delete p;
 }
 
@@ -496,10 +498,10 @@ int rptx_photons_emit(rptx_ctx* ctx, rptx_scene* scene, const rptx_params* param
         cap_s = cap_v = count * 16 + 1024;
     }
     while (rc == 0) {
-        cudaFree(p->d_rows[0]); cudaFree(p->d_rows[1]);
+        rptx_free_async(p->d_rows[0], ctx->stream); rptx_free_async(p->d_rows[1], ctx->stream);
         p->d_rows[0] = p->d_rows[1] = nullptr;
-        cudaError_t e = cudaMalloc((void**)&p->d_rows[0], std::max<uint64_t>(cap_s, 1) * sizeof(PhotonRec));
-        if (e == cudaSuccess) e = cudaMalloc((void**)&p->d_rows[1], std::max<uint64_t>(cap_v, 1) * sizeof(PhotonRec));
+        cudaError_t e = rptx_alloc_async((void**)&p->d_rows[0], std::max<uint64_t>(cap_s, 1) * sizeof(PhotonRec), ctx->stream);
+        if (e == cudaSuccess) e = rptx_alloc_async((void**)&p->d_rows[1], std::max<uint64_t>(cap_v, 1) * sizeof(PhotonRec), ctx->stream);
         if (e != cudaSuccess) { rc = ctx_fail(ctx, std::string("photon buffers: ") + cudaGetErrorString(e)); break; }
         p->cap[0] = cap_s; p->cap[1] = cap_v;
         rc = emit_once(ctx, scene, ep, p->d_rows[0], cap_s, p->d_rows[1], cap_v, counts);
@@ -527,10 +529,10 @@ static int photons_reserve(rptx_photons* p, int which, uint64_t need) {
     if (need <= p->cap[which]) return 0;
     const uint64_t cap = std::max<uint64_t>(need, p->cap[which] * 2);
     PhotonRec* nr = nullptr;
-    CK(cudaMalloc((void**)&nr, cap * sizeof(PhotonRec)));
+    CK(rptx_alloc_async((void**)&nr, cap * sizeof(PhotonRec), ctx->stream));
     if (p->n[which]) CK(cudaMemcpyAsync(nr, p->d_rows[which], p->n[which] * sizeof(PhotonRec), cudaMemcpyDeviceToDevice, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
-    cudaFree(p->d_rows[which]);
+    rptx_free_async(p->d_rows[which], ctx->stream);
     p->d_rows[which] = nr;
     p->cap[which] = cap;
     return 0;
@@ -595,7 +597,7 @@ int rptx_photons_stats(const rptx_photons* p, uint64_t* emitted, uint64_t* rays,
 void rptx_photon_map_destroy(rptx_photon_map* m) {
     if (!m) return;
     cudaSetDevice(m->ctx->device);
-    free_owned(m->surface.owned); free_owned(m->volume.owned); free_owned(m->bvh.owned); free_owned(m->owned);
+    free_owned(m->ctx, m->surface.owned); free_owned(m->ctx, m->volume.owned); free_owned(m->ctx, m->bvh.owned); free_owned(m->ctx, m->owned);
     delete m;
 }
 
@@ -625,16 +627,16 @@ int rptx_photon_map_build(rptx_ctx* ctx, rptx_scene* scene, rptx_photons* photon
         if (kind == RPTX_PHOTON_POINT_BEAM) {
             double *radius = nullptr, *center = nullptr, *rad = nullptr, *dir = nullptr, *power = nullptr;
             Aabb32 *boxes = nullptr, *obox = nullptr;
-            CK(dev_alloc(&radius, nv, &m->owned));
-            CK(dev_alloc(&boxes, nv, &m->owned));
+            CK(dev_alloc(ctx, &radius, nv, &m->owned));
+            CK(dev_alloc(ctx, &boxes, nv, &m->owned));
             if (nv) {
                 k_sphere_radius<<<grid_for(nv, 128), 128, 0, st>>>(m->volume.dev, radius, boxes);
                 ctx->launches++;
             }
             if (int r = build_box_bvh(ctx, boxes, nv, &m->bvh, &perm)) return r;
-            CK(dev_alloc(&center, 3 * (size_t)nv, &m->owned)); CK(dev_alloc(&rad, nv, &m->owned));
-            CK(dev_alloc(&dir, 3 * (size_t)nv, &m->owned)); CK(dev_alloc(&power, 3 * (size_t)nv, &m->owned));
-            CK(dev_alloc(&obox, nv, &m->owned));
+            CK(dev_alloc(ctx, &center, 3 * (size_t)nv, &m->owned)); CK(dev_alloc(ctx, &rad, nv, &m->owned));
+            CK(dev_alloc(ctx, &dir, 3 * (size_t)nv, &m->owned)); CK(dev_alloc(ctx, &power, 3 * (size_t)nv, &m->owned));
+            CK(dev_alloc(ctx, &obox, nv, &m->owned));
             if (nv) {
                 k_sphere_gather<<<grid_for(nv, 256), 256, 0, st>>>(m->volume.dev, radius, boxes, perm, nv, center, rad, dir, power, obox);
                 ctx->launches++;
@@ -646,17 +648,17 @@ int rptx_photon_map_build(rptx_ctx* ctx, rptx_scene* scene, rptx_photons* photon
             double *start = nullptr, *dirn = nullptr, *len = nullptr, *power = nullptr, *ostart = nullptr, *odirn = nullptr, *olen = nullptr,
                    *opower = nullptr;
             Aabb32 *boxes = nullptr, *obox = nullptr;
-            CK(dev_alloc(&start, 3 * (size_t)nv, &m->owned)); CK(dev_alloc(&dirn, 3 * (size_t)nv, &m->owned));
-            CK(dev_alloc(&len, nv, &m->owned)); CK(dev_alloc(&power, 3 * (size_t)nv, &m->owned));
-            CK(dev_alloc(&boxes, nv, &m->owned));
+            CK(dev_alloc(ctx, &start, 3 * (size_t)nv, &m->owned)); CK(dev_alloc(ctx, &dirn, 3 * (size_t)nv, &m->owned));
+            CK(dev_alloc(ctx, &len, nv, &m->owned)); CK(dev_alloc(ctx, &power, 3 * (size_t)nv, &m->owned));
+            CK(dev_alloc(ctx, &boxes, nv, &m->owned));
             if (nv) {
                 k_beam_make<<<grid_for(nv, 256), 256, 0, st>>>(photons->d_rows[1], canon_v, nv, start, dirn, len, power, boxes);
                 ctx->launches++;
             }
             if (int r = build_box_bvh(ctx, boxes, nv, &m->bvh, &perm)) return r;
-            CK(dev_alloc(&ostart, 3 * (size_t)nv, &m->owned)); CK(dev_alloc(&odirn, 3 * (size_t)nv, &m->owned));
-            CK(dev_alloc(&olen, nv, &m->owned)); CK(dev_alloc(&opower, 3 * (size_t)nv, &m->owned));
-            CK(dev_alloc(&obox, nv, &m->owned));
+            CK(dev_alloc(ctx, &ostart, 3 * (size_t)nv, &m->owned)); CK(dev_alloc(ctx, &odirn, 3 * (size_t)nv, &m->owned));
+            CK(dev_alloc(ctx, &olen, nv, &m->owned)); CK(dev_alloc(ctx, &opower, 3 * (size_t)nv, &m->owned));
+            CK(dev_alloc(ctx, &obox, nv, &m->owned));
             if (nv) {
                 k_beam_gather<<<grid_for(nv, 256), 256, 0, st>>>(start, dirn, len, power, boxes, perm, nv, ostart, odirn, olen, opower, obox);
                 ctx->launches++;
@@ -670,7 +672,7 @@ int rptx_photon_map_build(rptx_ctx* ctx, rptx_scene* scene, rptx_photons* photon
         return 0;
     };
     rc = body();
-    cudaFree(canon_s); cudaFree(canon_v); cudaFree(perm);
+    rptx_free_async(canon_s, ctx->stream); rptx_free_async(canon_v, ctx->stream); rptx_free_async(perm, ctx->stream);
     if (rc == 0) {
         cudaEventRecord(e1, st);
         cudaEventSynchronize(e1);
@@ -753,9 +755,9 @@ int rptx_photon_map_knn(rptx_photon_map* m, int32_t which, const double* q, size
     uint64_t* d_keys = nullptr;
     uint32_t* d_counts = nullptr;
     std::vector<void*> tmp;
-    auto done = [&](int rc) { free_owned(tmp); return rc; };
+    auto done = [&](int rc) { free_owned(ctx, tmp); return rc; };
 #define CKT(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return done(ctx_fail(ctx, std::string(#call) + ": " + cudaGetErrorString(e_))); } while (0)
-    CKT(dev_alloc(&d_q, 3 * n, &tmp)); CKT(dev_alloc(&d_d2, n * k, &tmp)); CKT(dev_alloc(&d_keys, n * k, &tmp)); CKT(dev_alloc(&d_counts, n, &tmp));
+    CKT(dev_alloc(ctx, &d_q, 3 * n, &tmp)); CKT(dev_alloc(ctx, &d_d2, n * k, &tmp)); CKT(dev_alloc(ctx, &d_keys, n * k, &tmp)); CKT(dev_alloc(ctx, &d_counts, n, &tmp));
     CKT(cudaMemcpyAsync(d_q, q, sizeof(double) * 3 * n, cudaMemcpyHostToDevice, st));
     const PointMapDev pmap = which == 0 ? m->surface.dev : m->volume.dev;
     if (k <= 32) k_knn_batch<32><<<grid_for(n, 128), 128, 0, st>>>(pmap, d_q, n, k, d_keys, d_d2, d_counts);
