@@ -24,6 +24,11 @@
 #include "shading.cuh"
 #include "trace.cuh"
 
+// resident blocks per SM asked of ptxas for the warp-per-sample gather kernel (register cap = 65536 / (128 * n))
+#ifndef RPTX_OCC_GATHER
+#define RPTX_OCC_GATHER 4
+#endif
+
 namespace rptx {
 
 namespace cg = cooperative_groups;
@@ -806,7 +811,7 @@ __global__ void __launch_bounds__(128) k_photon_gather(const __grid_constant__ S
 }
 
 // Camera pass for the point-point map: one warp per (pixel, lane) slot walks that slot's samples.
-__global__ void __launch_bounds__(128) k_photon_gather_warp(const __grid_constant__ SceneDev sc, const MediumDev md,
+__global__ void __launch_bounds__(128, RPTX_OCC_GATHER) k_photon_gather_warp(const __grid_constant__ SceneDev sc, const MediumDev md,
                                                             const __grid_constant__ PhotonMapDev pm, const __grid_constant__ GatherArgs ga,
                                                             unsigned long long* __restrict__ stats) {
     __shared__ WarpKnnSmem smem[4];
