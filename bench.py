@@ -303,7 +303,9 @@ def run_ours(args):
                                   peak_source=which,
                                   note="per launch (one wave); closest-hit traversal is issue-bound (62 % of issue slots, 16-23 of 32 lanes), "
                                        "not HBM-bound: the scene stays in L2 and DRAM traffic equals the path-state bytes; see DESIGN.md and profiles/"),
-                    rays_per_s=dict(extend=rays_e / max(ext_ms / 1e3, 1e-12), shadow=rays_s / max(sdw_ms / 1e3, 1e-12),
+                    rays_per_s=dict(extend=rays_e / max(ext_ms / 1e3, 1e-12),
+                                    # one-vertex paths (max_bounces 0): NEE visibility runs inside k_shade_final, no shadow kernel time of its own
+                                    shadow=(rays_s / (sdw_ms / 1e3) if sdw_ms > 0.05 * max(shd_ms, 1e-9) else None),
                                     total_step=(rays_e + rays_s) / step_time),
                     kernel_ms_per_step=dict(extend=ext_ms / args.steps, shade=shd_ms / args.steps, shadow=sdw_ms / args.steps, connect=con_ms / args.steps,
                                             device=dev_ms / args.steps, wall=1e3 * wall / args.steps),
@@ -353,7 +355,7 @@ def run_photons(args):
     r.device_scene()
     launches0 = 0
     for _ in range(args.warmup):
-        film, pmap, tm = rd.photon_render(r, max(n_total // 50, 1000), kind)
+        film, pmap, tm = rd.photon_render(r, n_total, kind)  # full size: the stream-ordered pool reaches its working set here
         launches0 = film.stats()["kernel_launches"]
         film.close(); pmap.close()
     clocks = ClockSampler(local)

@@ -11,7 +11,7 @@ timeout 600 python bench.py --steps 3 --warmup 3 --workload cornell --spp 256 --
 timeout 600 python bench.py --steps 2 --warmup 3 --workload lampshade --spp 128 --cpu-seconds 8 > gpurun_out/bench_lampshade.json 2> gpurun_out/bench_lampshade.err
 timeout 600 python bench.py --steps 2 --warmup 3 --workload fractal_teapots_mb5 --spp 32 --cpu-seconds 8 > gpurun_out/bench_fractal_mb5.json 2> gpurun_out/bench_fractal_mb5.err
 for k in photonphoton beamphoton beambeam; do
-timeout 600 python bench.py --steps 2 --warmup 1 --workload $k --photons 1e7 --cpu-seconds 8 > gpurun_out/bench_$k.json 2> gpurun_out/bench_$k.err
+timeout 600 python bench.py --steps 3 --warmup 3 --workload $k --photons 1e7 --cpu-seconds 8 > gpurun_out/bench_$k.json 2> gpurun_out/bench_$k.err
 done
 CMD="python bench.py --steps 1 --warmup 1 --cpu-seconds 0"
 $CMD > gpurun_out/plain.log 2>&1 && \
