@@ -928,11 +928,11 @@ static int run_waves(rptx_film* f, const BatchParams& bp) {
         {
             if (p.n_shadow) {
                 if (small) {
-                    if (sc.shadow_probe_mask) k_shadow<true, true><<<blocks, kBlock, 0, st>>>(sc, p, q);
-                    else k_shadow<false, true><<<blocks, kBlock, 0, st>>>(sc, p, q);
+                    if (sc.shadow_probe_mask) k_shadow_warp<true, true><<<blocks, kBlock, 0, st>>>(sc, p, q);
+                    else k_shadow_warp<false, true><<<blocks, kBlock, 0, st>>>(sc, p, q);
                 } else {
-                    if (sc.shadow_probe_mask) k_shadow<true, false><<<blocks, kBlock, 0, st>>>(sc, p, q);
-                    else k_shadow<false, false><<<blocks, kBlock, 0, st>>>(sc, p, q);
+                    if (sc.shadow_probe_mask) k_shadow_block<true, false><<<blocks, kBlock, 0, st>>>(sc, p, q);
+                    else k_shadow_block<false, false><<<blocks, kBlock, 0, st>>>(sc, p, q);
                 }
             }
             cudaEventRecord(f->evw[3], st);
