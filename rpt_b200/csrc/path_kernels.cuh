@@ -172,9 +172,12 @@ RPTX_D void sample_lights_dev(const SceneDev& sc, const PathPool& p, uint32_t sl
                               d3 pos, d3 n, d3 wo, d3 mc, Rng& rng, d3* direct) {
     sample_lights_each<SURFACE>(sc, mat, md, pos, n, wo, mc, rng, direct, [&](uint32_t k, d3 wi, double dist, d3 c) {
         const size_t o = (size_t)k * p.n_slots + slot;
-        p.sdx[o] = wi.x; p.sdy[o] = wi.y; p.sdz[o] = wi.z;
-        p.sdist[o] = dist;
         p.scx[o] = c.x; p.scy[o] = c.y; p.scz[o] = c.z;
+        // a candidate that contributes exactly zero is never traced (k_shadow): its ray need not be stored
+        if (!(c.x == 0.0 && c.y == 0.0 && c.z == 0.0)) {
+            p.sdx[o] = wi.x; p.sdy[o] = wi.y; p.sdz[o] = wi.z;
+            p.sdist[o] = dist;
+        }
     });
 }
 
