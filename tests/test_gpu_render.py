@@ -285,3 +285,53 @@ def test_one_vertex_kernel_equals_three_kernels(monkeypatch):
         assert np.array_equal(out[0][0], out[1][0]), make.__name__
         assert out[0][1:] == out[1][1:], (make.__name__, out[0][1:], out[1][1:])
         assert out[0][4] == size[0] * size[1] * 5
+
+
+def _feature_scene(hdri=True):
+    """Everything off the BASELINE configs in one scene: HDRI environment with bilinear lookup
+    (src/environment.rs:25-52), thin-lens camera (src/camera.rs:71-77), mirror / transmissive / Phong materials
+    (src/material.rs:196-262), a sphere light, a point light and a plane."""
+    import math
+
+    from rpt_b200 import Camera, Hdri, Light, Material, Object, Scene, cube, hex_color, plane, sphere
+
+    s = Scene()
+    if hdri:
+        h, w = 16, 32
+        yy, xx = np.mgrid[0:h, 0:w]
+        buf = np.stack([0.2 + 0.8 * xx / w, 0.3 + 0.5 * yy / h, 0.9 - 0.6 * xx / w], axis=-1)
+        s.environment = Hdri(w, h, buf)
+    else:
+        s.environment = (0.05, 0.06, 0.08)
+    s.add(Object(sphere().translate((-2.2, 0.0, 0.0))).material(Material.mirror()))
+    s.add(Object(sphere().translate((0.0, 0.0, 0.0))).material(Material.clear(1.5)))
+    s.add(Object(sphere().translate((2.2, 0.0, 0.0))).material(Material.specular(hex_color(0x2A9D8F), 8.0)))
+    s.add(Object(cube().rotate_y(0.6).scale((1.0, 0.6, 1.0)).translate((0.5, -0.7, 2.0))).material(Material.transparent(hex_color(0xE9C46A), 1.3)))
+    s.add(Object(plane((0.0, 1.0, 0.0), -1.0)).material(Material.diffuse(hex_color(0xAAAAAA))))
+    glow = sphere().scale((0.5, 0.5, 0.5)).translate((0.0, 3.0, 1.0))
+    s.add(Object(glow).material(Material.light(hex_color(0xFFFFFF), 20.0)))
+    s.add(Light.Object(Object(glow).material(Material.light(hex_color(0xFFFFFF), 20.0))))
+    s.add(Light.Ambient((0.02, 0.02, 0.02)))
+    s.add(Light.Point((30.0, 30.0, 30.0), (3.0, 4.0, 4.0)))
+    cam = Camera.look_at((0.0, 1.5, 9.0), (0.0, 0.0, 0.0), (0.0, 1.0, 0.0), math.pi / 5.0).focus((0.0, 0.0, 0.0), 0.15)
+    return s, cam, dict(width=64, height=48, max_bounces=4, num_samples=4)
+
+
+def test_feature_scene_same_seed():
+    for hdri in (True, False):
+        scene, cam, d = _feature_scene(hdri)
+        film, of, match, rmse = _same_seed(scene, cam, d, 64, 48, 4)
+        assert match >= MIN_MATCH, (hdri, match)
+        assert rmse <= MAX_REL_RMSE, (hdri, rmse)
+        assert film.mean().mean() > 1e-3
+
+
+def test_colored_glowing_fog_same_seed():
+    """Medium::colored_glowing_fog (src/medium.rs:99-121): emission 10, colour by y > 250, phase pi / 4 (precedence quirk)."""
+    from rpt_b200 import Medium
+
+    scene, cam, d = scenes.lampshade("pathtrace")
+    scene.media[0] = Medium.colored_glowing_fog(5e-5, 3e-3)
+    film, of, match, rmse = _same_seed(scene, cam, d, 48, 48, 4)
+    assert match >= MIN_MATCH, match
+    assert rmse <= MAX_REL_RMSE, rmse
