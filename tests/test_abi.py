@@ -60,3 +60,25 @@ def test_product_does_not_import_the_oracle():
                 text = open(os.path.join(dirpath, f)).read()
                 for needle in ("liborc", "import orc", "oracle/", "orc_"):
                     assert needle not in text, f"rpt_b200/{f} references the oracle ({needle})"
+
+
+def test_rust_sys_crate_declares_the_same_abi():
+    """rust/rpt-cuda-sys/src/lib.rs (the binding a Rust `rpt` mirror links; not compiled here: no rustc) names exactly
+    the header's entry points, with the header's argument counts, and its #[repr(C)] records have the header's fields."""
+    rs = open(os.path.join(ROOT, "rust", "rpt-cuda-sys", "src", "lib.rs")).read()
+    rs_fns = {m.group(1): m.group(2) for m in re.finditer(r"pub fn (rptx_[a-z0-9_]+)\(([^;]*?)\)\s*(?:->[^;]+)?;", rs, flags=re.S)}
+    assert sorted(rs_fns) == _header_symbols()
+    htext = re.sub(r"/\*.*?\*/", "", open(os.path.join(ROOT, "include", "rptx.h")).read(), flags=re.S)
+    for name, args in rs_fns.items():
+        m = re.search(r"\b" + name + r"\s*\(([^;]*?)\)\s*;", htext, flags=re.S)
+        assert m, name
+        hargs = m.group(1).strip()
+        n_h = 0 if hargs in ("", "void") else hargs.count(",") + 1
+        n_r = 0 if not args.strip() else args.count(":")
+        assert n_h == n_r, (name, n_h, n_r)
+    assert f"RPTX_ABI_VERSION: c_int = {A.load().rptx_abi_version()}" in rs
+    for struct, ctype in (("rptx_shape_desc", A.ShapeDesc), ("rptx_material", A.MaterialDesc), ("rptx_light", A.LightDesc),
+                          ("rptx_camera", A.CameraDesc), ("rptx_params", A.Params)):
+        body = re.search(r"pub struct " + struct + r" \{(.*?)\n\}", rs, flags=re.S).group(1)
+        fields = re.findall(r"pub (\w+):", body)
+        assert fields == [f[0] for f in ctype._fields_], struct
