@@ -172,6 +172,18 @@ struct Camera {
 
 constexpr uint32_t kSmallSceneMax = 16;
 
+// What phase 1 of closest_hit_small (trace.cuh) reads, as part of the kernel parameters: every lane of a warp walks
+// these tables in step, so they are warp-uniform loads from the constant bank instead of dependent L1 hits
+// (31.8 cycles each at 16-32 warps per SM was what bound the small-scene kernels).  5.4 KB.
+struct SmallTables {
+    float4 boxes[2 * kSmallSceneMax];  // padded f32 world box of each bounded instance
+    float4 trif[3 * 64];               // TriF records (v0, e1, e2) in slot order
+    Affine inv[kSmallSceneMax];        // world -> local of each bounded instance
+    int kind[kSmallSceneMax];
+    int root_ref[kSmallSceneMax];
+    int has_transform[kSmallSceneMax];
+};
+
 struct SceneDev {
     const BvhNode* nodes;       // node pool: TLAS first, then BLASes
     const Instance* instances;  // sorted in TLAS leaf order, then unbounded ones
@@ -191,6 +203,7 @@ struct SceneDev {
     const float4* small_boxes;   // [n_bounded][2] padded f32 box of each bounded instance
     uint32_t small_kind_mask[3]; // instances of kSphere / kPlane / kCube, bit = instance index
     uint32_t small_unbounded_mask;
+    SmallTables small;           // valid when small_scene
     uint32_t shadow_probe_mask;  // bit k: k-th shadow-casting light is probed at its sample first (trace.cuh nee_visible)
     double wmin[3], wmax[3];    // padded world bounds of the bounded instances
     int medium_kind;

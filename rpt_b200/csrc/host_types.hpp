@@ -69,6 +69,7 @@ struct rptx_scene {
     float4* d_small_boxes = nullptr;
     uint32_t small_kind_mask[3] = {0, 0, 0};
     uint32_t small_unbounded_mask = 0;
+    rptx::SmallTables small_tables = {};
     int tlas_root_ref = 0;
     uint32_t n_bounded = 0, n_unbounded = 0, n_shadow_lights = 0, shadow_probe_mask = 0;
     double wmin[3] = {0, 0, 0}, wmax[3] = {0, 0, 0};

@@ -322,6 +322,7 @@ SceneDev scene_dev(const rptx_scene* s) {
     sc.small_slots = s->d_small_slots; sc.small_boxes = s->d_small_boxes;
     for (int k = 0; k < 3; k++) sc.small_kind_mask[k] = s->small_kind_mask[k];
     sc.small_unbounded_mask = s->small_unbounded_mask;
+    sc.small = s->small_tables;
     for (int k = 0; k < 3; k++) { sc.wmin[k] = s->wmin[k]; sc.wmax[k] = s->wmax[k]; sc.env_color[k] = s->env_color[k]; }
     sc.medium_kind = s->medium_kind; sc.sigma_a = s->sigma_a; sc.sigma_s = s->sigma_s;
     sc.env_is_hdri = s->env_is_hdri ? 1 : 0; sc.env_w = s->env_w; sc.env_h = s->env_h; sc.env_pixels = s->d_env;
@@ -657,6 +658,22 @@ int rptx_scene_commit(rptx_scene* s) {
             CK(upload(&d_slots, slots, st));
             CK(upload(&d_sboxes, sboxes, st));
             s->d_small_slots = d_slots; s->d_small_boxes = d_sboxes;
+            // kernel-parameter copy of the tables phase 1 of closest_hit_small walks (SmallTables, common.cuh)
+            SmallTables& t = s->small_tables;
+            std::memset(&t, 0, sizeof(t));
+            uint32_t slot = 0;
+            for (uint32_t i = 0; i < s->n_bounded; i++) {
+                const Instance& in = ordered[i];
+                t.kind[i] = in.kind; t.root_ref[i] = in.root_ref; t.has_transform[i] = in.has_transform; t.inv[i] = in.inv;
+                t.boxes[2 * i] = sboxes[2 * i]; t.boxes[2 * i + 1] = sboxes[2 * i + 1];
+                if (in.kind == kMesh) {
+                    const uint32_t code = (uint32_t)(~in.root_ref);
+                    const uint32_t first = code >> 3, count = (code & 7u) + 1u;
+                    CK(cudaMemcpyAsync(&t.trif[3 * slot], d_trif + in.tri_base + first, sizeof(TriF) * count, cudaMemcpyDeviceToHost, st));
+                    slot += count;
+                }
+            }
+            CK(cudaStreamSynchronize(st));
         }
     }
     uint32_t* d_cubes = nullptr;

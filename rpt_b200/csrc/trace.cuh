@@ -208,9 +208,7 @@ RPTX_DN bool monomial_test(double h, d3 o, d3 d, double t_min, double t_best, do
 // f64 test.
 constexpr float kPreEps = 4e-6f;
 RPTX_D float l1(float x, float y, float z) { return fabsf(x) + fabsf(y) + fabsf(z); }
-RPTX_D bool tri_maybe_hit(const TriF* __restrict__ tf, float ox, float oy, float oz, float dx, float dy, float dz) {
-    const float4* q = reinterpret_cast<const float4*>(tf);
-    const float4 v0 = __ldg(q), e1 = __ldg(q + 1), e2 = __ldg(q + 2);
+RPTX_D bool tri_maybe_hit_v(const float4 v0, const float4 e1, const float4 e2, float ox, float oy, float oz, float dx, float dy, float dz) {
     const float px = dy * e2.z - dz * e2.y, py = dz * e2.x - dx * e2.z, pz = dx * e2.y - dy * e2.x;  // d x e2
     const float det = e1.x * px + e1.y * py + e1.z * pz;
     const float tx = ox - v0.x, ty = oy - v0.y, tz = oz - v0.z;
@@ -229,6 +227,10 @@ RPTX_D bool tri_maybe_hit(const TriF* __restrict__ tf, float ox, float oy, float
     if (us < -e_u || vs < -e_v) return false;
     if (us + vs > adet + e_det + e_u + e_v) return false;
     return true;  // includes NaN/inf cases (all comparisons false)
+}
+RPTX_D bool tri_maybe_hit(const TriF* __restrict__ tf, float ox, float oy, float oz, float dx, float dy, float dz) {
+    const float4* q = reinterpret_cast<const float4*>(tf);
+    return tri_maybe_hit_v(__ldg(q), __ldg(q + 1), __ldg(q + 2), ox, oy, oz, dx, dy, dz);
 }
 
 // KdTree::intersect first clips the ray against the tree's bounding box with NaN-ignoring
@@ -486,24 +488,23 @@ RPTX_D void closest_hit_small(const SceneDev& sc, const RayD& ray, double t_min,
         float tbest = f32_up(hit.t - wshift);
         tbest = tbest + fabsf(tbest) * kSlabSlack;
         uint32_t slot = 0;
+        const SmallTables& st = sc.small;  // kernel parameters: warp-uniform constant-bank loads
         for (uint32_t idx = 0; idx < sc.n_bounded; idx++) {
-            const Instance* __restrict__ in = sc.instances + idx;
-            if (in->kind != kMesh) {  // warp-uniform
-                const float4 a = __ldg(sc.small_boxes + 2 * idx), b = __ldg(sc.small_boxes + 2 * idx + 1);
+            if (st.kind[idx] != kMesh) {  // warp-uniform
+                const float4 a = st.boxes[2 * idx], b = st.boxes[2 * idx + 1];
                 float tn;
                 if (axis || (world && slab_f32(a.x, a.y, a.z, b.x, b.y, b.z, rf, tbest, &tn, tlow))) box_cand |= 1u << idx;
                 continue;
             }
-            const uint32_t code = (uint32_t)(~in->root_ref);
-            const uint32_t first = code >> 3, count = (code & 7u) + 1u;
+            const uint32_t count = ((uint32_t)(~st.root_ref[idx]) & 7u) + 1u;
             d3 lo = ray.o, ld = ray.d;
-            if (in->has_transform) { lo = xform_point(in->inv, ray.o); ld = xform_dir(in->inv, ray.d); }
-            const bool rejected = (ld.x == 0.0 || ld.y == 0.0 || ld.z == 0.0) && mesh_bounds_nan_reject(in, lo, ld);
+            if (st.has_transform[idx]) { lo = xform_point(st.inv[idx], ray.o); ld = xform_dir(st.inv[idx], ray.d); }
+            const bool rejected = (ld.x == 0.0 || ld.y == 0.0 || ld.z == 0.0) && mesh_bounds_nan_reject(sc.instances + idx, lo, ld);
             const float fox = (float)lo.x, foy = (float)lo.y, foz = (float)lo.z;
             const float fdx = (float)ld.x, fdy = (float)ld.y, fdz = (float)ld.z;
-            const TriF* __restrict__ trif = sc.trif + in->tri_base + first;
             for (uint32_t i = 0; i < count; i++, slot++)
-                if (!rejected && tri_maybe_hit(trif + i, fox, foy, foz, fdx, fdy, fdz)) tri_cand |= 1ull << slot;
+                if (!rejected && tri_maybe_hit_v(st.trif[3 * slot], st.trif[3 * slot + 1], st.trif[3 * slot + 2], fox, foy, foz, fdx, fdy, fdz))
+                    tri_cand |= 1ull << slot;
         }
     }
     // ---- phase 2: exact tests, each lane on its own candidates ----
