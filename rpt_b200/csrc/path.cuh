@@ -28,7 +28,9 @@ struct PathPool {
     // vertex being assembled
     double *dirx, *diry, *dirz;                  // direct light of the current vertex (medium mode)
     double *fx, *fy, *fz;                        // continuation weight (medium mode)
-    double *sdx, *sdy, *sdz, *sdist, *scx, *scy, *scz;  // [n_shadow][n_slots] NEE candidates
+    // NEE candidates, one 64-byte record per [light][slot]: {c.xyz, dist | d.xyz, -}.  Whole 32-byte sectors only: the
+    // contribution (always written / read) in the first, the shadow ray (jobs that are traced) in the second.
+    double* sjob;
     // forward accumulation (medium mode): throughput and radiance
     double *bx, *by, *bz, *lx, *ly, *lz;
     // per-level records for the clamped back-fold (surface mode): [n_slots][stack_depth][8]
@@ -50,6 +52,28 @@ RPTX_HD uint32_t pool_pixel(const PathPool& p, uint32_t slot) {
 }
 
 enum PathFlags : uint32_t { kFlagTerminate = 1u, kFlagHasShadow = 2u };
+
+RPTX_D void job_store_c(const PathPool& p, size_t o, d3 c, double dist) {
+    double2* r = reinterpret_cast<double2*>(p.sjob + o * 8);
+    r[0] = make_double2(c.x, c.y);
+    r[1] = make_double2(c.z, dist);
+}
+RPTX_D void job_store_d(const PathPool& p, size_t o, d3 d) {
+    double2* r = reinterpret_cast<double2*>(p.sjob + o * 8);
+    r[2] = make_double2(d.x, d.y);
+    r[3] = make_double2(d.z, 0.0);
+}
+RPTX_D d3 job_load_c(const PathPool& p, size_t o, double* dist) {
+    const double2* r = reinterpret_cast<const double2*>(p.sjob + o * 8);
+    const double2 a = r[0], b = r[1];
+    *dist = b.y;
+    return mk3(a.x, a.y, b.x);
+}
+RPTX_D d3 job_load_d(const PathPool& p, size_t o) {
+    const double2* r = reinterpret_cast<const double2*>(p.sjob + o * 8);
+    const double2 a = r[2], b = r[3];
+    return mk3(a.x, a.y, b.x);
+}
 
 struct Queues {
     uint32_t* cur;        // slot ids to process this wave

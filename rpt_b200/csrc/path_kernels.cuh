@@ -172,12 +172,9 @@ RPTX_D void sample_lights_dev(const SceneDev& sc, const PathPool& p, uint32_t sl
                               d3 pos, d3 n, d3 wo, d3 mc, Rng& rng, d3* direct) {
     sample_lights_each<SURFACE>(sc, mat, md, pos, n, wo, mc, rng, direct, [&](uint32_t k, d3 wi, double dist, d3 c) {
         const size_t o = (size_t)k * p.n_slots + slot;
-        p.scx[o] = c.x; p.scy[o] = c.y; p.scz[o] = c.z;
+        job_store_c(p, o, c, dist);
         // a candidate that contributes exactly zero is never traced (k_shadow): its ray need not be stored
-        if (!(c.x == 0.0 && c.y == 0.0 && c.z == 0.0)) {
-            p.sdx[o] = wi.x; p.sdy[o] = wi.y; p.sdz[o] = wi.z;
-            p.sdist[o] = dist;
-        }
+        if (!(c.x == 0.0 && c.y == 0.0 && c.z == 0.0)) job_store_d(p, o, wi);
     });
 }
 
@@ -379,7 +376,8 @@ __global__ void __launch_bounds__(kBlock, SMALL ? RPTX_OCC_SHADOW_SMALL : RPTX_O
                 c[r] = mk3(0, 0, 0);
                 if (has[r]) {
                     const size_t off = (size_t)k * p.n_slots + slot[r];
-                    c[r] = mk3(p.scx[off], p.scy[off], p.scz[off]);
+                    double dist_unused;
+                    c[r] = job_load_c(p, off, &dist_unused);
                     my_queries++;
                 }
                 job[r] = has[r] && !(c[r].x == 0.0 && c[r].y == 0.0 && c[r].z == 0.0);
@@ -413,8 +411,9 @@ __global__ void __launch_bounds__(kBlock, SMALL ? RPTX_OCC_SHADOW_SMALL : RPTX_O
                 const size_t off = (size_t)k * p.n_slots + js;
                 RayD ray;
                 ray.o = mk3(p.ox[js], p.oy[js], p.oz[js]);
-                ray.d = mk3(p.sdx[off], p.sdy[off], p.sdz[off]);
-                const double dist = p.sdist[off];
+                ray.d = job_load_d(p, off);
+                double dist;
+                job_load_c(p, off, &dist);
                 my_traced++;
                 if (nee_visible<PROBE, SMALL>(sc, ray, dist, &my_occl)) {
                     // direct += contribution, in light order like the reference's loop
@@ -458,8 +457,9 @@ __global__ void __launch_bounds__(kBlock, SMALL ? RPTX_OCC_SHADOW_SMALL : RPTX_O
             const size_t off = (size_t)k * p.n_slots + js;
             RayD ray;
             ray.o = mk3(p.ox[js], p.oy[js], p.oz[js]);
-            ray.d = mk3(p.sdx[off], p.sdy[off], p.sdz[off]);
-            const double dist = p.sdist[off];
+            ray.d = job_load_d(p, off);
+            double dist;
+            job_load_c(p, off, &dist);
             my_traced++;
             if (nee_visible<PROBE, SMALL>(sc, ray, dist, &my_occl)) {
                 // direct += contribution, in light order like the reference's loop
@@ -506,7 +506,8 @@ __global__ void __launch_bounds__(kBlock, SMALL ? RPTX_OCC_SHADOW_SMALL : RPTX_O
                 d3 c = mk3(0, 0, 0);
                 if (has) {
                     const size_t off = (size_t)k * p.n_slots + slot;
-                    c = mk3(p.scx[off], p.scy[off], p.scz[off]);
+                    double dist_unused;
+                    c = job_load_c(p, off, &dist_unused);
                     my_queries++;
                 }
                 const bool job = has && !(c.x == 0.0 && c.y == 0.0 && c.z == 0.0);

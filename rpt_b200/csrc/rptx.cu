@@ -740,8 +740,7 @@ static void film_carve(rptx_film* f, Carver& c) {
     if (gather_only) dptrs = {&p.ax, &p.ay, &p.az};
     for (double** d : dptrs) c.take(d, ns);
     if (!gather_only) {
-        std::vector<double**> sptrs = {&p.sdx, &p.sdy, &p.sdz, &p.sdist, &p.scx, &p.scy, &p.scz};
-        for (double** d : sptrs) c.take(d, ns * std::max<uint32_t>(p.n_shadow, 1));
+        c.take(&p.sjob, ns * std::max<uint32_t>(p.n_shadow, 1) * 8);
         if (p.record_mode) {  // surface mode: the vertex lives in its 64-byte level record
             c.take(&p.stack, ns * p.rec_stride * std::max<uint32_t>(p.stack_depth, 1));
         } else {              // medium mode: forward accumulation
