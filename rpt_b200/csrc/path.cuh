@@ -26,13 +26,12 @@ struct PathPool {
     uint32_t* depth;
     uint32_t* flags;
     // vertex being assembled
-    double *dirx, *diry, *dirz;                  // direct light of the current vertex (medium mode)
-    double *fx, *fy, *fz;                        // continuation weight (medium mode)
+    // medium mode, 64-byte records per slot (whole sectors instead of twelve 8-byte streams):
+    double* mvtx;   // vertex being assembled: {direct.xyz, - | continuation weight f.xyz, -}
+    double* mpath;  // forward accumulation: {throughput beta.xyz, - | radiance L.xyz, -}
     // NEE candidates, one 64-byte record per [light][slot]: {c.xyz, dist | d.xyz, -}.  Whole 32-byte sectors only: the
     // contribution (always written / read) in the first, the shadow ray (jobs that are traced) in the second.
     double* sjob;
-    // forward accumulation (medium mode): throughput and radiance
-    double *bx, *by, *bz, *lx, *ly, *lz;
     // per-level records for the clamped back-fold (surface mode): [n_slots][stack_depth][8]
     double* stack;
     // lane film: sum of finished samples of this slot in the current batch
@@ -72,6 +71,17 @@ RPTX_D d3 job_load_c(const PathPool& p, size_t o, double* dist) {
 RPTX_D d3 job_load_d(const PathPool& p, size_t o) {
     const double2* r = reinterpret_cast<const double2*>(p.sjob + o * 8);
     const double2 a = r[2], b = r[3];
+    return mk3(a.x, a.y, b.x);
+}
+
+RPTX_D void rec_store(double* base, uint32_t slot, int half, d3 v) {
+    double2* r = reinterpret_cast<double2*>(base + (size_t)slot * 8 + half * 4);
+    r[0] = make_double2(v.x, v.y);
+    r[1] = make_double2(v.z, 0.0);
+}
+RPTX_D d3 rec_load(const double* base, uint32_t slot, int half) {
+    const double2* r = reinterpret_cast<const double2*>(base + (size_t)slot * 8 + half * 4);
+    const double2 a = r[0], b = r[1];
     return mk3(a.x, a.y, b.x);
 }
 

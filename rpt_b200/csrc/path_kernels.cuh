@@ -83,8 +83,8 @@ RPTX_D void start_path(const PathPool& p, const BatchParams& bp, const Camera& c
     p.depth[slot] = 0;
     p.flags[slot] = 0;
     if (MEDIUM) {
-        p.bx[slot] = 1.0; p.by[slot] = 1.0; p.bz[slot] = 1.0;
-        p.lx[slot] = 0.0; p.ly[slot] = 0.0; p.lz[slot] = 0.0;
+        rec_store(p.mpath, slot, 0, mk3(1.0, 1.0, 1.0));
+        rec_store(p.mpath, slot, 1, mk3(0.0, 0.0, 0.0));
     }
 }
 
@@ -273,9 +273,8 @@ __global__ void __launch_bounds__(kShadeBlock, RPTX_OCC_SHADE) k_shade(const __g
             const double ph_p = md.phase;
             const double sa = md.sigma_s / md.extinction();
             // indirect = ((sa * L) / ph_p) (.) mc * phase / rr_p
-            p.fx[slot] = ((sa / ph_p) * mc.x * md.phase) / kRrMedium;
-            p.fy[slot] = ((sa / ph_p) * mc.y * md.phase) / kRrMedium;
-            p.fz[slot] = ((sa / ph_p) * mc.z * md.phase) / kRrMedium;
+            rec_f = mk3(((sa / ph_p) * mc.x * md.phase) / kRrMedium, ((sa / ph_p) * mc.y * md.phase) / kRrMedium,
+                        ((sa / ph_p) * mc.z * md.phase) / kRrMedium);
             p.dx[slot] = wi.x; p.dy[slot] = wi.y; p.dz[slot] = wi.z;
         } else {
             flags |= kFlagTerminate;
@@ -303,7 +302,7 @@ __global__ void __launch_bounds__(kShadeBlock, RPTX_OCC_SHADE) k_shade(const __g
                 const double ac = fabs(dot(wi, n));
                 if (MEDIUM) {
                     const double s = 1.0 / (pdf * kRrMedium);
-                    p.fx[slot] = s * f.x * ac; p.fy[slot] = s * f.y * ac; p.fz[slot] = s * f.z * ac;
+                    rec_f = mk3(s * f.x * ac, s * f.y * ac, s * f.z * ac);
                 } else {
                     rec_f = f; rec_pdf = pdf; rec_ac = ac;
                 }
@@ -315,7 +314,8 @@ __global__ void __launch_bounds__(kShadeBlock, RPTX_OCC_SHADE) k_shade(const __g
         if (!go) flags |= kFlagTerminate;
     }
     if (MEDIUM) {
-        p.dirx[slot] = direct.x; p.diry[slot] = direct.y; p.dirz[slot] = direct.z;
+        rec_store(p.mvtx, slot, 0, direct);
+        if (!(flags & kFlagTerminate)) rec_store(p.mvtx, slot, 1, rec_f);
     } else {
         // surface mode assembles the vertex directly in its level record of the clamp stack
         // ([slot][depth]{direct, f, pdf, |cos|}, 64 B): k_shadow adds the visible light samples to `direct`
@@ -423,7 +423,7 @@ __global__ void __launch_bounds__(kBlock, SMALL ? RPTX_OCC_SHADOW_SMALL : RPTX_O
                         rec[0] = make_double2(a.x + cj.x, a.y + cj.y);
                         rec[1] = make_double2(b.x + cj.z, b.y);
                     } else {
-                        p.dirx[js] += cj.x; p.diry[js] += cj.y; p.dirz[js] += cj.z;
+                        rec_store(p.mvtx, js, 0, rec_load(p.mvtx, js, 0) + cj);
                     }
                 }
             }
@@ -469,7 +469,7 @@ __global__ void __launch_bounds__(kBlock, SMALL ? RPTX_OCC_SHADOW_SMALL : RPTX_O
                     rec[0] = make_double2(a.x + cj.x, a.y + cj.y);
                     rec[1] = make_double2(b.x + cj.z, b.y);
                 } else {
-                    p.dirx[js] += cj.x; p.diry[js] += cj.y; p.dirz[js] += cj.z;
+                    rec_store(p.mvtx, js, 0, rec_load(p.mvtx, js, 0) + cj);
                 }
             }
         }
@@ -550,11 +550,12 @@ RPTX_D bool connect_vertex(const PathPool& p, const BatchParams& bp, const Camer
     const bool finished = (flags & kFlagTerminate) != 0;
     d3 L;
     if (MEDIUM) {
-        const d3 beta = mk3(p.bx[slot], p.by[slot], p.bz[slot]);
-        L = mk3(p.lx[slot], p.ly[slot], p.lz[slot]) + cmul(beta, direct);
+        const d3 beta = rec_load(p.mpath, slot, 0);
+        L = rec_load(p.mpath, slot, 1) + cmul(beta, direct);
         if (!finished) {
-            p.lx[slot] = L.x; p.ly[slot] = L.y; p.lz[slot] = L.z;
-            p.bx[slot] = beta.x * p.fx[slot]; p.by[slot] = beta.y * p.fy[slot]; p.bz[slot] = beta.z * p.fz[slot];
+            const d3 f = rec_load(p.mvtx, slot, 1);
+            rec_store(p.mpath, slot, 1, L);
+            rec_store(p.mpath, slot, 0, mk3(beta.x * f.x, beta.y * f.y, beta.z * f.z));
         }
     } else {
         // per-slot stack, one 64-byte record per level: [slot][level]{direct, f, pdf, |cos|}.  Only the
@@ -598,7 +599,7 @@ __global__ void __launch_bounds__(kBlock) k_connect(PathPool p, Queues q, BatchP
         uint32_t slot = 0;
         if (i < count) {
             slot = q.cur[i];
-            const d3 direct = MEDIUM ? mk3(p.dirx[slot], p.diry[slot], p.dirz[slot]) : mk3(0, 0, 0);
+            const d3 direct = MEDIUM ? rec_load(p.mvtx, slot, 0) : mk3(0, 0, 0);
             alive = connect_vertex<MEDIUM>(p, bp, cam, slot, direct, &my_started);
             q.keep[i] = alive ? 1 : 0;
         }

@@ -744,8 +744,8 @@ static void film_carve(rptx_film* f, Carver& c) {
         if (p.record_mode) {  // surface mode: the vertex lives in its 64-byte level record
             c.take(&p.stack, ns * p.rec_stride * std::max<uint32_t>(p.stack_depth, 1));
         } else {              // medium mode: forward accumulation
-            std::vector<double**> mptrs = {&p.dirx, &p.diry, &p.dirz, &p.fx, &p.fy, &p.fz, &p.bx, &p.by, &p.bz, &p.lx, &p.ly, &p.lz};
-            for (double** d : mptrs) c.take(d, ns);
+            c.take(&p.mvtx, ns * 8);
+            c.take(&p.mpath, ns * 8);
         }
         c.take(&p.hobj, ns); c.take(&p.rng, ns); c.take(&p.sample_j, ns); c.take(&p.depth, ns); c.take(&p.flags, ns);
         c.take(&f->q.cur, ns); c.take(&f->q.next, ns); c.take(&f->q.keep, ns);
