@@ -21,7 +21,11 @@ struct rptx_ctx {
     // (cudaMalloc of 23 GB costs ~50 ms; iterative_render / repeated render() calls would pay it every time).
     void* spare_arena = nullptr;
     size_t spare_arena_bytes = 0;
+    // multi-GPU: NCCL communicator of this rank (comm.cu), null for a single-device context
+    struct rptx_comm* comm = nullptr;
 };
+
+constexpr uint32_t kMaxBounces = 4096;  // rptx_params::max_bounces above this is rejected (the clamp stack is 64 B per level and slot)
 
 struct HostMesh {
     std::vector<rptx::RawTri> tris;  // original order
@@ -75,7 +79,7 @@ struct rptx_scene {
     double wmin[3] = {0, 0, 0}, wmax[3] = {0, 0, 0};
 };
 
-enum FilmMode : int { kFilmWavefront = 0, kFilmFused = 1, kFilmGather = 2 };
+enum FilmMode : int { kFilmWavefront = 0, kFilmFused = 1, kFilmGather = 2, kFilmPersist = 3 };
 
 struct rptx_film {
     rptx_ctx* ctx = nullptr;
@@ -88,6 +92,8 @@ struct rptx_film {
     rptx_params params;
     rptx::Camera cam;
     rptx::PathPool pool;
+    double* d_pstack = nullptr;    // persistent kernel, surface mode: clamp records [level][thread] (persist.cuh)
+    int persist_blocks = 0;        // grid of the persistent kernel (resident blocks of the device)
     rptx::Queues q;
     std::vector<void*> owned;
     double* d_batch_sum = nullptr;
@@ -115,4 +121,6 @@ namespace rptx_host {
 int ctx_fail(rptx_ctx* ctx, const std::string& msg);  // records the message, returns 1
 rptx::SceneDev scene_dev(const rptx_scene* s);
 rptx::MediumDev medium_dev(const rptx_scene* s);
+// persist.cu
+int persist_grid(int sm_count, bool medium, bool probe, bool small);
 }  // namespace rptx_host

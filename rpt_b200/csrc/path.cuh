@@ -8,6 +8,25 @@
 
 namespace rptx {
 
+constexpr int kBlock = 128;
+
+RPTX_D uint32_t lane_id() { return threadIdx.x & 31u; }
+RPTX_D void prefetch_l2(const void* ptr) { asm volatile("prefetch.global.L2 [%0];" ::"l"(ptr)); }
+
+// one atomic per warp for the run counters (a per-thread atomic on one address serialises)
+RPTX_D void stat_add(unsigned long long* __restrict__ dst, unsigned long long v) {
+    const unsigned active = __activemask();
+    const unsigned total = __reduce_add_sync(active, (unsigned)v);  // per-thread counts are small
+    if (lane_id() == (uint32_t)(__ffs(active) - 1) && total) atomicAdd(dst, (unsigned long long)total);
+}
+
+// same for counts that may exceed 32 bits per warp
+RPTX_D void stat_add64(unsigned long long* __restrict__ dst, unsigned long long v) {
+    const unsigned active = __activemask();
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(active, v, o);
+    if (lane_id() == 0 && v) atomicAdd(dst, v);
+}
+
 struct PathPool {
     uint32_t n_slots, n_pixels, n_lanes, n_shadow;  // n_shadow = non-ambient, non-directional lights
     uint32_t stack_depth;                           // max_bounces + 1 (surface mode only)

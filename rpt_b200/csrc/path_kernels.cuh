@@ -37,25 +37,6 @@
 
 namespace rptx {
 
-constexpr int kBlock = 128;
-
-RPTX_D uint32_t lane_id() { return threadIdx.x & 31u; }
-RPTX_D void prefetch_l2(const void* ptr) { asm volatile("prefetch.global.L2 [%0];" ::"l"(ptr)); }
-
-// one atomic per warp for the run counters (a per-thread atomic on one address serialises)
-RPTX_D void stat_add(unsigned long long* __restrict__ dst, unsigned long long v) {
-    const unsigned active = __activemask();
-    const unsigned total = __reduce_add_sync(active, (unsigned)v);  // per-thread counts are small
-    if (lane_id() == (uint32_t)(__ffs(active) - 1) && total) atomicAdd(dst, (unsigned long long)total);
-}
-
-// same for counts that may exceed 32 bits per warp
-RPTX_D void stat_add64(unsigned long long* __restrict__ dst, unsigned long long v) {
-    const unsigned active = __activemask();
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(active, v, o);
-    if (lane_id() == 0 && v) atomicAdd(dst, v);
-}
-
 // warp-ballot compaction: append `slot` of every lane with pred to q, one atomic per warp
 RPTX_D void queue_push(uint32_t* __restrict__ q, uint32_t* __restrict__ count, bool pred, uint32_t slot) {
     const unsigned active = __activemask();

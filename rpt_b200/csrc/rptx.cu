@@ -16,6 +16,7 @@
 #include "bvh_sah.hpp"
 #include "host_types.hpp"
 #include "path_kernels.cuh"
+#include "persist.cuh"
 
 using namespace rptx;
 
@@ -335,6 +336,11 @@ SceneDev scene_dev(const rptx_scene* s) {
 using rptx_host::medium_dev;
 using rptx_host::scene_dev;
 
+namespace rptx_host {
+cudaError_t launch_path_persist(bool medium, bool probe, bool small, int blocks, const SceneDev& sc, const MediumDev& md, const PersistArgs& a,
+                                unsigned long long* stats, cudaStream_t st);
+}
+
 extern "C" {
 
 int rptx_abi_version(void) { return RPTX_ABI_VERSION; }
@@ -555,11 +561,6 @@ int rptx_scene_commit(rptx_scene* s) {
         CK(cudaStreamSynchronize(st));
         rptx_free_async(d_boxes, st); rptx_free_async(d_perm, st);
     }
-    if (!s->meshes.empty()) {
-        // light sampling reads face normals from the raw pool: pull the computed ones back
-        // is unnecessary on the host; the device copy is authoritative.
-    }
-
     // 2. instances
     std::vector<Instance> bounded, unbounded;
     std::vector<PrimBox> boxes;
@@ -751,6 +752,8 @@ static void film_carve(rptx_film* f, Carver& c) {
         c.take(&f->q.cur, ns); c.take(&f->q.next, ns); c.take(&f->q.keep, ns);
         c.take(&f->d_select_tmp, f->select_tmp_bytes);
     }
+    if (f->mode == kFilmPersist && p.record_mode)
+        c.take(&f->d_pstack, (size_t)f->persist_blocks * kBlock * 8 * std::max<uint32_t>(p.stack_depth, 1));
     c.take(&f->q.counters, 8);
     c.take(&f->q.stats, 8);
     const size_t n3 = (size_t)p.n_pixels * 3;
@@ -800,6 +803,7 @@ static int choose_path_mode(const rptx_scene* s, const rptx_params* p) {
     const char* env = std::getenv("RPTX_PATH_MODE");
     if (env && std::strcmp(env, "wavefront") == 0) return kFilmWavefront;
     if (env && std::strcmp(env, "fused") == 0 && fits) return kFilmFused;
+    if (env && std::strcmp(env, "persist") == 0) return kFilmPersist;
     // measured (profiles/r1_v2_summary.md): the fused kernel wins only for one-vertex paths on small
     // scenes (teapot, max_bounces 0: +33 %); with bounces the wavefront's compaction wins 3-7x
     size_t tris = 0;
@@ -817,6 +821,7 @@ static int film_begin(rptx_ctx* ctx, rptx_scene* scene, const rptx_camera* camer
     if (!scene->committed) return ctx_fail(ctx, "scene not committed");
     if (params->width == 0 || params->height == 0) return ctx_fail(ctx, "empty image");
     if (params->shard_count == 0 || params->shard_index >= params->shard_count) return ctx_fail(ctx, "bad shard");
+    if (params->max_bounces > kMaxBounces) return ctx_fail(ctx, "max_bounces above 4096 is not supported");
     CK(cudaSetDevice(ctx->device));
     rptx_film* f = new rptx_film();
     f->ctx = ctx; f->scene = scene; f->params = *params;
@@ -832,7 +837,7 @@ static int film_begin(rptx_ctx* ctx, rptx_scene* scene, const rptx_camera* camer
     if (n_pixels >= (1ull << 31)) { delete f; return ctx_fail(ctx, "image too large"); }
     p.n_pixels = (uint32_t)n_pixels;
     p.width = params->width;
-    p.tiled = f->mode == kFilmWavefront && params->width % 8 == 0 && params->height % 4 == 0 && !std::getenv("RPTX_LINEAR_PIXELS");
+    p.tiled = (f->mode == kFilmWavefront || f->mode == kFilmPersist) && params->width % 8 == 0 && params->height % 4 == 0 && !std::getenv("RPTX_LINEAR_PIXELS");
     p.n_shadow = scene->n_shadow_lights;
     p.stack_depth = scene->medium_kind == RPTX_MEDIUM_NONE ? params->max_bounces + 1 : 1;
     p.record_mode = scene->medium_kind == RPTX_MEDIUM_NONE;
@@ -849,13 +854,23 @@ static int film_begin(rptx_ctx* ctx, rptx_scene* scene, const rptx_camera* camer
         size_t free_b = 0, total_b = 0;
         CK(cudaMemGetInfo(&free_b, &total_b));
         target = 1ull << 25;
-        while (target > (1ull << 21) && target * slot_bytes > free_b / 4) target >>= 1;
+        // deep clamp stacks (64 B x (max_bounces + 1) per slot) may take the pool below 2^21 slots, down to one lane
+        while (target > n_pixels && target * slot_bytes > free_b / 4) target >>= 1;
+    }
+    if (f->mode == kFilmPersist) {
+        // slots (pixel, sample lane) are claimed by the resident threads of ONE launch; ~128 per thread keep the tail
+        // (threads that run out of slots while others still walk theirs) under a percent of the batch
+        const bool small = scene->small_scene && !std::getenv("RPTX_NO_SMALL_SCENE");
+        f->persist_blocks = rptx_host::persist_grid(ctx->sm_count, scene->medium_kind != RPTX_MEDIUM_NONE, scene->shadow_probe_mask != 0, small);
+        if (const char* e = std::getenv("RPTX_PERSIST_BLOCKS")) f->persist_blocks = std::max(1, std::atoi(e));  // developer knob
+        target = 128ull * (uint64_t)f->persist_blocks * kBlock;
     }
     if (const char* e = std::getenv("RPTX_POOL_LOG2")) {  // developer knob: paths in flight
         const int v = std::atoi(e);
         if (v >= 10 && v <= 26) target = 1ull << v;
     }
     uint64_t lanes = std::max<uint64_t>(1, target / n_pixels);
+    if (f->mode == kFilmPersist) lanes = std::max<uint64_t>(1, (target + n_pixels - 1) / n_pixels);
     lanes = std::min<uint64_t>(lanes, 4096);
     lanes = std::min<uint64_t>(lanes, std::max<uint32_t>(params->num_samples, 1));
     p.n_lanes = (uint32_t)lanes;
@@ -998,7 +1013,25 @@ int rptx_render_sample_trace(rptx_film* f, uint32_t iterations) {
     const uint32_t full_lanes = p.n_lanes;
     p.n_lanes = std::max<uint32_t>(1, std::min(full_lanes, bp.n_local));
     int rc = 0;
-    if (f->mode == kFilmFused) {
+    if (f->mode == kFilmPersist) {
+        const SceneDev sc = scene_dev(f->scene);
+        const MediumDev md = medium_dev(f->scene);
+        PersistArgs pa;
+        std::memset(&pa, 0, sizeof(pa));
+        pa.cam = f->cam; pa.bp = bp; pa.n_pixels = p.n_pixels; pa.n_lanes = p.n_lanes; pa.n_slots = p.n_pixels * p.n_lanes;
+        pa.width = p.width; pa.tiled = p.tiled; pa.stack_depth = p.stack_depth;
+        pa.ax = p.ax; pa.ay = p.ay; pa.az = p.az; pa.stack = f->d_pstack; pa.next_slot = f->q.counters;
+        if (bp.n_local == 0) {  // this rank holds no sample of the batch
+            for (double* a : {p.ax, p.ay, p.az}) CK(cudaMemsetAsync(a, 0, sizeof(double) * pa.n_slots, st));
+        } else {
+            CK(cudaMemsetAsync(f->q.counters, 0, sizeof(uint32_t) * 8, st));
+            cudaError_t e = rptx_host::launch_path_persist(f->scene->medium_kind != RPTX_MEDIUM_NONE, sc.shadow_probe_mask != 0, sc.small_scene != 0,
+                                                           f->persist_blocks, sc, md, pa, f->q.stats, st);
+            ctx->launches++;
+            f->stats.waves++;
+            if (e != cudaSuccess) rc = ctx_fail(ctx, std::string("k_path_persist: ") + cudaGetErrorString(e));
+        }
+    } else if (f->mode == kFilmFused) {
         FusedArgs fa;
         fa.cam = f->cam; fa.bp = bp; fa.n_pixels = p.n_pixels; fa.n_lanes = p.n_lanes;
         fa.ax = p.ax; fa.ay = p.ay; fa.az = p.az;
@@ -1053,6 +1086,9 @@ int rptx_render_sample_commit(rptx_film* f, uint32_t iterations) {
 }
 
 int rptx_render_sample(rptx_film* f, uint32_t iterations) {
+    // a sharded film holds 1 / shard_count of the batch: committing it without the exchange would dim the image
+    if (f && f->params.shard_count > 1 && !f->ctx->comm)
+        return ctx_fail(f->ctx, "sharded films must use rptx_render_sample_trace + all-reduce + rptx_render_sample_commit, or a context with rptx_comm_init");
     if (int rc = rptx_render_sample_trace(f, iterations)) return rc;
     return rptx_render_sample_commit(f, iterations);
 }

@@ -13,11 +13,11 @@ import numpy as np
 from .scene import KdTree, Mesh, cube, hex_color, plane, polygon, sphere
 from .world import Camera, Light, Material, Medium, Object, Scene
 
-_TEAPOT = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "tests", "golden", "teapot_tris.npz")
+_TEAPOT = os.path.join(os.path.dirname(os.path.abspath(__file__)), "assets", "teapot_tris.npz")
 
 
 def teapot_mesh(path=None):
-    """The examples' teapot.obj as a Mesh.  Read from the committed triangle fixture (derived
+    """The examples' teapot.obj as a Mesh.  Read from the packaged triangle asset rpt_b200/assets/teapot_tris.npz (derived
     from the reference asset by tests/golden/make_fixtures.py) or from an .obj given by path /
     $RPTX_TEAPOT_OBJ."""
     path = path or os.environ.get("RPTX_TEAPOT_OBJ")

@@ -1,4 +1,4 @@
-"""Generates tests/golden/teapot_tris.npz from the reference's mesh asset.
+"""Generates rpt_b200/assets/teapot_tris.npz from the reference's mesh asset.
 
 Run in the build container only (reads /root/reference, which the GPU box does not have):
     python tests/golden/make_fixtures.py
@@ -13,7 +13,7 @@ import numpy as np
 sys.path.insert(0, os.path.join(os.path.dirname(__file__), "..", ".."))
 from rpt_b200.io import load_obj  # noqa: E402
 
-HERE = os.path.dirname(os.path.abspath(__file__))
+HERE = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "..", "rpt_b200", "assets")
 
 
 def main():

@@ -24,7 +24,7 @@ MIN_MATCH = 0.97
 MAX_REL_RMSE = 2e-2  # whole-image relative RMSE bound at equal seed (flipped samples only)
 
 
-@pytest.fixture(params=["wavefront", "fused"], autouse=True)
+@pytest.fixture(params=["wavefront", "fused", "persist"], autouse=True)
 def path_mode(request, monkeypatch):
     """Every test here runs against both kernel sets (RPTX_PATH_MODE is read at render begin)."""
     monkeypatch.setenv("RPTX_PATH_MODE", request.param)
@@ -150,7 +150,7 @@ def test_fused_equals_wavefront(monkeypatch):
     for name in ("cornell", "lampshade", "teapot"):
         scene, cam, d = getattr(scenes, name)() if name != "lampshade" else scenes.lampshade("pathtrace")
         means, modes = [], []
-        for mode in ("wavefront", "fused"):
+        for mode in ("wavefront", "fused", "persist"):
             monkeypatch.setenv("RPTX_PATH_MODE", mode)
             f = scenes.make_renderer(scene, cam, d, width=40, height=30, num_samples=3, seed=9, max_bounces=3).begin()
             f.sample(3)
@@ -158,8 +158,9 @@ def test_fused_equals_wavefront(monkeypatch):
             modes.append(f.stats()["path_mode"])
             st = f.stats()
             assert st["path_samples"] == 40 * 30 * 3
-        assert modes == [0, 1]
+        assert modes == [0, 1, 3]
         assert np.allclose(means[0], means[1], rtol=1e-12, atol=1e-300), name
+        assert np.allclose(means[0], means[2], rtol=1e-12, atol=1e-300), name
 
 
 def test_list_walk_equals_hierarchy(monkeypatch):

@@ -163,7 +163,7 @@ def test_monomial_surface_lowering():
 
 
 def test_teapot_fixture_is_the_reference_asset():
-    z = np.load(os.path.join(HERE, "golden", "teapot_tris.npz"))
+    z = np.load(os.path.join(HERE, "..", "rpt_b200", "assets", "teapot_tris.npz"))
     assert z["vertices"].shape == (2256, 3, 3) and z["normals"].shape == (2256, 3, 3)
     if os.path.exists("/root/reference/examples/teapot.obj"):  # build container only
         m = load_obj("/root/reference/examples/teapot.obj")
