@@ -214,8 +214,11 @@ class Box:
             dist.init_process_group("nccl", device_id=torch.device("cuda", self.local))
             self.dist = dist
         from rpt_b200 import Context
+        from rpt_b200 import dist as rd
 
         self.ctx = Context(self.local)
+        if self.world > 1 and not os.environ.get("RPTX_TORCH_COLLECTIVES"):
+            rd.init_comm(self.ctx)  # the library's own NCCL communicator: the exchanges run inside librptx.so
 
     def barrier(self):
         if self.dist is not None:

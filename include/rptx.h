@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define RPTX_ABI_VERSION 2
+#define RPTX_ABI_VERSION 3
 
 /* ---- shapes: src/shape.rs:19-26 (trait Shape), :102-109 (Transformed<T>) ---- */
 enum {
@@ -155,6 +155,23 @@ int         rptx_ctx_create(int device_id, rptx_ctx** out);
 void        rptx_ctx_destroy(rptx_ctx* ctx);
 const char* rptx_last_error(const rptx_ctx* ctx);
 
+/* ---- multi-GPU: one process (or host thread) per GPU, one context each ------------------------------
+ * The reference's two exchange points are `add_samples` after the rows' collect() (src/renderer.rs:169-170)
+ * and PhotonList::merge (src/photon.rs:153-160,675).  rptx_comm_init joins this rank's context into an NCCL
+ * communicator (libnccl.so.2 is loaded on first use; NVLink / NVSwitch inside a box).  On a context with a
+ * communicator
+ *   - rptx_render_sample on a film whose (shard_count, shard_index) equal (world, rank) traces this rank's
+ *     sample shard, all-reduces the f64 batch sums and commits the same batch mean on every rank;
+ *   - rptx_photon_render emits this rank's photon-index range, all-gathers the lists, builds the map on every
+ *     rank, gathers this rank's sample shard of the camera pass and all-reduces it.
+ * Rank 0 makes the id with rptx_comm_unique_id and hands its 128 bytes to the other ranks by whatever channel
+ * the host has (the Python host uses torch.distributed's store); every rank then calls rptx_comm_init. */
+#define RPTX_COMM_ID_BYTES 128
+int  rptx_comm_unique_id(void* id_out /* RPTX_COMM_ID_BYTES */);
+int  rptx_comm_init(rptx_ctx* ctx, const void* id, int world, int rank);
+int  rptx_comm_info(const rptx_ctx* ctx, int* world, int* rank);   /* (1, 0) without a communicator */
+void rptx_comm_destroy(rptx_ctx* ctx);                             /* before rptx_ctx_destroy */
+
 /* Scene (src/scene.rs:12-24).  Caller-owned arrays are copied. */
 int  rptx_scene_create(rptx_ctx* ctx, rptx_scene** out);
 void rptx_scene_destroy(rptx_scene* scene);
@@ -189,6 +206,9 @@ int  rptx_render_sample(rptx_film* film, uint32_t iterations);
  * two calls; commit divides by `iterations`, applies 2^EV and pushes the batch mean. */
 int  rptx_render_sample_trace(rptx_film* film, uint32_t iterations);
 int  rptx_render_sample_commit(rptx_film* film, uint32_t iterations);
+/* the exchange between the two, inside the library: NCCL all-reduce (sum) of the batch-sum film over the
+ * context's communicator, enqueued on the library's stream (no host synchronisation) */
+int  rptx_render_sample_allreduce(rptx_film* film);
 void* rptx_film_batch_sum_device_ptr(rptx_film* film);  /* device pointer, 3*w*h doubles */
 /* Buffer::image() src/buffer.rs:43-56 (box filter, clamp, gamma 2.2, truncating u8) */
 int  rptx_film_image_rgb8(rptx_film* film, uint8_t* out_rgb /* [h][w][3] */);
@@ -220,6 +240,9 @@ void rptx_photons_destroy(rptx_photons* photons);
 /* PhotonList::merge (:153-160): append rows (which: 0 surface, 1 volume) from host or device memory */
 int  rptx_photons_append_host(rptx_photons* photons, int32_t which, const void* rows, size_t n);
 int  rptx_photons_append_device(rptx_photons* photons, int32_t which, const void* d_rows, size_t n);
+/* PhotonList::merge across the communicator's ranks: *out = the concatenation, in rank order, of every rank's
+ * `local` list (ragged; rows go straight to their offset, no padding).  `local` stays valid. */
+int  rptx_photons_allgather(rptx_photons* local, rptx_photons** out);
 int  rptx_photons_count(const rptx_photons* photons, uint64_t counts[2]);
 void* rptx_photons_device_ptr(rptx_photons* photons, int32_t which);      /* rows on the device */
 int  rptx_photons_download(rptx_photons* photons, int32_t which, void* rows /* [n][13 x 8 B] */);

@@ -8,6 +8,7 @@
 #include <string>
 
 #include "../include/rptx.h"
+#include "builtin_scenes.hpp"
 #include "photon.hpp"
 #include "render.hpp"
 
@@ -91,6 +92,31 @@ extern "C" {
 void* orc_scene_create() { return new OScene(); }
 void orc_scene_destroy(void* s) { delete (OScene*)s; }
 const char* orc_last_error(void* s) { return ((OScene*)s)->err.c_str(); }
+
+// A BASELINE scene built natively from the example sources' literals (builtin_scenes.hpp), not from lowered records.
+// name: cornell | teapot | fractal_teapots | lampshade_{pathtrace,photonphoton,beamphoton,beambeam}; the teapot mesh (the
+// reference's examples/teapot.obj as triangles) is input data for the two teapot scenes.
+void* orc_scene_builtin(const char* name, const double* teapot_v, const double* teapot_n, size_t ntri) {
+    OScene* s = new OScene();
+    const std::string n = name ? name : "";
+    const char* variants[4] = {"lampshade_pathtrace", "lampshade_photonphoton", "lampshade_beamphoton", "lampshade_beambeam"};
+    bool ok = true;
+    if (n == "cornell") {
+        builtin::cornell(s->scene);
+    } else if (n == "teapot" || n == "fractal_teapots") {
+        if (!teapot_v || !teapot_n || !ntri) { delete s; return nullptr; }
+        auto mesh = builtin::mesh_from(teapot_v, teapot_n, ntri);
+        if (n == "teapot") builtin::teapot(s->scene, mesh);
+        else builtin::fractal_teapots(s->scene, mesh, &s->object_is_group);
+    } else {
+        ok = false;
+        for (int v = 0; v < 4; v++)
+            if (n == variants[v]) { builtin::lampshade(s->scene, v); ok = true; }
+    }
+    if (!ok) { delete s; return nullptr; }
+    s->object_is_group.resize(s->scene.objects.size(), false);
+    return s;
+}
 
 int orc_scene_add_mesh(void* sp, const double* v, const double* n, size_t ntri, uint32_t* mesh_id) {
     OScene* s = (OScene*)sp;

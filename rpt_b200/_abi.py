@@ -118,6 +118,7 @@ U32P = C.POINTER(C.c_uint32)
 U8P = C.POINTER(C.c_uint8)
 U64P = C.POINTER(C.c_uint64)
 PHOTON_ROW_F64 = 13  # RPTX_PHOTON_ROW_BYTES / 8
+COMM_ID_BYTES = 128
 
 # name -> (restype, argtypes): every symbol include/rptx.h declares
 PROTOTYPES = {
@@ -125,6 +126,10 @@ PROTOTYPES = {
     "rptx_ctx_create": (C.c_int, [C.c_int, C.POINTER(P)]),
     "rptx_ctx_destroy": (None, [P]),
     "rptx_last_error": (C.c_char_p, [P]),
+    "rptx_comm_unique_id": (C.c_int, [P]),
+    "rptx_comm_init": (C.c_int, [P, P, C.c_int, C.c_int]),
+    "rptx_comm_info": (C.c_int, [P, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    "rptx_comm_destroy": (None, [P]),
     "rptx_scene_create": (C.c_int, [P, C.POINTER(P)]),
     "rptx_scene_destroy": (None, [P]),
     "rptx_scene_add_mesh": (C.c_int, [P, DP, DP, C.c_size_t, U32P]),
@@ -139,6 +144,7 @@ PROTOTYPES = {
     "rptx_render_sample": (C.c_int, [P, C.c_uint32]),
     "rptx_render_sample_trace": (C.c_int, [P, C.c_uint32]),
     "rptx_render_sample_commit": (C.c_int, [P, C.c_uint32]),
+    "rptx_render_sample_allreduce": (C.c_int, [P]),
     "rptx_film_batch_sum_device_ptr": (C.c_void_p, [P]),
     "rptx_film_image_rgb8": (C.c_int, [P, U8P]),
     "rptx_film_variance": (C.c_int, [P, DP]),
@@ -148,6 +154,7 @@ PROTOTYPES = {
     "rptx_photons_destroy": (None, [P]),
     "rptx_photons_append_host": (C.c_int, [P, C.c_int32, P, C.c_size_t]),
     "rptx_photons_append_device": (C.c_int, [P, C.c_int32, P, C.c_size_t]),
+    "rptx_photons_allgather": (C.c_int, [P, C.POINTER(P)]),
     "rptx_photons_count": (C.c_int, [P, U64P]),
     "rptx_photons_device_ptr": (C.c_void_p, [P, C.c_int32]),
     "rptx_photons_download": (C.c_int, [P, C.c_int32, P]),
@@ -187,6 +194,6 @@ def load():
                 "or `make -C rpt_b200/csrc`. rpt_b200 has no CPU fallback."
             )
         _lib = bind(C.CDLL(LIB_PATH))
-        if _lib.rptx_abi_version() != 2:
+        if _lib.rptx_abi_version() != 3:
             raise ImportError("librptx.so ABI version mismatch")
     return _lib

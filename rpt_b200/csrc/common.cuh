@@ -25,6 +25,19 @@ constexpr uint32_t kNoHit = 0xffffffffu;
 struct d3 {
     double x, y, z;
 };
+// f64 division and square root expand inline to ~24 / ~20 instructions each; a kernel holding the whole path (persist.cuh)
+// has ~160 + ~45 such sites, a third of its code bytes, and is bound by instruction fetch.  With RPTX_NOINLINE_MATH the
+// translation unit shares ONE copy of each (same IEEE results: the bodies are the same operations).
+#if defined(__CUDA_ARCH__) && defined(RPTX_NOINLINE_MATH)
+static __device__ __noinline__ double rptx_nm_div(double a, double b) { return a / b; }
+static __device__ __noinline__ double rptx_nm_sqrt(double a) { return sqrt(a); }
+#define DDIV(a, b) rptx_nm_div((a), (b))
+#define DSQRT(a) rptx_nm_sqrt((a))
+#else
+#define DDIV(a, b) ((a) / (b))
+#define DSQRT(a) sqrt((a))
+#endif
+
 RPTX_HD d3 mk3(double x, double y, double z) { d3 r; r.x = x; r.y = y; r.z = z; return r; }
 RPTX_HD d3 operator+(d3 a, d3 b) { return mk3(a.x + b.x, a.y + b.y, a.z + b.z); }
 RPTX_HD d3 operator-(d3 a, d3 b) { return mk3(a.x - b.x, a.y - b.y, a.z - b.z); }
@@ -41,7 +54,7 @@ RPTX_HD double div_component(double a, double s, bool s_regular) {
 #ifdef __CUDA_ARCH__
     asm("" : "+d"(num));  // opaque: otherwise nvcc divides a / s anyway (slow path included) and selects afterwards
 #endif
-    const double q = num / s;
+    const double q = DDIV(num, s);
     return z ? a * s : q;
 }
 // scalar form, for quotients whose numerator is often exactly zero (a ray leaving a wall at coordinate 0
@@ -64,7 +77,7 @@ RPTX_HD d3 operator/(d3 a, double s) {
 RPTX_HD double dot(d3 a, d3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
 RPTX_HD d3 cross(d3 a, d3 b) { return mk3(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x); }
 RPTX_HD d3 cmul(d3 a, d3 b) { return mk3(a.x * b.x, a.y * b.y, a.z * b.z); }
-RPTX_HD double length(d3 a) { return sqrt(dot(a, a)); }
+RPTX_HD double length(d3 a) { return DSQRT(dot(a, a)); }
 RPTX_HD d3 normalize(d3 a) { return a / length(a); }
 RPTX_HD d3 reflect_vec(d3 i, d3 n) { return i - n * (dot(n, i) * 2.0); }  // glm::reflect_vec
 RPTX_HD double clampd(double v, double lo, double hi) { return v < lo ? lo : (v > hi ? hi : v); }

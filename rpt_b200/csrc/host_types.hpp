@@ -108,6 +108,7 @@ struct rptx_film {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     cudaEvent_t evw[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};  // per-wave kernel boundaries
     rptx_stats stats = {};
+    bool timing_pending = false;  // ev0 / ev1 of the last traced batch not read yet
 };
 
 // Stream-ordered allocation for everything that is created and destroyed per call (scene buffers, BVH build

@@ -13,6 +13,7 @@
 #include "bvh_build.cuh"
 #include "host_types.hpp"
 #include "photon.cuh"
+#include "photon_host.hpp"
 
 using namespace rptx;
 using rptx_host::ctx_fail;
@@ -23,13 +24,6 @@ using rptx_host::ctx_fail;
         if (e_ != cudaSuccess) return ctx_fail(ctx, std::string(#call) + ": " + cudaGetErrorString(e_)); \
     } while (0)
 
-struct rptx_photons {
-    rptx_ctx* ctx = nullptr;
-    PhotonRec* d_rows[2] = {nullptr, nullptr};  // [0] surface, [1] volume
-    uint64_t n[2] = {0, 0}, cap[2] = {0, 0};
-    uint64_t emitted = 0, rays = 0;
-    double emit_ms = 0;
-};
 
 namespace {
 
@@ -538,6 +532,18 @@ static int photons_reserve(rptx_photons* p, int which, uint64_t need) {
     return 0;
 }
 
+}  // extern "C"
+
+namespace rptx_host {
+int photons_resize(rptx_photons* p, int which, uint64_t n) {
+    if (int rc = photons_reserve(p, which, n)) return rc;
+    p->n[which] = n;
+    return 0;
+}
+}  // namespace rptx_host
+
+extern "C" {
+
 int rptx_photons_append_host(rptx_photons* p, int32_t which, const void* rows, size_t n) {
     if (!p) return 1;
     rptx_ctx* ctx = p->ctx;
@@ -793,11 +799,27 @@ int rptx_photon_render(rptx_ctx* ctx, rptx_scene* scene, const rptx_camera* came
     rptx_photons* ph = nullptr;
     rptx_photon_map* map = nullptr;
     rptx_film* film = nullptr;
-    int rc = rptx_photons_emit(ctx, scene, params, photon_count, 0, photon_count, kind, &ph);
+    // with a communicator (rptx_comm_init) the three passes shard as photon_render's rayon loops do (src/photon.rs:663-716):
+    // this rank emits its photon-index range, the lists are all-gathered, every rank gathers its sample shard of the camera
+    // pass and the batch sums are all-reduced
+    int world = 1, rank = 0;
+    rptx_comm_info(ctx, &world, &rank);
+    rptx_params prm = *params;
+    if (world > 1) { prm.shard_count = (uint32_t)world; prm.shard_index = (uint32_t)rank; }
+    else if (prm.shard_count > 1) return ctx_fail(ctx, "sharded photon_render needs a communicator (rptx_comm_init), or the three passes with the caller's own exchange");
+    const uint64_t lo = photon_count * (uint64_t)rank / (uint64_t)world, hi = photon_count * (uint64_t)(rank + 1) / (uint64_t)world;
+    int rc = rptx_photons_emit(ctx, scene, &prm, photon_count, lo, hi - lo, kind, &ph);
+    if (rc == 0 && world > 1) {
+        rptx_photons* full = nullptr;
+        rc = rptx_photons_allgather(ph, &full);
+        rptx_photons_destroy(ph);
+        ph = full;
+    }
     if (rc == 0) rc = rptx_photon_map_build(ctx, scene, ph, kind, &map);
     if (ph) { rptx_photons_destroy(ph); ph = nullptr; }
-    if (rc == 0) rc = rptx_photon_gather_begin(ctx, scene, camera, params, &film);
+    if (rc == 0) rc = rptx_photon_gather_begin(ctx, scene, camera, &prm, &film);
     if (rc == 0) rc = rptx_photon_gather_trace(film, map, params->num_samples);
+    if (rc == 0 && world > 1) rc = rptx_render_sample_allreduce(film);
     if (rc == 0) rc = rptx_render_sample_commit(film, params->num_samples);
     if (rc == 0 && out_rgb8) rc = rptx_film_image_rgb8(film, out_rgb8);
     if (rc == 0 && out_mean) rc = rptx_film_mean(film, out_mean);

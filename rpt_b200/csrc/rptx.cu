@@ -374,6 +374,7 @@ int rptx_ctx_create(int device_id, rptx_ctx** out) {
 
 void rptx_ctx_destroy(rptx_ctx* ctx) {
     if (!ctx) return;
+    if (ctx->comm) rptx_comm_destroy(ctx);
     if (ctx->spare_arena) cudaFree(ctx->spare_arena);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     if (ctx->h_pinned) cudaFreeHost(ctx->h_pinned);
@@ -753,7 +754,7 @@ static void film_carve(rptx_film* f, Carver& c) {
         c.take(&f->d_select_tmp, f->select_tmp_bytes);
     }
     if (f->mode == kFilmPersist && p.record_mode)
-        c.take(&f->d_pstack, (size_t)f->persist_blocks * kBlock * 8 * std::max<uint32_t>(p.stack_depth, 1));
+        c.take(&f->d_pstack, (size_t)f->persist_blocks * kPersistBlock * 8 * std::max<uint32_t>(p.stack_depth, 1));
     c.take(&f->q.counters, 8);
     c.take(&f->q.stats, 8);
     const size_t n3 = (size_t)p.n_pixels * 3;
@@ -863,7 +864,7 @@ static int film_begin(rptx_ctx* ctx, rptx_scene* scene, const rptx_camera* camer
         const bool small = scene->small_scene && !std::getenv("RPTX_NO_SMALL_SCENE");
         f->persist_blocks = rptx_host::persist_grid(ctx->sm_count, scene->medium_kind != RPTX_MEDIUM_NONE, scene->shadow_probe_mask != 0, small);
         if (const char* e = std::getenv("RPTX_PERSIST_BLOCKS")) f->persist_blocks = std::max(1, std::atoi(e));  // developer knob
-        target = 128ull * (uint64_t)f->persist_blocks * kBlock;
+        target = 128ull * (uint64_t)f->persist_blocks * kPersistBlock;
     }
     if (const char* e = std::getenv("RPTX_POOL_LOG2")) {  // developer knob: paths in flight
         const int v = std::atoi(e);
@@ -995,7 +996,11 @@ static int run_waves(rptx_film* f, const BatchParams& bp) {
 
 extern "C" {
 
-int rptx_render_sample_trace(rptx_film* f, uint32_t iterations) {
+static void film_collect_timing(rptx_film* f);
+
+// `sync`: the public split form hands the batch sums to the caller's own exchange, so it returns with the stream idle;
+// rptx_render_sample keeps everything stream-ordered (trace -> NCCL all-reduce -> commit) and synchronises once, in commit
+static int sample_trace_impl(rptx_film* f, uint32_t iterations, bool sync) {
     if (!f) return 1;
     rptx_ctx* ctx = f->ctx;
     if (iterations == 0) return ctx_fail(ctx, "iterations must be > 0");
@@ -1054,12 +1059,20 @@ int rptx_render_sample_trace(rptx_film* f, uint32_t iterations) {
     p.n_lanes = full_lanes;
     if (rc) return rc;
     CK(cudaEventRecord(f->ev1, st));
-    CK(cudaStreamSynchronize(st));
-    float ms = 0.f;
-    CK(cudaEventElapsedTime(&ms, f->ev0, f->ev1));
-    f->stats.device_ms = ms;
-    f->stats.trace_ms = f->stats.extend_ms + f->stats.shadow_ms;
+    f->timing_pending = true;  // read at the next synchronisation point (commit / stats): no host sync between trace and exchange
+    if (sync) { CK(cudaStreamSynchronize(st)); film_collect_timing(f); }
     return 0;
+}
+
+int rptx_render_sample_trace(rptx_film* f, uint32_t iterations) { return sample_trace_impl(f, iterations, true); }
+
+// device time of the last traced batch, once its events have completed
+static void film_collect_timing(rptx_film* f) {
+    if (!f->timing_pending) return;
+    f->timing_pending = false;
+    float ms = 0.f;
+    if (cudaEventSynchronize(f->ev1) == cudaSuccess && cudaEventElapsedTime(&ms, f->ev0, f->ev1) == cudaSuccess) f->stats.device_ms = ms;
+    f->stats.trace_ms = f->stats.extend_ms + f->stats.shadow_ms;
 }
 
 int rptx_render_sample_commit(rptx_film* f, uint32_t iterations) {
@@ -1081,6 +1094,7 @@ int rptx_render_sample_commit(rptx_film* f, uint32_t iterations) {
     k_batch_commit<<<grid_for(n3, 256), 256, 0, st>>>(f->d_batch_sum, n3, (double)iterations, exposure, mean, f->d_film_sum);
     ctx->launches++;
     CK(cudaStreamSynchronize(st));
+    film_collect_timing(f);
     f->next_sample += iterations;
     return 0;
 }
@@ -1089,7 +1103,9 @@ int rptx_render_sample(rptx_film* f, uint32_t iterations) {
     // a sharded film holds 1 / shard_count of the batch: committing it without the exchange would dim the image
     if (f && f->params.shard_count > 1 && !f->ctx->comm)
         return ctx_fail(f->ctx, "sharded films must use rptx_render_sample_trace + all-reduce + rptx_render_sample_commit, or a context with rptx_comm_init");
-    if (int rc = rptx_render_sample_trace(f, iterations)) return rc;
+    if (int rc = sample_trace_impl(f, iterations, false)) return rc;
+    if (f->params.shard_count > 1)
+        if (int rc = rptx_render_sample_allreduce(f)) return rc;
     return rptx_render_sample_commit(f, iterations);
 }
 
@@ -1159,6 +1175,7 @@ int rptx_stats_get(const rptx_film* f, rptx_stats* out) {
     cudaSetDevice(f->ctx->device);
     unsigned long long st[8] = {0};
     cudaStreamSynchronize(f->ctx->stream);
+    film_collect_timing(const_cast<rptx_film*>(f));
     cudaMemcpy(st, f->q.stats, sizeof(st), cudaMemcpyDeviceToHost);
     *out = f->stats;
     out->path_samples = st[0]; out->extend_rays = st[1]; out->shadow_rays = st[2];

@@ -29,7 +29,7 @@ RPTX_D d3 rot_apply(const Rot3& r, d3 v) {
 // few ulps — the size of the CUDA-vs-glibc libm differences the parity tests already allow —
 // without the f64 acos/sin/cos code (each several KB of SASS; k_shade was 105-143 KB and
 // instruction-cache bound).
-RPTX_D double sin_from_cos(double c) { return sqrt(fmax(0.0, 1.0 - c * c)); }
+RPTX_D double sin_from_cos(double c) { return DSQRT(fmax(0.0, 1.0 - c * c)); }
 
 // nalgebra Rotation3::from_axis_angle with (sin, cos) of the angle
 RPTX_D Rot3 rot_identity() {
@@ -65,7 +65,7 @@ RPTX_D bool rotation_between(d3 a, d3 b, Rot3* out) {
             // cosine alone, as in the reference (|na x nb| would be MORE accurate for nearly
             // (anti)parallel vectors, e.g. the (0,1,1e-8) fallback against -Y, and so differ from it)
             const double cs = dot(na, nb);
-            *out = rot_from_axis_sincos(c / sqrt(sq), sin_from_cos(cs), cs);
+            *out = rot_from_axis_sincos(c / DSQRT(sq), sin_from_cos(cs), cs);
             return true;
         }
         if (dot(na, nb) < 0.0) return false;
@@ -86,8 +86,8 @@ RPTX_DN bool mat_sample_f(const Material& m, d3 normal, d3 wo, Rng& rng, d3* wi,
         const double r1 = rng.gen();
         const double r2 = rng.gen();
         const double phi = 2.0 * kPi * r1;
-        const double ct = sqrt(r2), st = sin_from_cos(ct);  // theta = acos(sqrt(r2))
-        *pdf = ct / kPi;
+        const double ct = DSQRT(r2), st = sin_from_cos(ct);  // theta = acos(sqrt(r2))
+        *pdf = DDIV(ct, kPi);
         double sp, cp;
         sincos(phi, &sp, &cp);
         const d3 hemi = mk3(st * cp, ct, st * sp);
@@ -191,7 +191,7 @@ RPTX_D void medium_sample_ph(Rng& rng, d3* wi) {
 }
 RPTX_D double medium_sample_d(const MediumDev& md, Rng& rng) {
     const double random = rng.gen_range(0.0, 1.0);
-    return -log(random) / md.extinction();
+    return DDIV(-log(random), md.extinction());
 }
 
 // ---- light sampling ----
@@ -211,7 +211,7 @@ RPTX_D void sample_light_shape(const SceneDev& sc, const Light& l, d3 target, Rn
         const double area = 0.5 * length(cross(v2 - v1, v3 - v1));
         lv = u * v1 + vv * v2 + w * v3;
         ln = normalize(u * n1 + vv * n2 + w * n3);
-        lp = (1.0 / area) / (double)l.ntri;
+        lp = DDIV(DDIV(1.0, area), (double)l.ntri);
     } else if (l.shape_kind == kCube) {
         const double a = rng.gen() - 0.5;
         const double b = rng.gen() - 0.5;
@@ -250,10 +250,10 @@ RPTX_D void sample_light_shape(const SceneDev& sc, const Light& l, d3 target, Rn
     if (l.has_transform) {
         const d3 new_normal = normalize(mul3(l.nrm, ln));
         const double height = dot(mul3(l.lin, ln), new_normal);
-        const double base = l.scale / height;
+        const double base = DDIV(l.scale, height);
         *v = xform_point(l.fwd, lv);
         *n = new_normal;
-        *p = lp / base;
+        *p = DDIV(lp, base);
     } else {
         *v = lv; *n = ln; *p = lp;
     }
@@ -278,8 +278,8 @@ RPTX_DN void illuminate(const SceneDev& sc, const Light& l, d3 pos, Rng& rng, d3
         sample_light_shape(sc, l, pos, rng, &v, &n, &p);
         const d3 disp = v - pos;
         const double len = length(disp);
-        const double cosine = fmax(-dot(disp, n), 0.0) / len;
-        const double surface_area = fmax(cosine, 0.0) / (len * len);
+        const double cosine = DDIV(fmax(-dot(disp, n), 0.0), len);
+        const double surface_area = DDIV(fmax(cosine, 0.0), len * len);
         *intensity = mat_color(l.material) * mat_emittance(l.material) * surface_area / p;
         *wi = disp / len;
         *dist = len;
@@ -289,10 +289,11 @@ RPTX_DN void illuminate(const SceneDev& sc, const Light& l, d3 pos, Rng& rng, d3
 // Camera::cast_ray with the pixel mapping and jitter of Renderer::get_color (src/renderer.rs:173-181)
 RPTX_D void primary_ray(const Camera& cam, uint32_t width, uint32_t height, uint32_t x, uint32_t y, Rng& rng, d3* o, d3* d) {
     const double dim = (double)(width > height ? width : height);
-    const double xn = ((double)(2 * x + 1) - (double)width) / dim;
-    const double yn = ((double)(2 * (height - y) - 1) - (double)height) / dim;
-    const double dx = rng.gen_range(-1.0 / dim, 1.0 / dim);
-    const double dy = rng.gen_range(-1.0 / dim, 1.0 / dim);
+    const double xn = DDIV((double)(2 * x + 1) - (double)width, dim);
+    const double yn = DDIV((double)(2 * (height - y) - 1) - (double)height, dim);
+    const double jl = DDIV(-1.0, dim), jh = DDIV(1.0, dim);
+    const double dx = rng.gen_range(jl, jh);
+    const double dy = rng.gen_range(jl, jh);
     const double px = xn + dx, py = yn + dy;
     const double dd = cam.inv_tan_half_fov;
     const d3 right = normalize(cross(cam.direction, cam.up));

@@ -61,7 +61,7 @@ RPTX_D bool slab_f32(float bx0, float by0, float bz0, float bx1, float by1, floa
 // the f32 ray depend on it and the boxes are padded by 2^-21 of their extent, so one reciprocal per axis (1 ulp off
 // the quotient) serves both planes: three divisions instead of six per box entry.
 RPTX_D void clip_f64(const double* bmin, const double* bmax, d3 o, d3 d, double* t0, double* t1) {
-    const double ix = 1.0 / d.x, iy = 1.0 / d.y, iz = 1.0 / d.z;
+    const double ix = DDIV(1.0, d.x), iy = DDIV(1.0, d.y), iz = DDIV(1.0, d.z);
     const double ax = (bmin[0] - o.x) * ix, bx = (bmax[0] - o.x) * ix;
     const double ay = (bmin[1] - o.y) * iy, by = (bmax[1] - o.y) * iy;
     const double az = (bmin[2] - o.z) * iz, bz = (bmax[2] - o.z) * iz;
@@ -82,8 +82,8 @@ RPTX_D bool tri_test(const TriRec& tr, d3 o, d3 d, double t_min, double t_max, b
     const d3 d0 = mk3(tr.d0[0], tr.d0[1], tr.d0[2]), d1 = mk3(tr.d1[0], tr.d1[1], tr.d1[2]);
     const d3 d2 = (o + time * d) - v1;
     const double d20 = dot(d2, d0), d21 = dot(d2, d1);
-    const double v = (tr.d11 * d20 - tr.d01 * d21) / tr.denom;
-    const double w = (tr.d00 * d21 - tr.d01 * d20) / tr.denom;
+    const double v = DDIV(tr.d11 * d20 - tr.d01 * d21, tr.denom);
+    const double w = DDIV(tr.d00 * d21 - tr.d01 * d20, tr.denom);
     const double u = 1.0 - v - w;
     if (u >= 0.0 && v >= 0.0 && w >= 0.0) { *t = time; *vv = v; *ww = w; return true; }
     return false;
@@ -103,10 +103,10 @@ RPTX_D bool sphere_test(d3 o, d3 d, double t_min, double* t) {
     const double c = dot(o, o) - 1.0;
     double disc = b * b - a * c;
     if (signbit(disc)) return false;
-    disc = sqrt(disc);
-    const double t_minus = (-b - disc) / a;
+    disc = DSQRT(disc);
+    const double t_minus = DDIV(-b - disc, a);
     if (t_minus < t_min) {
-        const double t_plus = (-b + disc) / a;
+        const double t_plus = DDIV(-b + disc, a);
         if (t_plus < t_min) return false;
         *t = t_plus;
     } else {
@@ -146,7 +146,7 @@ RPTX_D bool plane_test(const Instance& in, d3 o, d3 d, double t_min, double* t) 
     const d3 n = mk3(in.plane_n[0], in.plane_n[1], in.plane_n[2]);
     const double cosine = dot(n, d);
     if (fabs(cosine) < 1e-8) return false;
-    const double time = (in.plane_v - dot(n, o)) / cosine;
+    const double time = DDIV(in.plane_v - dot(n, o), cosine);
     if (time >= t_min) { *t = time; return true; }
     return false;
 }

@@ -59,9 +59,30 @@ def all_gather_ragged(t, group=None):
     return torch.cat([p[:c] for p, c in zip(parts, counts)], dim=0), counts
 
 
+def init_comm(ctx, group=None):
+    """Join this rank's rptx context into an NCCL communicator that the LIBRARY owns (rptx_comm_init): rank 0 makes
+    the id, torch.distributed only carries its 128 bytes to the other ranks.  After this the exchanges of
+    sample_batch / photon_render run inside librptx.so on its own stream; torch is not on the data path."""
+    world, rank = world_rank(group)
+    if world == 1 or ctx.comm_info()[0] > 1:
+        return ctx
+    box = [ctx.comm_unique_id() if rank == 0 else None]
+    dist.broadcast_object_list(box, src=0, group=group)
+    ctx.comm_init(box[0], world, rank)
+    return ctx
+
+
+def _lib_comm(obj):
+    ctx = getattr(obj, "ctx", None)
+    return ctx is not None and hasattr(ctx, "comm_info") and ctx.comm_info()[0] > 1
+
+
 def sample_batch(film, iterations, group=None):
     """Renderer::sample(iterations) across ranks: trace the local shard, all-reduce the f64
     batch sums, commit the same batch mean on every rank."""
+    if _lib_comm(film):
+        film.sample(iterations)  # trace -> ncclAllReduce -> commit, all inside the library
+        return
     film.sample_trace(iterations)
     all_reduce_sum_(film.batch_sum_tensor(), group)
     if film.batch_sum_tensor().is_cuda:
@@ -102,19 +123,26 @@ def photon_render(renderer, photon_count, kind, group=None):
 
     world, rank = world_rank(group)
     lo, hi = photon_range(photon_count, world, rank)
+    lib_comm = _lib_comm(renderer.device_scene())
     t0 = time.perf_counter()
     local = renderer.emit_photons(photon_count, kind, first=lo, count=hi - lo)
     t1 = time.perf_counter()
-    full = merge_photons(local, PhotonList.empty(renderer.device_scene().ctx) if world > 1 else None, group)
+    if lib_comm:
+        full = local.allgather()
+    else:
+        full = merge_photons(local, PhotonList.empty(renderer.device_scene().ctx) if world > 1 else None, group)
     t2 = time.perf_counter()
     pmap = renderer.build_photon_map(full, kind)
     t3 = time.perf_counter()
     film = renderer.begin_gather()
     n = renderer._p["num_samples"]
     film.gather(pmap, n)
-    all_reduce_sum_(film.batch_sum_tensor(), group)
-    if film.batch_sum_tensor().is_cuda:
-        torch.cuda.current_stream().synchronize()
+    if lib_comm:
+        film.sample_allreduce()
+    else:
+        all_reduce_sum_(film.batch_sum_tensor(), group)
+        if film.batch_sum_tensor().is_cuda:
+            torch.cuda.current_stream().synchronize()
     film.sample_commit(n)
     t4 = time.perf_counter()
     counts = full.counts()

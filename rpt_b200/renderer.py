@@ -48,6 +48,23 @@ class Context:
     def error(self):
         return (self.lib.rptx_last_error(self.h) or b"").decode()
 
+    # ---- multi-GPU: this rank's context joins an NCCL communicator owned by the library ----
+    @staticmethod
+    def comm_unique_id():
+        """128-byte communicator id (an ncclUniqueId); rank 0 makes it, the host hands it to the other ranks."""
+        buf = C.create_string_buffer(A.COMM_ID_BYTES)
+        if A.load().rptx_comm_unique_id(buf):
+            raise RptxError("rptx_comm_unique_id failed (libnccl.so.2 not loadable?)")
+        return buf.raw
+
+    def comm_init(self, comm_id, world, rank):
+        self.check(self.lib.rptx_comm_init(self.h, C.c_char_p(comm_id), int(world), int(rank)), "rptx_comm_init")
+
+    def comm_info(self):
+        w, r = C.c_int(), C.c_int()
+        self.lib.rptx_comm_info(self.h, C.byref(w), C.byref(r))
+        return w.value, r.value
+
     def check(self, rc, what):
         if rc:
             raise RptxError(f"{what}: {self.error()}")
@@ -170,6 +187,12 @@ class PhotonList:
         h = C.c_void_p()
         ctx.check(ctx.lib.rptx_photons_create(ctx.h, C.byref(h)), "rptx_photons_create")
         return PhotonList(ctx, h)
+
+    def allgather(self):
+        """PhotonList::merge across the ranks of the context's communicator (NCCL inside the library)."""
+        h = C.c_void_p()
+        self.ctx.check(self.lib.rptx_photons_allgather(self.h, C.byref(h)), "rptx_photons_allgather")
+        return PhotonList(self.ctx, h)
 
     def counts(self):
         c = (C.c_uint64 * 2)()
@@ -307,6 +330,10 @@ class Film:
 
     def sample_trace(self, iterations):
         self.ctx.check(self.lib.rptx_render_sample_trace(self.h, int(iterations)), "rptx_render_sample_trace")
+
+    def sample_allreduce(self):
+        """The exchange between sample_trace and sample_commit, over the context's communicator."""
+        self.ctx.check(self.lib.rptx_render_sample_allreduce(self.h), "rptx_render_sample_allreduce")
 
     def sample_commit(self, iterations):
         self.ctx.check(self.lib.rptx_render_sample_commit(self.h, int(iterations)), "rptx_render_sample_commit")

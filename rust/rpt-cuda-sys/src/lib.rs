@@ -1,4 +1,4 @@
-//! `extern "C"` declarations of `include/rptx.h` (ABI version 2), one to one.
+//! `extern "C"` declarations of `include/rptx.h` (ABI version 3), one to one.
 //!
 //! The reference (neevparikh/rpt) has no FFI; its boundary is the Rust API of `src/renderer.rs` /
 //! `src/photon.rs`.  A drop-in `rpt` mirror keeps those types and lowers them into the POD records
@@ -7,7 +7,7 @@
 
 use std::os::raw::{c_char, c_int, c_void};
 
-pub const RPTX_ABI_VERSION: c_int = 2;
+pub const RPTX_ABI_VERSION: c_int = 3;
 
 // shapes: src/shape.rs:19-26 (trait Shape), :102-109 (Transformed<T>)
 pub const RPTX_SHAPE_SPHERE: i32 = 0;
@@ -36,6 +36,8 @@ pub const RPTX_PHOTON_POINT_BEAM: i32 = 1;
 pub const RPTX_PHOTON_BEAM_BEAM: i32 = 2;
 /// One photon record = position, direction, power, starting_position (f64 x 3 each) + u64 key.
 pub const RPTX_PHOTON_ROW_BYTES: usize = 104;
+/// Size of the communicator id rank 0 hands to the other ranks (an ncclUniqueId).
+pub const RPTX_COMM_ID_BYTES: usize = 128;
 
 #[repr(C)] pub struct rptx_ctx { _p: [u8; 0] }
 #[repr(C)] pub struct rptx_scene { _p: [u8; 0] }
@@ -143,6 +145,13 @@ extern "C" {
     pub fn rptx_ctx_destroy(ctx: *mut rptx_ctx);
     pub fn rptx_last_error(ctx: *const rptx_ctx) -> *const c_char;
 
+    // multi-GPU: one context per rank joined into an NCCL communicator; the exchanges replace `add_samples`
+    // (src/renderer.rs:169-170) and PhotonList::merge (src/photon.rs:153-160,675)
+    pub fn rptx_comm_unique_id(id_out: *mut c_void) -> c_int;
+    pub fn rptx_comm_init(ctx: *mut rptx_ctx, id: *const c_void, world: c_int, rank: c_int) -> c_int;
+    pub fn rptx_comm_info(ctx: *const rptx_ctx, world: *mut c_int, rank: *mut c_int) -> c_int;
+    pub fn rptx_comm_destroy(ctx: *mut rptx_ctx);
+
     // Scene, src/scene.rs:12-81
     pub fn rptx_scene_create(ctx: *mut rptx_ctx, out: *mut *mut rptx_scene) -> c_int;
     pub fn rptx_scene_destroy(scene: *mut rptx_scene);
@@ -160,6 +169,7 @@ extern "C" {
     pub fn rptx_render_sample(film: *mut rptx_film, iterations: u32) -> c_int;
     pub fn rptx_render_sample_trace(film: *mut rptx_film, iterations: u32) -> c_int;
     pub fn rptx_render_sample_commit(film: *mut rptx_film, iterations: u32) -> c_int;
+    pub fn rptx_render_sample_allreduce(film: *mut rptx_film) -> c_int;
     pub fn rptx_film_batch_sum_device_ptr(film: *mut rptx_film) -> *mut c_void;
     pub fn rptx_film_image_rgb8(film: *mut rptx_film, out_rgb: *mut u8) -> c_int;
     pub fn rptx_film_variance(film: *mut rptx_film, out: *mut f64) -> c_int;
@@ -171,6 +181,7 @@ extern "C" {
     pub fn rptx_photons_destroy(photons: *mut rptx_photons);
     pub fn rptx_photons_append_host(photons: *mut rptx_photons, which: i32, rows: *const c_void, n: usize) -> c_int;
     pub fn rptx_photons_append_device(photons: *mut rptx_photons, which: i32, d_rows: *const c_void, n: usize) -> c_int;
+    pub fn rptx_photons_allgather(local: *mut rptx_photons, out: *mut *mut rptx_photons) -> c_int;
     pub fn rptx_photons_count(photons: *const rptx_photons, counts: *mut u64) -> c_int;
     pub fn rptx_photons_device_ptr(photons: *mut rptx_photons, which: i32) -> *mut c_void;
     pub fn rptx_photons_download(photons: *mut rptx_photons, which: i32, rows: *mut c_void) -> c_int;

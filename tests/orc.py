@@ -33,6 +33,7 @@ def lib():
         sig = {
             "orc_scene_create": (P, []),
             "orc_scene_destroy": (None, [P]),
+            "orc_scene_builtin": (P, [C.c_char_p, DP, DP, C.c_size_t]),
             "orc_last_error": (C.c_char_p, [P]),
             "orc_scene_add_mesh": (C.c_int, [P, DP, DP, C.c_size_t, U32P]),
             "orc_scene_add_object": (C.c_int, [P, C.POINTER(A.ShapeDesc), C.POINTER(A.MaterialDesc), U32P]),
@@ -85,6 +86,23 @@ class OracleScene:
         self.h = self.L.orc_scene_create()
         self.low = lower_scene(scene)
         upload_scene(self.low, self)
+
+    @classmethod
+    def builtin(cls, name, teapot=None):
+        """A BASELINE scene built inside the oracle from the example sources' literals (oracle/builtin_scenes.hpp): no
+        Python lowering on the way.  teapot: (vertices [n,3,3], normals [n,3,3]) for the two teapot scenes."""
+        self = cls.__new__(cls)
+        self.L = lib()
+        self.low = None
+        if teapot is not None:
+            v = np.ascontiguousarray(teapot[0], np.float64)
+            n = np.ascontiguousarray(teapot[1], np.float64)
+            self.h = self.L.orc_scene_builtin(name.encode(), _dp(v), _dp(n), len(v))
+        else:
+            self.h = self.L.orc_scene_builtin(name.encode(), None, None, 0)
+        if not self.h:
+            raise ValueError(f"unknown builtin scene {name}")
+        return self
 
     def _ck(self, rc, what):
         if rc:

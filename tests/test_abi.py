@@ -27,7 +27,7 @@ def test_library_exports_every_declared_symbol():
     lib = C.CDLL(A.LIB_PATH)
     for name in _header_symbols():
         assert hasattr(lib, name), f"librptx.so does not export {name}"
-    assert A.load().rptx_abi_version() == 2
+    assert A.load().rptx_abi_version() == 3
 
 
 def test_struct_layouts_match_the_header():
@@ -82,3 +82,55 @@ def test_rust_sys_crate_declares_the_same_abi():
         body = re.search(r"pub struct " + struct + r" \{(.*?)\n\}", rs, flags=re.S).group(1)
         fields = re.findall(r"pub (\w+):", body)
         assert fields == [f[0] for f in ctype._fields_], struct
+
+
+def _split_top_level(args):
+    """Number of top-level comma-separated arguments of a call's argument text."""
+    depth, n, seen = 0, 0, False
+    for ch in args:
+        if ch in "([{<":
+            depth += 1
+        elif ch in ")]}>":
+            depth -= 1
+        elif ch == "," and depth == 0:
+            n += 1
+            continue
+        if not ch.isspace():
+            seen = True
+    return n + 1 if seen else 0
+
+
+def test_rust_mirror_crate_calls_the_declared_abi():
+    """rust/rpt (the `rpt` API mirror; source only, no rustc here): every `sys::rptx_*` call names an entry point of
+    include/rptx.h with the header's argument count, the hot-path entry points are all reached, and the reference's public
+    builder / render methods exist by name."""
+    src_dir = os.path.join(ROOT, "rust", "rpt", "src")
+    text = "".join(open(os.path.join(src_dir, f)).read() for f in sorted(os.listdir(src_dir)) if f.endswith(".rs"))
+    htext = re.sub(r"/\*.*?\*/", "", open(os.path.join(ROOT, "include", "rptx.h")).read(), flags=re.S)
+    called = set()
+    for m in re.finditer(r"sys::(rptx_[a-z0-9_]+)\s*\(", text):
+        name, i, depth = m.group(1), m.end(), 1
+        j = i
+        while depth:
+            depth += {"(": 1, ")": -1}.get(text[j], 0)
+            j += 1
+        n_call = _split_top_level(text[i:j - 1])
+        h = re.search(r"\b" + name + r"\s*\(([^;]*?)\)\s*;", htext, flags=re.S)
+        assert h, f"rust/rpt calls {name}, which include/rptx.h does not declare"
+        hargs = h.group(1).strip()
+        n_h = 0 if hargs in ("", "void") else hargs.count(",") + 1
+        assert n_call == n_h, (name, n_call, n_h)
+        called.add(name)
+    for must in ("rptx_ctx_create", "rptx_scene_create", "rptx_scene_add_mesh", "rptx_scene_add_object", "rptx_scene_add_light", "rptx_scene_set_medium",
+                 "rptx_scene_set_environment_color", "rptx_scene_set_environment_hdri", "rptx_scene_commit", "rptx_render_begin", "rptx_render_sample",
+                 "rptx_film_image_rgb8", "rptx_film_variance", "rptx_photon_render", "rptx_intersect_batch", "rptx_comm_init", "rptx_last_error"):
+        assert must in called, must
+    # the reference's API surface (src/renderer.rs:60-156, src/photon.rs:642-655, src/scene.rs:34-81, src/shape.rs:180-314)
+    for name in ("pub fn new(scene: &'a Scene, camera: Camera)", "pub fn width(", "pub fn height(", "pub fn exposure_value(", "pub fn stepsize(", "pub fn filter(",
+                 "pub fn max_bounces(", "pub fn num_samples(", "pub fn gather_size(", "pub fn gather_size_volume(", "pub fn watts(", "pub fn render(&self) -> RgbImage",
+                 "pub fn iterative_render<F>(&self, callback_interval: u32, mut callback: F)", "pub fn get_closest_hit(", "pub fn photon_map_render(",
+                 "pub fn photon_point_query_beam_render(", "pub fn photon_beam_query_beam_render(", "pub fn photon_render(", "impl SceneAdd<LightAndMeshObject> for Scene",
+                 "impl SceneAdd<(Transformed<Cube>, Material)> for Scene", "pub trait Transformable<T>", "pub fn polygon(", "pub fn homogeneous_isotropic(",
+                 "pub fn colored_glowing_fog(", "pub fn look_at(", "pub fn focus(", "pub fn load_obj(", "pub fn load_stl(", "pub fn image(&self) -> RgbImage",
+                 "pub fn variance(&self) -> f64"):
+        assert name in text, name

@@ -1,0 +1,78 @@
+"""-m gpu: the north star's second correctness check — converged images agree with the reference's own high-spp
+render within a stated relative-RMSE tolerance (BASELINE.json `metric`: "image RMSE vs reference").
+
+The reference cannot be built here, so "the reference's render" is the ORACLE's (tests/golden/converged_*.npz,
+written by tests/golden/make_converged.py: >= 16 384 spp at a reduced size, >= 1e6 photons for the photon
+integrators).  The GPU renders the same scene at the same size and spp with OTHER seeds (RNG streams differ from
+the fixture's, as they would against the real, entropy-seeded reference), so the two images differ by Monte Carlo
+noise only if the estimators agree:
+
+    rel_rmse = sqrt(mean((I - R)^2)) / mean(R)        on the linear mean image, before filter and gamma
+
+Tolerance: TOL x the fixture's `rel_rmse_mc`, the relative RMSE an independent render of the same estimator is
+expected to show (estimated from the fixture's two half-renders).  TOL = 2: the medium branch has no firefly clamp
+and its NEE term is 1/len^2-singular at the light, so the noise estimate itself is heavy-tailed.  The image mean
+must agree within 6 standard errors.  Four seeds (one + the three extra of SURVEY 8d)."""
+import os
+
+import numpy as np
+import pytest
+
+from rpt_b200 import scenes
+
+pytestmark = pytest.mark.gpu
+HERE = os.path.dirname(os.path.abspath(__file__))
+TOL = 2.0
+SEEDS = (12345, 1, 2, 3)
+PHOTON_KINDS = {"photonphoton": 0, "beamphoton": 1, "beambeam": 2}
+
+
+def _scene(name):
+    if name == "cornell":
+        return scenes.cornell()
+    if name == "lampshade":
+        return scenes.lampshade("pathtrace")
+    if name == "fractal_teapots":
+        return scenes.fractal_teapots()
+    if name == "fractal_teapots_mb5":
+        s, c, d = scenes.fractal_teapots()
+        return s, c, dict(d, max_bounces=5)
+    return scenes.lampshade(name)
+
+
+def rel_rmse(img, ref):
+    return float(np.sqrt(np.mean((img - ref) ** 2)) / np.mean(ref))
+
+
+@pytest.mark.parametrize("name", ["cornell", "lampshade", "fractal_teapots", "fractal_teapots_mb5", "photonphoton", "beamphoton", "beambeam"])
+def test_converged_image_matches_the_oracle(name):
+    path = os.path.join(HERE, "golden", f"converged_{name}.npz")
+    if not os.path.exists(path):
+        pytest.skip(f"{path} not generated (tests/golden/make_converged.py)")
+    z = np.load(path)
+    ref, spp, expected = z["mean"], int(z["spp"]), float(z["rel_rmse_mc"])
+    h, w = ref.shape[:2]
+    scene, cam, d = _scene(name)
+    rels, means = [], []
+    for seed in SEEDS:
+        over = dict(width=w, height=h, num_samples=spp, seed=seed)
+        if name in PHOTON_KINDS:
+            n = int(z["photons"])
+            if name != "photonphoton":
+                over["watts"] = (200000.0 / 13650.0) * n
+            r = scenes.make_renderer(scene, cam, d, **over)
+            _, img = r.photon_render(n, PHOTON_KINDS[name], want_mean=True)
+        else:
+            r = scenes.make_renderer(scene, cam, d, **over)
+            film = r.begin()
+            film.sample(spp)
+            img = film.mean()
+            film.close()
+        r.device_scene().close()
+        rels.append(rel_rmse(img, ref))
+        means.append(float(img.mean() / ref.mean()))
+    print(f"{name}: rel_rmse {['%.4g' % x for x in rels]} (expected from MC noise {expected:.4g}), mean ratio {['%.5f' % x for x in means]}")
+    assert max(rels) <= TOL * expected, (name, rels, expected)
+    # standard error of the image mean if pixel noises were independent; fireflies make it an underestimate -> 6 sigma
+    se = expected / np.sqrt(ref.size)
+    assert abs(np.mean(means) - 1.0) <= 6.0 * se + 1e-3, (name, means, se)
