@@ -311,32 +311,47 @@ def run_path(box, name, steps, warmup, scaling, cpu_seconds):
     if rank != 0:
         return None
 
-    # roofline of the dominant kernel.  The ray kernels keep the scene in L1/L2 and (small scenes) the path in registers:
-    # the bound is the SMs' instruction issue rate, measured by tools/peaks.cu.  achieved = warp instructions per second
-    # x live lanes / 32 (thread-instructions/s over 32), from the vertex count of THIS run x the per-vertex instruction
-    # counts of the committed ncu capture of this build.
+    # roofline of the dominant kernel (by CUDA-event time of THIS run).  Two candidate roofs, both measured on the box:
+    #   issue: the SMs' instruction issue rate (tools/peaks.cu -> profiles/r2_peaks.json); the ray kernels keep the scene in
+    #          L1/L2 and are bound here.  achieved = warp instructions/s x live lanes / 32, from the vertex count of this run
+    #          x the per-vertex instruction counts of the committed ncu capture of this build (profiles/r2_issue.json);
+    #   hbm:   algorithmic bytes / time against the measured copy bandwidth; the state kernels of the
+    #          wavefront (k_shade, k_connect) are bound here.
+    # `bound` is the roof the kernel is closer to.
     vertices = rays_e  # one closest-hit query per path vertex
-    dom_s = (acc["device"] if mode != "wavefront" else acc["extend"]) / 1e3
     ipk, ipk_src = issue_peak()
-    ic = issue_constants(name if mode != "wavefront" else name + ":wavefront")
-    roof = dict(bound="issue", kernel=("k_path_persist" if mode == "persistent" else "k_extend"), unit="Gwarp-inst/s", peak=ipk / 1e9, peak_source=ipk_src,
-                launches=int(st1["waves"] - st0["waves"]), vertices_per_launch=vertices / max(st1["waves"] - st0["waves"], 1))
-    if ic:
-        winst = ic["warp_inst_per_vertex"] * vertices
-        roof.update(achieved=winst * (ic["live_lanes"] / 32.0) / max(dom_s, 1e-12) / 1e9, issue_slots_frac=winst / max(dom_s, 1e-12) / ipk,
-                    live_lanes=ic["live_lanes"], warp_inst_per_vertex=ic["warp_inst_per_vertex"], traffic=ic.get("dram_bytes_per_launch"),
-                    capture=ic.get("capture"))
-        roof["frac"] = roof["achieved"] / roof["peak"]
-    else:
-        roof.update(achieved=None, frac=None, traffic=None, note="no ncu capture of this kernel committed yet (profiles/r2_issue.json)")
     hbm_peak, hbm_src = measured_peak_gbs()
+    waves = max(st1["waves"] - st0["waves"], 1)
+    alg_bytes = {"k_extend": 88, "k_shade": 280, "k_shade_final": 217, "k_shadow": 104, "k_connect": 185, "k_path_persist": 0}
     if mode == "wavefront":
-        ext_bytes = 4 + 48 + 8 + 4 + 24  # queue entry + ray read; t, object, normal written (DESIGN.md k_extend)
-        roof["hbm"] = dict(achieved=ext_bytes * rays_e / max(acc["extend"] / 1e3, 1e-12) / 1e9, peak=hbm_peak, unit="GB/s", peak_source=hbm_src,
-                           algorithmic_bytes_per_vertex=ext_bytes)
+        part = max(("extend", "shade", "shadow", "connect"), key=lambda k: acc[k])
+        kname = "k_shade_final" if (part == "shade" and d["max_bounces"] == 0 and name != "lampshade") else "k_" + part
+        dom_s = acc[part] / 1e3
+        ic = issue_constants(name + ":wavefront")
+        ick = (ic or {}).get("kernels", {}).get(kname) if ic else None
+        units = rays_s if part == "shadow" else vertices
     else:
-        roof["hbm"] = dict(achieved=0.0, peak=hbm_peak, unit="GB/s", peak_source=hbm_src, algorithmic_bytes_per_vertex=0,
-                           note="persistent kernel: the path lives in registers; HBM sees 24 B per (pixel, lane) slot per batch")
+        kname, dom_s, units = ("k_path_persist" if mode == "persistent" else "k_path_fused"), acc["device"] / 1e3, vertices
+        ic = issue_constants(name)
+        ick = ic
+    roof = dict(kernel=kname, launches=int(waves), vertices_per_launch=vertices / waves, share_of_step=dom_s / max(acc["device"] / 1e3, 1e-12))
+    hbm = dict(achieved=alg_bytes.get(kname, 0) * units / max(dom_s, 1e-12) / 1e9, peak=hbm_peak, unit="GB/s", peak_source=hbm_src,
+               algorithmic_bytes_per_vertex=alg_bytes.get(kname, 0))
+    hbm["frac"] = hbm["achieved"] / hbm_peak
+    issue = dict(peak=ipk / 1e9, unit="Gwarp-inst/s", peak_source=ipk_src)
+    if ick:
+        winst = ick["warp_inst_per_vertex"] * vertices
+        issue.update(achieved=winst * (ick["live_lanes"] / 32.0) / max(dom_s, 1e-12) / 1e9, issue_slots_frac=winst / max(dom_s, 1e-12) / ipk,
+                     live_lanes=ick["live_lanes"], warp_inst_per_vertex=ick["warp_inst_per_vertex"], capture=(ic or {}).get("capture"))
+        issue["frac"] = issue["achieved"] / issue["peak"]
+        traffic = ick.get("dram_bytes_per_vertex")
+        roof["traffic"] = traffic * vertices / waves if traffic is not None else ick.get("dram_bytes_per_launch")
+    else:
+        issue.update(achieved=None, frac=None, note="no ncu capture of this kernel committed (profiles/r2_issue.json)")
+        roof["traffic"] = None
+    pick = issue if (issue.get("frac") or 0.0) >= hbm["frac"] else hbm
+    roof.update(bound="issue" if pick is issue else "hbm", achieved=pick["achieved"], peak=pick["peak"], unit=pick["unit"], frac=pick["frac"],
+                peak_source=pick["peak_source"], issue=issue, hbm=hbm)
     cpu = None
     if world == 1 and cpu_seconds > 0:
         cpu, _ = cpu_sample(scene, cam, r.params(), cpu_seconds)

@@ -106,7 +106,9 @@ struct rptx_film {
     double** d_batch_ptrs = nullptr;
     uint64_t next_sample = 0;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
-    cudaEvent_t evw[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};  // per-wave kernel boundaries
+    cudaEvent_t evw[4][5] = {};   // per-wave kernel boundaries, one set per wave in flight (run_waves)
+    cudaEvent_t ev_done[4] = {};  // the wave's live count has landed in pinned memory
+    bool no_one_vertex = false;   // RPTX_NO_ONE_VERTEX
     rptx_stats stats = {};
     bool timing_pending = false;  // ev0 / ev1 of the last traced batch not read yet
 };

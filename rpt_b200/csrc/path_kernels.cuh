@@ -583,6 +583,8 @@ __global__ void __launch_bounds__(kBlock) k_connect(PathPool p, Queues q, BatchP
             const d3 direct = MEDIUM ? rec_load(p.mvtx, slot, 0) : mk3(0, 0, 0);
             alive = connect_vertex<MEDIUM>(p, bp, cam, slot, direct, &my_started);
             q.keep[i] = alive ? 1 : 0;
+        } else if (i < p.n_slots) {
+            q.keep[i] = 0;  // between the live count and the host's (lagged) bound: nothing to keep
         }
     }
     stat_add(&q.stats[0], my_started);
@@ -675,6 +677,8 @@ __global__ void __launch_bounds__(kBlock, RPTX_OCC_FINAL) k_shade_final(const __
             alive = true;
         }
         q.keep[i] = alive ? 1 : 0;
+    } else if (i < p.n_slots) {
+        q.keep[i] = 0;  // between the live count and the host's (lagged) bound: nothing to keep
     }
     stat_add(&q.stats[0], my_started);
     stat_add64(&q.stats[2], my_queries);

@@ -792,7 +792,11 @@ static int film_alloc(rptx_film* f) {
     CK(cudaMemsetAsync(f->d_batch_sum, 0, sizeof(double) * n3, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
     CK(cudaEventCreate(&f->ev0)); CK(cudaEventCreate(&f->ev1));
-    for (int k = 0; k < 5; k++) CK(cudaEventCreate(&f->evw[k]));
+    for (int r = 0; r < 4; r++) {
+        for (int k = 0; k < 5; k++) CK(cudaEventCreate(&f->evw[r][k]));
+        CK(cudaEventCreate(&f->ev_done[r]));
+    }
+    f->no_one_vertex = std::getenv("RPTX_NO_ONE_VERTEX") != nullptr;  // developer knob, read once per film
     return 0;
 }
 
@@ -908,11 +912,24 @@ void rptx_film_destroy(rptx_film* f) {
     if (f->d_batch_ptrs) cudaFree(f->d_batch_ptrs);
     if (f->ev0) cudaEventDestroy(f->ev0);
     if (f->ev1) cudaEventDestroy(f->ev1);
-    for (int k = 0; k < 5; k++) if (f->evw[k]) cudaEventDestroy(f->evw[k]);
+    for (int r = 0; r < 4; r++) {
+        for (int k = 0; k < 5; k++) if (f->evw[r][k]) cudaEventDestroy(f->evw[r][k]);
+        if (f->ev_done[r]) cudaEventDestroy(f->ev_done[r]);
+    }
     delete f;
 }
 
 }  // extern "C"
+
+// The wave loop.  The host never waits for the wave it just launched: the live count of wave w is copied to pinned memory
+// behind it and read kWaveLag waves later, so the launches of waves w+1 .. w+kWaveLag are already queued when wave w ends
+// (round 1 synchronised the stream once per wave: a launch-latency bubble per wave, 97 waves per lampshade batch).  Counts
+// never grow (a finished path's slot either regenerates in place or leaves the queue), so a count that is kWaveLag waves old
+// is an upper bound for the grid of the next wave; every kernel bounds itself by the device-side count, and k_connect /
+// k_shade_final clear the keep flags between the true count and the bound for the in-order compaction.  The loop ends when
+// a lagged count reads zero, i.e. after at most kWaveLag empty waves.
+constexpr int kWaveLag = 2;
+constexpr int kWaveRing = 4;
 
 template <bool MEDIUM>
 static int run_waves(rptx_film* f, const BatchParams& bp) {
@@ -927,18 +944,31 @@ static int run_waves(rptx_film* f, const BatchParams& bp) {
     ctx->launches++;
     const int persistent_blocks = ctx->sm_count * 8;
     const bool small = sc.small_scene != 0;
-    const bool one_vertex = !MEDIUM && bp.max_bounces == 0 && !std::getenv("RPTX_NO_ONE_VERTEX");  // k_shade_final
-    uint32_t* h_count = (uint32_t*)ctx->h_pinned;
-    uint32_t active = std::min<uint64_t>(p.n_slots, (uint64_t)p.n_pixels * std::min(p.n_lanes, bp.n_local));
-    while (active > 0) {
-        const int blocks = (int)std::min<uint64_t>(persistent_blocks, grid_for(active, kBlock));
-        cudaEventRecord(f->evw[0], st);
+    const bool one_vertex = !MEDIUM && bp.max_bounces == 0 && !f->no_one_vertex;  // k_shade_final
+    uint32_t* h_count = (uint32_t*)ctx->h_pinned;  // ring of kWaveRing counts
+    uint32_t bound = std::min<uint64_t>(p.n_slots, (uint64_t)p.n_pixels * std::min(p.n_lanes, bp.n_local));
+    auto collect = [&](int slot) -> uint32_t {  // wait for the wave in ring slot `slot`, add its kernel times, return its live count
+        cudaEventSynchronize(f->ev_done[slot]);
+        cudaEvent_t* e = f->evw[slot];
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, e[0], e[1]) == cudaSuccess) f->stats.extend_ms += ms;
+        if (cudaEventElapsedTime(&ms, e[1], e[2]) == cudaSuccess) f->stats.shade_ms += ms;
+        if (cudaEventElapsedTime(&ms, e[2], e[3]) == cudaSuccess) f->stats.shadow_ms += ms;
+        if (cudaEventElapsedTime(&ms, e[3], e[4]) == cudaSuccess) f->stats.connect_ms += ms;
+        return h_count[slot];
+    };
+    int launched = 0, collected = 0;
+    while (bound > 0) {
+        const int slot = launched % kWaveRing;
+        cudaEvent_t* e = f->evw[slot];
+        const int blocks = (int)std::min<uint64_t>(persistent_blocks, grid_for(bound, kBlock));
+        cudaEventRecord(e[0], st);
         if (small) k_extend<true><<<blocks, kBlock, 0, st>>>(sc, p, q);
         else k_extend<false><<<blocks, kBlock, 0, st>>>(sc, p, q);
-        cudaEventRecord(f->evw[1], st);
+        cudaEventRecord(e[1], st);
         if (one_vertex) {
             // the vertex ends the path: shade + NEE visibility + film add + regeneration in one kernel
-            const int g = (int)grid_for(active, kBlock);
+            const int g = (int)grid_for(bound, kBlock);
             if (small) {
                 if (sc.shadow_probe_mask) k_shade_final<true, true><<<g, kBlock, 0, st>>>(sc, p, q, bp, f->cam);
                 else k_shade_final<false, true><<<g, kBlock, 0, st>>>(sc, p, q, bp, f->cam);
@@ -946,18 +976,12 @@ static int run_waves(rptx_film* f, const BatchParams& bp) {
                 if (sc.shadow_probe_mask) k_shade_final<true, false><<<g, kBlock, 0, st>>>(sc, p, q, bp, f->cam);
                 else k_shade_final<false, false><<<g, kBlock, 0, st>>>(sc, p, q, bp, f->cam);
             }
-            cudaEventRecord(f->evw[2], st);
-            cudaEventRecord(f->evw[3], st);
-            {
-                size_t bytes = f->select_tmp_bytes;
-                CK(cub::DeviceSelect::Flagged(f->d_select_tmp, bytes, q.cur, q.keep, q.next, q.counters + 1, (int)active, st));
-            }
-            cudaEventRecord(f->evw[4], st);
-            ctx->launches += 4;
+            cudaEventRecord(e[2], st);
+            cudaEventRecord(e[3], st);
+            ctx->launches += 2;
         } else {
-        k_shade<MEDIUM><<<grid_for(active, kShadeBlock), kShadeBlock, 0, st>>>(sc, p, q, bp, md);
-        cudaEventRecord(f->evw[2], st);
-        {
+            k_shade<MEDIUM><<<grid_for(bound, kShadeBlock), kShadeBlock, 0, st>>>(sc, p, q, bp, md);
+            cudaEventRecord(e[2], st);
             if (p.n_shadow) {
                 if (small) {
                     if (sc.shadow_probe_mask) k_shadow_warp<true, true><<<blocks, kBlock, 0, st>>>(sc, p, q);
@@ -967,29 +991,26 @@ static int run_waves(rptx_film* f, const BatchParams& bp) {
                     else k_shadow_block<false, false><<<blocks, kBlock, 0, st>>>(sc, p, q);
                 }
             }
-            cudaEventRecord(f->evw[3], st);
-            k_connect<MEDIUM><<<grid_for(active, kBlock), kBlock, 0, st>>>(p, q, bp, f->cam);
-            {  // next = kept entries of cur, in order; the count lands in counters[1]
-                size_t bytes = f->select_tmp_bytes;
-                CK(cub::DeviceSelect::Flagged(f->d_select_tmp, bytes, q.cur, q.keep, q.next, q.counters + 1, (int)active, st));
-            }
-            cudaEventRecord(f->evw[4], st);
-            ctx->launches += p.n_shadow ? 6 : 5;  // + the two kernels of the select
+            cudaEventRecord(e[3], st);
+            k_connect<MEDIUM><<<grid_for(bound, kBlock), kBlock, 0, st>>>(p, q, bp, f->cam);
+            ctx->launches += p.n_shadow ? 4 : 3;
         }
+        {  // next = kept entries of cur, in order; the count lands in counters[1]
+            size_t bytes = f->select_tmp_bytes;
+            CK(cub::DeviceSelect::Flagged(f->d_select_tmp, bytes, q.cur, q.keep, q.next, q.counters + 1, (int)bound, st));
+            ctx->launches += 2;
         }
+        cudaEventRecord(e[4], st);
         k_wave_end<<<1, 1, 0, st>>>(q);
         ctx->launches++;
         f->stats.waves++;
         std::swap(q.cur, q.next);
-        CK(cudaMemcpyAsync(h_count, q.counters, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
-        CK(cudaStreamSynchronize(st));
-        active = *h_count;
-        float ms = 0.f;
-        if (cudaEventElapsedTime(&ms, f->evw[0], f->evw[1]) == cudaSuccess) f->stats.extend_ms += ms;
-        if (cudaEventElapsedTime(&ms, f->evw[1], f->evw[2]) == cudaSuccess) f->stats.shade_ms += ms;
-        if (cudaEventElapsedTime(&ms, f->evw[2], f->evw[3]) == cudaSuccess) f->stats.shadow_ms += ms;
-        if (cudaEventElapsedTime(&ms, f->evw[3], f->evw[4]) == cudaSuccess) f->stats.connect_ms += ms;
+        CK(cudaMemcpyAsync(h_count + slot, q.counters, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+        CK(cudaEventRecord(f->ev_done[slot], st));
+        launched++;
+        if (launched - collected > kWaveLag - 1) bound = std::min(bound, collect(collected++ % kWaveRing));
     }
+    while (collected < launched) collect(collected++ % kWaveRing);
     CK(cudaGetLastError());
     return 0;
 }
