@@ -2,6 +2,7 @@
 #include <cub/cub.cuh>
 
 #include "bvh_build.cuh"
+#include "host_types.hpp"
 
 namespace rptx {
 
@@ -155,10 +156,10 @@ int build_lbvh(const PrimBox* d_boxes, uint32_t n, float pad, int leaf_max, cons
     void* tmp = nullptr;
     size_t tmp_bytes = 0;
 #define RPTX_CK(x) do { e = (x); if (e != cudaSuccess) goto fail; } while (0)
-    RPTX_CK(cudaMallocAsync((void**)&keys_in, sizeof(uint64_t) * n, stream));
-    RPTX_CK(cudaMallocAsync((void**)&keys_out, sizeof(uint64_t) * n, stream));
-    RPTX_CK(cudaMallocAsync((void**)&ints, sizeof(int) * (size_t)n * 7, stream));
-    RPTX_CK(cudaMallocAsync((void**)&ibox, sizeof(PrimBox) * n, stream));
+    RPTX_CK(rptx_alloc_async((void**)&keys_in, sizeof(uint64_t) * n, stream));
+    RPTX_CK(rptx_alloc_async((void**)&keys_out, sizeof(uint64_t) * n, stream));
+    RPTX_CK(rptx_alloc_async((void**)&ints, sizeof(int) * (size_t)n * 7, stream));
+    RPTX_CK(rptx_alloc_async((void**)&ibox, sizeof(PrimBox) * n, stream));
     {
         float3 fmin = make_float3((float)cmin[0], (float)cmin[1], (float)cmin[2]);
         float3 finv;
@@ -170,7 +171,7 @@ int build_lbvh(const PrimBox* d_boxes, uint32_t n, float pad, int leaf_max, cons
         k_morton<<<B, T, 0, stream>>>(d_boxes, n, fmin, finv, keys_in);
         (*launches)++;
         RPTX_CK(cub::DeviceRadixSort::SortKeys(nullptr, tmp_bytes, keys_in, keys_out, (int)n, 0, 64, stream));
-        RPTX_CK(cudaMallocAsync((void**)&tmp, tmp_bytes ? tmp_bytes : 16, stream));
+        RPTX_CK(rptx_alloc_async((void**)&tmp, tmp_bytes ? tmp_bytes : 16, stream));
         RPTX_CK(cub::DeviceRadixSort::SortKeys(tmp, tmp_bytes, keys_in, keys_out, (int)n, 0, 64, stream));
         (*launches) += 1;
         int* left = ints;
@@ -206,8 +207,8 @@ int build_lbvh_sorted(const uint64_t* d_keys, const PrimBox* d_boxes, uint32_t n
     int* ints = nullptr;
     PrimBox* ibox = nullptr;
 #define RPTX_CK(x) do { e = (x); if (e != cudaSuccess) goto fail; } while (0)
-    RPTX_CK(cudaMallocAsync((void**)&ints, sizeof(int) * (size_t)n * 7, stream));
-    RPTX_CK(cudaMallocAsync((void**)&ibox, sizeof(PrimBox) * n, stream));
+    RPTX_CK(rptx_alloc_async((void**)&ints, sizeof(int) * (size_t)n * 7, stream));
+    RPTX_CK(rptx_alloc_async((void**)&ibox, sizeof(PrimBox) * n, stream));
     {
         const int T = 128;
         const int B = (int)((n + T - 1) / T);

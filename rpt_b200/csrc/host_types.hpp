@@ -116,7 +116,17 @@ struct rptx_film {
 // Stream-ordered allocation for everything that is created and destroyed per call (scene buffers, BVH build
 // scratch): cudaMalloc / cudaFree take a device-wide lock and, with a 20 GB film slab mapped, stalled for
 // 20-460 ms at random in the end-to-end loop; the pool (release threshold set in rptx_ctx_create) does neither.
-inline cudaError_t rptx_alloc_async(void** p, size_t bytes, cudaStream_t st) { return cudaMallocAsync(p, bytes ? bytes : 16, st); }
+// Large requests are rounded up to a coarse size class (+1.6 %, then the next multiple of 256 MB): two photon renders of the
+// same configuration differ by a few thousand rows, and the pool can only hand a cached block to a request that fits it —
+// without the classes a step whose lists were 0.01 % longer than the previous step's mapped fresh memory for every GB-sized
+// buffer (map build 110 ms -> 1.8 s in one step of two at 1e8 photons, profiles/r2_summary.md).
+inline cudaError_t rptx_alloc_async(void** p, size_t bytes, cudaStream_t st) {
+    if (bytes >= (32ull << 20)) {
+        const size_t cls = 256ull << 20;
+        bytes = (bytes + bytes / 64 + cls - 1) / cls * cls;
+    }
+    return cudaMallocAsync(p, bytes ? bytes : 16, st);
+}
 inline void rptx_free_async(const void* p, cudaStream_t st) { if (p) cudaFreeAsync(const_cast<void*>(p), st); }
 
 // host helpers shared by rptx.cu and photon.cu

@@ -5,7 +5,9 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdlib>
+#include <cstdio>
 #include <cstring>
+#include <ctime>
 #include <string>
 #include <vector>
 
@@ -38,6 +40,26 @@ struct BoxBvhHost {
 };
 
 int grid_for(size_t n, int block) { return (int)std::max<size_t>(1, (n + block - 1) / block); }
+
+// developer knob RPTX_TRACE_BUILD: per-phase wall time of the photon passes on stderr (synchronises the stream)
+struct PhaseTrace {
+    rptx_ctx* ctx;
+    bool on;
+    double t0;
+    static double now() {
+        timespec ts;
+        clock_gettime(CLOCK_MONOTONIC, &ts);
+        return ts.tv_sec * 1e3 + ts.tv_nsec * 1e-6;
+    }
+    explicit PhaseTrace(rptx_ctx* c) : ctx(c), on(std::getenv("RPTX_TRACE_BUILD") != nullptr), t0(0) { if (on) { cudaStreamSynchronize(ctx->stream); t0 = now(); } }
+    void mark(const char* what) {
+        if (!on) return;
+        cudaStreamSynchronize(ctx->stream);
+        const double t = now();
+        fprintf(stderr, "[rptx] %-28s %8.2f ms\n", what, t - t0);
+        t0 = t;
+    }
+};
 
 // Everything here comes from the stream-ordered pool on the library's stream: cudaMalloc / cudaFree
 // next to a mapped multi-GB film slab or photon list stall for 20-460 ms at random (profiles/r1_v2_summary.md).
@@ -336,11 +358,15 @@ int build_point_map(rptx_ctx* ctx, const PhotonRec* rows, const uint32_t* d_cano
         const double3 dmn = make_double3(mn[0], mn[1], mn[2]);
         const double3 inv = make_double3(mx[0] > mn[0] ? 1.0 / (mx[0] - mn[0]) : 0.0, mx[1] > mn[1] ? 1.0 / (mx[1] - mn[1]) : 0.0,
                                          mx[2] > mn[2] ? 1.0 / (mx[2] - mn[2]) : 0.0);
+        PhaseTrace trace(ctx);
         k_rows_morton<<<grid_for(n, 256), 256, 0, st>>>(rows, d_canon, n, dmn, inv, k0);
         ctx->launches++;
+        trace.mark("  morton keys");
         if (int r = sort_pairs(ctx, k0, k1, const_cast<uint32_t*>(d_canon), i1, n, 63)) return r;
+        trace.mark("  morton sort");
         k_rows_gather<<<grid_for(n, 256), 256, 0, st>>>(rows, i1, n, px, py, pz, dir, power, key);
         ctx->launches++;
+        trace.mark("  rows -> SoA");
         rptx_free_async(k0, ctx->stream); k0 = nullptr;
         rptx_free_async(i1, ctx->stream); i1 = nullptr;
         CK(dev_alloc(ctx, &boxes, n, nullptr));
@@ -348,6 +374,7 @@ int build_point_map(rptx_ctx* ctx, const PhotonRec* rows, const uint32_t* d_cano
         ctx->launches++;
         const int e = build_lbvh_sorted(k1, boxes, n, 0.0f, kPointLeaf, nodes, &out->dev.root_ref, st, &ctx->launches);
         if (e != 0) return ctx_fail(ctx, std::string("point map LBVH: ") + cudaGetErrorString((cudaError_t)e));
+        trace.mark("  boxes + LBVH");
         return 0;
     };
     rc = body();
@@ -480,6 +507,7 @@ int rptx_photons_emit(rptx_ctx* ctx, rptx_scene* scene, const rptx_params* param
     uint64_t counts[3] = {0, 0, 0};
     uint64_t cap_s, cap_v;
     int rc = 0;
+    PhaseTrace trace(ctx);
     if (count > (1ull << 17)) {
         // counting-only pilot over the first 2^16 photons sizes the append buffers
         EmitParams pilot = ep;
@@ -498,7 +526,9 @@ int rptx_photons_emit(rptx_ctx* ctx, rptx_scene* scene, const rptx_params* param
         if (e == cudaSuccess) e = rptx_alloc_async((void**)&p->d_rows[1], std::max<uint64_t>(cap_v, 1) * sizeof(PhotonRec), ctx->stream);
         if (e != cudaSuccess) { rc = ctx_fail(ctx, std::string("photon buffers: ") + cudaGetErrorString(e)); break; }
         p->cap[0] = cap_s; p->cap[1] = cap_v;
+        trace.mark("emit: pilot + buffers");
         rc = emit_once(ctx, scene, ep, p->d_rows[0], cap_s, p->d_rows[1], cap_v, counts);
+        trace.mark("emit: k_photon_trace");
         if (rc) break;
         if (counts[0] <= cap_s && counts[1] <= cap_v) break;
         cap_s = std::max(cap_s, counts[0]); cap_v = std::max(cap_v, counts[1]);  // deterministic walk: exact sizes now known
@@ -623,12 +653,17 @@ int rptx_photon_map_build(rptx_ctx* ctx, rptx_scene* scene, rptx_photons* photon
     int rc = 0;
     uint32_t *canon_s = nullptr, *canon_v = nullptr, *perm = nullptr;
     const uint32_t ns = (uint32_t)photons->n[0], nv = (uint32_t)photons->n[1];
+    PhaseTrace trace(ctx);
     auto body = [&]() -> int {
         if (int r = canonical_order(ctx, photons->d_rows[0], ns, &canon_s)) return r;
+        trace.mark("build: canonical surface");
         if (int r = build_point_map(ctx, photons->d_rows[0], canon_s, ns, &m->surface)) return r;
+        trace.mark("build: point map surface");
         if (int r = canonical_order(ctx, photons->d_rows[1], nv, &canon_v)) return r;
+        trace.mark("build: canonical volume");
         if (kind == RPTX_PHOTON_MAP || kind == RPTX_PHOTON_POINT_BEAM) {
             if (int r = build_point_map(ctx, photons->d_rows[1], canon_v, nv, &m->volume)) return r;
+            trace.mark("build: point map volume");
         }
         if (kind == RPTX_PHOTON_POINT_BEAM) {
             double *radius = nullptr, *center = nullptr, *rad = nullptr, *dir = nullptr, *power = nullptr;
@@ -675,6 +710,7 @@ int rptx_photon_map_build(rptx_ctx* ctx, rptx_scene* scene, rptx_photons* photon
         }
         CK(cudaGetLastError());
         CK(cudaStreamSynchronize(st));
+        trace.mark("build: spheres / beams + BVH");
         return 0;
     };
     rc = body();

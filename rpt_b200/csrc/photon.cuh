@@ -497,9 +497,21 @@ RPTX_DN d3 volume_estimate(const SceneDev& sc, const MediumDev& md, const Photon
     d3 volume_color = mk3(0, 0, 0);
     if (pm.kind == 1) {
         const SphereMapDev& sm = pm.spheres;
+        const float fox = (float)ray.o.x, foy = (float)ray.o.y, foz = (float)ray.o.z;
+        const float fdx = (float)ray.d.x, fdy = (float)ray.d.y, fdz = (float)ray.d.z;  // unit direction (primary_ray normalises)
         box_bvh_traverse(sm.bvh, r32, [&](uint32_t i) {
             ctr.candidates++;
             const d3 c = mk3(sm.center[3 * (size_t)i], sm.center[3 * (size_t)i + 1], sm.center[3 * (size_t)i + 2]);
+            {
+                // conservative f32 cull of the disk test below: the sphere contributes only if the centre lies within
+                // `radius` of the ray's line.  perp^2 = |c - o|^2 - ((c - o).d)^2 in f32 carries a relative error of a few
+                // 2^-23 of |c - o|^2; the margin is 16x that, and the exact f64 test decides everything inside it.
+                const float lx = (float)c.x - fox, ly = (float)c.y - foy, lz = (float)c.z - foz;
+                const float l2 = lx * lx + ly * ly + lz * lz;
+                const float s = lx * fdx + ly * fdy + lz * fdz;
+                const float rf = (float)sm.radius[i];
+                if (l2 - s * s > rf * rf * 1.0001f + l2 * 4e-6f) return;
+            }
             const d3 origin_to_center = c - ray.o;
             if (hit && length(origin_to_center) > t_hit) return;
             const double radius = sm.radius[i];
@@ -517,11 +529,28 @@ RPTX_DN d3 volume_estimate(const SceneDev& sc, const MediumDev& md, const Photon
         return volume_color;
     }
     const BeamMapDev& bm = pm.beams;
+    const float fox = (float)ray.o.x, foy = (float)ray.o.y, foz = (float)ray.o.z;
+    const float fdx = (float)ray.d.x, fdy = (float)ray.d.y, fdz = (float)ray.d.z;
     box_bvh_traverse(bm.bvh, r32, [&](uint32_t i) {
         ctr.candidates++;
         const size_t i3 = 3 * (size_t)i;
         const d3 bstart = mk3(bm.start[i3], bm.start[i3 + 1], bm.start[i3 + 2]);
         const d3 bdir = mk3(bm.dirn[i3], bm.dirn[i3 + 1], bm.dirn[i3 + 2]);
+        {
+            // conservative f32 cull of the `dist >= radius` test below.  `dist` is the distance between a point of the camera
+            // ray's line and a point of the beam's line, so it is at least the distance between the two lines,
+            // |l . (d x b)| / |d x b|.  Beams whose line passes farther than the radius (with a margin of 16x the f32
+            // rounding of the triple product, relative to |l| |d x b|) contribute nothing; nearly parallel lines and
+            // everything inside the margin go to the exact f64 test.
+            const float bx = (float)bdir.x, by = (float)bdir.y, bz = (float)bdir.z;
+            const float nx = fdy * bz - fdz * by, ny = fdz * bx - fdx * bz, nz = fdx * by - fdy * bx;
+            const float n2 = nx * nx + ny * ny + nz * nz;
+            const float lx = (float)bstart.x - fox, ly = (float)bstart.y - foy, lz = (float)bstart.z - foz;
+            const float trip = lx * nx + ly * ny + lz * nz;
+            const float l2 = lx * lx + ly * ly + lz * lz;
+            const float lim = (float)kBeamRadius * 1.0001f;
+            if (n2 > 1e-6f && trip * trip > (lim * lim + l2 * 4e-6f) * n2) return;
+        }
         const d3 l = bstart - ray.o;
         const d3 u = normalize(cross(l, bdir));
         const d3 n = normalize(cross(bdir, u));

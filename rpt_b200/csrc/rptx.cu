@@ -361,12 +361,13 @@ int rptx_ctx_create(int device_id, rptx_ctx** out) {
     CK(cudaGetDeviceProperties(&prop, device_id));
     ctx->sm_count = prop.multiProcessorCount;
     CK(cudaMallocHost((void**)&ctx->h_pinned, 64));
-    {  // scene tables, batch means, photon maps and every build scratch come from the stream-ordered pool; it keeps up to
-       // 16 GB mapped across synchronisations (a 1e7-photon map build cycles through ~4 GB; with a 1 GB threshold the pool
-       // re-mapped it on every call: build 40 -> 150 ms)
+    {  // scene tables, batch means, photon maps and every build scratch come from the stream-ordered pool.  It never trims:
+       // a 1e8-photon render cycles through ~45 GB of rows, maps and sort scratch per call, and with a finite release
+       // threshold (16 GB in round 1) the pool unmapped and re-mapped the excess at every synchronisation (beam-beam step
+       // 3.9 -> 6.2 s once another workload had run in the same process)
         cudaMemPool_t pool;
         CK(cudaDeviceGetDefaultMemPool(&pool, device_id));
-        uint64_t keep = 16ull << 30;
+        uint64_t keep = UINT64_MAX;
         CK(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep));
     }
     return 0;
