@@ -293,6 +293,22 @@ int  rptx_intersect_batch_device(rptx_scene* scene, const void* d_o, const void*
                                  void* d_inst_id, void* d_normal);
 int  rptx_stats_get(const rptx_film* film, rptx_stats* out);
 
+/* Allocation-free variant of rptx_intersect_batch.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid it).  Same inputs, outputs and results as
+ * rptx_intersect_batch (host arrays; any output pointer may be NULL), plus n_hits (may be NULL):
+ * the number of rays that hit something.  The device staging that rptx_intersect_batch
+ * cudaMalloc's per call lives in ONE fixed `static __device__` array of the library (about
+ * 5.8 MiB, held by every GPU that loads librptx.so until the process exits), so
+ *   - n > RPTX_INTERSECT_STATIC_MAX_RAYS is rejected (returns 1, message in rptx_last_error);
+ *   - the call performs no cudaMalloc / cudaFree / cudaMallocAsync;
+ *   - all calls on one GPU share the array: calls that overlap on the GPU (two contexts or two
+ *     host threads on the same device) race; calls through one context are serialised. */
+#define RPTX_INTERSECT_STATIC_MAX_RAYS 65536
+int  rptx_intersect_batch_static(rptx_scene* scene, const double* o, const double* d, size_t n,
+                                 double t_min, double* t, uint32_t* object_id, uint32_t* prim_id,
+                                 uint32_t* inst_id, double* normal, uint64_t* n_hits);
+
 #ifdef __cplusplus
 }
 #endif

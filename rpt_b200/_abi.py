@@ -119,6 +119,7 @@ U8P = C.POINTER(C.c_uint8)
 U64P = C.POINTER(C.c_uint64)
 PHOTON_ROW_F64 = 13  # RPTX_PHOTON_ROW_BYTES / 8
 COMM_ID_BYTES = 128
+INTERSECT_STATIC_MAX_RAYS = 65536  # RPTX_INTERSECT_STATIC_MAX_RAYS
 
 # name -> (restype, argtypes): every symbol include/rptx.h declares
 PROTOTYPES = {
@@ -170,6 +171,7 @@ PROTOTYPES = {
     "rptx_intersect_batch": (C.c_int, [P, DP, DP, C.c_size_t, C.c_double, DP, U32P, U32P, U32P, DP]),
     "rptx_intersect_batch_device": (C.c_int, [P, P, P, C.c_size_t, C.c_double, P, P, P, P, P]),
     "rptx_stats_get": (C.c_int, [P, C.POINTER(Stats)]),
+    "rptx_intersect_batch_static": (C.c_int, [P, DP, DP, C.c_size_t, C.c_double, DP, U32P, U32P, U32P, DP, U64P]),
 }
 
 _lib = None

@@ -148,6 +148,24 @@ class DeviceScene:
         self.ctx.check(rc, "rptx_intersect_batch")
         return t, obj, prim, inst, nrm
 
+    def intersect_batch_static(self, o, d, t_min=1e-12):
+        """intersect_batch through rptx_intersect_batch_static: no device allocation (the staging is a fixed static
+        device array of the library), at most A.INTERSECT_STATIC_MAX_RAYS rays per call.  Returns the same arrays plus
+        the number of rays that hit something.  No counterpart in the reference."""
+        o = np.ascontiguousarray(o, dtype=np.float64).reshape(-1, 3)
+        d = np.ascontiguousarray(d, dtype=np.float64).reshape(-1, 3)
+        n = len(o)
+        t = np.empty(n, np.float64)
+        obj = np.empty(n, np.uint32)
+        prim = np.empty(n, np.uint32)
+        inst = np.empty(n, np.uint32)
+        nrm = np.empty((n, 3), np.float64)
+        hits = C.c_uint64(0)
+        rc = self.lib.rptx_intersect_batch_static(self.h, _dp(o), _dp(d), n, t_min, _dp(t), obj.ctypes.data_as(A.U32P),
+                                                  prim.ctypes.data_as(A.U32P), inst.ctypes.data_as(A.U32P), _dp(nrm), C.byref(hits))
+        self.ctx.check(rc, "rptx_intersect_batch_static")
+        return t, obj, prim, inst, nrm, int(hits.value)
+
     def close(self):
         if self.h:
             self.lib.rptx_scene_destroy(self.h)

@@ -37,6 +37,7 @@ pub const RPTX_PHOTON_BEAM_BEAM: i32 = 2;
 /// One photon record = position, direction, power, starting_position (f64 x 3 each) + u64 key.
 pub const RPTX_PHOTON_ROW_BYTES: usize = 104;
 /// Size of the communicator id rank 0 hands to the other ranks (an ncclUniqueId).
+pub const RPTX_INTERSECT_STATIC_MAX_RAYS: usize = 65536;
 pub const RPTX_COMM_ID_BYTES: usize = 128;
 
 #[repr(C)] pub struct rptx_ctx { _p: [u8; 0] }
@@ -199,4 +200,6 @@ extern "C" {
     pub fn rptx_intersect_batch(scene: *mut rptx_scene, o: *const f64, d: *const f64, n: usize, t_min: f64, t: *mut f64, object_id: *mut u32, prim_id: *mut u32, inst_id: *mut u32, normal: *mut f64) -> c_int;
     pub fn rptx_intersect_batch_device(scene: *mut rptx_scene, d_o: *const c_void, d_d: *const c_void, n: usize, t_min: f64, d_t: *mut c_void, d_object_id: *mut c_void, d_prim_id: *mut c_void, d_inst_id: *mut c_void, d_normal: *mut c_void) -> c_int;
     pub fn rptx_stats_get(film: *const rptx_film, out: *mut rptx_stats) -> c_int;
+    /// allocation-free rptx_intersect_batch (static device scratch, n <= RPTX_INTERSECT_STATIC_MAX_RAYS); no counterpart in rpt
+    pub fn rptx_intersect_batch_static(scene: *mut rptx_scene, o: *const f64, d: *const f64, n: usize, t_min: f64, t: *mut f64, object_id: *mut u32, prim_id: *mut u32, inst_id: *mut u32, normal: *mut f64, n_hits: *mut u64) -> c_int;
 }
