@@ -159,72 +159,108 @@ RPTX_D void sample_lights_dev(const SceneDev& sc, const PathPool& p, uint32_t sl
     });
 }
 
-// shade: one thread per queue entry.  The three kinds of vertex (medium collision, surface hit, miss) run
-// different code, and a warp of 32 consecutive queue entries holds all three (lampshade: 12 of 32 lanes live
-// per instruction).  So each block first classifies its kShadeBlock entries (the class needs t, the hit
-// object and, with a medium, the free-flight draw) and re-deals them to its threads sorted by class
-// (stable counting sort through shared memory): all but two or three of its warps then run one kind only.
-// The entries stay within kShadeBlock queue positions of where they were, so the state accesses stay local.
+// shade: the three kinds of vertex (medium collision, surface hit, miss) run different code, and a warp of 32
+// consecutive queue entries holds all three (lampshade: 12 of 32 lanes live per instruction unsorted).  So a
+// block takes a TILE of `rounds` x kShadeBlock consecutive queue entries, classifies them (the class needs t,
+// the hit object and, with a medium, the free-flight draw), sorts the tile by class in shared memory (stable
+// counting sort: ballot ranks, a 32-wide scan per class) and walks the sorted tile kShadeBlock entries at a
+// time: only the two warp-rounds that straddle a class boundary are mixed.  Round 1 sorted kShadeBlock entries
+// only (two or three mixed warps of four: 19.4 live lanes on lampshade).  The entries stay within one tile of
+// their queue position, so the state accesses stay local; `rounds` is chosen by the host from the wave's size
+// (a small wave keeps one round, so that it still fills the SMs).
 constexpr int kShadeBlock = RPTX_SHADE_BLOCK;
+#ifndef RPTX_SHADE_ROUNDS
+#define RPTX_SHADE_ROUNDS 8
+#endif
+constexpr int kShadeRoundsMax = RPTX_SHADE_ROUNDS;
+constexpr int kShadeTile = kShadeBlock * kShadeRoundsMax;
+constexpr int kShadeWarps = kShadeBlock / 32;
+static_assert(kShadeWarps * kShadeRoundsMax <= 32 && kShadeBlock >= 96, "one 32-wide scan per class over the (round, warp) counts");
 
 template <bool MEDIUM>
 __global__ void __launch_bounds__(kShadeBlock, RPTX_OCC_SHADE) k_shade(const __grid_constant__ SceneDev sc, PathPool p, Queues q, BatchParams bp,
-                                                          MediumDev md) {
-    __shared__ uint32_t s_slot[kShadeBlock];
-    __shared__ uint32_t s_cnt[3][kShadeBlock / 32];
-    __shared__ double s_dsamp[MEDIUM ? kShadeBlock : 1];      // the free-flight draw travels with the entry
-    __shared__ uint64_t s_rng[MEDIUM ? kShadeBlock : 1];
-    uint32_t slot;
+                                                          MediumDev md, uint32_t rounds) {
+    __shared__ uint32_t s_slot[kShadeTile];
+    __shared__ uint16_t s_perm[kShadeTile];                   // sorted position -> tile position
+    __shared__ uint8_t s_cls[kShadeTile];
+    __shared__ uint32_t s_cnt[3][32];                         // per class: entries of (round, warp), then their exclusive scan
+    __shared__ uint32_t s_tot[3];
+    __shared__ double s_dsamp[MEDIUM ? kShadeTile : 1];       // the free-flight draw travels with the entry
+    __shared__ uint64_t s_rng[MEDIUM ? kShadeTile : 1];
+    const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
+    const uint32_t lt = (1u << lane) - 1u;
+    {
+        const uint32_t count = q.counters[0];
+        const uint32_t tile_base = blockIdx.x * (rounds * kShadeBlock);
+        if (threadIdx.x < 96) s_cnt[warp][lane] = 0;
+        __syncthreads();
+        for (uint32_t r = 0; r < rounds; r++) {
+            const uint32_t u = r * kShadeBlock + threadIdx.x;
+            const uint32_t i = tile_base + u;
+            uint32_t cls = 3;  // 0 medium collision, 1 surface, 2 miss, 3 no entry
+            if (i < count) {
+                const uint32_t slot0 = q.cur[i];
+#ifndef RPTX_NO_SHADE_PREFETCH
+                // the entry is dealt to another thread of this block below: start its state on the way to L2 now, so
+                // that the loads after the re-deal do not add a third DRAM round trip (queue -> hit object -> state)
+                prefetch_l2(p.ox + slot0); prefetch_l2(p.oy + slot0); prefetch_l2(p.oz + slot0);
+                prefetch_l2(p.dx + slot0); prefetch_l2(p.dy + slot0); prefetch_l2(p.dz + slot0);
+                prefetch_l2(p.hnx + slot0); prefetch_l2(p.hny + slot0); prefetch_l2(p.hnz + slot0);
+                prefetch_l2(p.depth + slot0);
+                if (!MEDIUM) { prefetch_l2(p.rng + slot0); prefetch_l2(p.ht + slot0); }
+#endif
+                const bool hit0 = p.hobj[slot0] != kNoHit;
+                cls = hit0 ? 1u : 2u;
+                if (MEDIUM) {
+                    Rng r0;
+                    r0.state = p.rng[slot0];
+                    const double ds = medium_sample_d(md, r0);
+                    if (ds < (hit0 ? p.ht[slot0] : kBackgroundDist)) cls = 0;
+                    s_dsamp[u] = ds;
+                    s_rng[u] = r0.state;
+                }
+                s_slot[u] = slot0;
+            }
+            s_cls[u] = (uint8_t)cls;
+#pragma unroll
+            for (uint32_t c = 0; c < 3; c++) {
+                const unsigned m = __ballot_sync(0xffffffffu, cls == c);
+                if (lane == 0) s_cnt[c][r * kShadeWarps + warp] = (uint32_t)__popc(m);
+            }
+        }
+        __syncthreads();
+        if (warp < 3) {  // warp c: exclusive scan of class c's counts in (round, warp) order
+            const uint32_t v = s_cnt[warp][lane];
+            uint32_t incl = v;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t up = __shfl_up_sync(0xffffffffu, incl, o);
+                if ((int)lane >= o) incl += up;
+            }
+            s_cnt[warp][lane] = incl - v;
+            if (lane == 31) s_tot[warp] = incl;
+        }
+        __syncthreads();
+        for (uint32_t r = 0; r < rounds; r++) {
+            const uint32_t u = r * kShadeBlock + threadIdx.x;
+            const uint32_t cls = s_cls[u];
+            uint32_t pos = 0;
+#pragma unroll
+            for (uint32_t c = 0; c < 3; c++) {
+                const unsigned m = __ballot_sync(0xffffffffu, cls == c);
+                if (cls == c) pos = s_cnt[c][r * kShadeWarps + warp] + (uint32_t)__popc(m & lt) + (c > 0 ? s_tot[0] : 0u) + (c > 1 ? s_tot[1] : 0u);
+            }
+            if (cls < 3) s_perm[pos] = (uint16_t)u;
+        }
+        __syncthreads();
+    }
+    const uint32_t total = s_tot[0] + s_tot[1] + s_tot[2];
+    for (uint32_t j = threadIdx.x; j < total; j += kShadeBlock) {
+    const uint32_t u = s_perm[j];
+    const uint32_t slot = s_slot[u];
     double dsamp = 0.0;
     Rng rng;
-    {
-        const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-        const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
-        uint32_t cls = 3, slot0 = 0;  // 0 medium collision, 1 surface, 2 miss, 3 no entry
-        if (i < q.counters[0]) {
-            slot0 = q.cur[i];
-#ifndef RPTX_NO_SHADE_PREFETCH
-            // the entry is dealt to another thread of this block below: start its state on the way to L2 now, so
-            // that the loads after the re-deal do not add a third DRAM round trip (queue -> hit object -> state)
-            prefetch_l2(p.ox + slot0); prefetch_l2(p.oy + slot0); prefetch_l2(p.oz + slot0);
-            prefetch_l2(p.dx + slot0); prefetch_l2(p.dy + slot0); prefetch_l2(p.dz + slot0);
-            prefetch_l2(p.hnx + slot0); prefetch_l2(p.hny + slot0); prefetch_l2(p.hnz + slot0);
-            prefetch_l2(p.depth + slot0);
-            if (!MEDIUM) { prefetch_l2(p.rng + slot0); prefetch_l2(p.ht + slot0); }
-#endif
-            const bool hit0 = p.hobj[slot0] != kNoHit;
-            cls = hit0 ? 1u : 2u;
-            if (MEDIUM) {
-                rng.state = p.rng[slot0];
-                dsamp = medium_sample_d(md, rng);
-                if (dsamp < (hit0 ? p.ht[slot0] : kBackgroundDist)) cls = 0;
-            }
-        }
-        uint32_t rank = 0;
-#pragma unroll
-        for (uint32_t c = 0; c < 3; c++) {
-            const unsigned m = __ballot_sync(0xffffffffu, cls == c);
-            if (cls == c) rank = (uint32_t)__popc(m & ((1u << lane) - 1u));
-            if (lane == 0) s_cnt[c][warp] = (uint32_t)__popc(m);
-        }
-        __syncthreads();
-        uint32_t before = 0, total = 0;
-#pragma unroll
-        for (uint32_t c = 0; c < 3; c++)
-            for (uint32_t w = 0; w < kShadeBlock / 32; w++) {
-                const uint32_t n = s_cnt[c][w];
-                total += n;
-                if (c < cls || (c == cls && w < warp)) before += n;
-            }
-        if (cls < 3) {
-            s_slot[before + rank] = slot0;
-            if (MEDIUM) { s_dsamp[before + rank] = dsamp; s_rng[before + rank] = rng.state; }
-        }
-        __syncthreads();
-        if (threadIdx.x >= total) return;
-        slot = s_slot[threadIdx.x];
-        if (MEDIUM) { dsamp = s_dsamp[threadIdx.x]; rng.state = s_rng[threadIdx.x]; }
-    }
+    if (MEDIUM) { dsamp = s_dsamp[u]; rng.state = s_rng[u]; }
     const d3 o = mk3(p.ox[slot], p.oy[slot], p.oz[slot]);
     const d3 d = mk3(p.dx[slot], p.dy[slot], p.dz[slot]);
     const double t = p.ht[slot];
@@ -311,6 +347,7 @@ __global__ void __launch_bounds__(kShadeBlock, RPTX_OCC_SHADE) k_shade(const __g
     }
     p.flags[slot] = flags;
     p.rng[slot] = rng.state;
+    }
 }
 
 // shadow: NEE visibility of the vertex's light samples (nee_visible, trace.cuh).  Passing

@@ -958,6 +958,8 @@ static int run_waves(rptx_film* f, const BatchParams& bp) {
         if (cudaEventElapsedTime(&ms, e[3], e[4]) == cudaSuccess) f->stats.connect_ms += ms;
         return h_count[slot];
     };
+    uint32_t shade_rounds_env = 0;  // experiments: RPTX_SHADE_TILE_ROUNDS=1..kShadeRoundsMax fixes the k_shade tile
+    if (const char* e = std::getenv("RPTX_SHADE_TILE_ROUNDS")) shade_rounds_env = (uint32_t)std::min(std::max(std::atoi(e), 0), kShadeRoundsMax);
     int launched = 0, collected = 0;
     while (bound > 0) {
         const int slot = launched % kWaveRing;
@@ -981,7 +983,15 @@ static int run_waves(rptx_film* f, const BatchParams& bp) {
             cudaEventRecord(e[3], st);
             ctx->launches += 2;
         } else {
-            k_shade<MEDIUM><<<grid_for(bound, kShadeBlock), kShadeBlock, 0, st>>>(sc, p, q, bp, md);
+            // class-sorted tile of `rounds` x kShadeBlock entries per block; a wave too small for ~4 rounds of resident blocks
+            // at that tile size keeps shorter tiles
+            // (measured, 1xB200: lampshade k_shade 368 / 284 / 259 / 235 ms per 256 spp at 1 / 2 / 4 / 8 rounds, 24.7 live lanes
+            // at 8; without a medium nearly every Cornell vertex is a surface hit and longer tiles only cost parallelism:
+            // 2.8 -> 3.1 ms, so that mode keeps one round)
+            const uint32_t rounds = shade_rounds_env ? shade_rounds_env
+                                    : !MEDIUM        ? 1u
+                                                     : (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>(kShadeRoundsMax, bound / ((uint64_t)ctx->sm_count * RPTX_OCC_SHADE * 4 * kShadeBlock)));
+            k_shade<MEDIUM><<<grid_for(bound, kShadeBlock * rounds), kShadeBlock, 0, st>>>(sc, p, q, bp, md, rounds);
             cudaEventRecord(e[2], st);
             if (p.n_shadow) {
                 if (small) {
