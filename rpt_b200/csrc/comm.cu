@@ -35,6 +35,8 @@ struct NcclApi {
     ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
     ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
     ncclResult_t (*Broadcast)(const void*, void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*Send)(const void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*Recv)(void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
     ncclResult_t (*GroupStart)() = nullptr;
     ncclResult_t (*GroupEnd)() = nullptr;
     const char* (*GetErrorString)(ncclResult_t) = nullptr;
@@ -56,6 +58,7 @@ NcclApi* nccl_api() {
     if (!api.field) { api.error = std::string("libnccl lacks ") + name; return &api; }
     SYM(GetUniqueId, "ncclGetUniqueId") SYM(CommInitRank, "ncclCommInitRank") SYM(CommDestroy, "ncclCommDestroy")
     SYM(AllReduce, "ncclAllReduce") SYM(AllGather, "ncclAllGather") SYM(Broadcast, "ncclBroadcast")
+    SYM(Send, "ncclSend") SYM(Recv, "ncclRecv")
     SYM(GroupStart, "ncclGroupStart") SYM(GroupEnd, "ncclGroupEnd") SYM(GetErrorString, "ncclGetErrorString")
 #undef SYM
     return &api;
@@ -79,6 +82,82 @@ struct rptx_comm {
         cudaError_t e_ = (call);                                                         \
         if (e_ != cudaSuccess) return ctx_fail(ctx, std::string(#call) + ": " + cudaGetErrorString(e_)); \
     } while (0)
+
+// ---- collectives for the library's own multi-GPU passes (photon.cu: sharded photon-map build) ----
+// All are enqueued on the context's stream; none synchronises.  Without a communicator (world 1) they are no-ops.
+namespace rptx_host {
+
+int comm_world(const rptx_ctx* ctx) { return ctx->comm ? ctx->comm->world : 1; }
+int comm_rank(const rptx_ctx* ctx) { return ctx->comm ? ctx->comm->rank : 0; }
+
+// op: 0 sum, 1 min, 2 max
+int comm_allreduce_f64(rptx_ctx* ctx, double* d_buf, size_t n, int op) {
+    if (!ctx->comm || n == 0) return 0;
+    const ncclRedOp_t ops[3] = {ncclSum, ncclMin, ncclMax};
+    CKN(nccl_api()->AllReduce(d_buf, d_buf, n, ncclFloat64, ops[op], ctx->comm->comm, ctx->stream));
+    return 0;
+}
+
+int comm_allreduce_u64_sum(rptx_ctx* ctx, unsigned long long* d_buf, size_t n) {
+    if (!ctx->comm || n == 0) return 0;
+    CKN(nccl_api()->AllReduce(d_buf, d_buf, n, ncclUint64, ncclSum, ctx->comm->comm, ctx->stream));
+    return 0;
+}
+
+// every rank contributes `bytes` at d_recv + rank * bytes (in place) and receives the others' blocks
+int comm_allgather_inplace(rptx_ctx* ctx, void* d_recv, size_t bytes) {
+    if (!ctx->comm || bytes == 0) return 0;
+    char* base = static_cast<char*>(d_recv);
+    CKN(nccl_api()->AllGather(base + (size_t)ctx->comm->rank * bytes, base, bytes, ncclUint8, ctx->comm->comm, ctx->stream));
+    return 0;
+}
+
+// ragged all-gather in place: segment r = [off[r], off[r] + cnt[r]) bytes of d_buf is valid on rank r and is broadcast from
+// there; `arrays` buffers with the same row partition (row sizes elem[a]) go out as ONE group
+int comm_allgatherv_inplace(rptx_ctx* ctx, void* const* d_bufs, const size_t* elem, int arrays, const unsigned long long* row_off,
+                            const unsigned long long* row_cnt) {
+    if (!ctx->comm) return 0;
+    NcclApi* a = nccl_api();
+    rptx_comm* c = ctx->comm;
+    CKN(a->GroupStart());
+    for (int k = 0; k < arrays; k++)
+        for (int r = 0; r < c->world; r++) {
+            const size_t bytes = (size_t)row_cnt[r] * elem[k];
+            if (!bytes) continue;
+            char* seg = static_cast<char*>(d_bufs[k]) + (size_t)row_off[r] * elem[k];
+            const ncclResult_t rr = a->Broadcast(seg, seg, bytes, ncclUint8, r, c->comm, ctx->stream);
+            if (rr != ncclSuccess) { a->GroupEnd(); return ctx_fail(ctx, std::string("ncclBroadcast: ") + a->GetErrorString(rr)); }
+        }
+    CKN(a->GroupEnd());
+    return 0;
+}
+
+// personalised exchange: send_cnt[r] bytes from d_send + send_off[r] go to rank r and land at d_recv + recv_off[s] on the
+// receiver, s the sender (grouped ncclSend / ncclRecv; the block a rank keeps is copied on the stream)
+int comm_alltoallv(rptx_ctx* ctx, const void* d_send, const size_t* send_off, const size_t* send_cnt, void* d_recv, const size_t* recv_off,
+                   const size_t* recv_cnt) {
+    const char* src = static_cast<const char*>(d_send);
+    char* dst = static_cast<char*>(d_recv);
+    if (!ctx->comm) {
+        if (send_cnt[0]) CK(cudaMemcpyAsync(dst + recv_off[0], src + send_off[0], send_cnt[0], cudaMemcpyDeviceToDevice, ctx->stream));
+        return 0;
+    }
+    NcclApi* a = nccl_api();
+    rptx_comm* c = ctx->comm;
+    if (send_cnt[c->rank]) CK(cudaMemcpyAsync(dst + recv_off[c->rank], src + send_off[c->rank], send_cnt[c->rank], cudaMemcpyDeviceToDevice, ctx->stream));
+    CKN(a->GroupStart());
+    for (int r = 0; r < c->world; r++) {
+        if (r == c->rank) continue;
+        ncclResult_t rr = ncclSuccess;
+        if (send_cnt[r]) rr = a->Send(src + send_off[r], send_cnt[r], ncclUint8, r, c->comm, ctx->stream);
+        if (rr == ncclSuccess && recv_cnt[r]) rr = a->Recv(dst + recv_off[r], recv_cnt[r], ncclUint8, r, c->comm, ctx->stream);
+        if (rr != ncclSuccess) { a->GroupEnd(); return ctx_fail(ctx, std::string("ncclSend/Recv: ") + a->GetErrorString(rr)); }
+    }
+    CKN(a->GroupEnd());
+    return 0;
+}
+
+}  // namespace rptx_host
 
 extern "C" {
 

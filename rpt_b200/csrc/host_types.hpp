@@ -136,4 +136,14 @@ rptx::SceneDev scene_dev(const rptx_scene* s);
 rptx::MediumDev medium_dev(const rptx_scene* s);
 // persist.cu
 int persist_grid(int sm_count, bool medium, bool probe, bool small);
+// comm.cu: collectives of the library's own multi-GPU passes, on the context's stream (no-ops / local copies without a communicator)
+int comm_world(const rptx_ctx* ctx);
+int comm_rank(const rptx_ctx* ctx);
+int comm_allreduce_f64(rptx_ctx* ctx, double* d_buf, size_t n, int op /* 0 sum, 1 min, 2 max */);
+int comm_allreduce_u64_sum(rptx_ctx* ctx, unsigned long long* d_buf, size_t n);
+int comm_allgather_inplace(rptx_ctx* ctx, void* d_recv, size_t bytes_per_rank);
+int comm_allgatherv_inplace(rptx_ctx* ctx, void* const* d_bufs, const size_t* elem, int arrays, const unsigned long long* row_off,
+                            const unsigned long long* row_cnt);
+int comm_alltoallv(rptx_ctx* ctx, const void* d_send, const size_t* send_off, const size_t* send_cnt, void* d_recv, const size_t* recv_off,
+                   const size_t* recv_cnt);
 }  // namespace rptx_host

@@ -275,6 +275,68 @@ __global__ void __launch_bounds__(128) k_knn_batch(const __grid_constant__ Point
     counts[i] = heap.size;
 }
 
+// ---- sharded build (one process per GPU; comm.cu) ----
+
+// out[i] = rows[idx[i]]: this rank's rows in (Morton, canonical) order, ready to be cut into per-destination runs
+__global__ void k_rows_permute(const PhotonRec* __restrict__ rows, const uint32_t* __restrict__ idx, uint32_t n, PhotonRec* __restrict__ out) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    out[i] = rows[idx[i]];
+}
+
+// lb[b] = number of (sorted) keys below b << shift, b = 0..bins (lb[bins] = n): summed over the ranks this is the global
+// rank of every bin boundary, from which all ranks pick the same splitters
+__global__ void k_bin_lower_bounds(const uint64_t* __restrict__ keys, uint32_t n, int shift, uint32_t bins, unsigned long long* __restrict__ lb) {
+    const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b > bins) return;
+    if (b == bins) { lb[b] = n; return; }
+    const uint64_t bound = (uint64_t)b << shift;
+    uint32_t lo = 0, hi = n;
+    while (lo < hi) {
+        const uint32_t mid = lo + ((hi - lo) >> 1);
+        if (keys[mid] < bound) lo = mid + 1; else hi = mid;
+    }
+    lb[b] = lo;
+}
+
+// cut[r] = this rank's first row that goes to rank r (cut[world] = n_local): rank r owns the bins [s_r, s_r+1), s_r the
+// first bin whose global lower bound reaches r/world of all rows
+__global__ void k_pick_splitters(const unsigned long long* __restrict__ lb_global, const unsigned long long* __restrict__ lb_local, uint32_t bins,
+                                 int world, unsigned long long* __restrict__ cut) {
+    const int r = threadIdx.x;
+    if (r > world) return;
+    if (r == 0) { cut[0] = 0; return; }
+    if (r == world) { cut[r] = lb_local[bins]; return; }
+    const unsigned long long total = lb_global[bins];
+    const unsigned long long target = total * (unsigned long long)r / (unsigned long long)world;  // total < 2^32
+    uint32_t lo = 0, hi = bins;
+    while (lo < hi) {
+        const uint32_t mid = lo + ((hi - lo) >> 1);
+        if (lb_global[mid] < target) lo = mid + 1; else hi = mid;
+    }
+    cut[r] = lb_local[lo];
+}
+
+// k_sphere_radius over the photons [first, first + count) of the (complete) volume map: one rank's share of the radius pass
+__global__ void __launch_bounds__(128) k_sphere_radius_range(const __grid_constant__ PointMapDev vm, uint32_t first, uint32_t count,
+                                                             double* __restrict__ radius, Aabb32* __restrict__ boxes) {
+    const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= count) return;
+    const uint32_t i = first + j;
+    const d3 p = mk3(vm.px[i], vm.py[i], vm.pz[i]);
+    KnnHeap<16> heap;
+    heap.k = kSphereKnn;
+    knn_query(vm, p, heap);
+    double m = -1.0;
+    for (uint32_t q = 0; q < heap.size; q++) m = fmax(m, heap.d2[q]);
+    const double r = sqrt(m);
+    radius[i] = r;
+    Aabb32 b;
+    b.mn[0] = (float)(p.x - r); b.mn[1] = (float)(p.y - r); b.mn[2] = (float)(p.z - r);
+    b.mx[0] = (float)(p.x + r); b.mx[1] = (float)(p.y + r); b.mx[2] = (float)(p.z + r);
+    boxes[i] = b;
+}
+
 // ---- host helpers ----
 
 int reduce_bounds(rptx_ctx* ctx, const double* d_blocks, int blocks, double mn[3], double mx[3]) {
@@ -380,6 +442,168 @@ int build_point_map(rptx_ctx* ctx, const PhotonRec* rows, const uint32_t* d_cano
     rc = body();
     rptx_free_async(k0, ctx->stream); rptx_free_async(k1, ctx->stream); rptx_free_async(i1, ctx->stream); rptx_free_async(boxes, ctx->stream);
     return rc;
+}
+
+// The same map from lists that are spread over the ranks of the context's communicator (row f1 of SURVEY.md §8: the
+// reference builds its kd-trees serially, src/photon.rs:193-199; here the N ranks split the work):
+//   1. global bounds (all-reduce min / max) -> every rank computes the Morton keys the one-rank build would;
+//   2. each rank sorts ITS rows by (Morton, canonical key) and counts them per Morton bin (2^20 bins = the key's top 20 bits);
+//      the summed counts give every rank the same N - 1 splitters: rank r owns the r-th N-th of the key space by population;
+//   3. personalised exchange (ncclSend / ncclRecv): a rank's sorted rows are already contiguous per destination;
+//   4. rank r sorts what it received (1 / N of the rows) and writes its segment of the FINAL Morton-ordered SoA arrays;
+//   5. ragged all-gather in place of the SoA segments and their Morton keys (88 B per photon instead of the 104-B rows);
+//   6. the implicit box tree (Karras hierarchy + refit) over the complete sorted keys, on every rank.
+// Sort, gather and key work are 1 / N per rank; step 6 is replicated.  The result is bit-identical to build_point_map over the
+// concatenated lists: same keys, same (Morton, canonical) order, same tree.
+constexpr int kShardBinBits = 20;
+
+int build_point_map_sharded(rptx_ctx* ctx, const PhotonRec* rows, uint32_t n_local, PointMapHost* out) {
+    using namespace rptx_host;
+    cudaStream_t st = ctx->stream;
+    const int world = comm_world(ctx), rank = comm_rank(ctx);
+    out->dev = PointMapDev{};
+    std::vector<void*> tmp;
+    auto done = [&](int rc) { free_owned(ctx, tmp); return rc; };
+#define CKT(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return done(ctx_fail(ctx, std::string(#call) + ": " + cudaGetErrorString(e_))); } while (0)
+#define RCT(call) do { if (int r_ = (call)) return done(r_); } while (0)
+    PhaseTrace trace(ctx);
+    // ---- 1. bounds ----
+    double mn[3] = {INFINITY, INFINITY, INFINITY}, mx[3] = {-INFINITY, -INFINITY, -INFINITY};
+    if (n_local) {
+        const int blocks = std::min(grid_for(n_local, 256), 1184);
+        double* d_b = nullptr;
+        CKT(dev_alloc(ctx, &d_b, (size_t)blocks * 6, &tmp));
+        k_rows_bounds<<<blocks, 256, 0, st>>>(rows, n_local, d_b);
+        ctx->launches++;
+        RCT(reduce_bounds(ctx, d_b, blocks, mn, mx));
+    }
+    double* d_mm = nullptr;
+    CKT(dev_alloc(ctx, &d_mm, 6, &tmp));
+    {
+        const double h[6] = {mn[0], mn[1], mn[2], mx[0], mx[1], mx[2]};
+        CKT(cudaMemcpyAsync(d_mm, h, sizeof(h), cudaMemcpyHostToDevice, st));
+        CKT(cudaStreamSynchronize(st));  // h goes out of scope
+        RCT(comm_allreduce_f64(ctx, d_mm, 3, 1));
+        RCT(comm_allreduce_f64(ctx, d_mm + 3, 3, 2));
+        double g[6];
+        CKT(cudaMemcpyAsync(g, d_mm, sizeof(g), cudaMemcpyDeviceToHost, st));
+        CKT(cudaStreamSynchronize(st));
+        for (int k = 0; k < 3; k++) { mn[k] = g[k]; mx[k] = g[3 + k]; }
+    }
+    const double3 dmn = make_double3(mn[0], mn[1], mn[2]);
+    const double3 inv = make_double3(mx[0] > mn[0] ? 1.0 / (mx[0] - mn[0]) : 0.0, mx[1] > mn[1] ? 1.0 / (mx[1] - mn[1]) : 0.0,
+                                     mx[2] > mn[2] ? 1.0 / (mx[2] - mn[2]) : 0.0);
+    // ---- 2. local (Morton, canonical) order and the splitters ----
+    uint32_t *canon = nullptr, *i1 = nullptr;
+    uint64_t *k0 = nullptr, *k1 = nullptr;
+    RCT(canonical_order(ctx, rows, n_local, &canon));
+    tmp.push_back(canon);
+    CKT(dev_alloc(ctx, &k0, n_local, &tmp)); CKT(dev_alloc(ctx, &k1, n_local, &tmp)); CKT(dev_alloc(ctx, &i1, n_local, &tmp));
+    if (n_local) {
+        k_rows_morton<<<grid_for(n_local, 256), 256, 0, st>>>(rows, canon, n_local, dmn, inv, k0);
+        ctx->launches++;
+        RCT(sort_pairs(ctx, k0, k1, canon, i1, n_local, 63));
+    }
+    const uint32_t bins = 1u << kShardBinBits;
+    unsigned long long *lb_local = nullptr, *lb_global = nullptr, *d_cut = nullptr, *d_mat = nullptr;
+    CKT(dev_alloc(ctx, &lb_local, (size_t)bins + 1, &tmp)); CKT(dev_alloc(ctx, &lb_global, (size_t)bins + 1, &tmp));
+    CKT(dev_alloc(ctx, &d_cut, (size_t)world + 1, &tmp)); CKT(dev_alloc(ctx, &d_mat, (size_t)world * world, &tmp));
+    k_bin_lower_bounds<<<grid_for((size_t)bins + 1, 256), 256, 0, st>>>(k1, n_local, 63 - kShardBinBits, bins, lb_local);
+    CKT(cudaMemcpyAsync(lb_global, lb_local, sizeof(unsigned long long) * ((size_t)bins + 1), cudaMemcpyDeviceToDevice, st));
+    RCT(comm_allreduce_u64_sum(ctx, lb_global, (size_t)bins + 1));
+    k_pick_splitters<<<1, 64, 0, st>>>(lb_global, lb_local, bins, world, d_cut);
+    ctx->launches += 2;
+    if (world > 63) return done(ctx_fail(ctx, "sharded photon-map build supports at most 63 ranks"));
+    std::vector<unsigned long long> cut((size_t)world + 1), mat((size_t)world * world);
+    CKT(cudaMemcpyAsync(cut.data(), d_cut, sizeof(unsigned long long) * cut.size(), cudaMemcpyDeviceToHost, st));
+    CKT(cudaStreamSynchronize(st));
+    {   // counts matrix: mat[s][r] = rows rank s sends to rank r
+        std::vector<unsigned long long> mine((size_t)world);
+        for (int r = 0; r < world; r++) mine[r] = cut[r + 1] - cut[r];
+        CKT(cudaMemcpyAsync(d_mat + (size_t)rank * world, mine.data(), sizeof(unsigned long long) * world, cudaMemcpyHostToDevice, st));
+        CKT(cudaStreamSynchronize(st));
+        RCT(comm_allgather_inplace(ctx, d_mat, sizeof(unsigned long long) * world));
+        CKT(cudaMemcpyAsync(mat.data(), d_mat, sizeof(unsigned long long) * mat.size(), cudaMemcpyDeviceToHost, st));
+        CKT(cudaStreamSynchronize(st));
+    }
+    std::vector<unsigned long long> seg_cnt((size_t)world, 0), seg_off((size_t)world, 0);
+    unsigned long long n_total = 0;
+    for (int r = 0; r < world; r++) {
+        for (int sr = 0; sr < world; sr++) seg_cnt[r] += mat[(size_t)sr * world + r];
+        seg_off[r] = n_total;
+        n_total += seg_cnt[r];
+    }
+    if (n_total >= (1ull << 28)) return done(ctx_fail(ctx, "photon map exceeds 2^28 records per list"));
+    trace.mark("  shard: local sort + splitters");
+    // ---- 3. exchange ----
+    const uint32_t m = (uint32_t)seg_cnt[rank];
+    PhotonRec *srows = nullptr, *rrows = nullptr;
+    CKT(dev_alloc(ctx, &srows, n_local, &tmp)); CKT(dev_alloc(ctx, &rrows, m, &tmp));
+    if (n_local) {
+        k_rows_permute<<<grid_for(n_local, 256), 256, 0, st>>>(rows, i1, n_local, srows);
+        ctx->launches++;
+    }
+    {
+        std::vector<size_t> so((size_t)world), sc((size_t)world), ro((size_t)world), rc((size_t)world);
+        size_t acc = 0;
+        for (int r = 0; r < world; r++) {
+            so[r] = (size_t)cut[r] * sizeof(PhotonRec);
+            sc[r] = (size_t)(cut[r + 1] - cut[r]) * sizeof(PhotonRec);
+            ro[r] = acc;
+            rc[r] = (size_t)mat[(size_t)r * world + rank] * sizeof(PhotonRec);
+            acc += rc[r];
+        }
+        RCT(comm_alltoallv(ctx, srows, so.data(), sc.data(), rrows, ro.data(), rc.data()));
+        CKT(cudaStreamSynchronize(st));  // the offset vectors go out of scope
+    }
+    trace.mark("  shard: exchange");
+    // ---- 4. this rank's segment of the final arrays ----
+    const uint32_t n = (uint32_t)n_total;
+    out->dev.n = n;
+    double *px = nullptr, *py = nullptr, *pz = nullptr, *dir = nullptr, *power = nullptr;
+    uint64_t *key = nullptr, *mkey = nullptr;
+    BvhNode* nodes = nullptr;
+    CKT(dev_alloc(ctx, &px, n, &out->owned)); CKT(dev_alloc(ctx, &py, n, &out->owned)); CKT(dev_alloc(ctx, &pz, n, &out->owned));
+    CKT(dev_alloc(ctx, &dir, 3 * (size_t)n, &out->owned)); CKT(dev_alloc(ctx, &power, 3 * (size_t)n, &out->owned));
+    CKT(dev_alloc(ctx, &key, n, &out->owned));
+    CKT(dev_alloc(ctx, &nodes, std::max<uint32_t>(n, 1), &out->owned));
+    CKT(dev_alloc(ctx, &mkey, n, &tmp));
+    out->dev.nodes = nodes;
+    out->dev.px = px; out->dev.py = py; out->dev.pz = pz; out->dev.dir = dir; out->dev.power = power; out->dev.key = key;
+    if (n == 0) return done(0);
+    if (m) {
+        uint32_t *canon2 = nullptr, *i2 = nullptr;
+        uint64_t* q0 = nullptr;
+        RCT(canonical_order(ctx, rrows, m, &canon2));
+        tmp.push_back(canon2);
+        CKT(dev_alloc(ctx, &q0, m, &tmp)); CKT(dev_alloc(ctx, &i2, m, &tmp));
+        const size_t off = (size_t)seg_off[rank];
+        k_rows_morton<<<grid_for(m, 256), 256, 0, st>>>(rrows, canon2, m, dmn, inv, q0);
+        ctx->launches++;
+        RCT(sort_pairs(ctx, q0, mkey + off, canon2, i2, m, 63));
+        k_rows_gather<<<grid_for(m, 256), 256, 0, st>>>(rrows, i2, m, px + off, py + off, pz + off, dir + 3 * off, power + 3 * off, key + off);
+        ctx->launches++;
+    }
+    trace.mark("  shard: segment sort + SoA");
+    // ---- 5. everybody gets every segment ----
+    {
+        void* bufs[7] = {px, py, pz, dir, power, key, mkey};
+        const size_t elem[7] = {8, 8, 8, 24, 24, 8, 8};
+        RCT(comm_allgatherv_inplace(ctx, bufs, elem, 7, seg_off.data(), seg_cnt.data()));
+        CKT(cudaStreamSynchronize(st));
+    }
+    trace.mark("  shard: all-gather segments");
+    // ---- 6. the tree ----
+    PrimBox* boxes = nullptr;
+    CKT(dev_alloc(ctx, &boxes, n, &tmp));
+    k_point_boxes<<<grid_for(n, 256), 256, 0, st>>>(px, py, pz, n, boxes);
+    ctx->launches++;
+    const int e = build_lbvh_sorted(mkey, boxes, n, 0.0f, kPointLeaf, nodes, &out->dev.root_ref, st, &ctx->launches);
+    if (e != 0) return done(ctx_fail(ctx, std::string("point map LBVH: ") + cudaGetErrorString((cudaError_t)e)));
+    trace.mark("  shard: boxes + LBVH");
+#undef CKT
+#undef RCT
+    return done(0);
 }
 
 // BVH::build over item boxes (bvh 0.6.0): LBVH with exact f32 unions.  perm[k] = item in leaf slot k.

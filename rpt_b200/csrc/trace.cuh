@@ -69,7 +69,14 @@ RPTX_D void clip_f64(const double* bmin, const double* bmax, d3 o, d3 d, double*
     *t1 = fmin(fmin(fmax(ax, bx), fmax(ay, by)), fmax(az, bz));
 }
 
-RPTX_D bool accept(const Hit& h, double t, uint32_t obj) { return t < h.t || (t == h.t && obj < h.obj); }
+// Ties on t: the reference walks its objects in index order and every shape but one replaces the record only for a
+// strictly smaller t, so the lowest index keeps a tie.  MonomialSurface::intersect rejects only r > record.time
+// (src/shape/monomial_surface.rs:84): a monomial surface TAKES a tie from whoever holds it and, once it holds the
+// record, keeps it against every later object (two monomials: the later index wins).  A monomial holder is marked by
+// Hit::prim == kMonoPrim.
+constexpr uint32_t kMonoPrim = 0x80000000u;
+RPTX_D bool accept(const Hit& h, double t, uint32_t obj) { return t < h.t || (t == h.t && obj < h.obj && h.prim != kMonoPrim); }
+RPTX_D bool accept_mono(const Hit& h, double t, uint32_t obj) { return t < h.t || (t == h.t && (h.prim != kMonoPrim || obj > h.obj)); }
 
 // Triangle::intersect, src/shape/mesh.rs:50-83, on the prepared record
 RPTX_D bool tri_test(const TriRec& tr, d3 o, d3 d, double t_min, double t_max, bool allow_eq, double* t, double* vv, double* ww) {
@@ -332,7 +339,7 @@ RPTX_D void closest_hit(const SceneDev& sc, const RayD& ray, double t_min, doubl
             TriRec tr;
             load_tri(tris + i, &tr);
             double t, v, w;
-            if (tri_test(tr, lo, ld, t_min, hit.t, cur_obj < hit.obj, &t, &v, &w) && (!WINDOW || t >= t_stop)) {
+            if (tri_test(tr, lo, ld, t_min, hit.t, cur_obj < hit.obj && hit.prim != kMonoPrim, &t, &v, &w) && (!WINDOW || t >= t_stop)) {
                 hit.t = t; hit.inst = cur_inst; hit.obj = cur_obj; hit.prim = i; hit.v = v; hit.w = w;
                 improved = true;
                 if (SHADOW && t < t_stop) return true;
@@ -442,8 +449,8 @@ RPTX_D void closest_hit(const SceneDev& sc, const RayD& ray, double t_min, doubl
                     if (kind == kSphere) ok = sphere_test(lo, ld, t_min, &t);
                     else if (kind == kCube) ok = cube_test(lo, ld, t_min, &t, &ccode);
                     else ok = monomial_test(in->plane_v, lo, ld, t_min, hit.t, &t);
-                    if (ok && (!WINDOW || t >= t_stop) && accept(hit, t, cur_obj)) {
-                        hit.t = t; hit.inst = idx; hit.obj = cur_obj; hit.prim = ccode;
+                    if (ok && (!WINDOW || t >= t_stop) && (kind == kMonomial ? accept_mono(hit, t, cur_obj) : accept(hit, t, cur_obj))) {
+                        hit.t = t; hit.inst = idx; hit.obj = cur_obj; hit.prim = kind == kMonomial ? kMonoPrim : ccode;
                         if (SHADOW && t < t_stop) return;
                         tbest = f32_up(hit.t - shift);
                         tbest = tbest + fabsf(tbest) * kSlabSlack;

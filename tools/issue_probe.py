@@ -69,8 +69,9 @@ def main():
                vertices=total_vertices, waves=n_waves,
                capture=f"ncu --metrics {metrics} -k regex:{kernel} of `bench.py --workload {name} {' '.join(extra)}` (tools/issue_probe.py)")
     data = {}
-    if os.path.exists(OUT):
-        data = json.load(open(OUT))
+    seed = OUT if os.path.exists(OUT) else os.path.join(ROOT, "profiles", "r2_issue.json")  # a fresh box starts from the committed file
+    if os.path.exists(seed):
+        data = json.load(open(seed))
     data[key] = rec
     json.dump(data, open(OUT, "w"), indent=1)
     print(key, json.dumps(rec))
