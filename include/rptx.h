@@ -110,8 +110,8 @@ typedef struct rptx_params {
     uint32_t max_bounces;
     uint32_t num_samples;
     uint32_t _pad;
-    uint64_t gather_size;
-    uint64_t gather_size_volume;
+    uint64_t gather_size;         /* k of the surface estimate; limits of this library: 1..1024 (the per-sample heap is a */
+    uint64_t gather_size_volume;  /* compile-time local array: 32 / 128 / 1024 variants); above 1024 the gather returns an error */
     double   watts;
     double   stepsize;            /* stored, never read (src/renderer.rs:42-43) */
     uint64_t seed;                /* the reference seeds from OS entropy; here runs are reproducible */
@@ -252,6 +252,15 @@ int  rptx_photons_stats(const rptx_photons* photons, uint64_t* emitted, uint64_t
  * new_beam_map_for_beam_estimate (:193-305).  The list may be destroyed afterwards. */
 int  rptx_photon_map_build(rptx_ctx* ctx, rptx_scene* scene, rptx_photons* photons, int32_t kind,
                            rptx_photon_map** out);
+/* The same map from lists that are spread over the ranks of the context's communicator (rptx_comm_init):
+ * `local_photons` is THIS rank's part (e.g. its rptx_photons_emit range).  The ranks split the build of the
+ * two kd-trees (:193-199) by Morton range - global splitters, one personalised row exchange, each rank sorts
+ * and lays out 1/N of the photons, the finished segments are all-gathered - and the 10-NN radius pass
+ * (:212-236) by photon index.  Every rank returns the complete map, identical to rptx_photon_map_build over
+ * the merged lists (rptx_photons_allgather).  Collective: every rank of the communicator must call it.
+ * Without a communicator it is rptx_photon_map_build. */
+int  rptx_photon_map_build_sharded(rptx_ctx* ctx, rptx_scene* scene, rptx_photons* local_photons,
+                                   int32_t kind, rptx_photon_map** out);
 void rptx_photon_map_destroy(rptx_photon_map* map);
 /* counts: surface photons, volume photons in the point map, spheres/beams in the BVH */
 int  rptx_photon_map_stats(const rptx_photon_map* map, uint64_t counts[3], double* build_ms);

@@ -161,6 +161,7 @@ PROTOTYPES = {
     "rptx_photons_download": (C.c_int, [P, C.c_int32, P]),
     "rptx_photons_stats": (C.c_int, [P, U64P, U64P, DP]),
     "rptx_photon_map_build": (C.c_int, [P, P, P, C.c_int32, C.POINTER(P)]),
+    "rptx_photon_map_build_sharded": (C.c_int, [P, P, P, C.c_int32, C.POINTER(P)]),
     "rptx_photon_map_destroy": (None, [P]),
     "rptx_photon_map_stats": (C.c_int, [P, U64P, DP]),
     "rptx_photon_gather_begin": (C.c_int, [P, P, C.POINTER(CameraDesc), C.POINTER(Params), C.POINTER(P)]),

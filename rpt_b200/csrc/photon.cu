@@ -636,6 +636,42 @@ int build_box_bvh(rptx_ctx* ctx, const Aabb32* d_boxes, uint32_t n, BoxBvhHost* 
     return 0;
 }
 
+// every rank's rows of one list, concatenated in rank order (PhotonList::merge across ranks for ONE list)
+int allgather_rows(rptx_ctx* ctx, const PhotonRec* rows, uint32_t n_local, PhotonRec** d_full, uint64_t* n_full) {
+    using namespace rptx_host;
+    cudaStream_t st = ctx->stream;
+    const int world = comm_world(ctx), rank = comm_rank(ctx);
+    *d_full = nullptr;
+    unsigned long long* d_cnt = nullptr;
+    CK(dev_alloc(ctx, &d_cnt, (size_t)world, nullptr));
+    const unsigned long long mine = n_local;
+    std::vector<unsigned long long> cnt((size_t)world), off((size_t)world);
+    cudaError_t e = cudaMemcpyAsync(d_cnt + rank, &mine, sizeof(mine), cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    int rc = e == cudaSuccess ? comm_allgather_inplace(ctx, d_cnt, sizeof(unsigned long long)) : ctx_fail(ctx, cudaGetErrorString(e));
+    if (rc == 0) {
+        e = cudaMemcpyAsync(cnt.data(), d_cnt, sizeof(unsigned long long) * world, cudaMemcpyDeviceToHost, st);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+        if (e != cudaSuccess) rc = ctx_fail(ctx, cudaGetErrorString(e));
+    }
+    rptx_free_async(d_cnt, st);
+    if (rc) return rc;
+    unsigned long long total = 0;
+    for (int r = 0; r < world; r++) { off[r] = total; total += cnt[r]; }
+    if (total >= (1ull << 32)) return ctx_fail(ctx, "photon list exceeds 2^32 records");
+    PhotonRec* full = nullptr;
+    CK(dev_alloc(ctx, &full, (size_t)total, nullptr));
+    if (n_local) CK(cudaMemcpyAsync(full + off[rank], rows, (size_t)n_local * sizeof(PhotonRec), cudaMemcpyDeviceToDevice, st));
+    void* bufs[1] = {full};
+    const size_t elem[1] = {sizeof(PhotonRec)};
+    rc = comm_allgatherv_inplace(ctx, bufs, elem, 1, off.data(), cnt.data());
+    if (rc == 0 && cudaStreamSynchronize(st) != cudaSuccess) rc = ctx_fail(ctx, "all-gather of photon rows failed");
+    if (rc) { rptx_free_async(full, st); return rc; }
+    *d_full = full;
+    *n_full = total;
+    return 0;
+}
+
 int find_photon_light(const rptx_scene* s, uint32_t* index) {
     for (size_t i = 0; i < s->lights.size(); i++)
         if (s->lights[i].kind == RPTX_LIGHT_OBJECT) { *index = (uint32_t)i; return 0; }
@@ -861,10 +897,14 @@ void rptx_photon_map_destroy(rptx_photon_map* m) {
     delete m;
 }
 
-int rptx_photon_map_build(rptx_ctx* ctx, rptx_scene* scene, rptx_photons* photons, int32_t kind, rptx_photon_map** out) {
+// sharded: `photons` is this rank's part of lists spread over the context's communicator; every rank ends up with the same,
+// complete map (build_point_map_sharded), the one rptx_photon_map_build makes of the merged lists
+static int photon_map_build_impl(rptx_ctx* ctx, rptx_scene* scene, rptx_photons* photons, int32_t kind, bool sharded, rptx_photon_map** out) {
     if (!ctx || !out) return 1;
     *out = nullptr;
     if (!scene || !photons) return ctx_fail(ctx, "rptx_photon_map_build: null argument");
+    // (RPTX_FORCE_SHARDED_BUILD: tests run the sharded code on one rank, where the exchanges are local copies)
+    if (sharded && rptx_host::comm_world(ctx) == 1 && !std::getenv("RPTX_FORCE_SHARDED_BUILD")) sharded = false;
     if (photons->ctx != ctx || scene->ctx != ctx) return ctx_fail(ctx, "objects belong to another context");
     if (kind < RPTX_PHOTON_MAP || kind > RPTX_PHOTON_BEAM_BEAM) return ctx_fail(ctx, "unknown photon render kind");
     CK(cudaSetDevice(ctx->device));
@@ -876,9 +916,29 @@ int rptx_photon_map_build(rptx_ctx* ctx, rptx_scene* scene, rptx_photons* photon
     m->ctx = ctx; m->scene = scene; m->kind = kind;
     int rc = 0;
     uint32_t *canon_s = nullptr, *canon_v = nullptr, *perm = nullptr;
-    const uint32_t ns = (uint32_t)photons->n[0], nv = (uint32_t)photons->n[1];
+    const uint32_t ns = (uint32_t)photons->n[0];
+    uint32_t nv = (uint32_t)photons->n[1];
+    const PhotonRec* vrows = photons->d_rows[1];
+    PhotonRec* vrows_full = nullptr;  // sharded beam-beam: the merged volume rows
     PhaseTrace trace(ctx);
     auto body = [&]() -> int {
+        if (sharded) {
+            if (int r = build_point_map_sharded(ctx, photons->d_rows[0], ns, &m->surface)) return r;
+            trace.mark("build: point map surface (sharded)");
+            if (kind == RPTX_PHOTON_MAP || kind == RPTX_PHOTON_POINT_BEAM) {
+                if (int r = build_point_map_sharded(ctx, photons->d_rows[1], nv, &m->volume)) return r;
+                nv = m->volume.dev.n;
+                trace.mark("build: point map volume (sharded)");
+            } else {
+                // the beams are made of the rows themselves, in canonical order: every rank needs every volume row
+                uint64_t total = 0;
+                if (int r = allgather_rows(ctx, photons->d_rows[1], nv, &vrows_full, &total)) return r;
+                vrows = vrows_full;
+                nv = (uint32_t)total;
+                if (int r = canonical_order(ctx, vrows, nv, &canon_v)) return r;
+                trace.mark("build: volume rows all-gather + canonical");
+            }
+        } else {
         if (int r = canonical_order(ctx, photons->d_rows[0], ns, &canon_s)) return r;
         trace.mark("build: canonical surface");
         if (int r = build_point_map(ctx, photons->d_rows[0], canon_s, ns, &m->surface)) return r;
@@ -889,12 +949,31 @@ int rptx_photon_map_build(rptx_ctx* ctx, rptx_scene* scene, rptx_photons* photon
             if (int r = build_point_map(ctx, photons->d_rows[1], canon_v, nv, &m->volume)) return r;
             trace.mark("build: point map volume");
         }
+        }
         if (kind == RPTX_PHOTON_POINT_BEAM) {
             double *radius = nullptr, *center = nullptr, *rad = nullptr, *dir = nullptr, *power = nullptr;
             Aabb32 *boxes = nullptr, *obox = nullptr;
             CK(dev_alloc(ctx, &radius, nv, &m->owned));
             CK(dev_alloc(ctx, &boxes, nv, &m->owned));
-            if (nv) {
+            if (nv && sharded) {
+                // the 10-NN radius pass (src/photon.rs:212-236) split by photon index, then all-gathered
+                const int world = rptx_host::comm_world(ctx);
+                std::vector<unsigned long long> off((size_t)world), cnt((size_t)world);
+                for (int r = 0; r < world; r++) {
+                    off[r] = (unsigned long long)nv * r / world;
+                    cnt[r] = (unsigned long long)nv * (r + 1) / world - off[r];
+                }
+                const int me = rptx_host::comm_rank(ctx);
+                if (cnt[me]) {
+                    k_sphere_radius_range<<<grid_for(cnt[me], 128), 128, 0, st>>>(m->volume.dev, (uint32_t)off[me], (uint32_t)cnt[me], radius, boxes);
+                    ctx->launches++;
+                }
+                void* bufs[2] = {radius, boxes};
+                const size_t elem[2] = {sizeof(double), sizeof(Aabb32)};
+                if (int r = rptx_host::comm_allgatherv_inplace(ctx, bufs, elem, 2, off.data(), cnt.data())) return r;
+                CK(cudaStreamSynchronize(st));
+                trace.mark("build: sphere radii (sharded)");
+            } else if (nv) {
                 k_sphere_radius<<<grid_for(nv, 128), 128, 0, st>>>(m->volume.dev, radius, boxes);
                 ctx->launches++;
             }
@@ -917,7 +996,7 @@ int rptx_photon_map_build(rptx_ctx* ctx, rptx_scene* scene, rptx_photons* photon
             CK(dev_alloc(ctx, &len, nv, &m->owned)); CK(dev_alloc(ctx, &power, 3 * (size_t)nv, &m->owned));
             CK(dev_alloc(ctx, &boxes, nv, &m->owned));
             if (nv) {
-                k_beam_make<<<grid_for(nv, 256), 256, 0, st>>>(photons->d_rows[1], canon_v, nv, start, dirn, len, power, boxes);
+                k_beam_make<<<grid_for(nv, 256), 256, 0, st>>>(vrows, canon_v, nv, start, dirn, len, power, boxes);
                 ctx->launches++;
             }
             if (int r = build_box_bvh(ctx, boxes, nv, &m->bvh, &perm)) return r;
@@ -939,6 +1018,7 @@ int rptx_photon_map_build(rptx_ctx* ctx, rptx_scene* scene, rptx_photons* photon
     };
     rc = body();
     rptx_free_async(canon_s, ctx->stream); rptx_free_async(canon_v, ctx->stream); rptx_free_async(perm, ctx->stream);
+    rptx_free_async(vrows_full, ctx->stream);
     if (rc == 0) {
         cudaEventRecord(e1, st);
         cudaEventSynchronize(e1);
@@ -950,6 +1030,14 @@ int rptx_photon_map_build(rptx_ctx* ctx, rptx_scene* scene, rptx_photons* photon
     if (rc) { rptx_photon_map_destroy(m); return rc; }
     *out = m;
     return 0;
+}
+
+int rptx_photon_map_build(rptx_ctx* ctx, rptx_scene* scene, rptx_photons* photons, int32_t kind, rptx_photon_map** out) {
+    return photon_map_build_impl(ctx, scene, photons, kind, false, out);
+}
+
+int rptx_photon_map_build_sharded(rptx_ctx* ctx, rptx_scene* scene, rptx_photons* local_photons, int32_t kind, rptx_photon_map** out) {
+    return photon_map_build_impl(ctx, scene, local_photons, kind, true, out);
 }
 
 int rptx_photon_map_stats(const rptx_photon_map* m, uint64_t counts[3], double* build_ms) {
@@ -1069,13 +1157,15 @@ int rptx_photon_render(rptx_ctx* ctx, rptx_scene* scene, const rptx_camera* came
     else if (prm.shard_count > 1) return ctx_fail(ctx, "sharded photon_render needs a communicator (rptx_comm_init), or the three passes with the caller's own exchange");
     const uint64_t lo = photon_count * (uint64_t)rank / (uint64_t)world, hi = photon_count * (uint64_t)(rank + 1) / (uint64_t)world;
     int rc = rptx_photons_emit(ctx, scene, &prm, photon_count, lo, hi - lo, kind, &ph);
-    if (rc == 0 && world > 1) {
+    if (rc == 0 && world > 1 && std::getenv("RPTX_REPLICATED_MAP_BUILD")) {  // round-1 scheme, kept for comparison runs
         rptx_photons* full = nullptr;
         rc = rptx_photons_allgather(ph, &full);
         rptx_photons_destroy(ph);
         ph = full;
+        if (rc == 0) rc = rptx_photon_map_build(ctx, scene, ph, kind, &map);
+    } else if (rc == 0) {
+        rc = rptx_photon_map_build_sharded(ctx, scene, ph, kind, &map);  // == rptx_photon_map_build without a communicator
     }
-    if (rc == 0) rc = rptx_photon_map_build(ctx, scene, ph, kind, &map);
     if (ph) { rptx_photons_destroy(ph); ph = nullptr; }
     if (rc == 0) rc = rptx_photon_gather_begin(ctx, scene, camera, &prm, &film);
     if (rc == 0) rc = rptx_photon_gather_trace(film, map, params->num_samples);

@@ -602,9 +602,11 @@ RPTX_D d3 estimate_indirect(const SceneDev& sc, const MediumDev& md, const Photo
 // The per-thread kNN above spends its time in heap sift loops over local memory with 2-3 of 32
 // lanes active (profiles/r1_v2_summary.md).  For the point-point estimator (k = 30..100) a whole
 // warp owns one camera sample instead: all lanes walk the tree together (uniform control flow),
-// a "warp leaf" is 32 consecutive photons tested one per lane, accepted candidates are appended
-// to a shared-memory list by ballot, and when the list is full a bitonic sort keeps the k best
-// and tightens the radius.  The k visibility rays of the surface estimate then run 32 at a time.
+// the photons of a leaf (at most kPointLeaf = 8: the leaf reference keeps the count in 3 bits) are tested one per
+// lane - so a leaf visit uses up to 8 of the 32 lanes; what the warp buys is the uniform tree walk, the
+// shared candidate list and the visibility rays - accepted candidates are appended to a shared-memory
+// list by ballot, and when the list is full a bitonic sort keeps the k best and tightens the radius.
+// The k visibility rays of the surface estimate then run 32 at a time.
 constexpr int kWarpCand = 256;       // candidate list capacity per warp (>= k + 32)
 constexpr uint32_t kWarpKnnMaxK = 128;
 

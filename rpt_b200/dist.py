@@ -11,6 +11,8 @@ Here the two exchange steps of the path are
 Nothing here computes radiance; `film` / `photons` are the C-ABI objects (or test doubles with
 the same methods).
 """
+import os
+
 import torch
 import torch.distributed as dist
 
@@ -127,12 +129,15 @@ def photon_render(renderer, photon_count, kind, group=None):
     t0 = time.perf_counter()
     local = renderer.emit_photons(photon_count, kind, first=lo, count=hi - lo)
     t1 = time.perf_counter()
-    if lib_comm:
+    sharded_build = bool(lib_comm) and world > 1 and not os.environ.get("RPTX_REPLICATED_MAP_BUILD")
+    if sharded_build:
+        full = local  # the ranks split the build by Morton range; no merged row list exists (rptx_photon_map_build_sharded)
+    elif lib_comm:
         full = local.allgather()
     else:
         full = merge_photons(local, PhotonList.empty(renderer.device_scene().ctx) if world > 1 else None, group)
     t2 = time.perf_counter()
-    pmap = renderer.build_photon_map(full, kind)
+    pmap = renderer.build_photon_map(full, kind, sharded=sharded_build)
     t3 = time.perf_counter()
     film = renderer.begin_gather()
     n = renderer._p["num_samples"]
@@ -145,7 +150,8 @@ def photon_render(renderer, photon_count, kind, group=None):
             torch.cuda.current_stream().synchronize()
     film.sample_commit(n)
     t4 = time.perf_counter()
-    counts = full.counts()
+    st = pmap.stats()
+    counts = (st["surface"], st["bvh_items"] if st["bvh_items"] else st["volume"])
     if full is not local:
         local.close()
     full.close()

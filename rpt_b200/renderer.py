@@ -269,11 +269,16 @@ class PhotonList:
 class PhotonMap:
     """rptx_photon_map: the reference's PhotonMap enum (src/photon.rs:185-189) on the device."""
 
-    def __init__(self, dscene, photons, kind):
+    def __init__(self, dscene, photons, kind, sharded=False):
+        """sharded: `photons` is this rank's part of lists spread over the context's communicator; the ranks split the
+        build and every rank gets the complete map (rptx_photon_map_build_sharded, collective)."""
         self.ctx, self.lib, self.kind = dscene.ctx, dscene.lib, int(kind)
         self.dscene = dscene
         h = C.c_void_p()
-        self.ctx.check(self.lib.rptx_photon_map_build(self.ctx.h, dscene.h, photons.h, int(kind), C.byref(h)), "rptx_photon_map_build")
+        if sharded:
+            self.ctx.check(self.lib.rptx_photon_map_build_sharded(self.ctx.h, dscene.h, photons.h, int(kind), C.byref(h)), "rptx_photon_map_build_sharded")
+        else:
+            self.ctx.check(self.lib.rptx_photon_map_build(self.ctx.h, dscene.h, photons.h, int(kind), C.byref(h)), "rptx_photon_map_build")
         self.h = h
 
     def stats(self):
@@ -483,9 +488,9 @@ class Renderer:
         """PASS 1, src/photon.rs:663-675 -> PhotonList on the device."""
         return PhotonList.emit(self.device_scene(), self.params(), photon_count, kind, first, count)
 
-    def build_photon_map(self, photons, kind):
-        """PASS 2, src/photon.rs:693-702."""
-        return PhotonMap(self.device_scene(), photons, kind)
+    def build_photon_map(self, photons, kind, sharded=False):
+        """PASS 2, src/photon.rs:693-702.  sharded: `photons` is this rank's part; collective over the library communicator."""
+        return PhotonMap(self.device_scene(), photons, kind, sharded=sharded)
 
     def begin_gather(self):
         """Film of PASS 3 (src/photon.rs:706-716); film.gather(map, n) then film.sample_commit(n)."""

@@ -188,6 +188,7 @@ extern "C" {
     pub fn rptx_photons_download(photons: *mut rptx_photons, which: i32, rows: *mut c_void) -> c_int;
     pub fn rptx_photons_stats(photons: *const rptx_photons, emitted: *mut u64, rays: *mut u64, emit_ms: *mut f64) -> c_int;
     pub fn rptx_photon_map_build(ctx: *mut rptx_ctx, scene: *mut rptx_scene, photons: *mut rptx_photons, kind: i32, out: *mut *mut rptx_photon_map) -> c_int;
+    pub fn rptx_photon_map_build_sharded(ctx: *mut rptx_ctx, scene: *mut rptx_scene, local_photons: *mut rptx_photons, kind: i32, out: *mut *mut rptx_photon_map) -> c_int;
     pub fn rptx_photon_map_destroy(map: *mut rptx_photon_map);
     pub fn rptx_photon_map_stats(map: *const rptx_photon_map, counts: *mut u64, build_ms: *mut f64) -> c_int;
     pub fn rptx_photon_gather_begin(ctx: *mut rptx_ctx, scene: *mut rptx_scene, camera: *const rptx_camera, params: *const rptx_params, out: *mut *mut rptx_film) -> c_int;

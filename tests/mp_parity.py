@@ -36,12 +36,30 @@ def main(out_path):
             film.close(); r.device_scene().close()
     # photon integrators: emission shards + all-gather + gather shards + all-reduce inside rptx_photon_render
     scene, cam, d = scenes.lampshade("photonphoton")
-    for kind, kname in ((0, "photonphoton"), (2, "beambeam")):
+    for kind, kname in ((0, "photonphoton"), (1, "beamphoton"), (2, "beambeam")):
         r = scenes.make_renderer(scene, cam, d, seed=3, width=24, height=24, num_samples=4)
         r._ctx = ctx
         _, mean = r.photon_render(30000, kind, want_mean=True)
         out[f"{kname}_multi"] = mean
         r.device_scene().close()
+    # the sharded map build itself (rptx_photon_map_build_sharded): same kNN answers, bit for bit, as the one-rank build
+    rngq = np.random.default_rng(4)
+    queries = np.stack([rngq.uniform(0, 556, 400), rngq.uniform(0, 548, 400), rngq.uniform(0, 559, 400)], axis=1)
+    for kind, kname in ((0, "photonphoton"), (1, "beamphoton")):
+        r = scenes.make_renderer(scene, cam, d, seed=3, width=24, height=24, num_samples=4)
+        r._ctx = ctx
+        lo, hi = rd.photon_range(50000, world, rank)
+        part = r.emit_photons(50000, kind, first=lo, count=hi - lo)
+        pm = r.build_photon_map(part, kind, sharded=True)
+        for which in (0, 1):
+            keys, d2, cnt = pm.knn(which, queries, 12)
+            out[f"knn_{kname}_{which}_multi_keys"], out[f"knn_{kname}_{which}_multi_d2"] = keys, d2
+        if kind == 1:
+            c, rad = pm.spheres()
+            out["spheres_multi_c"], out["spheres_multi_r"] = c, rad
+        st = pm.stats()
+        out[f"stats_{kname}_multi"] = np.array([st["surface"], st["volume"], st["bvh_items"]])
+        pm.close(); part.close(); r.device_scene().close()
     dist.barrier()
     if rank == 0:
         solo = Context(local)  # no communicator: the whole batch on one GPU
@@ -56,12 +74,26 @@ def main(out_path):
                 out[f"{name}_{mode}_solo"] = film.mean()
                 film.close(); r.device_scene().close()
         scene, cam, d = scenes.lampshade("photonphoton")
-        for kind, kname in ((0, "photonphoton"), (2, "beambeam")):
+        for kind, kname in ((0, "photonphoton"), (1, "beamphoton"), (2, "beambeam")):
             r = scenes.make_renderer(scene, cam, d, seed=3, width=24, height=24, num_samples=4)
             r._ctx = solo
             _, mean = r.photon_render(30000, kind, want_mean=True)
             out[f"{kname}_solo"] = mean
             r.device_scene().close()
+        for kind, kname in ((0, "photonphoton"), (1, "beamphoton")):
+            r = scenes.make_renderer(scene, cam, d, seed=3, width=24, height=24, num_samples=4)
+            r._ctx = solo
+            allp = r.emit_photons(50000, kind)
+            pm = r.build_photon_map(allp, kind)
+            for which in (0, 1):
+                keys, d2, cnt = pm.knn(which, queries, 12)
+                out[f"knn_{kname}_{which}_solo_keys"], out[f"knn_{kname}_{which}_solo_d2"] = keys, d2
+            if kind == 1:
+                c, rad = pm.spheres()
+                out["spheres_solo_c"], out["spheres_solo_r"] = c, rad
+            st = pm.stats()
+            out[f"stats_{kname}_solo"] = np.array([st["surface"], st["volume"], st["bvh_items"]])
+            pm.close(); allp.close(); r.device_scene().close()
         np.savez(out_path, **out)
     dist.barrier()
     dist.destroy_process_group()

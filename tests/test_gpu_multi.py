@@ -1,5 +1,5 @@
 """-m gpu, needs >= 2 devices: an N-rank render through the library's NCCL communicator (rptx_comm_init,
-rptx_render_sample_allreduce, rptx_photons_allgather) equals the 1-GPU render.  The RNG is keyed by the global
+rptx_render_sample_allreduce, rptx_photon_map_build_sharded) equals the 1-GPU render.  The RNG is keyed by the global
 sample / photon index and every slot adds its samples in a fixed order, so the path tracer's batch sums differ only
 by the association of the cross-rank sum: bit-identical is not promised by an all-reduce, 1e-13 relative is."""
 import os
@@ -34,7 +34,14 @@ def test_sharded_render_equals_single_gpu(tmp_path):
         for mode in ("wavefront", "persist"):
             a, b = z[f"{name}_{mode}_multi"], z[f"{name}_{mode}_solo"]
             assert np.allclose(a, b, rtol=1e-13, atol=1e-300), (name, mode, np.abs(a - b).max())
-    for kname in ("photonphoton", "beambeam"):
+    # the map the ranks build together is the one-rank map: same photons found, same distances, same sphere radii
+    for kname in ("photonphoton", "beamphoton"):
+        assert np.array_equal(z[f"stats_{kname}_multi"], z[f"stats_{kname}_solo"]), kname
+        for which in (0, 1):
+            assert np.array_equal(z[f"knn_{kname}_{which}_multi_keys"], z[f"knn_{kname}_{which}_solo_keys"]), (kname, which)
+            assert np.array_equal(z[f"knn_{kname}_{which}_multi_d2"], z[f"knn_{kname}_{which}_solo_d2"]), (kname, which)
+    assert np.array_equal(z["spheres_multi_c"], z["spheres_solo_c"]) and np.array_equal(z["spheres_multi_r"], z["spheres_solo_r"])
+    for kname in ("photonphoton", "beamphoton", "beambeam"):
         a, b = z[f"{kname}_multi"], z[f"{kname}_solo"]
         # same photon set and same map (the build canonicalises row order by key); gather sums associate differently
         assert np.allclose(a, b, rtol=1e-11, atol=1e-300), (kname, np.abs(a - b).max())

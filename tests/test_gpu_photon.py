@@ -113,6 +113,41 @@ def test_knn_exact():
     assert (cg == 0).all()
 
 
+@pytest.mark.parametrize("kind", [0, 1, 2])
+def test_sharded_build_code_path_equals_the_plain_build(kind, monkeypatch):
+    """rptx_photon_map_build_sharded on ONE rank (RPTX_FORCE_SHARDED_BUILD: splitters, cuts, exchange as local copies,
+    segment sort, tree): the same map as rptx_photon_map_build, bit for bit - kNN answers, sphere radii, the gather image.
+    tests/test_gpu_multi.py runs it over real ranks."""
+    scene, cam, r, osc = _setup(["photonphoton", "beamphoton", "beambeam"][kind])
+    rows_s, rows_v = osc.emit_photons(cam, r.params(), N_PHOTONS, kind)
+    plain = _gpu_map_from(r, rows_s, rows_v, kind)
+    monkeypatch.setenv("RPTX_FORCE_SHARDED_BUILD", "1")
+    pl = PhotonList.empty(r.device_scene().ctx)
+    rng = np.random.default_rng(8)
+    pl.append_host(0, rows_s[rng.permutation(len(rows_s))])
+    pl.append_host(1, rows_v[rng.permutation(len(rows_v))])
+    shard = r.build_photon_map(pl, kind, sharded=True)
+    assert shard.stats()["surface"] == plain.stats()["surface"] and shard.stats()["bvh_items"] == plain.stats()["bvh_items"]
+    q = np.concatenate([rows_s[rng.integers(0, len(rows_s), 300), :3] + rng.normal(scale=2.0, size=(300, 3)), rng.uniform(-50, 600, size=(200, 3))])
+    for which in ((0, 1) if kind != 2 else (0,)):
+        ka, da, ca = plain.knn(which, q, 30)
+        kb, db, cb = shard.knn(which, q, 30)
+        assert np.array_equal(ca, cb) and np.array_equal(da, db) and np.array_equal(ka, kb)
+    if kind == 1:
+        ca, ra = plain.spheres()
+        cb, rb = shard.spheres()
+        assert np.array_equal(ca, cb) and np.array_equal(ra, rb)
+    fa, fb = r.begin_gather(), r.begin_gather()
+    fa.gather(plain, 2); fa.sample_commit(2)
+    fb.gather(shard, 2); fb.sample_commit(2)
+    assert np.array_equal(fa.mean(), fb.mean())
+    # an empty list on this rank
+    monkeypatch.setenv("RPTX_FORCE_SHARDED_BUILD", "1")
+    e = PhotonList.empty(r.device_scene().ctx)
+    em = r.build_photon_map(e, kind, sharded=True)
+    assert em.stats()["surface"] == 0
+
+
 def test_sphere_radii_exact():
     scene, cam, r, osc = _setup("beamphoton")
     rows_s, rows_v = osc.emit_photons(cam, r.params(), N_PHOTONS, 1)
