@@ -916,13 +916,29 @@ static int photon_map_build_impl(rptx_ctx* ctx, rptx_scene* scene, rptx_photons*
     m->ctx = ctx; m->scene = scene; m->kind = kind;
     int rc = 0;
     uint32_t *canon_s = nullptr, *canon_v = nullptr, *perm = nullptr;
-    const uint32_t ns = (uint32_t)photons->n[0];
+    uint32_t ns = (uint32_t)photons->n[0];
     uint32_t nv = (uint32_t)photons->n[1];
+    const PhotonRec* srows = photons->d_rows[0];
     const PhotonRec* vrows = photons->d_rows[1];
-    PhotonRec* vrows_full = nullptr;  // sharded beam-beam: the merged volume rows
+    PhotonRec *srows_full = nullptr, *vrows_full = nullptr;  // merged rows, where the ranks need them whole
+    // Point maps are split by Morton range from 4 ranks on.  Measured at 1e8 photons (profiles/r2_summary.md): the exchange,
+    // the segment all-gather and the replicated tree cost about what the split sorts save at 2 ranks (photon-photon step
+    // 272 ms merged-and-replicated, 305 split) and win from 4 on (8 ranks: 239 -> 194 ms); below that the rows are merged
+    // and every rank builds the maps itself.  The radius pass of the beam-photon map is split at any rank count.
+    int min_world = 4;
+    if (const char* e = std::getenv("RPTX_SHARDED_MAPS_MIN_WORLD")) min_world = std::max(1, std::atoi(e));
+    const bool shard_maps = sharded && (rptx_host::comm_world(ctx) >= min_world || std::getenv("RPTX_FORCE_SHARDED_BUILD"));
     PhaseTrace trace(ctx);
     auto body = [&]() -> int {
-        if (sharded) {
+        if (sharded && !shard_maps) {
+            uint64_t ts = 0, tv = 0;
+            if (int r = allgather_rows(ctx, srows, ns, &srows_full, &ts)) return r;
+            if (int r = allgather_rows(ctx, vrows, nv, &vrows_full, &tv)) return r;
+            srows = srows_full; vrows = vrows_full;
+            ns = (uint32_t)ts; nv = (uint32_t)tv;
+            trace.mark("build: rows all-gather");
+        }
+        if (shard_maps) {
             if (int r = build_point_map_sharded(ctx, photons->d_rows[0], ns, &m->surface)) return r;
             trace.mark("build: point map surface (sharded)");
             if (kind == RPTX_PHOTON_MAP || kind == RPTX_PHOTON_POINT_BEAM) {
@@ -939,14 +955,15 @@ static int photon_map_build_impl(rptx_ctx* ctx, rptx_scene* scene, rptx_photons*
                 trace.mark("build: volume rows all-gather + canonical");
             }
         } else {
-        if (int r = canonical_order(ctx, photons->d_rows[0], ns, &canon_s)) return r;
+        if (int r = canonical_order(ctx, srows, ns, &canon_s)) return r;
         trace.mark("build: canonical surface");
-        if (int r = build_point_map(ctx, photons->d_rows[0], canon_s, ns, &m->surface)) return r;
+        if (int r = build_point_map(ctx, srows, canon_s, ns, &m->surface)) return r;
         trace.mark("build: point map surface");
-        if (int r = canonical_order(ctx, photons->d_rows[1], nv, &canon_v)) return r;
+        rptx_free_async(srows_full, ctx->stream); srows_full = nullptr;
+        if (int r = canonical_order(ctx, vrows, nv, &canon_v)) return r;
         trace.mark("build: canonical volume");
         if (kind == RPTX_PHOTON_MAP || kind == RPTX_PHOTON_POINT_BEAM) {
-            if (int r = build_point_map(ctx, photons->d_rows[1], canon_v, nv, &m->volume)) return r;
+            if (int r = build_point_map(ctx, vrows, canon_v, nv, &m->volume)) return r;
             trace.mark("build: point map volume");
         }
         }
@@ -1018,7 +1035,7 @@ static int photon_map_build_impl(rptx_ctx* ctx, rptx_scene* scene, rptx_photons*
     };
     rc = body();
     rptx_free_async(canon_s, ctx->stream); rptx_free_async(canon_v, ctx->stream); rptx_free_async(perm, ctx->stream);
-    rptx_free_async(vrows_full, ctx->stream);
+    rptx_free_async(vrows_full, ctx->stream); rptx_free_async(srows_full, ctx->stream);
     if (rc == 0) {
         cudaEventRecord(e1, st);
         cudaEventSynchronize(e1);

@@ -43,6 +43,7 @@ def main(out_path):
         out[f"{kname}_multi"] = mean
         r.device_scene().close()
     # the sharded map build itself (rptx_photon_map_build_sharded): same kNN answers, bit for bit, as the one-rank build
+    os.environ["RPTX_SHARDED_MAPS_MIN_WORLD"] = "2"  # the library splits the point maps from 4 ranks on; here at any count
     rngq = np.random.default_rng(4)
     queries = np.stack([rngq.uniform(0, 556, 400), rngq.uniform(0, 548, 400), rngq.uniform(0, 559, 400)], axis=1)
     for kind, kname in ((0, "photonphoton"), (1, "beamphoton")):
@@ -60,6 +61,13 @@ def main(out_path):
         st = pm.stats()
         out[f"stats_{kname}_multi"] = np.array([st["surface"], st["volume"], st["bvh_items"]])
         pm.close(); part.close(); r.device_scene().close()
+    # and once more through rptx_photon_render with the split maps (the renders above used the rank count's default)
+    r = scenes.make_renderer(scene, cam, d, seed=3, width=24, height=24, num_samples=4)
+    r._ctx = ctx
+    _, mean = r.photon_render(30000, 0, want_mean=True)
+    out["photonphoton_split_multi"] = mean
+    r.device_scene().close()
+    os.environ.pop("RPTX_SHARDED_MAPS_MIN_WORLD")
     dist.barrier()
     if rank == 0:
         solo = Context(local)  # no communicator: the whole batch on one GPU

@@ -41,6 +41,7 @@ def test_sharded_render_equals_single_gpu(tmp_path):
             assert np.array_equal(z[f"knn_{kname}_{which}_multi_keys"], z[f"knn_{kname}_{which}_solo_keys"]), (kname, which)
             assert np.array_equal(z[f"knn_{kname}_{which}_multi_d2"], z[f"knn_{kname}_{which}_solo_d2"]), (kname, which)
     assert np.array_equal(z["spheres_multi_c"], z["spheres_solo_c"]) and np.array_equal(z["spheres_multi_r"], z["spheres_solo_r"])
+    assert np.allclose(z["photonphoton_split_multi"], z["photonphoton_solo"], rtol=1e-11, atol=1e-300)
     for kname in ("photonphoton", "beamphoton", "beambeam"):
         a, b = z[f"{kname}_multi"], z[f"{kname}_solo"]
         # same photon set and same map (the build canonicalises row order by key); gather sums associate differently
