@@ -1,6 +1,9 @@
 // GPU LBVH build — see bvh_build.cuh.
 #include <cub/cub.cuh>
 
+#include <algorithm>
+#include <cstdlib>
+
 #include "bvh_build.cuh"
 #include "host_types.hpp"
 
@@ -234,6 +237,192 @@ int build_lbvh_sorted(const uint64_t* d_keys, const PrimBox* d_boxes, uint32_t n
 fail:
 #undef RPTX_CK
     if (ints) cudaFreeAsync(ints, stream); if (ibox) cudaFreeAsync(ibox, stream);
+    return (int)e;
+}
+
+// ---- PLOC: SAH-quality trees on the GPU ----------------------------------------------------------------------------
+// Parallel locally-ordered clustering (Meister & Bittner 2018) over the Morton order: every cluster looks kPlocRadius
+// neighbours to each side for the partner whose union has the smallest surface area; mutual nearest neighbours merge into a
+// new node; the survivors are compacted in order; repeat until one cluster is left.  The agglomeration follows the surface-area
+// heuristic instead of the Morton bits, which is what the LBVH lacks (photon maps keep the LBVH: points have no area).
+// The finished topology is laid out like the LBVH's: a node covers a contiguous range of the leaf order, subtrees of
+// <= leaf_max primitives collapse into leaf references, node 0 is the root.
+namespace {
+
+constexpr int kPlocRadius = 16;  // neighbours searched to each side (RPTX_PLOC_RADIUS; measured sweep in DESIGN.md section 5)
+
+struct PlocNode {
+    PrimBox box;
+    int left, right, parent;  // children: node ids (leaves are 0..n-1, inner nodes n..2n-2); parent -1 at the root
+    int size;                 // primitives below
+};
+
+__device__ __forceinline__ float box_area(const PrimBox& b) {
+    const float dx = b.mx[0] - b.mn[0], dy = b.mx[1] - b.mn[1], dz = b.mx[2] - b.mn[2];
+    return dx * dy + dy * dz + dz * dx;
+}
+
+__global__ void k_ploc_leaves(const PrimBox* __restrict__ boxes, const uint64_t* __restrict__ keys, uint32_t n, PlocNode* __restrict__ nodes,
+                              int* __restrict__ cluster) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    PlocNode nd;
+    nd.box = boxes[(uint32_t)(keys[i] & 0xffffffffu)];
+    nd.left = nd.right = -1; nd.parent = -1; nd.size = 1;
+    nodes[i] = nd;
+    cluster[i] = (int)i;
+}
+
+__global__ void k_ploc_nearest(const PlocNode* __restrict__ nodes, const int* __restrict__ cluster, int m, int radius, int* __restrict__ nn) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= m) return;
+    const PrimBox a = nodes[cluster[i]].box;
+    float best = CUDART_INF_F;
+    int arg = -1;
+    const int lo = max(0, i - radius), hi = min(m - 1, i + radius);
+    for (int j = lo; j <= hi; j++) {
+        if (j == i) continue;
+        const float c = box_area(merge(a, nodes[cluster[j]].box));
+        if (c < best) { best = c; arg = j; }  // ties: the smaller index, on both sides of a pair
+    }
+    nn[i] = arg;
+}
+
+__global__ void k_ploc_merge(PlocNode* __restrict__ nodes, const int* __restrict__ cluster, const int* __restrict__ nn, int m, int* __restrict__ next_node,
+                             int* __restrict__ out, uint8_t* __restrict__ keep) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= m) return;
+    const int j = nn[i];
+    int c = cluster[i];
+    uint8_t k = 1;
+    if (j >= 0 && nn[j] == i) {
+        if (i < j) {
+            const int cj = cluster[j];
+            const int id = atomicAdd(next_node, 1);
+            PlocNode nd;
+            nd.box = merge(nodes[c].box, nodes[cj].box);
+            nd.left = c; nd.right = cj; nd.parent = -1;
+            nd.size = nodes[c].size + nodes[cj].size;
+            nodes[id] = nd;
+            nodes[c].parent = id;
+            nodes[cj].parent = id;
+            c = id;
+        } else {
+            k = 0;
+        }
+    }
+    out[i] = c;
+    keep[i] = k;
+}
+
+// position of a node's first primitive in the leaf order: the sizes of the left siblings on the way to the root
+__global__ void k_ploc_first(const PlocNode* __restrict__ nodes, int total, int* __restrict__ first, int* __restrict__ max_depth) {
+    const int v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v >= total) return;
+    int pos = 0, depth = 0, c = v, p = nodes[v].parent;
+    while (p >= 0) {
+        if (nodes[p].right == c) pos += nodes[nodes[p].left].size;
+        c = p;
+        p = nodes[p].parent;
+        depth++;
+    }
+    first[v] = pos;
+    atomicMax(max_depth, depth);
+}
+
+__global__ void k_ploc_emit(const PlocNode* __restrict__ nodes, const int* __restrict__ first, const uint64_t* __restrict__ keys, int n, float pad,
+                            int leaf_max, BvhNode* __restrict__ out, uint32_t* __restrict__ perm) {
+    const int v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v >= 2 * n - 1) return;
+    if (v < n) { perm[first[v]] = (uint32_t)(keys[v] & 0xffffffffu); return; }
+    const PlocNode nd = nodes[v];
+    BvhNode o;
+    auto child = [&](int c, float* mn, float* mx, int* ref) {
+        const PlocNode ch = nodes[c];
+        *ref = ch.size <= leaf_max ? make_leaf_ref((uint32_t)first[c], (uint32_t)ch.size) : (2 * n - 2 - c);
+#pragma unroll
+        for (int k = 0; k < 3; k++) { mn[k] = __fsub_rd(ch.box.mn[k], pad); mx[k] = __fadd_ru(ch.box.mx[k], pad); }
+    };
+    child(nd.left, o.lmin, o.lmax, &o.left);
+    child(nd.right, o.rmin, o.rmax, &o.right);
+    o.pad0 = 0; o.pad1 = 0;
+    out[2 * n - 2 - v] = o;  // the root (created last) is node 0
+}
+
+}  // namespace
+
+// Same contract as build_lbvh.  Returns cudaErrorNotSupported when the tree came out deeper than max_depth (the caller then
+// builds the LBVH, whose depth is bounded by its key length).
+int build_ploc(const PrimBox* d_boxes, uint32_t n, float pad, int leaf_max, const double cmin[3], const double cmax[3], BvhNode* d_nodes,
+               uint32_t* d_perm, int* root_ref, int max_depth, cudaStream_t stream, uint64_t* launches) {
+    if (n == 0) { *root_ref = 0; return 0; }
+    cudaError_t e = cudaSuccess;
+    uint64_t *keys_in = nullptr, *keys_out = nullptr;
+    PlocNode* nodes = nullptr;
+    int *cl_a = nullptr, *cl_b = nullptr, *cl_t = nullptr, *nn = nullptr, *first = nullptr, *ctr = nullptr;
+    uint8_t* keep = nullptr;
+    void* tmp = nullptr;
+    size_t tmp_bytes = 0, sel_bytes = 0;
+    int h_ctr[3] = {0, 0, 0};  // [0] next node id, [1] clusters after the compaction, [2] max depth
+#define RPTX_CK(x) do { e = (x); if (e != cudaSuccess) goto fail; } while (0)
+    RPTX_CK(rptx_alloc_async((void**)&keys_in, sizeof(uint64_t) * n, stream));
+    RPTX_CK(rptx_alloc_async((void**)&keys_out, sizeof(uint64_t) * n, stream));
+    RPTX_CK(rptx_alloc_async((void**)&nodes, sizeof(PlocNode) * (2 * (size_t)n), stream));
+    RPTX_CK(rptx_alloc_async((void**)&cl_a, sizeof(int) * n, stream));
+    RPTX_CK(rptx_alloc_async((void**)&cl_b, sizeof(int) * n, stream));
+    RPTX_CK(rptx_alloc_async((void**)&cl_t, sizeof(int) * n, stream));
+    RPTX_CK(rptx_alloc_async((void**)&nn, sizeof(int) * n, stream));
+    RPTX_CK(rptx_alloc_async((void**)&first, sizeof(int) * (2 * (size_t)n), stream));
+    RPTX_CK(rptx_alloc_async((void**)&keep, n, stream));
+    RPTX_CK(rptx_alloc_async((void**)&ctr, sizeof(int) * 4, stream));
+    {
+        float3 fmin = make_float3((float)cmin[0], (float)cmin[1], (float)cmin[2]);
+        float3 finv;
+        finv.x = cmax[0] > cmin[0] ? (float)(1.0 / (cmax[0] - cmin[0])) : 0.f;
+        finv.y = cmax[1] > cmin[1] ? (float)(1.0 / (cmax[1] - cmin[1])) : 0.f;
+        finv.z = cmax[2] > cmin[2] ? (float)(1.0 / (cmax[2] - cmin[2])) : 0.f;
+        const int T = 128;
+        const int B = (int)((n + T - 1) / T);
+        k_morton<<<B, T, 0, stream>>>(d_boxes, n, fmin, finv, keys_in);
+        RPTX_CK(cub::DeviceRadixSort::SortKeys(nullptr, tmp_bytes, keys_in, keys_out, (int)n, 0, 64, stream));
+        RPTX_CK(cub::DeviceSelect::Flagged(nullptr, sel_bytes, cl_t, keep, cl_b, ctr + 1, (int)n, stream));
+        tmp_bytes = tmp_bytes > sel_bytes ? tmp_bytes : sel_bytes;
+        RPTX_CK(rptx_alloc_async((void**)&tmp, tmp_bytes ? tmp_bytes : 16, stream));
+        RPTX_CK(cub::DeviceRadixSort::SortKeys(tmp, tmp_bytes, keys_in, keys_out, (int)n, 0, 64, stream));
+        k_ploc_leaves<<<B, T, 0, stream>>>(d_boxes, keys_out, n, nodes, cl_a);
+        (*launches) += 3;
+        h_ctr[0] = (int)n;
+        RPTX_CK(cudaMemcpyAsync(ctr, h_ctr, sizeof(int) * 3, cudaMemcpyHostToDevice, stream));
+        int m = (int)n;
+        int radius = kPlocRadius;
+        if (const char* ev = std::getenv("RPTX_PLOC_RADIUS")) radius = std::min(256, std::max(1, std::atoi(ev)));
+        while (m > 1) {
+            const int Bm = (m + T - 1) / T;
+            k_ploc_nearest<<<Bm, T, 0, stream>>>(nodes, cl_a, m, radius, nn);
+            k_ploc_merge<<<Bm, T, 0, stream>>>(nodes, cl_a, nn, m, ctr, cl_t, keep);
+            size_t bytes = tmp_bytes;
+            RPTX_CK(cub::DeviceSelect::Flagged(tmp, bytes, cl_t, keep, cl_b, ctr + 1, m, stream));
+            (*launches) += 4;
+            RPTX_CK(cudaMemcpyAsync(h_ctr + 1, ctr + 1, sizeof(int), cudaMemcpyDeviceToHost, stream));
+            RPTX_CK(cudaStreamSynchronize(stream));
+            if (h_ctr[1] >= m || h_ctr[1] < 1) { e = cudaErrorUnknown; goto fail; }  // every pass merges at least the closest pair
+            m = h_ctr[1];
+            int* t = cl_a; cl_a = cl_b; cl_b = t;
+        }
+        const int total = 2 * (int)n - 1;
+        k_ploc_first<<<(total + T - 1) / T, T, 0, stream>>>(nodes, total, first, ctr + 2);
+        k_ploc_emit<<<(total + T - 1) / T, T, 0, stream>>>(nodes, first, keys_out, (int)n, pad, leaf_max, d_nodes, d_perm);
+        (*launches) += 2;
+        RPTX_CK(cudaMemcpyAsync(h_ctr + 2, ctr + 2, sizeof(int), cudaMemcpyDeviceToHost, stream));
+        RPTX_CK(cudaGetLastError());
+        RPTX_CK(cudaStreamSynchronize(stream));
+        *root_ref = (n <= (uint32_t)leaf_max) ? make_leaf_ref(0u, n) : 0;
+        if (h_ctr[2] > max_depth) e = cudaErrorNotSupported;
+    }
+fail:
+#undef RPTX_CK
+    for (void* p : {(void*)keys_in, (void*)keys_out, (void*)nodes, (void*)cl_a, (void*)cl_b, (void*)cl_t, (void*)nn, (void*)first, (void*)keep, (void*)ctr, tmp})
+        if (p) cudaFreeAsync(p, stream);
     return (int)e;
 }
 

@@ -25,4 +25,10 @@ int build_lbvh(const PrimBox* d_boxes, uint32_t n, float pad, int leaf_max, cons
 int build_lbvh_sorted(const uint64_t* d_keys, const PrimBox* d_boxes, uint32_t n, float pad, int leaf_max, BvhNode* d_nodes, int* root_ref,
                       cudaStream_t stream, uint64_t* launches);
 
+// SAH-quality tree on the GPU: PLOC (parallel locally-ordered clustering over the Morton order, surface-area merge criterion),
+// same contract and node layout as build_lbvh.  Replaces the reference's serial SAH-less median split (src/kdtree.rs:238-348)
+// for object meshes and the instance level.  cudaErrorNotSupported = deeper than max_depth (build the LBVH instead).
+int build_ploc(const PrimBox* d_boxes, uint32_t n, float pad, int leaf_max, const double cmin[3], const double cmax[3], BvhNode* d_nodes,
+               uint32_t* d_perm, int* root_ref, int max_depth, cudaStream_t stream, uint64_t* launches);
+
 }  // namespace rptx

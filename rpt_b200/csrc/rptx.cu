@@ -492,6 +492,11 @@ int rptx_scene_commit(rptx_scene* s) {
 
     // 1. meshes: upload raw triangles, build one BLAS per mesh (host SAH for small meshes, GPU LBVH otherwise)
     const bool lbvh_only = std::getenv("RPTX_LBVH_ONLY") != nullptr;  // developer knob: the GPU LBVH for every tree
+    // object trees: RPTX_BVH_BUILDER=ploc builds every tree on the GPU with the surface-area criterion (build_ploc), =host the
+    // binned-SAH trees of bvh_sah.hpp for up to 65 K items (the default, see DESIGN.md section 5 for the measured comparison)
+    bool gpu_sah = false;
+    if (const char* e = std::getenv("RPTX_BVH_BUILDER")) gpu_sah = std::string(e) == "ploc";
+    constexpr int kPlocMaxDepth = 56;  // two levels + sentinel must fit kStackSize = 128 pending entries
     std::vector<RawTri> raw_all;
     uint32_t tri_total = 0, node_total = 0;
     for (auto& m : s->meshes) {
@@ -532,7 +537,7 @@ int rptx_scene_commit(rptx_scene* s) {
         double e_abs = 0.0;
         for (int k = 0; k < 3; k++) e_abs = std::fmax(e_abs, std::fmax(std::fabs(m.bmin[k]), std::fabs(m.bmax[k])));
         m.pad = f32_upf(std::fmax(e_abs, 1e-30) * (1.0 / 2097152.0));  // E * 2^-21
-        if (n <= rptx_host::kSahMaxPrims && !lbvh_only) {
+        if (n <= rptx_host::kSahMaxPrims && !lbvh_only && !gpu_sah) {
             // small mesh: binned SAH on the host (bvh_sah.hpp), same node format, same padding
             std::vector<PrimBox> hb(n);
             for (uint32_t i = 0; i < n; i++)
@@ -554,7 +559,9 @@ int rptx_scene_commit(rptx_scene* s) {
             CK(rptx_alloc_async((void**)&d_perm, sizeof(uint32_t) * n, st));
             k_tri_boxes<<<grid_for(n, 128), 128, 0, st>>>(d_raw + m.raw_base, n, d_boxes);
             ctx->launches++;
-            const int rc = build_lbvh(d_boxes, n, m.pad, kLeafMax, m.bmin, m.bmax, d_nodes + m.node_base, d_perm, &m.root_ref, st, &ctx->launches);
+            int rc = (int)cudaErrorNotSupported;
+            if (gpu_sah) rc = build_ploc(d_boxes, n, m.pad, kLeafMax, m.bmin, m.bmax, d_nodes + m.node_base, d_perm, &m.root_ref, kPlocMaxDepth, st, &ctx->launches);
+            if (rc == (int)cudaErrorNotSupported) rc = build_lbvh(d_boxes, n, m.pad, kLeafMax, m.bmin, m.bmax, d_nodes + m.node_base, d_perm, &m.root_ref, st, &ctx->launches);
             if (rc != 0) { rptx_free_async(d_boxes, st); rptx_free_async(d_perm, st); return ctx_fail(ctx, std::string("BLAS build: ") + cudaGetErrorString((cudaError_t)rc)); }
         }
         k_tri_prepare<<<grid_for(n, 128), 128, 0, st>>>(d_raw + m.raw_base, d_perm, n, d_tris + m.tri_base, d_trif + m.tri_base, d_tn + m.tri_base,
@@ -603,7 +610,7 @@ int rptx_scene_commit(rptx_scene* s) {
             boxes.push_back(pb);
         }
         std::vector<uint32_t> perm(boxes.size());
-        if (boxes.size() <= rptx_host::kSahMaxPrims && !lbvh_only) {
+        if (boxes.size() <= rptx_host::kSahMaxPrims && !lbvh_only && !gpu_sah) {
             std::vector<BvhNode> hn;
             rptx_host::build_sah_host(boxes, wpad, 1, hn, perm, &s->tlas_root_ref);
             if (!hn.empty()) CK(copy_h2d(d_nodes, hn.data(), sizeof(BvhNode) * hn.size(), st));
@@ -612,7 +619,9 @@ int rptx_scene_commit(rptx_scene* s) {
             PrimBox* d_boxes = nullptr; uint32_t* d_perm = nullptr;
             CK(upload(&d_boxes, boxes, st));
             CK(rptx_alloc_async((void**)&d_perm, sizeof(uint32_t) * boxes.size(), st));
-            const int rc = build_lbvh(d_boxes, (uint32_t)boxes.size(), wpad, 1, wmn, wmx, d_nodes, d_perm, &s->tlas_root_ref, st, &ctx->launches);
+            int rc = (int)cudaErrorNotSupported;
+            if (gpu_sah) rc = build_ploc(d_boxes, (uint32_t)boxes.size(), wpad, 1, wmn, wmx, d_nodes, d_perm, &s->tlas_root_ref, kPlocMaxDepth, st, &ctx->launches);
+            if (rc == (int)cudaErrorNotSupported) rc = build_lbvh(d_boxes, (uint32_t)boxes.size(), wpad, 1, wmn, wmx, d_nodes, d_perm, &s->tlas_root_ref, st, &ctx->launches);
             if (rc != 0) { rptx_free_async(d_boxes, st); rptx_free_async(d_perm, st); return ctx_fail(ctx, std::string("TLAS build: ") + cudaGetErrorString((cudaError_t)rc)); }
             CK(cudaMemcpyAsync(perm.data(), d_perm, sizeof(uint32_t) * perm.size(), cudaMemcpyDeviceToHost, st));
             CK(cudaStreamSynchronize(st));

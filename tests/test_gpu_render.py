@@ -224,24 +224,40 @@ def test_film_slab_is_recycled_and_pool_size_does_not_matter(monkeypatch):
 
 def test_sah_trees_equal_lbvh_trees(monkeypatch):
     """Small meshes and the instance level get a host-built SAH tree, larger ones the GPU LBVH (RPTX_LBVH_ONLY forces
-    it everywhere).  The accelerator only orders the search: same hits, same batch, bit for bit."""
+    it everywhere); RPTX_BVH_BUILDER=ploc builds every tree on the GPU with the surface-area criterion (build_ploc).
+    The accelerator only orders the search: same hits, same batch, bit for bit."""
     monkeypatch.setenv("RPTX_PATH_MODE", "wavefront")
-    for name in ("teapot", "fractal_teapots"):
+    for name in ("teapot", "fractal_teapots", "monomial_glass"):
         scene, cam, d = getattr(scenes, name)()
         means = []
-        for lbvh in (False, True):
-            if lbvh:
-                monkeypatch.setenv("RPTX_LBVH_ONLY", "1")
-            else:
-                monkeypatch.delenv("RPTX_LBVH_ONLY", raising=False)
+        for env in ({}, {"RPTX_LBVH_ONLY": "1"}, {"RPTX_BVH_BUILDER": "ploc"}, {"RPTX_BVH_BUILDER": "ploc", "RPTX_NO_SMALL_SCENE": "1"}):
+            for k in ("RPTX_LBVH_ONLY", "RPTX_BVH_BUILDER", "RPTX_NO_SMALL_SCENE"):
+                monkeypatch.delenv(k, raising=False)
+            for k, v in env.items():
+                monkeypatch.setenv(k, v)
             r = scenes.make_renderer(scene, cam, d, width=96, height=64, num_samples=2, seed=5, max_bounces=2)
             f = r.begin()
             f.sample(2)
             means.append(f.mean())
             f.close()
             r.device_scene().close()
-        monkeypatch.delenv("RPTX_LBVH_ONLY", raising=False)
-        assert np.array_equal(means[0], means[1]), name
+        for k in ("RPTX_LBVH_ONLY", "RPTX_BVH_BUILDER", "RPTX_NO_SMALL_SCENE"):
+            monkeypatch.delenv(k, raising=False)
+        for m in means[1:]:
+            assert np.array_equal(means[0], m), name
+    # Cornell through the hierarchy (the small-scene walk off) with PLOC trees: polygons are one-leaf meshes under a PLOC TLAS
+    scene, cam, d = scenes.cornell()
+    means = []
+    for env in ({"RPTX_NO_SMALL_SCENE": "1"}, {"RPTX_NO_SMALL_SCENE": "1", "RPTX_BVH_BUILDER": "ploc"}):
+        for k, v in env.items():
+            monkeypatch.setenv(k, v)
+        f = scenes.make_renderer(scene, cam, d, width=64, height=48, num_samples=2, seed=5, max_bounces=3).begin()
+        f.sample(2)
+        means.append(f.mean())
+        f.close()
+        monkeypatch.delenv("RPTX_BVH_BUILDER", raising=False)
+    monkeypatch.delenv("RPTX_NO_SMALL_SCENE", raising=False)
+    assert np.array_equal(means[0], means[1])
 
 
 def test_monomial_glass_same_seed():
