@@ -2,6 +2,7 @@
 #include <cub/cub.cuh>
 
 #include <algorithm>
+#include <cstdio>
 #include <cstdlib>
 
 #include "bvh_build.cuh"
@@ -249,7 +250,7 @@ fail:
 // <= leaf_max primitives collapse into leaf references, node 0 is the root.
 namespace {
 
-constexpr int kPlocRadius = 16;  // neighbours searched to each side (RPTX_PLOC_RADIUS; measured sweep in DESIGN.md section 5)
+constexpr int kPlocRadius = 64;  // neighbours searched to each side (RPTX_PLOC_RADIUS; measured sweep in DESIGN.md section 5)
 
 struct PlocNode {
     PrimBox box;
@@ -280,10 +281,18 @@ __global__ void k_ploc_nearest(const PlocNode* __restrict__ nodes, const int* __
     float best = CUDART_INF_F;
     int arg = -1;
     const int lo = max(0, i - radius), hi = min(m - 1, i + radius);
+    // Ties on the cost are common (instances of one mesh on a regular pattern: equal boxes, equal gaps).  Broken by index
+    // they form chains - everybody prefers its left neighbour and only the pair at the end is mutual: one merge per pass,
+    // 800 passes for the 937 instances of fractal_teapots.  A symmetric hash of the pair breaks them instead: the pair with
+    // the smallest hash among both partners' ties is mutual, about a third of the tied pairs per pass.
+    unsigned best_h = 0xffffffffu;
     for (int j = lo; j <= hi; j++) {
         if (j == i) continue;
         const float c = box_area(merge(a, nodes[cluster[j]].box));
-        if (c < best) { best = c; arg = j; }  // ties: the smaller index, on both sides of a pair
+        const unsigned p = (unsigned)min(i, j), q = (unsigned)max(i, j);
+        unsigned h = p * 0x9E3779B1u ^ (q + 0x7F4A7C15u) * 0x85EBCA77u;
+        h ^= h >> 15; h *= 0x2C1B3C6Du; h ^= h >> 12;
+        if (c < best || (c == best && h < best_h)) { best = c; best_h = h; arg = j; }
     }
     nn[i] = arg;
 }
@@ -393,7 +402,7 @@ int build_ploc(const PrimBox* d_boxes, uint32_t n, float pad, int leaf_max, cons
         (*launches) += 3;
         h_ctr[0] = (int)n;
         RPTX_CK(cudaMemcpyAsync(ctr, h_ctr, sizeof(int) * 3, cudaMemcpyHostToDevice, stream));
-        int m = (int)n;
+        int m = (int)n, passes = 0;
         int radius = kPlocRadius;
         if (const char* ev = std::getenv("RPTX_PLOC_RADIUS")) radius = std::min(256, std::max(1, std::atoi(ev)));
         while (m > 1) {
@@ -405,7 +414,8 @@ int build_ploc(const PrimBox* d_boxes, uint32_t n, float pad, int leaf_max, cons
             (*launches) += 4;
             RPTX_CK(cudaMemcpyAsync(h_ctr + 1, ctr + 1, sizeof(int), cudaMemcpyDeviceToHost, stream));
             RPTX_CK(cudaStreamSynchronize(stream));
-            if (h_ctr[1] >= m || h_ctr[1] < 1) { e = cudaErrorUnknown; goto fail; }  // every pass merges at least the closest pair
+            if (h_ctr[1] >= m || h_ctr[1] < 1) { e = cudaErrorNotSupported; goto fail; }  // a pass without a merge (hash collision on a tie): the caller builds the LBVH
+            passes++;
             m = h_ctr[1];
             int* t = cl_a; cl_a = cl_b; cl_b = t;
         }
@@ -417,6 +427,7 @@ int build_ploc(const PrimBox* d_boxes, uint32_t n, float pad, int leaf_max, cons
         RPTX_CK(cudaGetLastError());
         RPTX_CK(cudaStreamSynchronize(stream));
         *root_ref = (n <= (uint32_t)leaf_max) ? make_leaf_ref(0u, n) : 0;
+        if (std::getenv("RPTX_TRACE_BUILD")) fprintf(stderr, "[rptx] PLOC: %u items, radius %d, %d passes, depth %d\n", n, radius, passes, h_ctr[2]);
         if (h_ctr[2] > max_depth) e = cudaErrorNotSupported;
     }
 fail:

@@ -29,9 +29,10 @@ struct RayF {
 };
 
 constexpr float kSlabSlack = 1e-6f;
-// Pending entries of the two-level walk: a BVH2 walk holds at most one entry per level.  Host SAH trees are at most 36
-// levels deep (bvh_sah.hpp); the Karras LBVH over 30-bit Morton codes + 32-bit index tie-break (bvh_build.cu) at most 62:
-// TLAS 62 + sentinel + root + BLAS 62 = 126.  Only touched entries cost cache lines.
+// Pending entries of the two-level walk: a BVH2 walk holds at most one entry per level.  PLOC trees are accepted up to 56
+// levels (rptx.cu: kPlocMaxDepth), host SAH trees are at most 36 deep (bvh_sah.hpp), the Karras LBVH over 30-bit Morton
+// codes + 32-bit index tie-break (bvh_build.cu) at most 62: TLAS 62 + sentinel + root + BLAS 62 = 126.  Only touched
+// entries cost cache lines.
 constexpr int kStackSize = 128;
 
 RPTX_D float f32_up(double x) { return __double2float_ru(x); }

@@ -223,14 +223,15 @@ def test_film_slab_is_recycled_and_pool_size_does_not_matter(monkeypatch):
 
 
 def test_sah_trees_equal_lbvh_trees(monkeypatch):
-    """Small meshes and the instance level get a host-built SAH tree, larger ones the GPU LBVH (RPTX_LBVH_ONLY forces
-    it everywhere); RPTX_BVH_BUILDER=ploc builds every tree on the GPU with the surface-area criterion (build_ploc).
+    """Object trees are built on the GPU with the surface-area criterion (PLOC, build_ploc); RPTX_LBVH_ONLY forces the Morton
+    LBVH everywhere, RPTX_BVH_BUILDER=host the binned-SAH trees from the host (round 1's default for up to 65 K items).
     The accelerator only orders the search: same hits, same batch, bit for bit."""
     monkeypatch.setenv("RPTX_PATH_MODE", "wavefront")
     for name in ("teapot", "fractal_teapots", "monomial_glass"):
         scene, cam, d = getattr(scenes, name)()
         means = []
-        for env in ({}, {"RPTX_LBVH_ONLY": "1"}, {"RPTX_BVH_BUILDER": "ploc"}, {"RPTX_BVH_BUILDER": "ploc", "RPTX_NO_SMALL_SCENE": "1"}):
+        for env in ({}, {"RPTX_LBVH_ONLY": "1"}, {"RPTX_BVH_BUILDER": "host"}, {"RPTX_BVH_BUILDER": "ploc", "RPTX_NO_SMALL_SCENE": "1"},
+                    {"RPTX_BVH_BUILDER": "ploc", "RPTX_PLOC_RADIUS": "3"}):
             for k in ("RPTX_LBVH_ONLY", "RPTX_BVH_BUILDER", "RPTX_NO_SMALL_SCENE"):
                 monkeypatch.delenv(k, raising=False)
             for k, v in env.items():
@@ -245,10 +246,10 @@ def test_sah_trees_equal_lbvh_trees(monkeypatch):
             monkeypatch.delenv(k, raising=False)
         for m in means[1:]:
             assert np.array_equal(means[0], m), name
-    # Cornell through the hierarchy (the small-scene walk off) with PLOC trees: polygons are one-leaf meshes under a PLOC TLAS
+    # Cornell through the hierarchy (the small-scene walk off): polygons are one-leaf meshes under a PLOC / host-SAH TLAS
     scene, cam, d = scenes.cornell()
     means = []
-    for env in ({"RPTX_NO_SMALL_SCENE": "1"}, {"RPTX_NO_SMALL_SCENE": "1", "RPTX_BVH_BUILDER": "ploc"}):
+    for env in ({"RPTX_NO_SMALL_SCENE": "1"}, {"RPTX_NO_SMALL_SCENE": "1", "RPTX_BVH_BUILDER": "host"}):
         for k, v in env.items():
             monkeypatch.setenv(k, v)
         f = scenes.make_renderer(scene, cam, d, width=64, height=48, num_samples=2, seed=5, max_bounces=3).begin()
