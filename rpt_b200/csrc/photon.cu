@@ -1092,7 +1092,7 @@ int rptx_photon_gather_trace(rptx_film* f, rptx_photon_map* m, uint32_t iteratio
     const SceneDev sc = rptx_host::scene_dev(f->scene);
     const MediumDev md = rptx_host::medium_dev(f->scene);
     CK(cudaEventRecord(f->ev0, st));
-    const bool warp_mode = m->kind == RPTX_PHOTON_MAP && kmax <= kWarpKnnMaxK && !std::getenv("RPTX_GATHER_PER_THREAD");
+    const bool warp_mode = kmax <= kWarpKnnMaxK && !std::getenv("RPTX_GATHER_PER_THREAD");
     if (warp_mode) {
         // one warp per slot: ~64 K slots keep every SM busy for several rounds
         ga.n_lanes = std::max<uint32_t>(1, std::min<uint32_t>(ga.n_lanes, std::max<uint32_t>(1, 65536u / ga.n_pixels)));

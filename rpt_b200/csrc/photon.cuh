@@ -424,6 +424,96 @@ struct GatherCounters {
     unsigned long long knn, visibility, candidates;
 };
 
+// ---- candidate tests of the beam estimators (volume_estimate, src/photon.rs:439-593), shared by the per-thread and the
+// warp-cooperative camera pass.  *_cull: conservative f32 rejection (true = cannot contribute); *_exact: the reference's f64 test
+// and contribution.
+struct VolumeQuery {
+    RayD ray;
+    bool hit;
+    double t_hit, extinction;
+    d3 mc;
+    float fox, foy, foz, fdx, fdy, fdz;  // unit direction (primary_ray normalises)
+};
+
+RPTX_D VolumeQuery make_volume_query(const MediumDev& md, const RayD& ray, bool hit, double t_hit) {
+    VolumeQuery q;
+    q.ray = ray; q.hit = hit; q.t_hit = t_hit;
+    q.extinction = md.extinction();
+    q.mc = md.color(mk3(0, 0, 0));
+    q.fox = (float)ray.o.x; q.foy = (float)ray.o.y; q.foz = (float)ray.o.z;
+    q.fdx = (float)ray.d.x; q.fdy = (float)ray.d.y; q.fdz = (float)ray.d.z;
+    return q;
+}
+
+// The sphere contributes only if its centre lies within `radius` of the ray's line.  perp^2 = |c - o|^2 - ((c - o).d)^2 in
+// f32 carries a relative error of a few 2^-23 of |c - o|^2; the margin is 16x that, and the exact f64 test decides everything
+// inside it.
+RPTX_D bool sphere_cull(const SphereMapDev& sm, const VolumeQuery& q, uint32_t i) {
+    const float lx = (float)sm.center[3 * (size_t)i] - q.fox, ly = (float)sm.center[3 * (size_t)i + 1] - q.foy,
+                lz = (float)sm.center[3 * (size_t)i + 2] - q.foz;
+    const float l2 = lx * lx + ly * ly + lz * lz;
+    const float s = lx * q.fdx + ly * q.fdy + lz * q.fdz;
+    const float rf = (float)sm.radius[i];
+    return l2 - s * s > rf * rf * 1.0001f + l2 * 4e-6f;
+}
+
+RPTX_D void sphere_exact(const SphereMapDev& sm, const MediumDev& md, const VolumeQuery& q, uint32_t i, d3* volume_color) {
+    const d3 c = mk3(sm.center[3 * (size_t)i], sm.center[3 * (size_t)i + 1], sm.center[3 * (size_t)i + 2]);
+    const d3 origin_to_center = c - q.ray.o;
+    if (q.hit && length(origin_to_center) > q.t_hit) return;
+    const double radius = sm.radius[i];
+    const double radius_squared = radius * radius;
+    const double disk_distance = dot(origin_to_center, q.ray.d);
+    const double dn = length((q.ray.o + disk_distance * q.ray.d) - c);
+    const double distance_squared = dn * dn;
+    if (disk_distance > 0.0 && distance_squared < radius_squared) {
+        const double weight = k2_kernel(distance_squared / radius_squared) / radius_squared;
+        const double tr = exp(-q.extinction * disk_distance);
+        const d3 ppow = mk3(sm.power[3 * (size_t)i], sm.power[3 * (size_t)i + 1], sm.power[3 * (size_t)i + 2]);
+        *volume_color = *volume_color + tr * cmul(ppow, q.mc) * md.phase * weight * 1.0;
+    }
+}
+
+// `dist` of the exact test is the distance between a point of the camera ray's line and a point of the beam's line, so it is
+// at least the distance between the two lines, |l . (d x b)| / |d x b|.  Beams whose line passes farther than the radius (with
+// a margin of 16x the f32 rounding of the triple product, relative to |l| |d x b|) contribute nothing; nearly parallel lines
+// and everything inside the margin go to the exact f64 test.
+RPTX_D bool beam_cull(const BeamMapDev& bm, const VolumeQuery& q, uint32_t i) {
+    const size_t i3 = 3 * (size_t)i;
+    const float bx = (float)bm.dirn[i3], by = (float)bm.dirn[i3 + 1], bz = (float)bm.dirn[i3 + 2];
+    const float nx = q.fdy * bz - q.fdz * by, ny = q.fdz * bx - q.fdx * bz, nz = q.fdx * by - q.fdy * bx;
+    const float n2 = nx * nx + ny * ny + nz * nz;
+    const float lx = (float)bm.start[i3] - q.fox, ly = (float)bm.start[i3 + 1] - q.foy, lz = (float)bm.start[i3 + 2] - q.foz;
+    const float trip = lx * nx + ly * ny + lz * nz;
+    const float l2 = lx * lx + ly * ly + lz * lz;
+    const float lim = (float)kBeamRadius * 1.0001f;
+    return n2 > 1e-6f && trip * trip > (lim * lim + l2 * 4e-6f) * n2;
+}
+
+RPTX_D void beam_exact(const BeamMapDev& bm, const MediumDev& md, const VolumeQuery& q, uint32_t i, d3* volume_color) {
+    const size_t i3 = 3 * (size_t)i;
+    const d3 bstart = mk3(bm.start[i3], bm.start[i3 + 1], bm.start[i3 + 2]);
+    const d3 bdir = mk3(bm.dirn[i3], bm.dirn[i3 + 1], bm.dirn[i3 + 2]);
+    const d3 l = bstart - q.ray.o;
+    const d3 u = normalize(cross(l, bdir));
+    const d3 n = normalize(cross(bdir, u));
+    const double t = dot(n, l) / dot(n, q.ray.d);
+    const d3 query_collision = q.ray.o + t * q.ray.d;
+    if (q.hit && t >= q.t_hit) return;
+    const double dd = dot(q.ray.d, bdir);
+    const double inv_sin_theta = 1.0 / sqrt(fmax(0.0, 1.0 - dd * dd));
+    const double beam_t = dot(bdir, query_collision - bstart);
+    const double beam_len = bm.len[i];
+    if (beam_t < 0.0 || beam_t > beam_len) return;
+    const d3 beam_collision = bstart + beam_t * bdir;
+    const double dist = length(query_collision - beam_collision);
+    if (dist >= kBeamRadius) return;
+    const d3 ppow = mk3(bm.power[i3], bm.power[i3 + 1], bm.power[i3 + 2]);
+    const d3 color = q.extinction * cmul(ppow, q.mc) * md.phase * inv_sin_theta * transmittance(md, t) * transmittance(md, beam_t) *
+                     k2_kernel(dist / kBeamRadius) / (2.0 * kBeamRadius);
+    *volume_color = *volume_color + color;
+}
+
 // surface_estimate, src/photon.rs:327-375
 template <int KMAX>
 RPTX_DN d3 surface_estimate(const SceneDev& sc, const PhotonMapDev& pm, const RayD& ray, d3 wo, double t_hit, d3 normal,
@@ -493,82 +583,22 @@ RPTX_DN d3 volume_estimate(const SceneDev& sc, const MediumDev& md, const Photon
         return surface_estimate<KMAX>(sc, pm, ray, wo, t_hit, normal, mat, ctr) * transmittance(md, t_hit) / (1.0 - d_cdf);
     }
     const Ray32 r32 = make_ray32(ray.o, ray.d);
-    const d3 mc = md.color(mk3(0, 0, 0));
+    const VolumeQuery vq = make_volume_query(md, ray, hit, t_hit);
     d3 volume_color = mk3(0, 0, 0);
     if (pm.kind == 1) {
         const SphereMapDev& sm = pm.spheres;
-        const float fox = (float)ray.o.x, foy = (float)ray.o.y, foz = (float)ray.o.z;
-        const float fdx = (float)ray.d.x, fdy = (float)ray.d.y, fdz = (float)ray.d.z;  // unit direction (primary_ray normalises)
         box_bvh_traverse(sm.bvh, r32, [&](uint32_t i) {
             ctr.candidates++;
-            const d3 c = mk3(sm.center[3 * (size_t)i], sm.center[3 * (size_t)i + 1], sm.center[3 * (size_t)i + 2]);
-            {
-                // conservative f32 cull of the disk test below: the sphere contributes only if the centre lies within
-                // `radius` of the ray's line.  perp^2 = |c - o|^2 - ((c - o).d)^2 in f32 carries a relative error of a few
-                // 2^-23 of |c - o|^2; the margin is 16x that, and the exact f64 test decides everything inside it.
-                const float lx = (float)c.x - fox, ly = (float)c.y - foy, lz = (float)c.z - foz;
-                const float l2 = lx * lx + ly * ly + lz * lz;
-                const float s = lx * fdx + ly * fdy + lz * fdz;
-                const float rf = (float)sm.radius[i];
-                if (l2 - s * s > rf * rf * 1.0001f + l2 * 4e-6f) return;
-            }
-            const d3 origin_to_center = c - ray.o;
-            if (hit && length(origin_to_center) > t_hit) return;
-            const double radius = sm.radius[i];
-            const double radius_squared = radius * radius;
-            const double disk_distance = dot(origin_to_center, ray.d);
-            const double dn = length((ray.o + disk_distance * ray.d) - c);
-            const double distance_squared = dn * dn;
-            if (disk_distance > 0.0 && distance_squared < radius_squared) {
-                const double weight = k2_kernel(distance_squared / radius_squared) / radius_squared;
-                const double tr = exp(-extinction * disk_distance);
-                const d3 ppow = mk3(sm.power[3 * (size_t)i], sm.power[3 * (size_t)i + 1], sm.power[3 * (size_t)i + 2]);
-                volume_color = volume_color + tr * cmul(ppow, mc) * md.phase * weight * 1.0;
-            }
+            if (sphere_cull(sm, vq, i)) return;
+            sphere_exact(sm, md, vq, i, &volume_color);
         });
         return volume_color;
     }
     const BeamMapDev& bm = pm.beams;
-    const float fox = (float)ray.o.x, foy = (float)ray.o.y, foz = (float)ray.o.z;
-    const float fdx = (float)ray.d.x, fdy = (float)ray.d.y, fdz = (float)ray.d.z;
     box_bvh_traverse(bm.bvh, r32, [&](uint32_t i) {
         ctr.candidates++;
-        const size_t i3 = 3 * (size_t)i;
-        const d3 bstart = mk3(bm.start[i3], bm.start[i3 + 1], bm.start[i3 + 2]);
-        const d3 bdir = mk3(bm.dirn[i3], bm.dirn[i3 + 1], bm.dirn[i3 + 2]);
-        {
-            // conservative f32 cull of the `dist >= radius` test below.  `dist` is the distance between a point of the camera
-            // ray's line and a point of the beam's line, so it is at least the distance between the two lines,
-            // |l . (d x b)| / |d x b|.  Beams whose line passes farther than the radius (with a margin of 16x the f32
-            // rounding of the triple product, relative to |l| |d x b|) contribute nothing; nearly parallel lines and
-            // everything inside the margin go to the exact f64 test.
-            const float bx = (float)bdir.x, by = (float)bdir.y, bz = (float)bdir.z;
-            const float nx = fdy * bz - fdz * by, ny = fdz * bx - fdx * bz, nz = fdx * by - fdy * bx;
-            const float n2 = nx * nx + ny * ny + nz * nz;
-            const float lx = (float)bstart.x - fox, ly = (float)bstart.y - foy, lz = (float)bstart.z - foz;
-            const float trip = lx * nx + ly * ny + lz * nz;
-            const float l2 = lx * lx + ly * ly + lz * lz;
-            const float lim = (float)kBeamRadius * 1.0001f;
-            if (n2 > 1e-6f && trip * trip > (lim * lim + l2 * 4e-6f) * n2) return;
-        }
-        const d3 l = bstart - ray.o;
-        const d3 u = normalize(cross(l, bdir));
-        const d3 n = normalize(cross(bdir, u));
-        const double t = dot(n, l) / dot(n, ray.d);
-        const d3 query_collision = ray.o + t * ray.d;
-        if (hit && t >= t_hit) return;
-        const double dd = dot(ray.d, bdir);
-        const double inv_sin_theta = 1.0 / sqrt(fmax(0.0, 1.0 - dd * dd));
-        const double beam_t = dot(bdir, query_collision - bstart);
-        const double beam_len = bm.len[i];
-        if (beam_t < 0.0 || beam_t > beam_len) return;
-        const d3 beam_collision = bstart + beam_t * bdir;
-        const double dist = length(query_collision - beam_collision);
-        if (dist >= kBeamRadius) return;
-        const d3 ppow = mk3(bm.power[i3], bm.power[i3 + 1], bm.power[i3 + 2]);
-        const d3 color = extinction * cmul(ppow, mc) * md.phase * inv_sin_theta * transmittance(md, t) * transmittance(md, beam_t) *
-                         k2_kernel(dist / kBeamRadius) / (2.0 * kBeamRadius);
-        volume_color = volume_color + color;
+        if (beam_cull(bm, vq, i)) return;
+        beam_exact(bm, md, vq, i, &volume_color);
     });
     return volume_color;
 }
@@ -615,6 +645,26 @@ struct WarpKnnSmem {
     uint32_t idx[kWarpCand];
     double stack_d[kKnnStack];
     uint32_t stack[kKnnStack];
+};
+
+// Beam estimators by a warp (warp_volume_boxes): the lanes share ONE camera ray and walk the sphere / beam BVH together.
+// The per-thread walk ran 6-9 of 32 lanes (ncu, profiles/r2_summary.md): neighbouring samples sit in different parts of
+// node walk / leaf loop / f32 cull / f64 test.  Here every stage is its own dense loop over a shared list:
+//   nodes:  a shared LIFO of node references; 32 are popped at a time, one per lane; inner nodes push the children the ray
+//           hits, leaves append their items to `cand`;
+//   cand:   items whose own box and f32 cull are still to be tested, 32 at a time; survivors go to `exact`;
+//   exact:  the reference's f64 test and contribution, 32 at a time; per-lane partial sums, added over the warp at the end.
+constexpr int kWarpBoxStack = 1536;   // node references (a pop of 32 pushes at most 64; near the top the walk pops one at a time)
+constexpr int kWarpBoxCand = 320;     // < 32 left over + 32 leaves x 8 items
+constexpr int kWarpBoxExact = 64;     // < 32 left over + 32 survivors
+struct WarpBoxSmem {
+    int stack[kWarpBoxStack];
+    uint32_t cand[kWarpBoxCand];
+    uint32_t exact[kWarpBoxExact];
+};
+union WarpGatherSmem {  // the kNN of the surface estimate and the box walk never overlap in time
+    WarpKnnSmem knn;
+    WarpBoxSmem box;
 };
 
 // ascending bitonic sort of the first n (power of two, <= kWarpCand) candidates by d2
@@ -797,6 +847,120 @@ RPTX_D d3 warp_estimate_point_point(const SceneDev& sc, const MediumDev& md, con
     return warp_surface_estimate(sc, pm, ray, wo, h.t, n, mat, sm, ctr) * transmittance(md, h.t) / (1.0 - d_cdf);
 }
 
+// volume_estimate for the beam-query maps (kind 1: photon spheres, kind 2: photon beams) by a warp.  Same candidates, same
+// tests and same contributions as the per-thread walk (BVH::traverse semantics: an item is a candidate when the ray hits its
+// own f32 box); only the order of the additions differs.  All lanes return the same colour.
+RPTX_D d3 warp_volume_boxes(const MediumDev& md, const PhotonMapDev& pm, const RayD& ray, bool hit, double t_hit, WarpBoxSmem& sm,
+                            GatherCounters& ctr) {
+    const uint32_t lane = threadIdx.x & 31u;
+    const unsigned lt = (1u << lane) - 1u;
+    const BoxBvhDev& b = pm.kind == 1 ? pm.spheres.bvh : pm.beams.bvh;
+    const VolumeQuery vq = make_volume_query(md, ray, hit, t_hit);
+    const Ray32 r = make_ray32(ray.o, ray.d);
+    d3 part = mk3(0, 0, 0);
+    if (b.n == 0) return part;
+    uint32_t top = 0, ncand = 0, nexact = 0;  // warp-uniform
+    bool untested_single = b.n == 1;          // a single-leaf root is returned untested (box_bvh_traverse)
+    if (lane == 0) sm.stack[0] = b.root_ref;
+    top = 1;
+    __syncwarp();
+    auto run_exact = [&](uint32_t n) {  // the last n entries of `exact`, one per lane
+        if (lane < n) {
+            const uint32_t i = sm.exact[nexact - n + lane];
+            if (pm.kind == 1) sphere_exact(pm.spheres, md, vq, i, &part);
+            else beam_exact(pm.beams, md, vq, i, &part);
+        }
+        nexact -= n;
+        __syncwarp();
+    };
+    auto run_cand = [&](uint32_t n) {  // the last n entries of `cand`: own box + f32 cull, survivors -> exact
+        bool keep = false;
+        uint32_t i = 0;
+        if (lane < n) {
+            i = sm.cand[ncand - n + lane];
+            const Aabb32 bx = b.boxes[i];
+            if (untested_single || ray32_hits(r, bx.mn, bx.mx)) {
+                ctr.candidates++;
+                keep = pm.kind == 1 ? !sphere_cull(pm.spheres, vq, i) : !beam_cull(pm.beams, vq, i);
+            }
+        }
+        ncand -= n;
+        const unsigned m = __ballot_sync(0xffffffffu, keep);
+        if (keep) sm.exact[nexact + __popc(m & lt)] = i;
+        nexact += __popc(m);
+        __syncwarp();
+        if (nexact >= 32u) run_exact(32u);
+    };
+    while (top > 0 || ncand > 0) {
+        if (ncand >= 32u || top == 0) { run_cand(ncand < 32u ? ncand : 32u); continue; }
+        // pop: 32 references, or one at a time near the top of the stack (a depth-first walk then adds at most one entry
+        // per level of the subtree it is in)
+        const uint32_t n = top + 128u > (uint32_t)kWarpBoxStack ? 1u : (top < 32u ? top : 32u);
+        top -= n;
+        int ref = 0;
+        bool have = lane < n;
+        if (have) ref = sm.stack[top + lane];
+        __syncwarp();
+        bool hl = false, hr = false;
+        int left = 0, right = 0;
+        uint32_t first = 0, count = 0;
+        if (have && ref >= 0) {
+            const float4* np = reinterpret_cast<const float4*>(b.nodes + ref);
+            const float4 a = __ldg(np), bb = __ldg(np + 1), c = __ldg(np + 2), d = __ldg(np + 3);
+            const float lmn[3] = {a.x, a.y, a.z}, lmx[3] = {bb.x, bb.y, bb.z}, rmn[3] = {c.x, c.y, c.z}, rmx[3] = {d.x, d.y, d.z};
+            hl = ray32_hits(r, lmn, lmx); hr = ray32_hits(r, rmn, rmx);
+            left = __float_as_int(a.w); right = __float_as_int(c.w);
+        } else if (have) {
+            const uint32_t code = (uint32_t)(~ref);
+            first = code >> 3; count = (code & 7u) + 1u;
+        }
+        // children: the right ones first, so that the left child of the last lane is on top (the per-thread walk's order)
+        const unsigned mr = __ballot_sync(0xffffffffu, hr);
+        if (hr) sm.stack[top + __popc(mr & lt)] = right;
+        top += __popc(mr);
+        const unsigned ml = __ballot_sync(0xffffffffu, hl);
+        if (hl) sm.stack[top + __popc(ml & lt)] = left;
+        top += __popc(ml);
+        // leaf items
+#pragma unroll 1
+        for (uint32_t k = 0; k < 8u; k++) {
+            const unsigned mk = __ballot_sync(0xffffffffu, count > k);
+            if (mk == 0) break;
+            if (count > k) sm.cand[ncand + __popc(mk & lt)] = first + k;
+            ncand += __popc(mk);
+        }
+        __syncwarp();
+    }
+    if (nexact) run_exact(nexact);
+    return warp_sum(part);
+}
+
+// estimate_indirect (src/photon.rs:596-627) by a warp, all three maps
+RPTX_D d3 warp_estimate_indirect(const SceneDev& sc, const MediumDev& md, const PhotonMapDev& pm, const RayD& ray, Rng& rng,
+                                 WarpGatherSmem& sm, GatherCounters& ctr) {
+    if (pm.kind == 0) return warp_estimate_point_point(sc, md, pm, ray, rng, sm.knn, ctr);
+    const d3 wo = -normalize(ray.d);
+    Hit h;
+    h.t = CUDART_INF;
+    closest_hit<kClosest>(sc, ray, kEpsilon, 0.0, h);
+    const bool medium = md.kind != 0;
+    const bool hit = h.inst != kNoHit;
+    Material mat;
+    mat.kind = 0; mat.albedo[0] = mat.albedo[1] = mat.albedo[2] = 0.0; mat.emittance = 0.0; mat.shininess = 0.0; mat.ior = 1.0;
+    d3 n = mk3(0, 0, 0);
+    if (hit) {
+        uint32_t prim, inst;
+        n = hit_normal(sc, ray, h, &prim, &inst);
+        mat = sc.materials[h.obj];
+    }
+    if (!medium) return hit ? warp_surface_estimate(sc, pm, ray, wo, h.t, n, mat, sm.knn, ctr) : env_color(sc, ray.d);
+    const d3 volume_color = warp_volume_boxes(md, pm, ray, hit, hit ? h.t : CUDART_INF, sm.box, ctr);
+    if (!hit) return volume_color;
+    __syncwarp();
+    const d3 surface_color = warp_surface_estimate(sc, pm, ray, wo, h.t, n, mat, sm.knn, ctr) * transmittance(md, h.t);
+    return surface_color + volume_color;
+}
+
 struct GatherArgs {
     Camera cam;
     BatchParams bp;
@@ -841,12 +1005,12 @@ __global__ void __launch_bounds__(128) k_photon_gather(const __grid_constant__ S
     }
 }
 
-// Camera pass for the point-point map: one warp per (pixel, lane) slot walks that slot's samples.
+// Camera pass by warps (all three maps): one warp per (pixel, lane) slot walks that slot's samples.
 __global__ void __launch_bounds__(128, RPTX_OCC_GATHER) k_photon_gather_warp(const __grid_constant__ SceneDev sc, const MediumDev md,
                                                             const __grid_constant__ PhotonMapDev pm, const __grid_constant__ GatherArgs ga,
                                                             unsigned long long* __restrict__ stats) {
-    __shared__ WarpKnnSmem smem[4];
-    WarpKnnSmem& sm = smem[threadIdx.x >> 5];
+    __shared__ WarpGatherSmem smem[4];
+    WarpGatherSmem& sm = smem[threadIdx.x >> 5];
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t slot = blockIdx.x * 4 + (threadIdx.x >> 5);
     GatherCounters ctr = {0, 0, 0};
@@ -860,7 +1024,7 @@ __global__ void __launch_bounds__(128, RPTX_OCC_GATHER) k_photon_gather_warp(con
             Rng rng = Rng::make(ga.bp.seed, kDomainGather, pixel, s);
             RayD ray;
             primary_ray(ga.cam, ga.bp.width, ga.bp.height, x, y, rng, &ray.o, &ray.d);
-            sum = sum + warp_estimate_point_point(sc, md, pm, ray, rng, sm, ctr);
+            sum = sum + warp_estimate_indirect(sc, md, pm, ray, rng, sm, ctr);
             if (lane == 0) my_samples++;
             __syncwarp();
         }
@@ -870,10 +1034,13 @@ __global__ void __launch_bounds__(128, RPTX_OCC_GATHER) k_photon_gather_warp(con
     const unsigned long long a = __reduce_add_sync(0xffffffffu, (unsigned)my_samples);
     const unsigned long long b = __reduce_add_sync(0xffffffffu, (unsigned)ctr.knn);
     const unsigned long long c = __reduce_add_sync(0xffffffffu, (unsigned)ctr.visibility);
+    unsigned long long d = ctr.candidates;  // may pass 2^32 per warp at 1e8 photons
+    for (int o = 16; o > 0; o >>= 1) d += __shfl_down_sync(0xffffffffu, d, o);
     if (lane == 0) {
         if (a) { atomicAdd(&stats[0], a); atomicAdd(&stats[1], a); }
         if (b) atomicAdd(&stats[5], b);
         if (c) atomicAdd(&stats[6], c);
+        if (d) atomicAdd(&stats[7], d);
     }
 }
 

@@ -188,21 +188,50 @@ def test_gather_same_map_same_seed(variant):
     assert st["path_samples"] == 32 * 32 * 3
 
 
-def test_gather_warp_and_per_thread_kernels_agree(monkeypatch):
-    """The point-point camera pass has a warp-cooperative kernel (default, k <= 128) and the
-    per-thread one (larger k, and the beam kinds): same kNN sets, different summation order."""
-    scene, cam, r, osc = _setup("photonphoton", w=24, h=24, spp=3)
-    ph = r.emit_photons(30000, 0)
-    gm = r.build_photon_map(ph, 0)
-    means = []
+@pytest.mark.parametrize("kind", [0, 1, 2])
+def test_gather_warp_and_per_thread_kernels_agree(kind, monkeypatch):
+    """The camera pass has a warp-cooperative kernel (default for k <= 128: shared kNN for the point estimates, a shared
+    walk of the sphere / beam BVH with dense candidate lists for the beam estimates) and the per-thread one (larger k):
+    same kNN sets, same candidates (the counter is equal), same contributions, different summation order."""
+    variant = ["photonphoton", "beamphoton", "beambeam"][kind]
+    scene, cam, r, osc = _setup(variant, w=24, h=24, spp=3)
+    ph = r.emit_photons(30000, kind)
+    gm = r.build_photon_map(ph, kind)
+    means, cands, queries = [], [], []
     for per_thread in (False, True):
         if per_thread:
             monkeypatch.setenv("RPTX_GATHER_PER_THREAD", "1")
         f = r.begin_gather()
         f.gather(gm, 3); f.sample_commit(3)
         means.append(f.mean())
-        assert f.stats()["gather_queries"] == 24 * 24 * 3
+        st = f.stats()
+        if kind == 0:
+            assert st["gather_queries"] == 24 * 24 * 3  # one kNN per sample: at the collision or at the surface
+        queries.append(st["gather_queries"])            # beam kinds: one per camera ray that hits a surface
+        cands.append(st.get("gather_candidates"))
+    assert queries[0] == queries[1] > 0
     assert np.allclose(means[0], means[1], rtol=1e-11, atol=1e-300)
+    if cands[0] is not None:
+        assert cands[0] == cands[1]
+        assert kind == 0 or cands[0] > 0
+    # a one-item BVH (returned untested by BVH::traverse) and an empty one
+    for nvol in (1, 0):
+        rows_s, rows_v = ph.rows(0), ph.rows(1)[:nvol]
+        pl = PhotonList.empty(r.device_scene().ctx)
+        pl.append_host(0, rows_s); pl.append_host(1, rows_v)
+        small = r.build_photon_map(pl, kind)
+        out = []
+        for per_thread in (False, True):
+            if per_thread:
+                monkeypatch.setenv("RPTX_GATHER_PER_THREAD", "1")
+            else:
+                monkeypatch.delenv("RPTX_GATHER_PER_THREAD", raising=False)
+            f = r.begin_gather()
+            f.gather(small, 2); f.sample_commit(2)
+            out.append(f.mean())
+        monkeypatch.delenv("RPTX_GATHER_PER_THREAD", raising=False)
+        # (an empty volume map makes the point-point estimate 0/0 on both paths, like the reference's division)
+        assert np.allclose(out[0], out[1], rtol=1e-11, atol=1e-300, equal_nan=True), nvol
 
 
 def test_gather_shards_sum_to_whole():
