@@ -263,6 +263,10 @@ __device__ __forceinline__ float box_area(const PrimBox& b) {
     return dx * dy + dy * dz + dz * dx;
 }
 
+__global__ void k_iota(uint32_t* __restrict__ perm, uint32_t n) {
+    for (uint32_t i = threadIdx.x; i < n; i += blockDim.x) perm[i] = i;
+}
+
 __global__ void k_ploc_leaves(const PrimBox* __restrict__ boxes, const uint64_t* __restrict__ keys, uint32_t n, PlocNode* __restrict__ nodes,
                               int* __restrict__ cluster) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -365,6 +369,12 @@ __global__ void k_ploc_emit(const PlocNode* __restrict__ nodes, const int* __res
 int build_ploc(const PrimBox* d_boxes, uint32_t n, float pad, int leaf_max, const double cmin[3], const double cmax[3], BvhNode* d_nodes,
                uint32_t* d_perm, int* root_ref, int max_depth, cudaStream_t stream, uint64_t* launches) {
     if (n == 0) { *root_ref = 0; return 0; }
+    if (n <= (uint32_t)leaf_max) {  // the whole mesh is one leaf (a polygon of the Cornell box): no tree, identity order
+        k_iota<<<1, 32, 0, stream>>>(d_perm, n);
+        (*launches)++;
+        *root_ref = make_leaf_ref(0u, n);
+        return (int)cudaGetLastError();
+    }
     cudaError_t e = cudaSuccess;
     uint64_t *keys_in = nullptr, *keys_out = nullptr;
     PlocNode* nodes = nullptr;

@@ -220,6 +220,52 @@ __global__ void k_beam_gather(const double* __restrict__ start, const double* __
     obox[i] = boxes[s];
 }
 
+// ---- beam segments (BeamSegDev, photon.cuh) ----
+__global__ void k_seg_count(const double* __restrict__ len, uint32_t n, uint32_t* __restrict__ count) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const double l = len[i];
+    uint32_t k = l > 0.0 && l < 1e300 ? (uint32_t)fmin(ceil(l / kBeamSegLen), (double)kBeamMaxSeg) : 1u;  // NaN / inf lengths: one piece
+    count[i] = k < 1u ? 1u : k;
+}
+
+// piece k of K of beam i: the box of the points within the radius (plus a margin for the rounding of floor(beam_t K / len)) of
+// the axis between len k / K and len (k + 1) / K, rounded outward to f32
+__global__ void k_seg_make(const double* __restrict__ start, const double* __restrict__ dirn, const double* __restrict__ len,
+                           const uint32_t* __restrict__ offset, const uint32_t* __restrict__ count, uint32_t n, Aabb32* __restrict__ boxes,
+                           uint32_t* __restrict__ beam, uint16_t* __restrict__ kk, uint16_t* __restrict__ KK) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t K = count[i], o = offset[i];
+    const d3 a = mk3(start[3 * (size_t)i], start[3 * (size_t)i + 1], start[3 * (size_t)i + 2]);
+    const d3 d = mk3(dirn[3 * (size_t)i], dirn[3 * (size_t)i + 1], dirn[3 * (size_t)i + 2]);
+    const double l = len[i];
+    const double m = kBeamRadius * 1.0001 + 1e-9 * (fabs(a.x) + fabs(a.y) + fabs(a.z) + fabs(l));
+    for (uint32_t k = 0; k < K; k++) {
+        const d3 p = a + (l * (double)k / (double)K) * d, q = a + (l * (double)(k + 1) / (double)K) * d;
+        Aabb32 b;
+        b.mn[0] = __double2float_rd(fmin(p.x, q.x) - m); b.mx[0] = __double2float_ru(fmax(p.x, q.x) + m);
+        b.mn[1] = __double2float_rd(fmin(p.y, q.y) - m); b.mx[1] = __double2float_ru(fmax(p.y, q.y) + m);
+        b.mn[2] = __double2float_rd(fmin(p.z, q.z) - m); b.mx[2] = __double2float_ru(fmax(p.z, q.z) + m);
+        if (K == 1u && !(l > 0.0 && l < 1e300)) {  // a degenerate beam keeps an unbounded piece: its own box decides
+            for (int c = 0; c < 3; c++) { b.mn[c] = -3.0e38f; b.mx[c] = 3.0e38f; }
+        }
+        boxes[o + k] = b;
+        beam[o + k] = i;
+        kk[o + k] = (uint16_t)k;
+        KK[o + k] = (uint16_t)K;
+    }
+}
+
+__global__ void k_seg_gather(const Aabb32* __restrict__ boxes, const uint32_t* __restrict__ beam, const uint16_t* __restrict__ kk,
+                             const uint16_t* __restrict__ KK, const uint32_t* __restrict__ perm, uint32_t n, Aabb32* __restrict__ obox,
+                             uint32_t* __restrict__ obeam, uint16_t* __restrict__ okk, uint16_t* __restrict__ oKK) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t s = perm[i];
+    obox[i] = boxes[s]; obeam[i] = beam[s]; okk[i] = kk[s]; oKK[i] = KK[s];
+}
+
 // per-block bounds of finite f32 boxes (Morton normalisation of the box BVH)
 __global__ void __launch_bounds__(256) k_box_bounds(const Aabb32* __restrict__ boxes, uint32_t n, double* __restrict__ out) {
     double mn[3] = {CUDART_INF, CUDART_INF, CUDART_INF}, mx[3] = {-CUDART_INF, -CUDART_INF, -CUDART_INF};
@@ -686,6 +732,7 @@ struct rptx_photon_map {
     int kind = 0;
     PointMapHost surface, volume;
     BoxBvhHost bvh;
+    BoxBvhHost seg_bvh;  // over the beam segments (BeamSegDev)
     SphereMapDev spheres = {};
     BeamMapDev beams = {};
     std::vector<void*> owned;
@@ -893,7 +940,8 @@ int rptx_photons_stats(const rptx_photons* p, uint64_t* emitted, uint64_t* rays,
 void rptx_photon_map_destroy(rptx_photon_map* m) {
     if (!m) return;
     cudaSetDevice(m->ctx->device);
-    free_owned(m->ctx, m->surface.owned); free_owned(m->ctx, m->volume.owned); free_owned(m->ctx, m->bvh.owned); free_owned(m->ctx, m->owned);
+    free_owned(m->ctx, m->surface.owned); free_owned(m->ctx, m->volume.owned); free_owned(m->ctx, m->bvh.owned); free_owned(m->ctx, m->seg_bvh.owned);
+    free_owned(m->ctx, m->owned);
     delete m;
 }
 
@@ -1027,6 +1075,40 @@ static int photon_map_build_impl(rptx_ctx* ctx, rptx_scene* scene, rptx_photons*
             m->bvh.dev.boxes = obox;
             m->beams.bvh = m->bvh.dev;
             m->beams.start = ostart; m->beams.dirn = odirn; m->beams.len = olen; m->beams.power = opower;
+            m->beams.seg = BeamSegDev{};
+            if (nv && !std::getenv("RPTX_NO_BEAM_SEGMENTS")) {
+                // the segments of the warp camera pass (BeamSegDev): count, offsets, boxes, their own BVH, leaf order
+                uint32_t *cnt = nullptr, *off = nullptr, *sbeam = nullptr, *obeam = nullptr, *perm2 = nullptr;
+                uint16_t *sk = nullptr, *sK = nullptr, *ok = nullptr, *oK = nullptr;
+                Aabb32 *sbox = nullptr, *osbox = nullptr;
+                std::vector<void*> tmp;
+                auto fin = [&](int rc2) { free_owned(ctx, tmp); rptx_free_async(perm2, st); return rc2; };
+                CK(dev_alloc(ctx, &cnt, nv, &tmp)); CK(dev_alloc(ctx, &off, nv, &tmp));
+                k_seg_count<<<grid_for(nv, 256), 256, 0, st>>>(olen, nv, cnt);
+                size_t scan_bytes = 0;
+                CK(cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, cnt, off, (int)nv, st));
+                void* scan_tmp = nullptr;
+                CK(dev_alloc(ctx, (char**)&scan_tmp, scan_bytes, &tmp));
+                CK(cub::DeviceScan::ExclusiveSum(scan_tmp, scan_bytes, cnt, off, (int)nv, st));
+                uint32_t last[2] = {0, 0};
+                CK(cudaMemcpyAsync(&last[0], off + (nv - 1), sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+                CK(cudaMemcpyAsync(&last[1], cnt + (nv - 1), sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+                CK(cudaStreamSynchronize(st));
+                const uint32_t ns = last[0] + last[1];
+                CK(dev_alloc(ctx, &sbox, ns, &tmp)); CK(dev_alloc(ctx, &sbeam, ns, &tmp)); CK(dev_alloc(ctx, &sk, ns, &tmp)); CK(dev_alloc(ctx, &sK, ns, &tmp));
+                k_seg_make<<<grid_for(nv, 128), 128, 0, st>>>(ostart, odirn, olen, off, cnt, nv, sbox, sbeam, sk, sK);
+                ctx->launches += 4;
+                if (int r = build_box_bvh(ctx, sbox, ns, &m->seg_bvh, &perm2)) return fin(r);
+                CK(dev_alloc(ctx, &osbox, ns, &m->owned)); CK(dev_alloc(ctx, &obeam, ns, &m->owned));
+                CK(dev_alloc(ctx, &ok, ns, &m->owned)); CK(dev_alloc(ctx, &oK, ns, &m->owned));
+                k_seg_gather<<<grid_for(ns, 256), 256, 0, st>>>(sbox, sbeam, sk, sK, perm2, ns, osbox, obeam, ok, oK);
+                ctx->launches++;
+                CK(cudaStreamSynchronize(st));
+                m->seg_bvh.dev.boxes = osbox;
+                m->beams.seg.bvh = m->seg_bvh.dev;
+                m->beams.seg.beam = obeam; m->beams.seg.k = ok; m->beams.seg.K = oK;
+                fin(0);
+            }
         }
         CK(cudaGetLastError());
         CK(cudaStreamSynchronize(st));

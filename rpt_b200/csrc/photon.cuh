@@ -333,6 +333,9 @@ RPTX_D Ray32 make_ray32(d3 origin, d3 dir) {
     }
     return r;
 }
+// LINE = true: the whole line through the ray, both directions (beam segments: the reference's beam test has no t > 0
+// condition, a closest approach behind the camera counts as long as the ray hits the beam's own box in front of it)
+template <bool LINE = false>
 RPTX_D bool ray32_hits(const Ray32& r, const float* mn, const float* mx) {
     float ray_min = ((r.sign[0] ? mx[0] : mn[0]) - r.o[0]) * r.inv[0];
     float ray_max = ((r.sign[0] ? mn[0] : mx[0]) - r.o[0]) * r.inv[0];
@@ -345,7 +348,7 @@ RPTX_D bool ray32_hits(const Ray32& r, const float* mn, const float* mx) {
     const float z_max = ((r.sign[2] ? mn[2] : mx[2]) - r.o[2]) * r.inv[2];
     if (ray_min > z_max || z_min > ray_max) return false;
     if (z_max < ray_max) ray_max = z_max;
-    return ray_max > 0.0f;
+    return LINE || ray_max > 0.0f;
 }
 
 struct BoxBvhDev {
@@ -364,7 +367,24 @@ struct SphereMapDev {
     const double* power;   // [n][3]
 };
 // PhotonBeam (src/photon.rs:46-59), leaf order
+// Culling structure of the warp camera pass over photon beams.  A beam's own box (the reference's, src/photon.rs:76-105) is
+// the box of a long thin cylinder: at 1e8 photons a camera ray hits the boxes of 10 000 of the 2e5 beams and 97 % of them
+// pass nowhere near the beam.  The beams are therefore cut into segments of ~kBeamSegLen, each with the box of ITS piece of the
+// cylinder, under a second BVH.  A segment stands for the contributions whose closest-approach parameter beam_t falls into its
+// piece - floor(beam_t * K / len) == k, a partition of [0, len], so every contribution is counted exactly once - and the ray
+// that makes such a contribution passes within the radius of that piece, i.e. through the segment's box.  The beam's own box
+// is still tested (the reference never sees a beam whose box the ray misses); the result is the per-beam walk's.
+constexpr double kBeamSegLen = 12.0;
+constexpr uint32_t kBeamMaxSeg = 64;
+struct BeamSegDev {
+    BoxBvhDev bvh;         // over the segments; bvh.boxes = segment boxes, leaf order
+    const uint32_t* beam;  // [n] beam (BeamMapDev index) of the segment
+    const uint16_t* k;     // [n] piece of the beam ...
+    const uint16_t* K;     // [n] ... of so many
+};
+
 struct BeamMapDev {
+    BeamSegDev seg;        // seg.bvh.n == 0: not built
     BoxBvhDev bvh;
     const double* start;  // [n][3]
     const double* dirn;   // [n][3] normalised start -> end
@@ -474,6 +494,13 @@ RPTX_D void sphere_exact(const SphereMapDev& sm, const MediumDev& md, const Volu
     }
 }
 
+// piece of [0, len] that beam_t falls into, of K equal pieces (both ends of [0, len] included)
+RPTX_HD uint32_t beam_segment_of(double beam_t, double len, uint32_t K) {
+    const double x = beam_t * (double)K / len;
+    const uint32_t k = x > 0.0 ? (uint32_t)x : 0u;  // NaN (len == 0) -> 0
+    return k < K ? k : K - 1u;
+}
+
 // `dist` of the exact test is the distance between a point of the camera ray's line and a point of the beam's line, so it is
 // at least the distance between the two lines, |l . (d x b)| / |d x b|.  Beams whose line passes farther than the radius (with
 // a margin of 16x the f32 rounding of the triple product, relative to |l| |d x b|) contribute nothing; nearly parallel lines
@@ -490,7 +517,9 @@ RPTX_D bool beam_cull(const BeamMapDev& bm, const VolumeQuery& q, uint32_t i) {
     return n2 > 1e-6f && trip * trip > (lim * lim + l2 * 4e-6f) * n2;
 }
 
-RPTX_D void beam_exact(const BeamMapDev& bm, const MediumDev& md, const VolumeQuery& q, uint32_t i, d3* volume_color) {
+// seg_K > 1: only the contribution whose beam_t lies in piece seg_k of seg_K (BeamSegDev)
+RPTX_D void beam_exact(const BeamMapDev& bm, const MediumDev& md, const VolumeQuery& q, uint32_t i, d3* volume_color, uint32_t seg_k = 0,
+                       uint32_t seg_K = 1) {
     const size_t i3 = 3 * (size_t)i;
     const d3 bstart = mk3(bm.start[i3], bm.start[i3 + 1], bm.start[i3 + 2]);
     const d3 bdir = mk3(bm.dirn[i3], bm.dirn[i3 + 1], bm.dirn[i3 + 2]);
@@ -505,6 +534,7 @@ RPTX_D void beam_exact(const BeamMapDev& bm, const MediumDev& md, const VolumeQu
     const double beam_t = dot(bdir, query_collision - bstart);
     const double beam_len = bm.len[i];
     if (beam_t < 0.0 || beam_t > beam_len) return;
+    if (seg_K > 1u && beam_segment_of(beam_t, beam_len, seg_K) != seg_k) return;
     const d3 beam_collision = bstart + beam_t * bdir;
     const double dist = length(query_collision - beam_collision);
     if (dist >= kBeamRadius) return;
@@ -854,13 +884,15 @@ RPTX_D d3 warp_volume_boxes(const MediumDev& md, const PhotonMapDev& pm, const R
                             GatherCounters& ctr) {
     const uint32_t lane = threadIdx.x & 31u;
     const unsigned lt = (1u << lane) - 1u;
-    const BoxBvhDev& b = pm.kind == 1 ? pm.spheres.bvh : pm.beams.bvh;
+    const bool segs = pm.kind == 2 && pm.beams.seg.bvh.n != 0;  // beams: walk the segments (BeamSegDev)
+    const BoxBvhDev& b = pm.kind == 1 ? pm.spheres.bvh : (segs ? pm.beams.seg.bvh : pm.beams.bvh);
     const VolumeQuery vq = make_volume_query(md, ray, hit, t_hit);
     const Ray32 r = make_ray32(ray.o, ray.d);
     d3 part = mk3(0, 0, 0);
     if (b.n == 0) return part;
     uint32_t top = 0, ncand = 0, nexact = 0;  // warp-uniform
-    bool untested_single = b.n == 1;          // a single-leaf root is returned untested (box_bvh_traverse)
+    // a one-item BVH is returned untested (box_bvh_traverse); with segments that is the one BEAM's own box
+    const bool untested_single = segs ? pm.beams.bvh.n == 1 : b.n == 1;
     if (lane == 0) sm.stack[0] = b.root_ref;
     top = 1;
     __syncwarp();
@@ -868,6 +900,7 @@ RPTX_D d3 warp_volume_boxes(const MediumDev& md, const PhotonMapDev& pm, const R
         if (lane < n) {
             const uint32_t i = sm.exact[nexact - n + lane];
             if (pm.kind == 1) sphere_exact(pm.spheres, md, vq, i, &part);
+            else if (segs) beam_exact(pm.beams, md, vq, pm.beams.seg.beam[i], &part, pm.beams.seg.k[i], pm.beams.seg.K[i]);
             else beam_exact(pm.beams, md, vq, i, &part);
         }
         nexact -= n;
@@ -879,7 +912,17 @@ RPTX_D d3 warp_volume_boxes(const MediumDev& md, const PhotonMapDev& pm, const R
         if (lane < n) {
             i = sm.cand[ncand - n + lane];
             const Aabb32 bx = b.boxes[i];
-            if (untested_single || ray32_hits(r, bx.mn, bx.mx)) {
+            if (segs) {
+                // the segment's box prunes; the beam's own box is the reference's candidate test
+                if (ray32_hits<true>(r, bx.mn, bx.mx)) {
+                    const uint32_t beam = pm.beams.seg.beam[i];
+                    const Aabb32 own = pm.beams.bvh.boxes[beam];
+                    if (untested_single || ray32_hits(r, own.mn, own.mx)) {
+                        ctr.candidates++;
+                        keep = !beam_cull(pm.beams, vq, beam);
+                    }
+                }
+            } else if (untested_single || ray32_hits(r, bx.mn, bx.mx)) {
                 ctr.candidates++;
                 keep = pm.kind == 1 ? !sphere_cull(pm.spheres, vq, i) : !beam_cull(pm.beams, vq, i);
             }
@@ -908,7 +951,8 @@ RPTX_D d3 warp_volume_boxes(const MediumDev& md, const PhotonMapDev& pm, const R
             const float4* np = reinterpret_cast<const float4*>(b.nodes + ref);
             const float4 a = __ldg(np), bb = __ldg(np + 1), c = __ldg(np + 2), d = __ldg(np + 3);
             const float lmn[3] = {a.x, a.y, a.z}, lmx[3] = {bb.x, bb.y, bb.z}, rmn[3] = {c.x, c.y, c.z}, rmx[3] = {d.x, d.y, d.z};
-            hl = ray32_hits(r, lmn, lmx); hr = ray32_hits(r, rmn, rmx);
+            hl = segs ? ray32_hits<true>(r, lmn, lmx) : ray32_hits(r, lmn, lmx);
+            hr = segs ? ray32_hits<true>(r, rmn, rmx) : ray32_hits(r, rmn, rmx);
             left = __float_as_int(a.w); right = __float_as_int(c.w);
         } else if (have) {
             const uint32_t code = (uint32_t)(~ref);
