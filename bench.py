@@ -45,7 +45,7 @@ EXAMPLE = {
     "beambeam": "examples/volumetric_beambeam_lampshade.rs",
 }
 # the other BASELINE configs measured beside the headline at N = 1: (workload, steps, warmup)
-EXTRA = [("cornell", 10, 3), ("fractal_teapots", 3, 3), ("fractal_teapots_mb5", 3, 3), ("photonphoton", 2, 1), ("beambeam", 2, 1)]
+EXTRA = [("cornell", 10, 3), ("fractal_teapots", 3, 3), ("fractal_teapots_mb5", 3, 3), ("photonphoton", 2, 2), ("beambeam", 2, 2)]
 
 _OVERRIDES = {}
 
@@ -485,6 +485,23 @@ def run_photons(box, name, steps, warmup, scaling, cpu_seconds, photons):
         alg = PHOTON_ROW_BYTES * (ns + nv) / world
         kernel = "k_photon_trace"
     ach = alg / max(dom_s, 1e-12) / 1e9
+    roof = dict(bound="hbm", kernel=kernel, achieved=ach, peak=peak, unit="GB/s", frac=ach / peak, traffic=None, peak_source=which,
+                algorithmic_bytes_per_launch=alg, note=f"dominant pass of the step: {dom} ({1e3 * dom_s:.1f} ms of {1e3 * step:.1f})")
+    # the walk and the camera pass are issue-bound traversal kernels: with the ncu constants of this build at this size
+    # (tools/issue_probe.py <workload> --photons N -> profiles/r2_issue.json "<workload>:photon") report the issue roofline too
+    ic = (issue_constants(name + ":photon") or {})
+    kc = ic.get("kernels", {}).get({"gather": "k_photon_gather", "emit": "k_photon_trace"}.get(dom, ""))
+    if kc and abs(ic.get("photons", 0) - n_total) <= 0.01 * n_total:
+        ipeak, isrc = issue_peak()
+        units = (w * h * spp if dom == "gather" else n_total) / world
+        iach = kc["warp_inst_per_unit"] * units * (kc["live_lanes"] / 32.0) / max(dom_s, 1e-12)
+        roof["hbm"] = dict(achieved=ach, peak=peak, unit="GB/s", frac=ach / peak, algorithmic_bytes_per_launch=alg)
+        roof["issue"] = dict(achieved=iach / 1e9, peak=ipeak / 1e9, unit="Gwarp-inst/s", frac=iach / ipeak, peak_source=isrc,
+                             warp_inst_per_unit=kc["warp_inst_per_unit"], live_lanes=kc["live_lanes"],
+                             unit_of_work="gather sample" if dom == "gather" else "emitted photon", capture=ic.get("capture"))
+        roof["traffic"] = kc["dram_bytes_per_unit"] * units
+        if iach / ipeak > ach / peak:
+            roof.update(bound="issue", achieved=iach / 1e9, peak=ipeak / 1e9, unit="Gwarp-inst/s", frac=iach / ipeak, peak_source=isrc)
     cpu = None
     if world == 1 and cpu_seconds > 0:
         cpu = cpu_photons(scene, cam, r.params(), kind, cpu_seconds)
@@ -497,9 +514,7 @@ def run_photons(box, name, steps, warmup, scaling, cpu_seconds, photons):
                 passes_ms={k: v / steps for k, v in acc.items()},
                 photons=dict(surface=ns, volume=nv, bvh_items=mst["bvh_items"], gather_samples=w * h * spp,
                              knn_queries=fst["gather_queries"], visibility_rays=fst["gather_visibility"], candidates=fst["gather_candidates"]),
-                roofline=dict(bound="hbm", kernel=kernel, achieved=ach, peak=peak, unit="GB/s", frac=ach / peak, traffic=None, peak_source=which,
-                              algorithmic_bytes_per_launch=alg, note=f"dominant pass of the step: {dom} ({1e3 * dom_s:.1f} ms of {1e3 * step:.1f})"),
-                cpu_baseline=cpu, rmse=rmse_probe(box, name))
+                roofline=roof, cpu_baseline=cpu, rmse=rmse_probe(box, name))
     if cpu:
         line["x_cpu"] = dict(value=line["value"] / cpu["value"], e2e=line["e2e"]["value"] / cpu["value"], note=f"same-run host CPU port, {cpu['cores']} threads")
     return line
@@ -579,6 +594,7 @@ def main():
         extras = []
         for name, st, wu in EXTRA:
             try:
+                box.ctx.trim()  # each config starts from an empty device: the previous one's cached GBs are not its problem
                 x = run_one(box, name, st, wu, args)
             except Exception as e:  # an extra config must not take the headline down
                 x = dict(config=dict(workload=name), error=repr(e))

@@ -154,6 +154,9 @@ int         rptx_abi_version(void);
 int         rptx_ctx_create(int device_id, rptx_ctx** out);
 void        rptx_ctx_destroy(rptx_ctx* ctx);
 const char* rptx_last_error(const rptx_ctx* ctx);
+/* Release the device memory the context keeps cached between calls (stream-ordered pool blocks, the spare film slab).  No
+ * counterpart in the reference (its allocator is the process heap); for hosts that switch workloads. */
+int         rptx_ctx_trim(rptx_ctx* ctx);
 
 /* ---- multi-GPU: one process (or host thread) per GPU, one context each ------------------------------
  * The reference's two exchange points are `add_samples` after the rows' collect() (src/renderer.rs:169-170)

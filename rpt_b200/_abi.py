@@ -127,6 +127,7 @@ PROTOTYPES = {
     "rptx_ctx_create": (C.c_int, [C.c_int, C.POINTER(P)]),
     "rptx_ctx_destroy": (None, [P]),
     "rptx_last_error": (C.c_char_p, [P]),
+    "rptx_ctx_trim": (C.c_int, [P]),
     "rptx_comm_unique_id": (C.c_int, [P]),
     "rptx_comm_init": (C.c_int, [P, P, C.c_int, C.c_int]),
     "rptx_comm_info": (C.c_int, [P, C.POINTER(C.c_int), C.POINTER(C.c_int)]),

@@ -384,6 +384,20 @@ void rptx_ctx_destroy(rptx_ctx* ctx) {
 
 const char* rptx_last_error(const rptx_ctx* ctx) { return ctx ? ctx->err.c_str() : "null context"; }
 
+// Hands the memory this context keeps cached (the stream-ordered pool never trims on its own, and a destroyed film leaves its
+// slab for the next one) back to the device.  For hosts that switch between workloads with different footprints: a 1e8-photon
+// render caches ~45 GB, and the next workload's first allocations would otherwise have to squeeze them out one by one.
+int rptx_ctx_trim(rptx_ctx* ctx) {
+    if (!ctx) return 1;
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (ctx->spare_arena) { cudaFree(ctx->spare_arena); ctx->spare_arena = nullptr; ctx->spare_arena_bytes = 0; }
+    cudaMemPool_t pool;
+    CK(cudaDeviceGetDefaultMemPool(&pool, ctx->device));
+    CK(cudaMemPoolTrimTo(pool, 0));
+    return 0;
+}
+
 int rptx_scene_create(rptx_ctx* ctx, rptx_scene** out) {
     if (!ctx || !out) return 1;
     rptx_scene* s = new rptx_scene();

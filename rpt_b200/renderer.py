@@ -69,6 +69,10 @@ class Context:
         if rc:
             raise RptxError(f"{what}: {self.error()}")
 
+    def trim(self):
+        """Give the device memory this context caches between calls (pool blocks, the spare film slab) back to the device."""
+        self.check(self.lib.rptx_ctx_trim(self.h), "rptx_ctx_trim")
+
     def close(self):
         if self.h:
             self.lib.rptx_ctx_destroy(self.h)

@@ -145,6 +145,7 @@ extern "C" {
     pub fn rptx_ctx_create(device_id: c_int, out: *mut *mut rptx_ctx) -> c_int;
     pub fn rptx_ctx_destroy(ctx: *mut rptx_ctx);
     pub fn rptx_last_error(ctx: *const rptx_ctx) -> *const c_char;
+    pub fn rptx_ctx_trim(ctx: *mut rptx_ctx) -> c_int;
 
     // multi-GPU: one context per rank joined into an NCCL communicator; the exchanges replace `add_samples`
     // (src/renderer.rs:169-170) and PhotonList::merge (src/photon.rs:153-160,675)
