@@ -199,7 +199,7 @@ int build_lbvh(const PrimBox* d_boxes, uint32_t n, float pad, int leaf_max, cons
     }
 fail:
 #undef RPTX_CK
-    if (keys_in) cudaFreeAsync(keys_in, stream); if (keys_out) cudaFreeAsync(keys_out, stream); if (ints) cudaFreeAsync(ints, stream); if (ibox) cudaFreeAsync(ibox, stream); if (tmp) cudaFreeAsync(tmp, stream);
+    rptx_free_async(keys_in, stream); rptx_free_async(keys_out, stream); rptx_free_async(ints, stream); rptx_free_async(ibox, stream); rptx_free_async(tmp, stream);
     return (int)e;
 }
 
@@ -237,7 +237,7 @@ int build_lbvh_sorted(const uint64_t* d_keys, const PrimBox* d_boxes, uint32_t n
     }
 fail:
 #undef RPTX_CK
-    if (ints) cudaFreeAsync(ints, stream); if (ibox) cudaFreeAsync(ibox, stream);
+    rptx_free_async(ints, stream); rptx_free_async(ibox, stream);
     return (int)e;
 }
 
@@ -443,7 +443,7 @@ int build_ploc(const PrimBox* d_boxes, uint32_t n, float pad, int leaf_max, cons
 fail:
 #undef RPTX_CK
     for (void* p : {(void*)keys_in, (void*)keys_out, (void*)nodes, (void*)cl_a, (void*)cl_b, (void*)cl_t, (void*)nn, (void*)first, (void*)keep, (void*)ctr, tmp})
-        if (p) cudaFreeAsync(p, stream);
+        rptx_free_async(p, stream);
     return (int)e;
 }
 

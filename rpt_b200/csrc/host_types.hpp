@@ -1,6 +1,8 @@
 // Host-side objects behind the opaque handles of include/rptx.h.
 #pragma once
+#include <algorithm>
 #include <array>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -116,18 +118,17 @@ struct rptx_film {
 // Stream-ordered allocation for everything that is created and destroyed per call (scene buffers, BVH build
 // scratch): cudaMalloc / cudaFree take a device-wide lock and, with a 20 GB film slab mapped, stalled for
 // 20-460 ms at random in the end-to-end loop; the pool (release threshold set in rptx_ctx_create) does neither.
-// Large requests are rounded up to a coarse size class (+1.6 %, then the next multiple of 256 MB): two photon renders of the
-// same configuration differ by a few thousand rows, and the pool can only hand a cached block to a request that fits it —
-// without the classes a step whose lists were 0.01 % longer than the previous step's mapped fresh memory for every GB-sized
-// buffer (map build 110 ms -> 1.8 s in one step of two at 1e8 photons, profiles/r2_summary.md).
-inline cudaError_t rptx_alloc_async(void** p, size_t bytes, cudaStream_t st) {
-    if (bytes >= (32ull << 20)) {
-        const size_t cls = 256ull << 20;
-        bytes = (bytes + bytes / 64 + cls - 1) / cls * cls;
-    }
-    return cudaMallocAsync(p, bytes ? bytes : 16, st);
-}
-inline void rptx_free_async(const void* p, cudaStream_t st) { if (p) cudaFreeAsync(const_cast<void*>(p), st); }
+// Large requests (>= 32 MB: photon rows, maps, sort and tree scratch - GBs each at 1e8 photons) do not go to the pool at all.
+// The pool sub-allocates: a smaller request may split the cached block a larger one needs a moment later, the larger one then
+// maps fresh memory inside a timed step (0.2-0.8 s for 5-20 GB), and which step pays is random (one in three at 1e8 photons, in
+// every size-rounding scheme tried: profiles/r2_summary.md section 6).  They are served by a caching allocator over cudaMalloc
+// instead (rptx.cu): sizes are sticky (a request reuses the smallest size handed out before that holds it with at most 30 % to
+// spare, else gets 10 % headroom rounded to 256 MB), freed blocks wait in a per-stream list of whole blocks that are never split,
+// and a block is only ever reused on the stream it was used on (stream order makes that safe without a synchronisation).
+// cudaMalloc runs in the first calls only; rptx_ctx_trim / rptx_ctx_destroy give the cached blocks back.
+cudaError_t rptx_alloc_async(void** p, size_t bytes, cudaStream_t st);
+void rptx_free_async(const void* p, cudaStream_t st);
+void rptx_block_cache_release(cudaStream_t st);  // cudaFree every cached block of the stream (which must be idle)
 
 // host helpers shared by rptx.cu and photon.cu
 namespace rptx_host {

@@ -9,6 +9,9 @@
 #include <cstring>
 #include <memory>
 #include <string>
+#include <map>
+#include <mutex>
+#include <unordered_map>
 #include <vector>
 
 #include "../../include/rptx.h"
@@ -135,6 +138,77 @@ float f32_upf(double x) {
 
 // Host->device copy ordered on the context's (non-blocking) stream.  A plain cudaMemcpy from
 // pageable memory may return before the DMA lands and does not order against that stream.
+}  // namespace (reopened below): the block cache has external linkage (host_types.hpp)
+
+namespace {
+struct BlockCache {
+    std::mutex mu;
+    std::vector<size_t> sizes;                                        // sticky sizes, ascending
+    std::unordered_map<const void*, std::pair<size_t, cudaStream_t>> live;  // blocks handed out
+    std::map<cudaStream_t, std::multimap<size_t, void*>> idle;        // cached whole blocks per stream
+};
+BlockCache& block_cache() { static BlockCache c; return c; }
+constexpr size_t kBigBlock = 32ull << 20;
+}  // namespace
+
+cudaError_t rptx_alloc_async(void** p, size_t bytes, cudaStream_t st) {
+    if (bytes < kBigBlock) return cudaMallocAsync(p, bytes ? bytes : 16, st);
+    BlockCache& c = block_cache();
+    std::lock_guard<std::mutex> lock(c.mu);
+    size_t want = 0;
+    for (size_t r : c.sizes)
+        if (r >= bytes) { if (r <= bytes + bytes / 10 * 3) want = r; break; }
+    if (!want) {
+        const size_t cls = 256ull << 20;
+        want = (bytes + bytes / 10 + cls - 1) / cls * cls;
+        c.sizes.insert(std::upper_bound(c.sizes.begin(), c.sizes.end(), want), want);
+    }
+    auto& idle = c.idle[st];
+    auto it = idle.lower_bound(want);
+    if (it != idle.end() && it->first <= want + want / 10 * 3) {
+        *p = it->second;
+        c.live[*p] = {it->first, st};
+        idle.erase(it);
+        return cudaSuccess;
+    }
+    cudaError_t e = cudaMalloc(p, want);
+    if (e != cudaSuccess) {  // out of memory: give the idle blocks of this stream back and try once more
+        cudaGetLastError();
+        cudaStreamSynchronize(st);
+        for (auto& kv : idle) cudaFree(kv.second);
+        idle.clear();
+        e = cudaMalloc(p, want);
+    }
+    if (e == cudaSuccess) c.live[*p] = {want, st};
+    return e;
+}
+
+void rptx_free_async(const void* p, cudaStream_t st) {
+    if (!p) return;
+    BlockCache& c = block_cache();
+    {
+        std::lock_guard<std::mutex> lock(c.mu);
+        auto it = c.live.find(p);
+        if (it != c.live.end()) {
+            c.idle[it->second.second].emplace(it->second.first, const_cast<void*>(p));
+            c.live.erase(it);
+            return;
+        }
+    }
+    cudaFreeAsync(const_cast<void*>(p), st);
+}
+
+void rptx_block_cache_release(cudaStream_t st) {
+    BlockCache& c = block_cache();
+    std::lock_guard<std::mutex> lock(c.mu);
+    auto it = c.idle.find(st);
+    if (it == c.idle.end()) return;
+    for (auto& kv : it->second) cudaFree(kv.second);
+    c.idle.erase(it);
+}
+
+namespace {
+
 cudaError_t copy_h2d(void* dst, const void* src, size_t bytes, cudaStream_t st) {
     cudaError_t e = cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, st);
     if (e == cudaSuccess) e = cudaStreamSynchronize(st);
@@ -377,7 +451,7 @@ void rptx_ctx_destroy(rptx_ctx* ctx) {
     if (!ctx) return;
     if (ctx->comm) rptx_comm_destroy(ctx);
     if (ctx->spare_arena) cudaFree(ctx->spare_arena);
-    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    if (ctx->stream) { cudaStreamSynchronize(ctx->stream); rptx_block_cache_release(ctx->stream); cudaStreamDestroy(ctx->stream); }
     if (ctx->h_pinned) cudaFreeHost(ctx->h_pinned);
     delete ctx;
 }
@@ -392,6 +466,7 @@ int rptx_ctx_trim(rptx_ctx* ctx) {
     CK(cudaSetDevice(ctx->device));
     CK(cudaStreamSynchronize(ctx->stream));
     if (ctx->spare_arena) { cudaFree(ctx->spare_arena); ctx->spare_arena = nullptr; ctx->spare_arena_bytes = 0; }
+    rptx_block_cache_release(ctx->stream);
     cudaMemPool_t pool;
     CK(cudaDeviceGetDefaultMemPool(&pool, ctx->device));
     CK(cudaMemPoolTrimTo(pool, 0));
