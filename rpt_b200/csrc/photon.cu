@@ -512,6 +512,7 @@ int build_point_map_sharded(rptx_ctx* ctx, const PhotonRec* rows, uint32_t n_loc
     auto done = [&](int rc) { free_owned(ctx, tmp); return rc; };
 #define CKT(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return done(ctx_fail(ctx, std::string(#call) + ": " + cudaGetErrorString(e_))); } while (0)
 #define RCT(call) do { if (int r_ = (call)) return done(r_); } while (0)
+    if (world > 63) return ctx_fail(ctx, "sharded photon-map build supports at most 63 ranks");  // k_pick_splitters: one block of 64
     PhaseTrace trace(ctx);
     // ---- 1. bounds ----
     double mn[3] = {INFINITY, INFINITY, INFINITY}, mx[3] = {-INFINITY, -INFINITY, -INFINITY};
@@ -559,7 +560,6 @@ int build_point_map_sharded(rptx_ctx* ctx, const PhotonRec* rows, uint32_t n_loc
     RCT(comm_allreduce_u64_sum(ctx, lb_global, (size_t)bins + 1));
     k_pick_splitters<<<1, 64, 0, st>>>(lb_global, lb_local, bins, world, d_cut);
     ctx->launches += 2;
-    if (world > 63) return done(ctx_fail(ctx, "sharded photon-map build supports at most 63 ranks"));
     std::vector<unsigned long long> cut((size_t)world + 1), mat((size_t)world * world);
     CKT(cudaMemcpyAsync(cut.data(), d_cut, sizeof(unsigned long long) * cut.size(), cudaMemcpyDeviceToHost, st));
     CKT(cudaStreamSynchronize(st));

@@ -435,10 +435,9 @@ int rptx_ctx_create(int device_id, rptx_ctx** out) {
     CK(cudaGetDeviceProperties(&prop, device_id));
     ctx->sm_count = prop.multiProcessorCount;
     CK(cudaMallocHost((void**)&ctx->h_pinned, 64));
-    {  // scene tables, batch means, photon maps and every build scratch come from the stream-ordered pool.  It never trims:
-       // a 1e8-photon render cycles through ~45 GB of rows, maps and sort scratch per call, and with a finite release
-       // threshold (16 GB in round 1) the pool unmapped and re-mapped the excess at every synchronisation (beam-beam step
-       // 3.9 -> 6.2 s once another workload had run in the same process)
+    {  // scene tables, batch means and every allocation under 32 MB come from the stream-ordered pool (larger ones from the block
+       // cache above: rptx_alloc_async).  The pool never trims: with a finite release threshold (16 GB in round 1) it unmapped and
+       // re-mapped the excess at every synchronisation (beam-beam step 3.9 -> 6.2 s once another workload had run in the process)
         cudaMemPool_t pool;
         CK(cudaDeviceGetDefaultMemPool(&pool, device_id));
         uint64_t keep = UINT64_MAX;

@@ -65,6 +65,14 @@ pub fn comm_unique_id() -> [u8; sys::RPTX_COMM_ID_BYTES] {
     id
 }
 
+/// Give the device memory the context keeps cached between renders (block cache, pool, spare film slab) back to the device:
+/// for a host that renders scenes of very different footprints one after another.  No counterpart in rpt.
+pub fn trim_device_cache() {
+    let guard = context();
+    let ctx = guard.as_ref().unwrap();
+    check(ctx.raw, unsafe { sys::rptx_ctx_trim(ctx.raw) });
+}
+
 /// (world, rank) of the process's context; (1, 0) without a communicator.
 pub(crate) fn comm_info(ctx: &Ctx) -> (i32, i32) {
     let (mut world, mut rank) = (1, 0);
