@@ -149,7 +149,19 @@ def cpu_sample(scene, cam, params, seconds, threads=0):
     sec, ctr = of.time_rows(0, h, stride, 1)
     rows = len(range(0, h, stride))
     rate = rows * w / max(sec, 1e-9)  # path-samples/s
-    spp = int(max(1, min(params.num_samples, seconds * rate / (rows * w))))
+    # ~`seconds` of CPU work: the workload's spp over as many spread rows as that buys; a workload smaller than the budget
+    # (cornell at 16 spp is 0.8 s of CPU) is timed whole, with more spp per pixel (the samples are i.i.d.: same cost each)
+    target = seconds * rate
+    spp = max(1, params.num_samples)
+    want_rows = target / (w * spp)
+    if want_rows >= h:
+        stride, spp = 1, int(max(spp, target / (h * w)))
+    elif want_rows >= 64:
+        stride = max(1, int(h / want_rows))
+    else:  # keep ~64 rows spread over the image and cut the samples per pixel instead
+        stride = max(1, h // 64)
+        spp = int(max(1, target / (len(range(0, h, stride)) * w)))
+    rows = len(range(0, h, stride))
     sec, ctr = of.time_rows(0, h, stride, spp)
     paths = rows * w * spp
     return dict(value=paths / sec / 1e6, unit=METRIC, cores=cores, kind="port",

@@ -86,10 +86,22 @@ struct EmitParams {
 // restores the canonical one (photon.cu canonical_order).  The reference's recursion deposits a vertex
 // only when the walk continues past it (:842-866), which the loop reproduces by depositing right after a
 // successful sample_f.
-constexpr int kRefillLanes = 8;
+// idle lanes at which a warp pulls new photons (one atomic for all of them).  Measured at 1e8 photons, emission ms for the
+// photon-photon / beam-beam lampshade: 16 lanes 139 / 233, 8 (round 1) 111 / 223, 4: 99 / 175, 2: 96 / 160, 1: 96 / 159 - the
+// atomic is cheap next to a lane idling through a neighbour's whole walk
+#ifndef RPTX_REFILL_LANES
+#define RPTX_REFILL_LANES 1
+#endif
+constexpr int kRefillLanes = RPTX_REFILL_LANES;
 
+// resident blocks asked of ptxas for the walk (registers = 65536 / (128 * n)).  Measured at 1e8 photons, emission ms for the
+// photon-photon / beam-beam lampshade: 3 blocks (142 registers as compiled freely) 115 / 250, 4 (128) 108 / 217, 5 (96) 108 / 216,
+// 6 (80, 352 B of spills) 113 / 230
+#ifndef RPTX_OCC_EMIT
+#define RPTX_OCC_EMIT 4
+#endif
 template <bool SMALL>
-__global__ void __launch_bounds__(128) k_photon_trace(const __grid_constant__ SceneDev sc, const MediumDev md, const EmitParams ep,
+__global__ void __launch_bounds__(128, RPTX_OCC_EMIT) k_photon_trace(const __grid_constant__ SceneDev sc, const MediumDev md, const EmitParams ep,
                                                       PhotonSink surf, PhotonSink vol, unsigned long long* __restrict__ work_head,
                                                       unsigned long long* __restrict__ stats) {
     const uint32_t lane = threadIdx.x & 31u;
