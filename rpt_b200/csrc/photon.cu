@@ -221,11 +221,11 @@ __global__ void k_beam_gather(const double* __restrict__ start, const double* __
 }
 
 // ---- beam segments (BeamSegDev, photon.cuh) ----
-__global__ void k_seg_count(const double* __restrict__ len, uint32_t n, uint32_t* __restrict__ count) {
+__global__ void k_seg_count(const double* __restrict__ len, uint32_t n, double seg_len, uint32_t* __restrict__ count) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const double l = len[i];
-    uint32_t k = l > 0.0 && l < 1e300 ? (uint32_t)fmin(ceil(l / kBeamSegLen), (double)kBeamMaxSeg) : 1u;  // NaN / inf lengths: one piece
+    uint32_t k = l > 0.0 && l < 1e300 ? (uint32_t)fmin(ceil(l / seg_len), (double)kBeamMaxSeg) : 1u;  // NaN / inf lengths: one piece
     count[i] = k < 1u ? 1u : k;
 }
 
@@ -1084,7 +1084,9 @@ static int photon_map_build_impl(rptx_ctx* ctx, rptx_scene* scene, rptx_photons*
                 std::vector<void*> tmp;
                 auto fin = [&](int rc2) { free_owned(ctx, tmp); rptx_free_async(perm2, st); return rc2; };
                 CK(dev_alloc(ctx, &cnt, nv, &tmp)); CK(dev_alloc(ctx, &off, nv, &tmp));
-                k_seg_count<<<grid_for(nv, 256), 256, 0, st>>>(olen, nv, cnt);
+                double seg_len = kBeamSegLen;
+                if (const char* e = std::getenv("RPTX_BEAM_SEG_LEN")) seg_len = std::max(0.5, std::atof(e));  // developer knob
+                k_seg_count<<<grid_for(nv, 256), 256, 0, st>>>(olen, nv, seg_len, cnt);
                 size_t scan_bytes = 0;
                 CK(cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, cnt, off, (int)nv, st));
                 void* scan_tmp = nullptr;

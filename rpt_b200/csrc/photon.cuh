@@ -381,12 +381,14 @@ struct SphereMapDev {
 // PhotonBeam (src/photon.rs:46-59), leaf order
 // Culling structure of the warp camera pass over photon beams.  A beam's own box (the reference's, src/photon.rs:76-105) is
 // the box of a long thin cylinder: at 1e8 photons a camera ray hits the boxes of 10 000 of the 2e5 beams and 97 % of them
-// pass nowhere near the beam.  The beams are therefore cut into segments of ~kBeamSegLen, each with the box of ITS piece of the
+// pass nowhere near the beam.  The beams are therefore cut into segments of ~kBeamSegLen (16 radii), each with the box of ITS piece of the
 // cylinder, under a second BVH.  A segment stands for the contributions whose closest-approach parameter beam_t falls into its
 // piece - floor(beam_t * K / len) == k, a partition of [0, len], so every contribution is counted exactly once - and the ray
 // that makes such a contribution passes within the radius of that piece, i.e. through the segment's box.  The beam's own box
 // is still tested (the reference never sees a beam whose box the ray misses); the result is the per-beam walk's.
-constexpr double kBeamSegLen = 12.0;
+// measured at 1e8 photons (2e5 beams), camera pass ms at segment lengths 4 / 8 / 12 / 24 / 48 / 96 / 192: 207 / 197 / 192 / 179 /
+// 170 / 179 / 224 (one box per beam: 700); RPTX_BEAM_SEG_LEN overrides
+constexpr double kBeamSegLen = 48.0;
 constexpr uint32_t kBeamMaxSeg = 64;
 struct BeamSegDev {
     BoxBvhDev bvh;         // over the segments; bvh.boxes = segment boxes, leaf order
