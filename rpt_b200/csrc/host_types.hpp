@@ -111,6 +111,7 @@ struct rptx_film {
     cudaEvent_t evw[4][5] = {};   // per-wave kernel boundaries, one set per wave in flight (run_waves)
     cudaEvent_t ev_done[4] = {};  // the wave's live count has landed in pinned memory
     bool no_one_vertex = false;   // RPTX_NO_ONE_VERTEX
+    uint32_t shade_rounds = 0;    // RPTX_SHADE_TILE_ROUNDS (0: chosen per wave)
     rptx_stats stats = {};
     bool timing_pending = false;  // ev0 / ev1 of the last traced batch not read yet
 };

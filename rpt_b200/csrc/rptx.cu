@@ -897,6 +897,7 @@ static int film_alloc(rptx_film* f) {
         CK(cudaEventCreate(&f->ev_done[r]));
     }
     f->no_one_vertex = std::getenv("RPTX_NO_ONE_VERTEX") != nullptr;  // developer knob, read once per film
+    if (const char* e = std::getenv("RPTX_SHADE_TILE_ROUNDS")) f->shade_rounds = (uint32_t)std::min(std::max(std::atoi(e), 0), kShadeRoundsMax);  // experiments: fixes the k_shade tile
     return 0;
 }
 
@@ -1057,8 +1058,7 @@ static int run_waves(rptx_film* f, const BatchParams& bp) {
         if (cudaEventElapsedTime(&ms, e[3], e[4]) == cudaSuccess) f->stats.connect_ms += ms;
         return h_count[slot];
     };
-    uint32_t shade_rounds_env = 0;  // experiments: RPTX_SHADE_TILE_ROUNDS=1..kShadeRoundsMax fixes the k_shade tile
-    if (const char* e = std::getenv("RPTX_SHADE_TILE_ROUNDS")) shade_rounds_env = (uint32_t)std::min(std::max(std::atoi(e), 0), kShadeRoundsMax);
+    const uint32_t shade_rounds_env = f->shade_rounds;
     int launched = 0, collected = 0;
     while (bound > 0) {
         const int slot = launched % kWaveRing;
