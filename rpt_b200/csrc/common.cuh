@@ -8,6 +8,15 @@
 #include <stdint.h>
 
 #define RPTX_HD __host__ __device__ __forceinline__
+// -DRPTX_CHECKED: device-side assertions on every shared-memory list, queue and traversal-stack write of the kernels (the pool
+// refuses compute-sanitizer; `make -C rpt_b200/csrc checked` builds librptx_checked.so and tools/gpu.sh checked runs the parity
+// suite on it).  A failed assertion traps the kernel and the next CUDA call of the host reports it.
+#ifdef RPTX_CHECKED
+#include <cassert>
+#define RPTX_ASSERT(c) assert(c)
+#else
+#define RPTX_ASSERT(c) ((void)0)
+#endif
 #define RPTX_D __device__ __forceinline__
 // big bodies that kernels call from several sites: one copy each keeps the kernels inside the
 // instruction cache (the ray kernels were 100-400 KB of SASS when everything was inlined)

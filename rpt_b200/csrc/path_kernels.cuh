@@ -46,7 +46,7 @@ RPTX_D void queue_push(uint32_t* __restrict__ q, uint32_t* __restrict__ count, b
     uint32_t base = 0;
     if ((int)lane_id() == leader) base = atomicAdd(count, (uint32_t)__popc(mask));
     base = __shfl_sync(active, base, leader);
-    if (pred) q[base + __popc(mask & ((1u << lane_id()) - 1u))] = slot;
+    if (pred) q[base + __popc(mask & ((1u << lane_id()) - 1u))] = slot;  // (queue_push is unused by the ordered-compaction wave loop)
 }
 
 template <bool MEDIUM>
@@ -250,6 +250,7 @@ __global__ void __launch_bounds__(kShadeBlock, RPTX_OCC_SHADE) k_shade(const __g
                 const unsigned m = __ballot_sync(0xffffffffu, cls == c);
                 if (cls == c) pos = s_cnt[c][r * kShadeWarps + warp] + (uint32_t)__popc(m & lt) + (c > 0 ? s_tot[0] : 0u) + (c > 1 ? s_tot[1] : 0u);
             }
+            RPTX_ASSERT(cls >= 3 || (pos < rounds * kShadeBlock && u < (uint32_t)kShadeTile));
             if (cls < 3) s_perm[pos] = (uint16_t)u;
         }
         __syncthreads();
@@ -419,6 +420,7 @@ __global__ void __launch_bounds__(kBlock, SMALL ? RPTX_OCC_SHADOW_SMALL : RPTX_O
             for (int r = 0; r < kShadowPer; r++)
                 if (job[r]) {
                     const uint32_t at = before[r] + rank[r];
+                    RPTX_ASSERT(at < (uint32_t)kShadowChunk && slot[r] < p.n_slots);
                     s_slot[at] = slot[r];
                     s_c[0][at] = c[r].x; s_c[1][at] = c[r].y; s_c[2][at] = c[r].z;
                 }
@@ -532,6 +534,7 @@ __global__ void __launch_bounds__(kBlock, SMALL ? RPTX_OCC_SHADOW_SMALL : RPTX_O
                 const unsigned m = __ballot_sync(0xffffffffu, job);
                 if (job) {
                     const uint32_t at = fill + (uint32_t)__popc(m & ((1u << lane) - 1u));
+                    RPTX_ASSERT(at < 64u && slot < p.n_slots);
                     s_slot[warp][at] = slot;
                     s_c[warp][0][at] = c.x; s_c[warp][1][at] = c.y; s_c[warp][2][at] = c.z;
                 }

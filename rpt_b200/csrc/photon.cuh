@@ -292,6 +292,7 @@ RPTX_DN void knn_query(const PointMapDev& m, d3 q, KnnHeap<KMAX>& h) {
             const bool v0 = d0 * kBoxShrink <= w, v1 = d1 * kBoxShrink <= w;
             if (v0 && v1) {
                 const bool first0 = d0 <= d1;
+                RPTX_ASSERT(sp < kKnnStack);
                 stack[sp] = first0 ? right : left;
                 stack_d[sp] = first0 ? d1 : d0;
                 sp++;
@@ -422,7 +423,7 @@ RPTX_D void box_bvh_traverse(const BoxBvhDev& b, const Ray32& r, F&& f) {
             const float lmn[3] = {a.x, a.y, a.z}, lmx[3] = {bb.x, bb.y, bb.z}, rmn[3] = {c.x, c.y, c.z}, rmx[3] = {d.x, d.y, d.z};
             const bool hl = ray32_hits(r, lmn, lmx), hr = ray32_hits(r, rmn, rmx);
             const int left = __float_as_int(a.w), right = __float_as_int(c.w);
-            if (hl && hr) { stack[sp++] = right; cur = left; continue; }
+            if (hl && hr) { RPTX_ASSERT(sp < kStackSize); stack[sp++] = right; cur = left; continue; }
             if (hl) { cur = left; continue; }
             if (hr) { cur = right; continue; }
         } else {
@@ -758,6 +759,7 @@ RPTX_D uint32_t warp_knn(const PointMapDev& m, d3 q, uint32_t k, WarpKnnSmem& sm
             const bool v0 = d0 * kBoxShrink <= worst, v1 = d1 * kBoxShrink <= worst;
             if (v0 && v1) {
                 const bool first0 = d0 <= d1;
+                RPTX_ASSERT(sp < (uint32_t)kKnnStack);
                 if (lane == 0) { sm.stack[sp] = (uint32_t)(first0 ? right : left); sm.stack_d[sp] = first0 ? d1 : d0; }
                 sp++;
                 cur = first0 ? left : right;
@@ -787,6 +789,7 @@ RPTX_D uint32_t warp_knn(const PointMapDev& m, d3 q, uint32_t k, WarpKnnSmem& sm
             const unsigned mask = __ballot_sync(0xffffffffu, take);
             if (take) {
                 const uint32_t at = count + __popc(mask & ((1u << lane) - 1u));
+                RPTX_ASSERT(at < (uint32_t)kWarpCand);
                 sm.d2[at] = dd; sm.idx[at] = i;
             }
             count += __popc(mask);
@@ -943,6 +946,7 @@ RPTX_D d3 warp_volume_boxes(const MediumDev& md, const PhotonMapDev& pm, const R
         }
         ncand -= n;
         const unsigned m = __ballot_sync(0xffffffffu, keep);
+        RPTX_ASSERT(nexact + 32u <= (uint32_t)kWarpBoxExact);
         if (keep) sm.exact[nexact + __popc(m & lt)] = i;
         nexact += __popc(m);
         __syncwarp();
@@ -974,6 +978,8 @@ RPTX_D d3 warp_volume_boxes(const MediumDev& md, const PhotonMapDev& pm, const R
         }
         // children: the right ones first, so that the left child of the last lane is on top (the per-thread walk's order)
         const unsigned mr = __ballot_sync(0xffffffffu, hr);
+        RPTX_ASSERT(top + 64u <= (uint32_t)kWarpBoxStack || n == 1u);
+        RPTX_ASSERT(top + 2u <= (uint32_t)kWarpBoxStack);
         if (hr) sm.stack[top + __popc(mr & lt)] = right;
         top += __popc(mr);
         const unsigned ml = __ballot_sync(0xffffffffu, hl);
@@ -984,6 +990,7 @@ RPTX_D d3 warp_volume_boxes(const MediumDev& md, const PhotonMapDev& pm, const R
         for (uint32_t k = 0; k < 8u; k++) {
             const unsigned mk = __ballot_sync(0xffffffffu, count > k);
             if (mk == 0) break;
+            RPTX_ASSERT(ncand + 32u <= (uint32_t)kWarpBoxCand);
             if (count > k) sm.cand[ncand + __popc(mk & lt)] = first + k;
             ncand += __popc(mk);
         }

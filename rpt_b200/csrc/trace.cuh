@@ -363,6 +363,7 @@ RPTX_D void closest_hit(const SceneDev& sc, const RayD& ray, double t_min, doubl
             const int left = __float_as_int(a.w), right = __float_as_int(c.w);
             if (hl && hr) {
                 const bool lf = tl <= tr;
+                RPTX_ASSERT(sp < kStackSize);
                 stack[sp] = lf ? right : left;
                 stack_t[sp] = lf ? tr : tl;
                 sp++;
@@ -436,6 +437,7 @@ RPTX_D void closest_hit(const SceneDev& sc, const RayD& ray, double t_min, doubl
                         tbest = tbest + fabsf(tbest) * kSlabSlack;
                         nodes = sc.nodes + in->node_base;
                         in_blas = true;
+                        RPTX_ASSERT(sp + 1 < kStackSize);
                         stack[sp] = kSentinel;
                         stack_t[sp] = -CUDART_INF_F;
                         sp++;

@@ -1,7 +1,7 @@
 #!/bin/bash
 # One parameterised GPU-box script (replaces the per-round gpu_*.sh / r2_run*.sh copies):
 #   gpurun [--gpus N] --timeout T -- 'bash tools/gpu.sh <recipe> [args]'
-# recipes: peaks | tests [pytest args] | smoke | line <tag> <bench args> | ncu <tag> <regex> <skip> <count> <bench args> |
+# recipes: peaks | tests [pytest args] | checked [pytest args] | smoke | line <tag> <bench args> | ncu <tag> <regex> <skip> <count> <bench args> |
 #          launches | probe | photons [N] | multi <N>
 # Everything it writes goes to gpurun_out/ (merged back by gpurun).
 set -u
@@ -43,6 +43,9 @@ peaks)
 tests)
   timeout 1500 python -m pytest tests -m gpu -x -q "$@" > gpurun_out/pytest.log 2>&1; echo "pytest rc=$?" >> gpurun_out/pytest.log
   tail -15 gpurun_out/pytest.log ;;
+checked)  # the parity suite on the assertion build (make -C rpt_b200/csrc checked); a tripped assertion fails the test that hit it
+  RPTX_LIBRARY=$PWD/rpt_b200/librptx_checked.so timeout 1500 python -m pytest tests -m gpu -q "$@" > gpurun_out/pytest_checked.log 2>&1
+  echo "pytest rc=$?" >> gpurun_out/pytest_checked.log; tail -8 gpurun_out/pytest_checked.log ;;
 smoke)
   timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smoke.log 2>&1; tail -3 gpurun_out/smoke.log ;;
 line)
