@@ -182,6 +182,29 @@ def test_list_walk_equals_hierarchy(monkeypatch):
         assert np.array_equal(means[0], means[1]), name
 
 
+def test_trim_gives_cached_memory_back_and_changes_nothing():
+    """rptx_ctx_trim (Context.trim): the block cache, the pool and the spare film slab go back to the device between
+    workloads; the next render of the same batch is identical, bit for bit, and photon renders still work."""
+    scene, cam, d = scenes.cornell()
+    r = scenes.make_renderer(scene, cam, d, width=48, height=40, num_samples=3, seed=4, max_bounces=3)
+    f = r.begin()
+    f.sample(3)
+    a = f.mean()
+    f.close()
+    r.device_scene().ctx.trim()
+    r.device_scene().ctx.trim()  # idempotent
+    f = r.begin()
+    f.sample(3)
+    assert np.array_equal(a, f.mean())
+    f.close()
+    scene2, cam2, d2 = scenes.lampshade("photonphoton")
+    r2 = scenes.make_renderer(scene2, cam2, d2, width=16, height=16, num_samples=2, seed=4)
+    _, m1 = r2.photon_render(20000, 0, want_mean=True)
+    r2.device_scene().ctx.trim()
+    _, m2 = r2.photon_render(20000, 0, want_mean=True)
+    assert np.allclose(m1, m2, rtol=1e-11, atol=1e-300, equal_nan=True)
+
+
 def test_tiled_slots_equal_row_major(monkeypatch):
     """Slots walk the image in 8x4 tiles when the size allows it; the RNG is keyed by the pixel, so the
     batch is the one the row-major walk produces, bit for bit."""
